@@ -1,0 +1,108 @@
+// b2g_api.cu — library-wide state of the C ABI: version, thread-local error text, driver entry points,
+// and the weight re-packing kernel that feeds the implicit-GEMM convolutions.
+#include <string.h>
+
+#include "b2g_conv.cuh"
+#include "b2g_host.h"
+#include "b2g_ptx.cuh"
+
+namespace b2g {
+
+char* error_buffer() {
+  static thread_local char buf[512] = {0};
+  return buf;
+}
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess) return nullptr;
+    if (q != cudaDriverEntryPointSuccess) return nullptr;
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+int num_sms() {
+  static int n = []() {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return 148;
+    return v;
+  }();
+  return n;
+}
+
+// One thread per packed element: wpacked[ph][n][tap*Ck + c] (bf16) <- w[ky][kx][d2][d3] (fp32) * scales.
+__global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip,
+                                        const float* __restrict__ w, const float* __restrict__ scale_scalar,
+                                        const float* __restrict__ scale_d2, const float* __restrict__ scale_d3,
+                                        __nv_bfloat16* __restrict__ out, int phases, int taps, long total) {
+  const int Cn = n_is_d3 ? D3 : D2;  // GEMM-N channels
+  const int Ck = n_is_d3 ? D2 : D3;  // GEMM-K channels per tap
+  const float s0 = scale_scalar ? *scale_scalar : 1.f;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % Ck);
+    long r = i / Ck;
+    const int tap = (int)(r % taps);
+    r /= taps;
+    const int n = (int)(r % Cn);
+    const int ph = (int)(r / Cn);
+    int ky, kx;
+    if (kind == B2G_CONVT_K4S2) {
+      int d;
+      convt_tap(ph >> 1, tap >> 1, &ky, &d);
+      convt_tap(ph & 1, tap & 1, &kx, &d);
+    } else {
+      ky = tap / kw;
+      kx = tap % kw;
+      if (flip) {
+        ky = kh - 1 - ky;
+        kx = kw - 1 - kx;
+      }
+    }
+    const int d2 = n_is_d3 ? c : n;
+    const int d3 = n_is_d3 ? n : c;
+    float v = w[(((long)ky * kw + kx) * D2 + d2) * D3 + d3] * s0;
+    if (scale_d2) v *= scale_d2[d2];
+    if (scale_d3) v *= scale_d3[d3];
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
+
+}  // namespace b2g
+
+using namespace b2g;
+
+extern "C" int b2g_version(void) { return 100; }
+extern "C" const char* b2g_last_error(void) { return error_buffer(); }
+
+extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, const float* w,
+                                    const float* scale_scalar, const float* scale_d2, const float* scale_d3,
+                                    void* wpacked, b2g_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!w || !wpacked) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: null pointer");
+  int phases, taps;
+  if (kind == B2G_CONV_K3S1) {
+    if (kh != 3 || kw != 3) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: K3S1 needs a 3x3 kernel");
+    phases = 1; taps = 9;
+  } else if (kind == B2G_CONV_K4S2) {
+    if (kh != 4 || kw != 4 || flip) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: K4S2 needs 4x4, no flip");
+    phases = 1; taps = 16;
+  } else if (kind == B2G_CONVT_K4S2) {
+    if (kh != 4 || kw != 4 || flip) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: CONVT needs 4x4, no flip");
+    phases = 4; taps = 4;
+  } else {
+    return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: unknown kind %d", kind);
+  }
+  const long total = (long)phases * taps * D2 * D3;
+  const int threads = 256;
+  long blocks = (total + threads - 1) / threads;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_conv_weight_kernel<<<(int)blocks, threads, 0, stream>>>(kind, kh, kw, D2, D3, n_is_d3, flip, w, scale_scalar,
+                                                                scale_d2, scale_d3,
+                                                                static_cast<__nv_bfloat16*>(wpacked), phases, taps, total);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}

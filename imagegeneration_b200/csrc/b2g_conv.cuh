@@ -1,0 +1,132 @@
+// b2g_conv.cuh — tile plan shared by the implicit-GEMM conv kernels (fprop / dgrad / convT) and wgrad.
+//
+// Every conv role is one GEMM  D[M, Cout] = A[M, taps*Cin] * Wp[Cout, taps*Cin]^T  per output phase, where the
+// M index runs over a "phase grid" (N, Hg, Wg) of pixels and the A tile of tap t is the input tensor read at
+// grid position + (dy_t, dx_t) through one of up to 4 TMA tensor maps (zero fill outside = SAME padding).
+//   K3S1   : 1 phase, 9 taps, grid = input = output.                       in(y+ky-1, x+kx-1)
+//   K4S2   : 1 phase, 16 taps, grid = output; the input is seen as 4 parity sub-grids (one tensor map each):
+//            in(2y+ky-1, 2x+kx-1) = sub[(ky+1)&1][(kx+1)&1](y + floor((ky-1)/2), x + floor((kx-1)/2))
+//   CONVT  : 4 phases (py,px) x 4 taps (jy,jx), grid = input, output pixel (2y+py, 2x+px):
+//            py=0: ky = 1 (dy 0), 3 (dy -1);  py=1: ky = 0 (dy +1), 2 (dy 0)   [Y = 2*iy + ky - 1]
+#pragma once
+#include <cuda.h>
+#include <stdint.h>
+
+#include "../../include/b200gan.h"
+
+namespace b2g {
+
+constexpr int kMaxTapEntries = 16;  // phases * taps <= 16 for all kinds
+
+struct ConvPlan {
+  int kind;
+  int phases, taps;        // taps per phase
+  int N, Hg, Wg;           // phase grid (GEMM M space)
+  int bw, bh, bn;          // pixel tile box, bw*bh*bn == tile_pixels
+  int tiles_w, tiles_h, tiles_n, m_tiles;
+  int Cin, Cout;           // GEMM K per tap, GEMM N
+  int Hout, Wout, os;      // output tensor dims and output stride (1 or 2)
+  int8_t tap_map[kMaxTapEntries];  // which A tensor map
+  int8_t tap_dy[kMaxTapEntries];
+  int8_t tap_dx[kMaxTapEntries];
+  int8_t ph_y[4], ph_x[4];         // output phase offsets
+  int n_amaps;                     // 1 or 4
+};
+
+// ky (0..3) of a 4x4 stride-2 conv -> (parity sub-grid row, row offset inside the sub-grid)
+__host__ __device__ inline void k4s2_tap(int k, int* parity, int* off) {
+  // input coordinate 2*o + k - 1:  k=0 -> 2(o-1)+1 ; k=1 -> 2o ; k=2 -> 2o+1 ; k=3 -> 2(o+1)
+  *parity = (k + 1) & 1;
+  *off = (k == 0) ? -1 : (k == 3 ? 1 : 0);
+}
+// convT phase p (0/1), tap j (0/1) -> (kernel index k, input offset d) with Y = 2*iy + k - 1, Y = 2*y + p
+__host__ __device__ inline void convt_tap(int p, int j, int* k, int* d) {
+  if (p == 0) { *k = j == 0 ? 1 : 3; *d = j == 0 ? 0 : -1; }
+  else        { *k = j == 0 ? 0 : 2; *d = j == 0 ? 1 : 0; }
+}
+
+inline bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+
+// Chooses the pixel tile (bw, bh, bn) with bw*bh*bn == tile_pixels that wastes the fewest rows.
+// Returns false when the grid width cannot be tiled (Wg must divide tile_pixels or be a multiple of it).
+inline bool choose_tile(int tile_pixels, int N, int Hg, int Wg, int* bw, int* bh, int* bn) {
+  int w;
+  if (Wg >= tile_pixels) {
+    if (Wg % tile_pixels) return false;
+    w = tile_pixels;
+  } else {
+    if (!is_pow2(Wg)) return false;
+    w = Wg;
+  }
+  int rest = tile_pixels / w;
+  long best_cost = -1;
+  int best_h = 1;
+  for (int h = 1; h <= rest; h *= 2) {
+    int n = rest / h;
+    long cost = (long)((Hg + h - 1) / h) * h * (long)((N + n - 1) / n) * n;
+    if (best_cost < 0 || cost < best_cost || (cost == best_cost && h > best_h)) {
+      best_cost = cost;
+      best_h = h;
+    }
+  }
+  *bw = w;
+  *bh = best_h;
+  *bn = rest / best_h;
+  return true;
+}
+
+// Fills the geometry + tap tables for a conv role. Returns false on unsupported shapes.
+inline bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout, int tile_pixels, ConvPlan* p) {
+  p->kind = kind;
+  p->N = N;
+  p->Cin = Cin;
+  p->Cout = Cout;
+  for (int i = 0; i < 4; ++i) p->ph_y[i] = p->ph_x[i] = 0;
+  if (kind == B2G_CONV_K3S1) {
+    p->phases = 1; p->taps = 9; p->n_amaps = 1;
+    p->Hg = Hin; p->Wg = Win; p->Hout = Hin; p->Wout = Win; p->os = 1;
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) {
+        int t = ky * 3 + kx;
+        p->tap_map[t] = 0; p->tap_dy[t] = (int8_t)(ky - 1); p->tap_dx[t] = (int8_t)(kx - 1);
+      }
+  } else if (kind == B2G_CONV_K4S2) {
+    if ((Hin & 1) || (Win & 1)) return false;
+    p->phases = 1; p->taps = 16; p->n_amaps = 4;
+    p->Hg = Hin / 2; p->Wg = Win / 2; p->Hout = Hin / 2; p->Wout = Win / 2; p->os = 1;
+    for (int ky = 0; ky < 4; ++ky)
+      for (int kx = 0; kx < 4; ++kx) {
+        int py, dy, px, dx;
+        k4s2_tap(ky, &py, &dy);
+        k4s2_tap(kx, &px, &dx);
+        int t = ky * 4 + kx;
+        p->tap_map[t] = (int8_t)(py * 2 + px); p->tap_dy[t] = (int8_t)dy; p->tap_dx[t] = (int8_t)dx;
+      }
+  } else if (kind == B2G_CONVT_K4S2) {
+    p->phases = 4; p->taps = 4; p->n_amaps = 1;
+    p->Hg = Hin; p->Wg = Win; p->Hout = Hin * 2; p->Wout = Win * 2; p->os = 2;
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px) {
+        int ph = py * 2 + px;
+        p->ph_y[ph] = (int8_t)py; p->ph_x[ph] = (int8_t)px;
+        for (int jy = 0; jy < 2; ++jy)
+          for (int jx = 0; jx < 2; ++jx) {
+            int ky, dy, kx, dx;
+            convt_tap(py, jy, &ky, &dy);
+            convt_tap(px, jx, &kx, &dx);
+            int e = ph * 4 + jy * 2 + jx;
+            p->tap_map[e] = 0; p->tap_dy[e] = (int8_t)dy; p->tap_dx[e] = (int8_t)dx;
+          }
+      }
+  } else {
+    return false;
+  }
+  if (!choose_tile(tile_pixels, N, p->Hg, p->Wg, &p->bw, &p->bh, &p->bn)) return false;
+  p->tiles_w = p->Wg / p->bw;
+  p->tiles_h = (p->Hg + p->bh - 1) / p->bh;
+  p->tiles_n = (N + p->bn - 1) / p->bn;
+  p->m_tiles = p->tiles_w * p->tiles_h * p->tiles_n;
+  return true;
+}
+
+}  // namespace b2g

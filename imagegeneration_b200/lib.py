@@ -1,0 +1,87 @@
+"""ctypes binding of libb200gan.so (the C ABI declared in include/b200gan.h).
+
+The product path has no CPU or library fallback: if the shared library is missing or a call fails, a
+`B200GanError` is raised.  Only raw device pointers, sizes and the CUDA stream handle cross this boundary.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+PKG_DIR = Path(__file__).resolve().parent
+LIB_PATH = PKG_DIR / "libb200gan.so"
+
+# enums mirrored from include/b200gan.h
+CONV_K3S1, CONV_K4S2, CONVT_K4S2 = 0, 1, 2
+ACT_NONE, ACT_LEAKY, ACT_RELU, ACT_TANH = 0, 1, 2, 3
+
+
+class B200GanError(RuntimeError):
+    pass
+
+
+class ConvArgs(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int),
+        ("N", C.c_int), ("Hin", C.c_int), ("Win", C.c_int), ("Cin", C.c_int),
+        ("Cout", C.c_int),
+        ("inp", C.c_void_p),
+        ("wpacked", C.c_void_p),
+        ("out", C.c_void_p),
+        ("bias", C.c_void_p),
+        ("act", C.c_int),
+        ("alpha", C.c_float),
+        ("dropout_thresh8", C.c_int),
+        ("dropout_seed", C.c_ulonglong),
+        ("yprev", C.c_void_p),
+        ("dact", C.c_int),
+        ("dact_alpha", C.c_float), ("dact_scale", C.c_float), ("dact_zero", C.c_float),
+    ]
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Loads libb200gan.so once; raises if it has not been built (see imagegeneration_b200/build.py)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise B200GanError(
+            f"{LIB_PATH} is missing: build it with `python -m imagegeneration_b200.build` "
+            "(there is no CPU fallback for the B200 kernels)")
+    lib = C.CDLL(str(LIB_PATH))
+    lib.b2g_version.restype = C.c_int
+    lib.b2g_last_error.restype = C.c_char_p
+    lib.b2g_conv_igemm.restype = C.c_int
+    lib.b2g_conv_igemm.argtypes = [C.POINTER(ConvArgs), C.c_void_p]
+    lib.b2g_pack_conv_weight.restype = C.c_int
+    lib.b2g_pack_conv_weight.argtypes = [C.c_int] * 7 + [C.c_void_p] * 5 + [C.c_void_p]
+    _declare_rest(lib)
+    _lib = lib
+    return lib
+
+
+def _declare_rest(lib: C.CDLL) -> None:
+    """argtypes for the entry points added after the conv kernels (kept tolerant while the ABI grows)."""
+    for name, argtypes in _EXTRA_SIGNATURES.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            raise B200GanError(f"libb200gan.so does not export {name}; rebuild the library")
+        fn.restype = C.c_int
+        fn.argtypes = argtypes
+
+
+_EXTRA_SIGNATURES: dict[str, list] = {}
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().b2g_last_error()
+        raise B200GanError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")
+
+
+# Names every build of the library must export (tests/test_abi.py checks them against include/b200gan.h).
+def exported_symbols() -> list[str]:
+    return ["b2g_version", "b2g_last_error", "b2g_conv_igemm", "b2g_pack_conv_weight", *_EXTRA_SIGNATURES]

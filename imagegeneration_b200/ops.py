@@ -1,0 +1,83 @@
+"""Tensor-level wrappers over the C ABI: they validate shapes, allocate outputs with torch (device memory and
+streams are torch's job) and pass raw pointers to libb200gan.so.  No arithmetic happens in Python/torch here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import lib as _lib
+from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K3S1, CONV_K4S2, CONVT_K4S2, ConvArgs,
+                  B200GanError, check)
+
+__all__ = ["pack_conv_weight", "conv_igemm", "CONV_K3S1", "CONV_K4S2", "CONVT_K4S2", "ACT_NONE", "ACT_LEAKY",
+           "ACT_RELU", "ACT_TANH"]
+
+_KIND_GEOM = {CONV_K3S1: (3, 1, 9), CONV_K4S2: (4, 1, 16), CONVT_K4S2: (4, 4, 4)}  # k, phases, taps
+
+
+def _ptr(t: torch.Tensor | None):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(*ts: torch.Tensor | None) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise B200GanError("b200gan ops need CUDA tensors: there is no CPU fallback")
+        if t is not None and not t.is_contiguous():
+            raise B200GanError("b200gan ops need contiguous tensors")
+
+
+def pack_conv_weight(kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = False,
+                     scale_scalar: torch.Tensor | None = None, scale_d2: torch.Tensor | None = None,
+                     scale_d3: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fp32 Keras-layout conv weight [kh,kw,d2,d3] -> bf16 packed [phases, Cn, taps*Ck] for conv_igemm."""
+    _need_cuda(w, scale_scalar, scale_d2, scale_d3, out)
+    k, phases, taps = _KIND_GEOM[kind]
+    kh, kw, d2, d3 = w.shape
+    if w.dtype != torch.float32 or kh != k or kw != k:
+        raise B200GanError(f"pack_conv_weight: expected fp32 [{k},{k},d2,d3], got {tuple(w.shape)} {w.dtype}")
+    cn, ck = (d3, d2) if n_is_d3 else (d2, d3)
+    if out is None:
+        out = torch.empty((phases, cn, taps * ck), dtype=torch.bfloat16, device=w.device)
+    check(_lib.load().b2g_pack_conv_weight(kind, kh, kw, d2, d3, int(n_is_d3), int(flip), _ptr(w),
+                                           _ptr(scale_scalar), _ptr(scale_d2), _ptr(scale_d3), _ptr(out),
+                                           _stream()), "b2g_pack_conv_weight")
+    return out
+
+
+def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Tensor | None = None, *,
+               bias: torch.Tensor | None = None, act: int = ACT_NONE, alpha: float = 0.0,
+               dropout_thresh8: int = 0, dropout_seed: int = 0, yprev: torch.Tensor | None = None,
+               dact: int = ACT_NONE, dact_alpha: float = 0.0, dact_scale: float = 1.0,
+               dact_zero: float = 0.0) -> torch.Tensor:
+    """Tensor-core implicit-GEMM conv / transposed conv with fused epilogue (see include/b200gan.h)."""
+    _need_cuda(x, wpacked, out, bias, yprev)
+    n, h, w, cin = x.shape
+    k, phases, taps = _KIND_GEOM[kind]
+    if x.dtype != torch.bfloat16 or wpacked.dtype != torch.bfloat16:
+        raise B200GanError("conv_igemm: activations and packed weights must be bf16")
+    if wpacked.shape[0] != phases or wpacked.shape[2] != taps * cin:
+        raise B200GanError(f"conv_igemm: packed weight {tuple(wpacked.shape)} does not match kind/Cin={cin}")
+    cout = wpacked.shape[1]
+    ho, wo = {CONV_K3S1: (h, w), CONV_K4S2: (h // 2, w // 2), CONVT_K4S2: (h * 2, w * 2)}[kind]
+    if out is None:
+        out = torch.empty((n, ho, wo, cout), dtype=torch.bfloat16, device=x.device)
+    elif tuple(out.shape) != (n, ho, wo, cout) or out.dtype != torch.bfloat16:
+        raise B200GanError("conv_igemm: bad output tensor")
+    if yprev is not None and (tuple(yprev.shape) != tuple(out.shape) or yprev.dtype != torch.bfloat16):
+        raise B200GanError("conv_igemm: yprev must match the output")
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout):
+        raise B200GanError("conv_igemm: bias must be fp32 [Cout]")
+    a = ConvArgs(kind=kind, N=n, Hin=h, Win=w, Cin=cin, Cout=cout, inp=x.data_ptr(), wpacked=wpacked.data_ptr(),
+                 out=out.data_ptr(), bias=None if bias is None else bias.data_ptr(), act=act, alpha=alpha,
+                 dropout_thresh8=dropout_thresh8, dropout_seed=dropout_seed & 0xFFFFFFFFFFFFFFFF,
+                 yprev=None if yprev is None else yprev.data_ptr(), dact=dact, dact_alpha=dact_alpha,
+                 dact_scale=dact_scale, dact_zero=dact_zero)
+    check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
+    return out

@@ -1,0 +1,94 @@
+/* b200gan.h — C ABI of libb200gan.so: the sm_100a kernels behind the SNDCGAN training step.
+ *
+ * The reference (jonathan-schilling/imageGeneration) has NO native/FFI interface: its hot path is Python that
+ * composes Keras layers (sndcgan/SNDCGAN.py:25-128 builders, :241-269 train_step) and every device op is
+ * dispatched by TensorFlow. The drop-in boundary is therefore the Python API (imagegeneration_b200/sndcgan.py
+ * mirrors it name for name); this header is the C boundary *underneath* that API — one entry point per TF op
+ * family that train_step executes. Each declaration cites the reference call site whose TF op it replaces.
+ *
+ * Conventions: plain pointers + sizes only (no torch types); every pointer is a DEVICE pointer unless stated;
+ * all calls are asynchronous on `stream`; nothing is allocated or freed by the library; return 0 on success,
+ * <0 = error code below (message via b2g_last_error()); never throws.
+ */
+#ifndef B200GAN_H_
+#define B200GAN_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b2g_stream_t; /* cudaStream_t */
+
+enum {
+  B2G_OK = 0,
+  B2G_E_INVALID_ARG = -1,
+  B2G_E_UNSUPPORTED_SHAPE = -2,
+  B2G_E_CUDA = -3,
+  B2G_E_DRIVER = -4
+};
+
+int b2g_version(void);
+const char* b2g_last_error(void); /* thread-local, valid until the next failing call on this thread */
+
+/* ---- implicit-GEMM convolutions on tcgen05 tensor cores (TMA-fed, TMEM accumulators) -------------------
+ * Activations are NHWC bf16. Weights are *packed* bf16 [phases][Cout][taps*Cin] (K-major rows), produced by
+ * b2g_pack_conv_weight from the fp32 master weights kept in the reference's Keras layouts.
+ *
+ * kind:
+ *   B2G_CONV_K3S1   3x3 stride-1 SAME conv (9 taps).           Hout=Hin,   Wout=Win
+ *       replaces Conv2D k3 s1 fwd (SNDCGAN.py:87-90,101-104,115-118) and, with flipped/transposed packing,
+ *       its Conv2DBackpropInput (tape.gradient at :248,:256,:266).
+ *   B2G_CONV_K4S2   4x4 stride-2 SAME conv (16 taps).          Hout=Hin/2, Wout=Win/2
+ *       replaces Conv2D k4 s2 fwd (SNDCGAN.py:80-83,94-97,108-111) and the input-gradient of
+ *       Conv2DTranspose k4 s2 (generator backward, :248).
+ *   B2G_CONVT_K4S2  4x4 stride-2 SAME transposed conv as 4 sub-pixel phases of 2x2 taps. Hout=2Hin, Wout=2Win
+ *       replaces Conv2DTranspose k4 s2 fwd (SNDCGAN.py:36-39,43-46,50-53) and the input-gradient of
+ *       Conv2D k4 s2 (discriminator backward).
+ */
+enum { B2G_CONV_K3S1 = 0, B2G_CONV_K4S2 = 1, B2G_CONVT_K4S2 = 2 };
+enum { B2G_ACT_NONE = 0, B2G_ACT_LEAKY = 1, B2G_ACT_RELU = 2, B2G_ACT_TANH = 3 };
+
+typedef struct b2g_conv_args {
+  int kind;
+  int N, Hin, Win, Cin; /* input activation, NHWC */
+  int Cout;             /* GEMM-N: channels of the produced tensor */
+  const void* in;       /* bf16 [N,Hin,Win,Cin] */
+  const void* wpacked;  /* bf16 [phases][Cout][taps*Cin] */
+  void* out;            /* bf16 [N,Hout,Wout,Cout] */
+  /* fused epilogue, applied in this order to the fp32 accumulator */
+  const float* bias; /* per-Cout fp32, or NULL                  (BiasAdd / BatchNorm beta, SNDCGAN.py:40,73) */
+  int act;           /* B2G_ACT_*                                (LeakyReLU :77, ReLU :41)                   */
+  float alpha;       /* LeakyReLU slope                                                                      */
+  int dropout_thresh8;         /* 0 = off; element dropped when its hash byte < thresh8 (p = thresh8/256);
+                                  survivors scaled by 256/(256-thresh8)            (Dropout, SNDCGAN.py:78) */
+  unsigned long long dropout_seed;
+  /* backward use: multiply by the activation derivative recovered from the saved forward output `yprev`
+     (same shape as out): dact=LEAKY: y>0 -> dscale, y<0 -> alpha*dscale, y==0 -> dzero (dropped element);
+     dact=RELU: y>0 -> 1 else 0; dact=TANH: (1-y^2). */
+  const void* yprev; /* bf16 or NULL */
+  int dact;
+  float dact_alpha, dact_scale, dact_zero;
+} b2g_conv_args;
+
+int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
+
+/* Repack an fp32 master conv weight (Keras layout [kh][kw][d2][d3]) into the bf16 K-major layout a
+ * b2g_conv_igemm role needs, folding a scale (1/sigma of spectral norm, or gamma/sqrt(var+eps) of the
+ * inference-mode BatchNorm that follows the conv, SNDCGAN.py:40) so the scaled fp32 weight is never
+ * materialised.
+ *   n_is_d3 = 1: GEMM-N indexes d3 and GEMM-K indexes d2 (Conv2D fwd with HWIO; ConvT dgrad with HWOI)
+ *   n_is_d3 = 0: GEMM-N indexes d2 and GEMM-K indexes d3 (ConvT fwd with HWOI; Conv2D dgrad with HWIO)
+ *   flip    = 1: spatially flipped taps (dgrad of a stride-1 conv)
+ *   scale_scalar (device ptr to one float, may be NULL) multiplies everything (use 1/sigma);
+ *   scale_d2 / scale_d3 (device ptr to per-d2 / per-d3 floats, may be NULL).
+ */
+int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, const float* w,
+                         const float* scale_scalar, const float* scale_d2, const float* scale_d3, void* wpacked,
+                         b2g_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GAN_H_ */
