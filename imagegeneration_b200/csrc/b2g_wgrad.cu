@@ -1,0 +1,300 @@
+// b2g_wgrad.cu — weight-gradient implicit GEMM on tcgen05 with MN-major (pixel-reduction) operands.
+//
+//   dW[tap][a][b] = sum over grid pixels  S[pixel shifted by tap, a] * U[pixel, b]        (fp32, atomically
+//   accumulated into the caller's zero-initialised gradient buffer; split-K over pixel ranges)
+//
+//   S = the tensor the taps shift over (conv: the layer input x; convT: the output gradient), read through the
+//       same TMA tap plan as the forward conv (K3S1: 9 shifts; K4S2: 16 taps over 4 parity sub-grids);
+//   U = the tensor living on the reduction grid itself (conv: output gradient; convT: the layer input).
+// Both tiles arrive as [64 pixels][64 channels] 128B-swizzled TMA boxes, i.e. the reduction index (pixel) is the
+// slow one: they are fed to tcgen05.mma as MN-major A (M = channels of one operand) and MN-major B.
+// Whichever operand has a multiple of 128 channels becomes the M side; the epilogue transposes if needed.
+//
+// Replaces Conv2DBackpropFilter (tape.gradient at sndcgan/SNDCGAN.py:248,:256,:266) for the Conv2D layers
+// :80-118 and the Conv2DTranspose layers :36-53.
+#include "b2g_conv.cuh"
+#include "b2g_host.h"
+#include "b2g_ptx.cuh"
+
+namespace b2g {
+
+struct alignas(64) WgradKernelParams {
+  CUtensorMap smap[4];  // shifted operand (1 or 4 maps)
+  CUtensorMap umap;     // unshifted operand
+  ConvPlan plan;        // tap plan + 64-pixel tiling of the reduction grid
+  int m_is_shifted;     // 1: M side = S (a), N side = U (b);  0: M side = U (b), N side = S (a) -> transposed store
+  int Cm, Cn;           // channels on the M / N side
+  int m_tiles, n_tiles, splits, ptiles;
+  int Ca, Cb;           // output is [taps][Ca][Cb]
+  float* out;
+};
+
+template <int BLOCK_N>
+struct WgradCfg {
+  static constexpr int kTileK = 64;                 // pixels per k-step
+  static constexpr int kBoxBytes = kTileK * 128;    // one [64 pix][64 ch] box
+  static constexpr int kMBytes = 2 * kBoxBytes;     // 128 channels
+  static constexpr int kNBytes = (BLOCK_N / 64) * kBoxBytes;
+  static constexpr int kStageBytes = kMBytes + kNBytes;
+  static constexpr int kStages = BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8);
+  static constexpr int kTmemCols = 2 * BLOCK_N;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;
+};
+
+constexpr int kWgradThreads = 192;
+
+struct WgradItem {
+  int tap, m_tile, n_tile, p_begin, p_end;
+};
+__device__ __forceinline__ WgradItem decode_item(const WgradKernelParams& p, int item) {
+  WgradItem w;
+  const int taps = p.plan.taps;
+  w.tap = item % taps;
+  int r = item / taps;
+  w.m_tile = r % p.m_tiles;
+  r /= p.m_tiles;
+  w.n_tile = r % p.n_tiles;
+  const int split = r / p.n_tiles;
+  w.p_begin = (int)((long)split * p.ptiles / p.splits);
+  w.p_end = (int)((long)(split + 1) * p.ptiles / p.splits);
+  return w;
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_constant__ WgradKernelParams p) {
+  using Cfg = WgradCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const ConvPlan& pl = p.plan;
+  const int total_items = pl.taps * p.m_tiles * p.n_tiles * p.splits;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < pl.n_amaps; ++i) tma_prefetch_desc(&p.smap[i]);
+    tma_prefetch_desc(&p.umap);
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        const WgradItem wi = decode_item(p, item);
+        const CUtensorMap* sm = &p.smap[pl.tap_map[wi.tap]];
+        const int dy = pl.tap_dy[wi.tap], dx = pl.tap_dx[wi.tap];
+        const int m_c0 = wi.m_tile * 128, n_c0 = wi.n_tile * BLOCK_N;
+        for (int pt = wi.p_begin; pt < wi.p_end; ++pt) {
+          const int tw = pt % pl.tiles_w;
+          const int r2 = pt / pl.tiles_w;
+          const int th = r2 % pl.tiles_h;
+          const int tn = r2 / pl.tiles_h;
+          const int w0 = tw * pl.bw, h0 = th * pl.bh, n0 = tn * pl.bn;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* m_dst = smem + stage * Cfg::kStageBytes;
+          uint8_t* n_dst = m_dst + Cfg::kMBytes;
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          if (p.m_is_shifted) {
+#pragma unroll
+            for (int g = 0; g < 2; ++g)
+              tma_load_4d(m_dst + g * Cfg::kBoxBytes, sm, &full_bar[stage], m_c0 + g * 64, w0 + dx, h0 + dy, n0);
+#pragma unroll
+            for (int g = 0; g < BLOCK_N / 64; ++g)
+              tma_load_4d(n_dst + g * Cfg::kBoxBytes, &p.umap, &full_bar[stage], n_c0 + g * 64, w0, h0, n0);
+          } else {
+#pragma unroll
+            for (int g = 0; g < 2; ++g)
+              tma_load_4d(m_dst + g * Cfg::kBoxBytes, &p.umap, &full_bar[stage], m_c0 + g * 64, w0, h0, n0);
+#pragma unroll
+            for (int g = 0; g < BLOCK_N / 64; ++g)
+              tma_load_4d(n_dst + g * Cfg::kBoxBytes, sm, &full_bar[stage], n_c0 + g * 64, w0 + dx, h0 + dy, n0);
+          }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, BLOCK_N);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
+        const WgradItem wi = decode_item(p, item);
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(&tempty_bar[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+        const int k_steps = wi.p_end - wi.p_begin;
+        for (int ks = 0; ks < k_steps; ++ks) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t m_addr = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t n_addr = m_addr + Cfg::kMBytes;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // 16 pixels per MMA = two 8-line swizzle groups = 2048 bytes
+            umma_f16(d_tmem, umma_smem_desc(m_addr + k * 2048, Cfg::kBoxBytes, 1024),
+                     umma_smem_desc(n_addr + k * 2048, Cfg::kBoxBytes, 1024), idesc, (ks | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[as]);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;  // M index inside the tile
+    int it = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
+      const WgradItem wi = decode_item(p, item);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      const bool nonempty = wi.p_end > wi.p_begin;
+      mbar_wait(&tfull_bar[as], aphase);
+      tc_fence_after();
+      const int m = wi.m_tile * 128 + row;
+      float* obase = p.out + (size_t)wi.tap * p.Ca * p.Cb;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
+        tmem_ld_wait();
+        if (nonempty) {
+          const int n = wi.n_tile * BLOCK_N + c * 32;
+          if (p.m_is_shifted) {  // out[a = m][b = n..n+31]: contiguous per thread
+            float* dst = obase + (size_t)m * p.Cb + n;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(__uint_as_float(r[j])),
+                           "f"(__uint_as_float(r[j + 1])), "f"(__uint_as_float(r[j + 2])),
+                           "f"(__uint_as_float(r[j + 3]))
+                           : "memory");
+            }
+          } else {  // out[a = n + j][b = m]: coalesced across the warp's lanes
+#pragma unroll
+            for (int j = 0; j < 32; ++j) atomicAdd(obase + (size_t)(n + j) * p.Cb + m, __uint_as_float(r[j]));
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+template <int BLOCK_N>
+static int launch_wgrad(const WgradKernelParams& kp, int total_items, cudaStream_t stream) {
+  using Cfg = WgradCfg<BLOCK_N>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int grid = total_items < num_sms() ? total_items : num_sms();
+  wgrad_kernel<BLOCK_N><<<grid, kWgradThreads, Cfg::kSmemBytes, stream>>>(kp);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+}  // namespace b2g
+
+using namespace b2g;
+
+extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!a || !a->shifted || !a->unshifted || !a->dw) return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: null pointer");
+  if (a->kind != B2G_CONV_K3S1 && a->kind != B2G_CONV_K4S2)
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: kind must be K3S1 or K4S2 (tap plan of the shifted operand)");
+  if (a->Ca % 64 || a->Cb % 64 || a->Ca <= 0 || a->Cb <= 0)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: channels (%d,%d) must be multiples of 64", a->Ca, a->Cb);
+  if (a->Ca % 128 && a->Cb % 128)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: one of Ca=%d, Cb=%d must be a multiple of 128", a->Ca, a->Cb);
+
+  WgradKernelParams kp;
+  memset(&kp, 0, sizeof(kp));
+  // plan over the shifted operand's geometry; its grid (Hg, Wg) is the unshifted operand's spatial size
+  if (!build_conv_plan(a->kind, a->N, a->Hs, a->Ws, a->Ca, a->Cb, 64, &kp.plan))
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: cannot tile N=%d Hs=%d Ws=%d", a->N, a->Hs, a->Ws);
+  const ConvPlan& pl = kp.plan;
+  kp.m_is_shifted = (a->Ca % 128 == 0) ? 1 : 0;
+  kp.Cm = kp.m_is_shifted ? a->Ca : a->Cb;
+  kp.Cn = kp.m_is_shifted ? a->Cb : a->Ca;
+  const int block_n = kp.Cn % 256 == 0 ? 256 : (kp.Cn % 128 == 0 ? 128 : 64);
+  kp.m_tiles = kp.Cm / 128;
+  kp.n_tiles = kp.Cn / block_n;
+  kp.ptiles = pl.m_tiles;
+  kp.Ca = a->Ca;
+  kp.Cb = a->Cb;
+  kp.out = a->dw;
+  // split-K: aim for ~4 work items per SM, at least 8 k-steps each
+  const int base_items = pl.taps * kp.m_tiles * kp.n_tiles;
+  int splits = (4 * num_sms() + base_items - 1) / base_items;
+  if (splits > kp.ptiles / 8) splits = kp.ptiles / 8;
+  if (splits < 1) splits = 1;
+  kp.splits = splits;
+
+  const size_t es = 2;
+  const uint32_t box[4] = {64u, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bn};
+  const char* sbase = static_cast<const char*>(a->shifted);
+  if (pl.n_amaps == 1) {
+    const uint64_t dims[4] = {(uint64_t)a->Ca, (uint64_t)a->Ws, (uint64_t)a->Hs, (uint64_t)a->N};
+    const uint64_t str[3] = {(uint64_t)a->Ca * es, (uint64_t)a->Ws * a->Ca * es, (uint64_t)a->Hs * a->Ws * a->Ca * es};
+    int rc = make_tmap(&kp.smap[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, sbase, dims, str, box);
+    if (rc) return rc;
+  } else {
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px) {
+        const uint64_t dims[4] = {(uint64_t)a->Ca, (uint64_t)a->Ws / 2, (uint64_t)a->Hs / 2, (uint64_t)a->N};
+        const uint64_t str[3] = {(uint64_t)2 * a->Ca * es, (uint64_t)2 * a->Ws * a->Ca * es,
+                                 (uint64_t)a->Hs * a->Ws * a->Ca * es};
+        int rc = make_tmap(&kp.smap[py * 2 + px], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                           sbase + ((size_t)py * a->Ws + px) * a->Ca * es, dims, str, box);
+        if (rc) return rc;
+      }
+  }
+  {
+    const uint64_t dims[4] = {(uint64_t)a->Cb, (uint64_t)pl.Wg, (uint64_t)pl.Hg, (uint64_t)a->N};
+    const uint64_t str[3] = {(uint64_t)a->Cb * es, (uint64_t)pl.Wg * a->Cb * es, (uint64_t)pl.Hg * pl.Wg * a->Cb * es};
+    int rc = make_tmap(&kp.umap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a->unshifted, dims, str, box);
+    if (rc) return rc;
+  }
+  const int total_items = base_items * kp.splits;
+  switch (block_n) {
+    case 256: return launch_wgrad<256>(kp, total_items, stream);
+    case 128: return launch_wgrad<128>(kp, total_items, stream);
+    default: return launch_wgrad<64>(kp, total_items, stream);
+  }
+}

@@ -39,6 +39,17 @@ class ConvArgs(C.Structure):
     ]
 
 
+class WgradArgs(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int),
+        ("N", C.c_int), ("Hs", C.c_int), ("Ws", C.c_int),
+        ("Ca", C.c_int), ("Cb", C.c_int),
+        ("shifted", C.c_void_p),
+        ("unshifted", C.c_void_p),
+        ("dw", C.c_void_p),
+    ]
+
+
 _lib = None
 
 
@@ -73,7 +84,9 @@ def _declare_rest(lib: C.CDLL) -> None:
         fn.argtypes = argtypes
 
 
-_EXTRA_SIGNATURES: dict[str, list] = {}
+_EXTRA_SIGNATURES: dict[str, list] = {
+    "b2g_conv_wgrad": [C.POINTER(WgradArgs), C.c_void_p],
+}
 
 
 def check(rc: int, what: str) -> None:

@@ -8,10 +8,11 @@ import ctypes as C
 import torch
 
 from . import lib as _lib
+from .lib import WgradArgs
 from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K3S1, CONV_K4S2, CONVT_K4S2, ConvArgs,
                   B200GanError, check)
 
-__all__ = ["pack_conv_weight", "conv_igemm", "CONV_K3S1", "CONV_K4S2", "CONVT_K4S2", "ACT_NONE", "ACT_LEAKY",
+__all__ = ["pack_conv_weight", "conv_igemm", "conv_wgrad", "CONV_K3S1", "CONV_K4S2", "CONVT_K4S2", "ACT_NONE", "ACT_LEAKY",
            "ACT_RELU", "ACT_TANH"]
 
 _KIND_GEOM = {CONV_K3S1: (3, 1, 9), CONV_K4S2: (4, 1, 16), CONVT_K4S2: (4, 4, 4)}  # k, phases, taps
@@ -81,3 +82,24 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                  dact_scale=dact_scale, dact_zero=dact_zero)
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
     return out
+
+
+def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
+    """dw[tap][a][b] += sum_pixels shifted[tap-shifted pixel, a] * unshifted[pixel, b] (see include/b200gan.h).
+
+    dw is fp32 [k,k,Ca,Cb] and is accumulated into (zero it first for a fresh gradient)."""
+    _need_cuda(shifted, unshifted, dw)
+    n, hs, ws, ca = shifted.shape
+    cb = unshifted.shape[3]
+    k = 3 if kind == CONV_K3S1 else 4
+    hg, wg = (hs, ws) if kind == CONV_K3S1 else (hs // 2, ws // 2)
+    if tuple(unshifted.shape) != (n, hg, wg, cb):
+        raise B200GanError(f"conv_wgrad: unshifted operand {tuple(unshifted.shape)} != {(n, hg, wg, cb)}")
+    if shifted.dtype != torch.bfloat16 or unshifted.dtype != torch.bfloat16 or dw.dtype != torch.float32:
+        raise B200GanError("conv_wgrad: operands must be bf16 and dw fp32")
+    if dw.numel() != k * k * ca * cb:
+        raise B200GanError("conv_wgrad: bad dw size")
+    a = WgradArgs(kind=kind, N=n, Hs=hs, Ws=ws, Ca=ca, Cb=cb, shifted=shifted.data_ptr(),
+                  unshifted=unshifted.data_ptr(), dw=dw.data_ptr())
+    check(_lib.load().b2g_conv_wgrad(C.byref(a), _stream()), "b2g_conv_wgrad")
+    return dw

@@ -88,6 +88,25 @@ int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, 
                          const float* scale_scalar, const float* scale_d2, const float* scale_d3, void* wpacked,
                          b2g_stream_t stream);
 
+/* ---- conv / convT weight gradient on tensor cores ---------------------------------------------------------
+ *   dw[tap][a][b] += sum_{n,y,x} shifted[n, tap(y,x), a] * unshifted[n, y, x, b]      (fp32 atomics; the
+ *   caller zero-fills dw first).  `kind` is the tap plan of the shifted operand:
+ *     Conv2D k3 s1  [3,3,Cin,Cout]:  kind=K3S1, shifted = layer input x   (Ca=Cin),  unshifted = dY (Cb=Cout)
+ *     Conv2D k4 s2  [4,4,Cin,Cout]:  kind=K4S2, shifted = layer input x   (Ca=Cin),  unshifted = dY (Cb=Cout)
+ *     Conv2DTranspose k4 s2 [4,4,Cout,Cin]: kind=K4S2, shifted = dY (Ca=Cout), unshifted = layer input (Cb=Cin)
+ *   Hs, Ws = spatial size of the shifted operand; the unshifted one is (Hs,Ws) for K3S1, (Hs/2,Ws/2) for K4S2.
+ *   Replaces Conv2DBackpropFilter behind tape.gradient (sndcgan/SNDCGAN.py:248,:256,:266). */
+typedef struct b2g_wgrad_args {
+  int kind;
+  int N, Hs, Ws;
+  int Ca, Cb;
+  const void* shifted;   /* bf16 [N,Hs,Ws,Ca] */
+  const void* unshifted; /* bf16 [N,Hg,Wg,Cb] */
+  float* dw;             /* fp32 [taps][Ca][Cb], accumulated into */
+} b2g_wgrad_args;
+
+int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
