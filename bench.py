@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py — SNDCGAN 256x144 training throughput (BASELINE.json metric) on N B200s of one node.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (sm_100a kernels)
+  python bench.py --impl reference --steps K --warmup W     the reference's CPU path (PyTorch-CPU restatement,
+                                                            TensorFlow is not installable here) on the host cores
+For N > 1 launch with `python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...`.
+
+A "step" = one SNDCGAN.train_step (1 G update + 2 D updates, sndcgan/SNDCGAN.py:241-269) on a synthetic batch of
+64 images per GPU (BASELINE config[1]; weak scaling: N GPUs -> global batch 64*N, = config[2]'s 512 at N=8).
+Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+IMAGE_SIZE = (144, 256, 3)
+METRIC = "SNDCGAN 256x144 train images/sec"
+FLOP_PER_IMAGE = 146.26e9   # one train_step, algorithmic
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d, "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in out.strip().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# reference arm / CPU baseline: the oracle restatement of the reference's train_step on the host cores
+# ----------------------------------------------------------------------------------------------------------
+def _oracle_step_factory(batch):
+    import torch
+    from oracle import sndcgan_oracle as O
+    orc = O.OracleSNDCGAN(IMAGE_SIZE, dropout=0.5, seed=62)
+    g = torch.Generator().manual_seed(1234)
+    real = torch.rand((batch, *IMAGE_SIZE), generator=g) * 2 - 1
+    z = torch.rand((batch, 128), generator=g) * 2 - 1
+    shapes = [(144, 256, 64), (72, 128, 128), (72, 128, 128), (36, 64, 256), (36, 64, 256), (18, 32, 512), (18, 32, 512)]
+
+    def masks():
+        return [(torch.rand((batch, *s), generator=g) >= 0.5).float() for s in shapes]
+
+    def step():
+        return orc.train_step(real, z, masks(), masks(), masks())
+    return step
+
+
+def cpu_baseline(target_seconds=20.0):
+    """Oracle train_step on the host cores: one step at batch 16 fp32 (BASELINE config[0]) unless a 1-image probe
+    says that would take much longer than `target_seconds`, in which case a smaller batch is used."""
+    import torch
+    cores = torch.get_num_threads()
+    probe = _oracle_step_factory(1)
+    t0 = time.perf_counter()
+    probe()
+    t1 = time.perf_counter() - t0
+    batch = 16
+    while batch > 1 and t1 * batch > 2.0 * target_seconds:
+        batch //= 2
+    step = _oracle_step_factory(batch)
+    t0 = time.perf_counter()
+    step()
+    dt = time.perf_counter() - t0
+    return {"value": batch / dt, "unit": "images/s", "cores": cores, "kind": "port",
+            "sample": f"1 oracle train_step (PyTorch-CPU restatement of SNDCGAN.py:241-269, fp32, dropout 0.5) at "
+                      f"batch {batch}, {dt:.2f} s, {cores} threads; TensorFlow itself is not installable here"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    cores = torch.get_num_threads()
+    probe = _oracle_step_factory(1)
+    t0 = time.perf_counter()
+    probe()
+    t1 = time.perf_counter() - t0
+    total = args.steps + args.warmup
+    batch = 16
+    while batch > 1 and t1 * batch * total > 150.0:
+        batch //= 2
+    step = _oracle_step_factory(batch)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = batch * args.steps / dt
+    sample = (f"{args.steps} oracle train_steps at batch {batch} per step (bounded sample of the batch-64 workload), "
+              f"{cores} host threads")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "SNDCGAN one G+D train_step at 256x144, fp32, CPU (PyTorch restatement of the "
+                                   "reference; TensorFlow unavailable)", "batch_per_step": batch},
+            "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from imagegeneration_b200 import lib
+    from imagegeneration_b200.sndcgan import DeviceFeeder, SNDCGANEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the B200 path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    pg = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        pg = dist.group.WORLD
+    B = args.batch
+    eng = SNDCGANEngine(B, dropout=0.5, image_size=IMAGE_SIZE, seed=62, spectral_norm=args.spectral_norm,
+                        loss=args.loss, process_group=pg)
+    g = torch.Generator().manual_seed(1234 + rank)
+    real_host = [(torch.rand((B, *IMAGE_SIZE), generator=g) * 2 - 1).pin_memory() for _ in range(2)]
+    z_host = [(torch.rand((B, 128), generator=g) * 2 - 1).pin_memory() for _ in range(2)]
+    real_dev = [t.cuda() for t in real_host]
+    z_dev = [t.cuda() for t in z_host]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing: `value`
+    for i in range(args.warmup):
+        eng.train_step(real_dev[i & 1], z_dev[i & 1])
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0 = lib.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        out = eng.train_step(real_dev[i & 1], z_dev[i & 1])
+    e1.record()
+    barrier()
+    launches = lib.launch_count - l0
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if sampler else None
+    losses = [float(x) for x in out[:4]]
+    ms_per_step = ms_total / args.steps
+    value = B * world * args.steps / (ms_total * 1e-3)
+
+    # ---- end-to-end timing through the public API with HOST buffers: `e2e`
+    feeder = DeviceFeeder(B, IMAGE_SIZE)
+    feeder.put(real_host[0], z_host[0])
+    for i in range(2):  # warm the copy path
+        feeder.put(real_host[(i + 1) & 1], z_host[(i + 1) & 1])
+        r, z, slot = feeder.get()
+        o = eng.train_step(r, z)
+        feeder.release(slot)
+        torch.stack(o[:4]).cpu()
+    barrier()
+    d2h = 4 * 4 + 2 * B * 4
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(args.steps):
+        feeder.put(real_host[(i + 1) & 1], z_host[(i + 1) & 1])   # next batch: H2D overlaps this step
+        r, z, slot = feeder.get()
+        o = eng.train_step(r, z)
+        feeder.release(slot)
+        _l = torch.stack(o[:4]).cpu()                               # D2H of the step's losses + logits
+        _a, _b = o[4].cpu(), o[5].cpu()
+    feeder.get()  # drain the last prefetched batch
+    t1.record()
+    barrier()
+    e2e_ms = max_over_ranks(t0.elapsed_time(t1))
+    e2e_value = B * world * args.steps / (e2e_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel family: one instrumented step (events around every tensor-core launch)
+    lib.profile_sink = []
+    eng.train_step(real_dev[0], z_dev[0])
+    torch.cuda.synchronize()
+    agg = {}
+    for name, flops, a, b in lib.profile_sink:
+        d = agg.setdefault(name, [0.0, 0.0, 0])
+        d[0] += flops
+        d[1] += a.elapsed_time(b) * 1e-3
+        d[2] += 1
+    lib.profile_sink = None
+    peaks, peak_kind = _peaks()
+    peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
+    roof = {}
+    for name, (fl, sec, cnt) in agg.items():
+        roof[name] = {"bound": "tensor", "achieved": fl / sec / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
+                      "frac": fl / sec / 1e12 / peak_tf, "traffic": None, "launches_per_step": cnt,
+                      "ms_per_step": sec * 1e3, "peak_kind": f"{peak_kind} sustained bf16"}
+    tc_ms = sum(v["ms_per_step"] for v in roof.values())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {
+        "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "SNDCGAN one G+D train_step at 256x144 (1 G + 2 D Adam updates, 3 D forwards), "
+                               "bf16 activations / fp32 accumulate + master weights, dropout 0.5",
+                   "batch_per_gpu": B, "global_batch": B * world, "parallelism": f"dp{world}",
+                   "loss": args.loss, "spectral_norm": bool(args.spectral_norm),
+                   "l2": "per-step working set (~6 GB of activations) is much larger than the 126 MB L2"},
+        "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": feeder.bytes_per_batch,
+                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roof.get("conv_igemm"),
+        "roofline_wgrad": roof.get("conv_wgrad"),
+        "step_model": {"tflops_per_gpu_whole_step": FLOP_PER_IMAGE * B / (ms_per_step * 1e-3) / 1e12,
+                       "frac_of_peak_whole_step": FLOP_PER_IMAGE * B / (ms_per_step * 1e-3) / 1e12 / peak_tf,
+                       "tensor_core_kernels_ms": tc_ms, "other_ms": ms_per_step - tc_ms},
+        "losses_last_step": losses,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
+    ap.add_argument("--loss", default="bce", choices=["bce", "hinge"])
+    ap.add_argument("--spectral-norm", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

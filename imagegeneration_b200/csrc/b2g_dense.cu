@@ -1,0 +1,301 @@
+// b2g_dense.cu — the two dense layers of the SNDCGAN step and the loss.
+//   G stem  : Dense(128 -> 512*h*w, no bias) + inference BatchNorm + ReLU   (sndcgan/SNDCGAN.py:31-34)
+//             HBM-bound on the 151 MB fp32 weight; forward and backward read/write it exactly once per
+//             batch chunk of 32 samples.
+//   D head  : Flatten + Dense(1) (:122-123), BinaryCrossentropy(from_logits) (:170,:246,:254,:262) or hinge,
+//             and the head's backward which also applies conv7's LeakyReLU/Dropout derivative.
+#include "b2g_host.h"
+#include "b2g_ptx.cuh"
+
+namespace b2g {
+
+constexpr int kDenseBC = 32;   // batch chunk held in registers
+constexpr int kDenseK = 128;   // z size (sndcgan/Trainer.py:8)
+
+// out[b][j] = relu(gscale[j] * sum_k z[b][k] W[k][j] + beta[j]),  gscale = gamma * inv_std
+__global__ void __launch_bounds__(128) dense_g_fwd_kernel(const float* __restrict__ z, const float* __restrict__ W,
+                                                          const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float inv_std,
+                                                          __nv_bfloat16* __restrict__ out, int B, int F) {
+  __shared__ __align__(16) float zs[kDenseK][kDenseBC];
+  const int j = (blockIdx.x * 128 + threadIdx.x) * 2;
+  const bool live = j < F;
+  for (int b0 = 0; b0 < B; b0 += kDenseBC) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < kDenseK * kDenseBC; i += 128) {
+      const int k = i / kDenseBC, b = i % kDenseBC;
+      zs[k][b] = (b0 + b < B) ? z[(size_t)(b0 + b) * kDenseK + k] : 0.f;
+    }
+    __syncthreads();
+    if (!live) continue;
+    float acc0[kDenseBC], acc1[kDenseBC];
+#pragma unroll
+    for (int b = 0; b < kDenseBC; ++b) acc0[b] = acc1[b] = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < kDenseK; ++k) {
+      const float2 w = __ldg(reinterpret_cast<const float2*>(W + (size_t)k * F + j));
+#pragma unroll
+      for (int b4 = 0; b4 < kDenseBC / 4; ++b4) {
+        const float4 zz = *reinterpret_cast<const float4*>(&zs[k][b4 * 4]);
+        acc0[b4 * 4 + 0] += zz.x * w.x; acc1[b4 * 4 + 0] += zz.x * w.y;
+        acc0[b4 * 4 + 1] += zz.y * w.x; acc1[b4 * 4 + 1] += zz.y * w.y;
+        acc0[b4 * 4 + 2] += zz.z * w.x; acc1[b4 * 4 + 2] += zz.z * w.y;
+        acc0[b4 * 4 + 3] += zz.w * w.x; acc1[b4 * 4 + 3] += zz.w * w.y;
+      }
+    }
+    const float g0 = gamma[j] * inv_std, g1 = gamma[j + 1] * inv_std;
+    const float be0 = beta[j], be1 = beta[j + 1];
+#pragma unroll
+    for (int b = 0; b < kDenseBC; ++b) {
+      if (b0 + b < B) {
+        const float y0 = fmaxf(acc0[b] * g0 + be0, 0.f), y1 = fmaxf(acc1[b] * g1 + be1, 0.f);
+        *reinterpret_cast<uint32_t*>(out + (size_t)(b0 + b) * F + j) = pack_bf16x2(y0, y1);
+      }
+    }
+  }
+}
+
+// Backward of the stem for one batch chunk [b0, b0+32): dq = dL/d(BN output before ReLU) with ReLU' applied.
+//   dbeta[j] (+)= sum_b dq[b][j];  G[k][j] = sum_b z[b][k] dq[b][j];  dW[k][j] (+)= gscale[j] * G[k][j];
+//   dgamma[j] (+)= inv_std * sum_k W[k][j] * G[k][j]      (x_hat never materialised)
+__global__ void __launch_bounds__(128) dense_g_bwd_kernel(const float* __restrict__ z, const float* __restrict__ W,
+                                                          const float* __restrict__ gamma, float inv_std,
+                                                          const __nv_bfloat16* __restrict__ dq,
+                                                          float* __restrict__ dW, float* __restrict__ dgamma,
+                                                          float* __restrict__ dbeta, int B, int F, int b0,
+                                                          int accumulate) {
+  __shared__ __align__(16) float zs[kDenseK][kDenseBC];
+  for (int i = threadIdx.x; i < kDenseK * kDenseBC; i += 128) {
+    const int k = i / kDenseBC, b = i % kDenseBC;
+    zs[k][b] = (b0 + b < B) ? z[(size_t)(b0 + b) * kDenseK + k] : 0.f;
+  }
+  __syncthreads();
+  const int j = (blockIdx.x * 128 + threadIdx.x) * 2;
+  if (j >= F) return;
+  float d0[kDenseBC], d1[kDenseBC];
+  float sb0 = 0.f, sb1 = 0.f;
+#pragma unroll
+  for (int b = 0; b < kDenseBC; ++b) {
+    uint32_t v = 0;
+    if (b0 + b < B) v = __ldg(reinterpret_cast<const uint32_t*>(dq + (size_t)(b0 + b) * F + j));
+    d0[b] = bf16_lo(v);
+    d1[b] = bf16_hi(v);
+    sb0 += d0[b];
+    sb1 += d1[b];
+  }
+  const float g0 = gamma[j] * inv_std, g1 = gamma[j + 1] * inv_std;
+  float sg0 = 0.f, sg1 = 0.f;
+#pragma unroll 2
+  for (int k = 0; k < kDenseK; ++k) {
+    float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+    for (int b4 = 0; b4 < kDenseBC / 4; ++b4) {
+      const float4 zz = *reinterpret_cast<const float4*>(&zs[k][b4 * 4]);
+      a0 += zz.x * d0[b4 * 4] + zz.y * d0[b4 * 4 + 1] + zz.z * d0[b4 * 4 + 2] + zz.w * d0[b4 * 4 + 3];
+      a1 += zz.x * d1[b4 * 4] + zz.y * d1[b4 * 4 + 1] + zz.z * d1[b4 * 4 + 2] + zz.w * d1[b4 * 4 + 3];
+    }
+    const float2 w = __ldg(reinterpret_cast<const float2*>(W + (size_t)k * F + j));
+    sg0 += w.x * a0;
+    sg1 += w.y * a1;
+    float2* dst = reinterpret_cast<float2*>(dW + (size_t)k * F + j);
+    float2 o = make_float2(a0 * g0, a1 * g1);
+    if (accumulate) {
+      const float2 old = *dst;
+      o.x += old.x;
+      o.y += old.y;
+    }
+    *dst = o;
+  }
+  if (accumulate) {
+    dgamma[j] += sg0 * inv_std; dgamma[j + 1] += sg1 * inv_std;
+    dbeta[j] += sb0; dbeta[j + 1] += sb1;
+  } else {
+    dgamma[j] = sg0 * inv_std; dgamma[j + 1] = sg1 * inv_std;
+    dbeta[j] = sb0; dbeta[j + 1] = sb1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// D head: partial dot products  part[b][s] = sum_{j in slice s} x[b][j] * w[j]
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) dhead_partial_kernel(const __nv_bfloat16* __restrict__ x,
+                                                            const float* __restrict__ w, float* __restrict__ part,
+                                                            int F, int S) {
+  const int b = blockIdx.y, s = blockIdx.x;
+  const int per = ((F / 8 + S - 1) / S);  // 8-element groups per slice
+  const int g0 = s * per, g1 = min(g0 + per, F / 8);
+  const uint4* xp = reinterpret_cast<const uint4*>(x + (size_t)b * F);
+  const float4* wp = reinterpret_cast<const float4*>(w);
+  float acc = 0.f;
+  for (int g = g0 + threadIdx.x; g < g1; g += 256) {
+    const uint4 v = __ldg(xp + g);
+    const float4 wa = __ldg(wp + 2 * g), wb = __ldg(wp + 2 * g + 1);
+    acc += bf16_lo(v.x) * wa.x + bf16_hi(v.x) * wa.y + bf16_lo(v.y) * wa.z + bf16_hi(v.y) * wa.w +
+           bf16_lo(v.z) * wb.x + bf16_hi(v.z) * wb.y + bf16_lo(v.w) * wb.z + bf16_hi(v.w) * wb.w;
+  }
+  __shared__ float red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    part[b * S + s] = t;
+  }
+}
+
+// logits[b] = wscale * sum_s part[b][s] + bias;  loss and dL/dlogit.  One block.
+//   loss_kind 0: BCE-with-logits against `label`;  1: D hinge (label 1: relu(1-x), 0: relu(1+x));  2: G hinge (-x)
+//   loss_out[0] = inv_batch * sum_b loss_b ;  dlogit[b] = inv_batch * dloss_b/dx ; loss_out[1] = inv_batch*sum sigmoid
+__global__ void dhead_loss_kernel(const float* __restrict__ part, int S, const float* __restrict__ wscale,
+                                  const float* __restrict__ bias, int B, int loss_kind, float label, float inv_batch,
+                                  float* __restrict__ logits, float* __restrict__ dlogit,
+                                  float* __restrict__ loss_out) {
+  __shared__ float red[2][32];
+  const float sc = wscale ? *wscale : 1.f;
+  float lsum = 0.f, psum = 0.f;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float t = 0.f;
+    for (int s = 0; s < S; ++s) t += part[b * S + s];
+    const float x = t * sc + bias[0];
+    logits[b] = x;
+    const float sig = 1.f / (1.f + __expf(-x));
+    float l, d;
+    if (loss_kind == 0) {
+      l = fmaxf(x, 0.f) - x * label + log1pf(__expf(-fabsf(x)));
+      d = sig - label;
+    } else if (loss_kind == 1) {
+      if (label > 0.5f) { l = fmaxf(1.f - x, 0.f); d = x < 1.f ? -1.f : 0.f; }
+      else              { l = fmaxf(1.f + x, 0.f); d = x > -1.f ? 1.f : 0.f; }
+    } else {
+      l = -x;
+      d = -1.f;
+    }
+    dlogit[b] = d * inv_batch;
+    lsum += l;
+    psum += sig;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lsum += __shfl_xor_sync(0xffffffffu, lsum, o);
+    psum += __shfl_xor_sync(0xffffffffu, psum, o);
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = lsum; red[1][threadIdx.x >> 5] = psum; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, c = 0.f;
+    for (int i = 0; i < (int)(blockDim.x + 31) / 32; ++i) { a += red[0][i]; c += red[1][i]; }
+    loss_out[0] = a * inv_batch;
+    loss_out[1] = c * inv_batch;
+  }
+}
+
+// Head backward: dx[b][j] = dlogit[b] * wscale * w[j] * act'(x[b][j]);  dw[j] (+)= sum_b dlogit[b] * x[b][j];
+// db (+)= sum_b dlogit[b].   act' = LeakyReLU/Dropout derivative recovered from the saved conv7 output x.
+__global__ void __launch_bounds__(256) dhead_bwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                        const float* __restrict__ w, const float* __restrict__ wscale,
+                                                        const float* __restrict__ dlogit, int B, int F, float alpha,
+                                                        float dscale, float dzero, __nv_bfloat16* __restrict__ dx,
+                                                        float* __restrict__ dw, float* __restrict__ db) {
+  const int g = blockIdx.x * 256 + threadIdx.x;
+  if (g == 0 && db) {
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dlogit[b];
+    db[0] += s;
+  }
+  if (g >= F / 8) return;
+  const float sc = wscale ? *wscale : 1.f;
+  const float4 wa = __ldg(reinterpret_cast<const float4*>(w) + 2 * g), wb = __ldg(reinterpret_cast<const float4*>(w) + 2 * g + 1);
+  const float wv[8] = {wa.x * sc, wa.y * sc, wa.z * sc, wa.w * sc, wb.x * sc, wb.y * sc, wb.z * sc, wb.w * sc};
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int b = 0; b < B; ++b) {
+    const float dl = __ldg(dlogit + b);
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + (size_t)b * F) + g);
+    const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+    float o[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float y0 = bf16_lo(w4[i]), y1 = bf16_hi(w4[i]);
+      acc[2 * i] += dl * y0;
+      acc[2 * i + 1] += dl * y1;
+      const float f0 = y0 > 0.f ? dscale : (y0 < 0.f ? alpha * dscale : dzero);
+      const float f1 = y1 > 0.f ? dscale : (y1 < 0.f ? alpha * dscale : dzero);
+      o[2 * i] = dl * wv[2 * i] * f0;
+      o[2 * i + 1] = dl * wv[2 * i + 1] * f1;
+    }
+    uint4 ov;
+    ov.x = pack_bf16x2(o[0], o[1]); ov.y = pack_bf16x2(o[2], o[3]);
+    ov.z = pack_bf16x2(o[4], o[5]); ov.w = pack_bf16x2(o[6], o[7]);
+    reinterpret_cast<uint4*>(dx + (size_t)b * F)[g] = ov;
+  }
+  if (dw) {
+    float4* dp = reinterpret_cast<float4*>(dw) + 2 * g;
+    float4 a = dp[0], c = dp[1];
+    a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
+    c.x += acc[4]; c.y += acc[5]; c.z += acc[6]; c.w += acc[7];
+    dp[0] = a;
+    dp[1] = c;
+  }
+}
+
+}  // namespace b2g
+
+using namespace b2g;
+
+extern "C" int b2g_dense_g_fwd(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
+                               void* out, int B, int F, b2g_stream_t stream_) {
+  if (!z || !W || !gamma || !beta || !out) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_fwd: null pointer");
+  if (F % 2) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_fwd: F must be even");
+  const int grid = (F / 2 + 127) / 128;
+  dense_g_fwd_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(z, W, gamma, beta, inv_std,
+                                                                            static_cast<__nv_bfloat16*>(out), B, F);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+extern "C" int b2g_dense_g_bwd(const float* z, const float* W, const float* gamma, float inv_std, const void* dq,
+                               float* dW, float* dgamma, float* dbeta, int B, int F, b2g_stream_t stream_) {
+  if (!z || !W || !gamma || !dq || !dW || !dgamma || !dbeta) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_bwd: null pointer");
+  if (F % 2) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_bwd: F must be even");
+  const int grid = (F / 2 + 127) / 128;
+  for (int b0 = 0; b0 < B; b0 += kDenseBC) {
+    dense_g_bwd_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
+        z, W, gamma, inv_std, static_cast<const __nv_bfloat16*>(dq), dW, dgamma, dbeta, B, F, b0, b0 > 0);
+    B2G_LAUNCH_CHECK();
+  }
+  return B2G_OK;
+}
+
+extern "C" int b2g_dhead_fwd_loss(const void* x, const float* w, const float* wscale, const float* bias, int B,
+                                  int F, int loss_kind, float label, float inv_batch, float* workspace,
+                                  int workspace_floats, float* logits, float* dlogit, float* loss_out,
+                                  b2g_stream_t stream_) {
+  if (!x || !w || !bias || !workspace || !logits || !dlogit || !loss_out)
+    return fail(B2G_E_INVALID_ARG, "b2g_dhead_fwd_loss: null pointer");
+  if (F % 8) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dhead_fwd_loss: F must be a multiple of 8");
+  int S = (4 * num_sms() + B - 1) / B;
+  if (S < 1) S = 1;
+  if (S > 64) S = 64;
+  if (workspace_floats < B * S) return fail(B2G_E_INVALID_ARG, "b2g_dhead_fwd_loss: workspace needs %d floats", B * S);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  dhead_partial_kernel<<<dim3(S, B), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), w, workspace, F, S);
+  B2G_LAUNCH_CHECK();
+  dhead_loss_kernel<<<1, 256, 0, stream>>>(workspace, S, wscale, bias, B, loss_kind, label, inv_batch, logits, dlogit,
+                                           loss_out);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+extern "C" int b2g_dhead_bwd(const void* x, const float* w, const float* wscale, const float* dlogit, int B, int F,
+                             float alpha, float dscale, float dzero, void* dx, float* dw, float* db,
+                             b2g_stream_t stream_) {
+  if (!x || !w || !dlogit || !dx) return fail(B2G_E_INVALID_ARG, "b2g_dhead_bwd: null pointer");
+  if (F % 8) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dhead_bwd: F must be a multiple of 8");
+  const int grid = (F / 8 + 255) / 256;
+  dhead_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(x), w, wscale, dlogit, B, F, alpha, dscale, dzero,
+      static_cast<__nv_bfloat16*>(dx), dw, db);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}

@@ -84,12 +84,43 @@ def _declare_rest(lib: C.CDLL) -> None:
         fn.argtypes = argtypes
 
 
+_P, _I, _F, _L, _U64 = C.c_void_p, C.c_int, C.c_float, C.c_long, C.c_ulonglong
 _EXTRA_SIGNATURES: dict[str, list] = {
-    "b2g_conv_wgrad": [C.POINTER(WgradArgs), C.c_void_p],
+    "b2g_conv_wgrad": [C.POINTER(WgradArgs), _P],
+    # in, w, wscale, bias, out, N, H, W, act, alpha, thresh8, seed, yprev, dact, stream
+    "b2g_conv3x3_c3_to_c64": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _I, _U64, _P, _I, _P],
+    # in, w, wscale, out, N, H, W, act, yprev, dact, stream
+    "b2g_conv3x3_c64_to_c3": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
+    # t3, t64, dw, dbias, N, H, W, stream
+    "b2g_wgrad3x3_c3_c64": [_P, _P, _P, _P, _I, _I, _I, _P],
+    # z, W, gamma, beta, inv_std, out, B, F, stream
+    "b2g_dense_g_fwd": [_P, _P, _P, _P, _F, _P, _I, _I, _P],
+    # z, W, gamma, inv_std, dq, dW, dgamma, dbeta, B, F, stream
+    "b2g_dense_g_bwd": [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _P],
+    # x, w, wscale, bias, B, F, loss_kind, label, inv_batch, ws, ws_floats, logits, dlogit, loss_out, stream
+    "b2g_dhead_fwd_loss": [_P, _P, _P, _P, _I, _I, _I, _F, _F, _P, _I, _P, _P, _P, _P],
+    # x, w, wscale, dlogit, B, F, alpha, dscale, dzero, dx, dw, db, stream
+    "b2g_dhead_bwd": [_P, _P, _P, _P, _I, _I, _F, _F, _F, _P, _P, _P, _P],
+    # w, g, m, v, n, lr_t, b1, b2, eps, gscale, stream
+    "b2g_adam": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _P],
+    # x, out, P, C, stream
+    "b2g_colsum_bf16": [_P, _P, _L, _I, _P],
+    # W, G, gamma, inv_std, dgamma, taps, Co, Ci, stream
+    "b2g_bn_fold_finalize": [_P, _P, _P, _F, _P, _I, _I, _I, _P],
+    # n, W**, u**, v_raw**, t_raw**, scal**, K*, C*, stream
+    "b2g_spectral_norm_multi": [_I, _P, _P, _P, _P, _P, _P, _P, _P],
+    # W, G, u, v_raw, scal, dot_scratch, K, C, stream
+    "b2g_sn_grad_finalize": [_P, _P, _P, _P, _P, _P, _I, _I, _P],
 }
 
 
-def check(rc: int, what: str) -> None:
+profile_sink = None  # when a list: ops.* append (kernel, flops, start_event, end_event) around tensor-core launches
+launch_count = 0  # kernels launched through this binding (bench.py reports it as gpu_launches)
+
+
+def check(rc: int, what: str, launches: int = 1) -> None:
+    global launch_count
+    launch_count += launches
     if rc != 0:
         msg = load().b2g_last_error()
         raise B200GanError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")

@@ -26,6 +26,22 @@ def _stream() -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def _prof_begin():
+    if _lib.profile_sink is None:
+        return None
+    ev = torch.cuda.Event(enable_timing=True)
+    ev.record()
+    return ev
+
+
+def _prof_end(ev, name, flops):
+    if ev is None:
+        return
+    end = torch.cuda.Event(enable_timing=True)
+    end.record()
+    _lib.profile_sink.append((name, flops, ev, end))
+
+
 def _need_cuda(*ts: torch.Tensor | None) -> None:
     for t in ts:
         if t is not None and not t.is_cuda:
@@ -80,7 +96,10 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                  dropout_thresh8=dropout_thresh8, dropout_seed=dropout_seed & 0xFFFFFFFFFFFFFFFF,
                  yprev=None if yprev is None else yprev.data_ptr(), dact=dact, dact_alpha=dact_alpha,
                  dact_scale=dact_scale, dact_zero=dact_zero)
+    ev = _prof_begin()
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
+    _prof_end(ev, "conv_igemm", 2.0 * n * h * w * cin * cout * (16 if kind == CONVT_K4S2 else taps) /
+              (4 if kind == CONV_K4S2 else 1))
     return out
 
 
@@ -101,5 +120,7 @@ def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: to
         raise B200GanError("conv_wgrad: bad dw size")
     a = WgradArgs(kind=kind, N=n, Hs=hs, Ws=ws, Ca=ca, Cb=cb, shifted=shifted.data_ptr(),
                   unshifted=unshifted.data_ptr(), dw=dw.data_ptr())
+    ev = _prof_begin()
     check(_lib.load().b2g_conv_wgrad(C.byref(a), _stream()), "b2g_conv_wgrad")
+    _prof_end(ev, "conv_wgrad", 2.0 * n * hg * wg * ca * cb * k * k)
     return dw

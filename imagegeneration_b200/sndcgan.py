@@ -1,0 +1,611 @@
+"""Host-side mirror of the reference's SNDCGAN API (sndcgan/SNDCGAN.py) driving the sm_100a kernels.
+
+Same names and call shapes as the reference so it is a drop-in for the training-step path:
+  make_dcgan_generator(output_size)                      SNDCGAN.py:25-66
+  make_dcgan_discriminator(dropout_rate, input_size)     SNDCGAN.py:69-128
+  SNDCGAN(...).train_step(input_real, input_z) -> 6-tuple SNDCGAN.py:241-269
+Models are callables `model(x, training=bool)` exposing `.trainable_variables` in Keras order and Keras
+layouts (Conv2D HWIO, Conv2DTranspose HWOI, Dense [in,out]); tensors are torch CUDA tensors, NHWC.
+
+Everything numerical happens in libb200gan.so (imagegeneration_b200/csrc); torch only owns device memory,
+streams and (for data parallel runs) the NCCL process group.  There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import lib as _lib
+from . import ops
+from .lib import ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K3S1, CONV_K4S2, CONVT_K4S2, B200GanError, check
+
+BN_EPS = 1e-3                    # Keras BatchNormalization default epsilon
+INV_STD = 1.0 / math.sqrt(1.0 + BN_EPS)   # inference BN with moving_var = 1
+LEAKY_ALPHA = 0.1                # SNDCGAN.py:77
+Z_SIZE = 128                     # Trainer.py:8
+
+_MASK64 = 0xFFFFFFFFFFFFFFFF
+
+
+def _splitmix64(x: int) -> int:
+    x = (x + 0x9E3779B97F4A7C15) & _MASK64
+    z = x
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _MASK64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _MASK64
+    return z ^ (z >> 31)
+
+
+def rate_to_thresh8(rate: float) -> int:
+    return max(0, min(255, int(round(rate * 256.0))))
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _glorot_uniform(shape, gen):
+    if len(shape) == 2:
+        fan_in, fan_out = shape
+    else:
+        rf = 1
+        for d in shape[:-2]:
+            rf *= d
+        fan_in, fan_out = shape[-2] * rf, shape[-1] * rf
+    limit = math.sqrt(6.0 / (fan_in + fan_out))
+    return ((torch.rand(shape, generator=gen, dtype=torch.float64) * 2 - 1) * limit).to(torch.float32)
+
+
+class ParamArena:
+    """All variables of one network in flat fp32 device buffers (weights, grads, Adam m and v) so that one
+    fused Adam launch and one NCCL all-reduce cover the whole network.  Variables are views into the arena."""
+
+    def __init__(self, shapes: list[tuple[str, tuple[int, ...]]], device):
+        self.names = [n for n, _ in shapes]
+        self.shapes = [s for _, s in shapes]
+        self.offsets = []
+        off = 0
+        for s in self.shapes:
+            self.offsets.append(off)
+            n = 1
+            for d in s:
+                n *= d
+            off += (n + 3) // 4 * 4
+        self.numel = off
+        self.w = torch.zeros(off, dtype=torch.float32, device=device)
+        self.g = torch.zeros(off, dtype=torch.float32, device=device)
+        self.m = torch.zeros(off, dtype=torch.float32, device=device)
+        self.v = torch.zeros(off, dtype=torch.float32, device=device)
+
+    def _views(self, flat):
+        out = []
+        for s, o in zip(self.shapes, self.offsets):
+            n = 1
+            for d in s:
+                n *= d
+            out.append(flat[o:o + n].view(s))
+        return out
+
+    @property
+    def variables(self):
+        return self._views(self.w)
+
+    @property
+    def grads(self):
+        return self._views(self.g)
+
+
+class Adam:
+    """tf.keras.optimizers.Adam(learning_rate) (SNDCGAN.py:165,168): beta 0.9/0.999, epsilon 1e-7."""
+
+    def __init__(self, learning_rate=0.001, beta_1=0.9, beta_2=0.999, epsilon=1e-7):
+        self.learning_rate = learning_rate
+        self.beta_1, self.beta_2, self.epsilon = beta_1, beta_2, epsilon
+        self.iterations = 0
+
+    def apply_arena(self, arena: ParamArena, gscale: float = 1.0) -> None:
+        self.iterations += 1
+        t = self.iterations
+        lr_t = self.learning_rate * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
+        check(_lib.load().b2g_adam(_p(arena.w), _p(arena.g), _p(arena.m), _p(arena.v), arena.numel, lr_t,
+                                   self.beta_1, self.beta_2, self.epsilon, gscale, _stream()), "b2g_adam")
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Generator  (SNDCGAN.py:25-66)
+# ----------------------------------------------------------------------------------------------------------
+class Generator:
+    name = "SNDC_Generator"
+
+    def __init__(self, output_size, device="cuda", seed=62):
+        self.output_size = tuple(output_size)
+        h, w, c = self.output_size
+        if c != 3 or h % 8 or w % 8:
+            raise B200GanError("generator needs an (H, W, 3) output with H, W divisible by 8")
+        self.h0, self.w0 = h // 8, w // 8
+        self.F = 512 * self.h0 * self.w0
+        self.device = torch.device(device)
+        shapes = [("dense/kernel", (Z_SIZE, self.F)), ("bn0/gamma", (self.F,)), ("bn0/beta", (self.F,)),
+                  ("convt1/kernel", (4, 4, 256, 512)), ("bn1/gamma", (256,)), ("bn1/beta", (256,)),
+                  ("convt2/kernel", (4, 4, 128, 256)), ("bn2/gamma", (128,)), ("bn2/beta", (128,)),
+                  ("convt3/kernel", (4, 4, 64, 128)), ("bn3/gamma", (64,)), ("bn3/beta", (64,)),
+                  ("convt4/kernel", (3, 3, 3, 64))]
+        self.arena = ParamArena(shapes, self.device)
+        gen = torch.Generator().manual_seed(seed)
+        for name, v in zip(self.arena.names, self.arena.variables):
+            if name.endswith("kernel"):
+                v.copy_(_glorot_uniform(tuple(v.shape), gen))
+            elif name.endswith("gamma"):
+                v.fill_(1.0)
+        self._inv_std = torch.full((1,), INV_STD, dtype=torch.float32, device=self.device)
+        self._wp_f = [None] * 3           # packed fprop weights
+        self._wp_d = [None] * 3           # packed dgrad weights
+        self._packed_dirty = True
+        self._bufs = {}
+        self._z = None
+
+    # -- Keras-like surface
+    @property
+    def trainable_variables(self):
+        return self.arena.variables
+
+    def set_weights(self, tensors):
+        for v, t in zip(self.arena.variables, tensors):
+            v.copy_(t.to(self.device, torch.float32))
+        self._packed_dirty = True
+
+    def __call__(self, z, training=False):
+        # BatchNorm runs in inference mode whatever `training` says: the moving statistics stay at (0, 1) in the
+        # reference because its train_step never passes training=True to the generator (SNDCGAN.py:243).
+        return self.forward(z)
+
+    # -- engine
+    def _buf(self, key, shape, dtype):
+        t = self._bufs.get(key)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = torch.empty(shape, dtype=dtype, device=self.device)
+            self._bufs[key] = t
+        return t
+
+    def repack(self):
+        v = self.arena.variables
+        for i, k in enumerate((3, 6, 9)):
+            gamma = v[k + 1]   # folded BatchNorm scale gamma * inv_std goes into the packed bf16 weights
+            self._wp_f[i] = ops.pack_conv_weight(CONVT_K4S2, v[k], n_is_d3=False, scale_scalar=self._inv_std,
+                                                 scale_d2=gamma, out=self._wp_f[i])
+            self._wp_d[i] = ops.pack_conv_weight(CONV_K4S2, v[k], n_is_d3=True, scale_scalar=self._inv_std,
+                                                 scale_d2=gamma, out=self._wp_d[i])
+        self._packed_dirty = False
+
+    def forward(self, z):
+        lib = _lib.load()
+        if z.dtype != torch.float32 or not z.is_cuda or z.shape[1] != Z_SIZE:
+            raise B200GanError("generator input must be a CUDA fp32 tensor [B, 128]")
+        z = z.contiguous()
+        if self._packed_dirty:
+            self.repack()
+        B = z.shape[0]
+        v = self.arena.variables
+        h0, w0 = self.h0, self.w0
+        a0 = self._buf("a0", (B, h0, w0, 512), torch.bfloat16)
+        check(lib.b2g_dense_g_fwd(_p(z), _p(v[0]), _p(v[1]), _p(v[2]), INV_STD, _p(a0), B, self.F, _stream()),
+              "b2g_dense_g_fwd")
+        acts = [a0]
+        x = a0
+        for i, k in enumerate((3, 6, 9)):
+            cout = v[k].shape[2]
+            out = self._buf(f"a{i + 1}", (B, x.shape[1] * 2, x.shape[2] * 2, cout), torch.bfloat16)
+            ops.conv_igemm(CONVT_K4S2, x, self._wp_f[i], out, bias=v[k + 2], act=ACT_RELU)
+            acts.append(out)
+            x = out
+        H, W, _ = self.output_size
+        g_out = self._buf("g_out", (B, H, W, 3), torch.float32)
+        check(lib.b2g_conv3x3_c64_to_c3(_p(x), _p(v[12]), None, _p(g_out), B, H, W, ACT_TANH, None, ACT_NONE,
+                                         _stream()), "b2g_conv3x3_c64_to_c3")
+        self._acts = acts
+        self._z = z
+        self.g_out = g_out
+        return g_out
+
+    def zero_grads(self):
+        # the dense kernel / bn0 gradients are overwritten by the stem backward; conv gradients are accumulated
+        tail = self.arena.offsets[3]
+        self.arena.g[tail:].zero_()
+
+    def backward(self, d_pre_tanh):
+        """d_pre_tanh: fp32 [B,H,W,3] = dL/d(convT4 output before tanh).  Fills arena.g."""
+        lib = _lib.load()
+        v, g = self.arena.variables, self.arena.grads
+        a0, a1, a2, a3 = self._acts
+        B, H, W, _ = d_pre_tanh.shape
+        self.zero_grads()
+        # convT4 (64 -> 3, k3 s1): wgrad + input gradient with ReLU' of a3
+        check(lib.b2g_wgrad3x3_c3_c64(_p(d_pre_tanh), _p(a3), _p(g[12]), None, B, H, W, _stream()),
+              "b2g_wgrad3x3_c3_c64")
+        dq = self._buf("dq3", tuple(a3.shape), torch.bfloat16)
+        check(lib.b2g_conv3x3_c3_to_c64(_p(d_pre_tanh), _p(v[12]), None, None, _p(dq), B, H, W, ACT_NONE, 0.0, 0, 0,
+                                         _p(a3), ACT_RELU, _stream()), "b2g_conv3x3_c3_to_c64")
+        acts_in = [a0, a1, a2]
+        for i in (2, 1, 0):
+            k = (3, 6, 9)[i]
+            x_in = acts_in[i]
+            cout, cin = v[k].shape[2], v[k].shape[3]
+            # beta gradient, raw weight gradient (w.r.t. the folded weight), then gamma gradient + rescale
+            check(lib.b2g_colsum_bf16(_p(dq), _p(g[k + 2]), dq.numel() // cout, cout, _stream()), "b2g_colsum_bf16")
+            ops.conv_wgrad(CONV_K4S2, dq, x_in, g[k])
+            check(lib.b2g_bn_fold_finalize(_p(v[k]), _p(g[k]), _p(v[k + 1]), INV_STD, _p(g[k + 1]), 16, cout, cin,
+                                           _stream()), "b2g_bn_fold_finalize")
+            dprev = self._buf(f"dq{i}", tuple(x_in.shape), torch.bfloat16)
+            ops.conv_igemm(CONV_K4S2, dq, self._wp_d[i], dprev, yprev=x_in, dact=ACT_RELU)
+            dq = dprev
+        check(lib.b2g_dense_g_bwd(_p(self._z), _p(v[0]), _p(v[1]), INV_STD, _p(dq), _p(g[0]), _p(g[1]), _p(g[2]),
+                                  B, self.F, _stream()), "b2g_dense_g_bwd", (B + 31) // 32)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Discriminator  (SNDCGAN.py:69-128)
+# ----------------------------------------------------------------------------------------------------------
+D_CONVS = [("conv1", 3, 1, 3, 64), ("conv2", 4, 2, 64, 128), ("conv3", 3, 1, 128, 128), ("conv4", 4, 2, 128, 256),
+           ("conv5", 3, 1, 256, 256), ("conv6", 4, 2, 256, 512), ("conv7", 3, 1, 512, 512)]
+
+
+class Discriminator:
+    name = "SNDC_Discriminator"
+
+    def __init__(self, dropout_rate, input_size, device="cuda", seed=63, spectral_norm=False):
+        self.input_size = tuple(input_size)
+        h, w, c = self.input_size
+        if c != 3 or h % 8 or w % 8:
+            raise B200GanError("discriminator needs an (H, W, 3) input with H, W divisible by 8")
+        self.dropout_rate = float(dropout_rate)
+        self.thresh8 = rate_to_thresh8(self.dropout_rate)
+        self.keep_scale = 256.0 / (256.0 - self.thresh8)
+        self.device = torch.device(device)
+        self.F = 512 * (h // 8) * (w // 8)
+        shapes = []
+        for name, k, _s, cin, cout in D_CONVS:
+            shapes += [(f"{name}/kernel", (k, k, cin, cout)), (f"{name}/bias", (cout,))]
+        shapes += [("dense/kernel", (self.F, 1)), ("dense/bias", (1,))]
+        self.arena = ParamArena(shapes, self.device)
+        gen = torch.Generator().manual_seed(seed)
+        for name, v in zip(self.arena.names, self.arena.variables):
+            if name.endswith("kernel"):
+                v.copy_(_glorot_uniform(tuple(v.shape), gen))
+        self._wp_f = [None] * 7
+        self._wp_d = [None] * 7
+        self._packed_dirty = True
+        self._bufs = {}
+        self.spectral_norm = bool(spectral_norm)
+        if self.spectral_norm:
+            self._init_sn(seed + 1)
+
+    # -- spectral norm state (north-star feature; absent from the reference)
+    def _init_sn(self, seed):
+        gen = torch.Generator().manual_seed(seed)
+        v = self.arena.variables
+        self.sn_u, self.sn_vraw, self.sn_traw, self.sn_scal = [], [], [], []
+        Ks, Cs = [], []
+        for i in range(8):
+            wt = v[2 * i]
+            cout = wt.shape[-1]
+            k = wt.numel() // cout
+            u = torch.randn(cout, generator=gen, dtype=torch.float64)
+            self.sn_u.append((u / u.norm()).to(torch.float32).to(self.device))
+            self.sn_vraw.append(torch.zeros(k, dtype=torch.float32, device=self.device))
+            self.sn_traw.append(torch.zeros(cout, dtype=torch.float32, device=self.device))
+            self.sn_scal.append(torch.zeros(4, dtype=torch.float32, device=self.device))
+            Ks.append(k)
+            Cs.append(cout)
+        arr = lambda ts: (C.c_void_p * 8)(*[t.data_ptr() for t in ts])
+        self._sn_args = (arr([v[2 * i] for i in range(8)]), arr(self.sn_u), arr(self.sn_vraw), arr(self.sn_traw),
+                         arr(self.sn_scal), (C.c_int * 8)(*Ks), (C.c_int * 8)(*Cs))
+        self._sn_K, self._sn_C = Ks, Cs
+        self._sn_dot = torch.zeros(1, dtype=torch.float32, device=self.device)
+
+    def sn_power_iteration(self):
+        a = self._sn_args
+        check(_lib.load().b2g_spectral_norm_multi(8, a[0], a[1], a[2], a[3], a[4], a[5], a[6], _stream()),
+              "b2g_spectral_norm_multi", 2)
+        self._packed_dirty = True
+
+    def _inv_sigma(self, i):
+        return self.sn_scal[i][2:3] if self.spectral_norm else None
+
+    # -- Keras-like surface
+    @property
+    def trainable_variables(self):
+        return self.arena.variables
+
+    def set_weights(self, tensors):
+        for v, t in zip(self.arena.variables, tensors):
+            v.copy_(t.to(self.device, torch.float32))
+        self._packed_dirty = True
+
+    def __call__(self, x, training=False, dropout_seeds=None):
+        """Keras-style call: returns the logits [B,1] (SNDCGAN.py:244,252,260)."""
+        if training and dropout_seeds is None and self.thresh8:
+            self._call_count = getattr(self, "_call_count", 0) + 1
+            dropout_seeds = [_splitmix64(0xD15C0000 + self._call_count * 8 + i) for i in range(7)]
+        self.forward(x, training=training, dropout_seeds=dropout_seeds)
+        _loss, logits = self.head_loss(0, 1.0, 1.0 / x.shape[0])
+        return logits.clone()
+
+    def _buf(self, key, shape, dtype):
+        t = self._bufs.get(key)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = torch.empty(shape, dtype=dtype, device=self.device)
+            self._bufs[key] = t
+        return t
+
+    def repack(self):
+        v = self.arena.variables
+        for i in range(1, 7):
+            _name, k, s, _ci, _co = D_CONVS[i]
+            sc = self._inv_sigma(i)
+            if s == 1:
+                self._wp_f[i] = ops.pack_conv_weight(CONV_K3S1, v[2 * i], n_is_d3=True, scale_scalar=sc,
+                                                     out=self._wp_f[i])
+                self._wp_d[i] = ops.pack_conv_weight(CONV_K3S1, v[2 * i], n_is_d3=False, flip=True, scale_scalar=sc,
+                                                     out=self._wp_d[i])
+            else:
+                self._wp_f[i] = ops.pack_conv_weight(CONV_K4S2, v[2 * i], n_is_d3=True, scale_scalar=sc,
+                                                     out=self._wp_f[i])
+                self._wp_d[i] = ops.pack_conv_weight(CONVT_K4S2, v[2 * i], n_is_d3=False, scale_scalar=sc,
+                                                     out=self._wp_d[i])
+        self._packed_dirty = False
+
+    def forward(self, x, training=False, dropout_seeds=None):
+        """x: fp32 CUDA [B,H,W,3].  With training=True dropout is active; `dropout_seeds` (7 ints) makes the
+        masks reproducible (tests regenerate them with oracle/dropout_hash.py)."""
+        lib = _lib.load()
+        if x.dtype != torch.float32 or not x.is_cuda or tuple(x.shape[1:]) != self.input_size:
+            raise B200GanError(f"discriminator input must be a CUDA fp32 tensor [B,{self.input_size}]")
+        x = x.contiguous()
+        if self.spectral_norm and training:
+            self.sn_power_iteration()
+        if self._packed_dirty:
+            self.repack()
+        B, H, W, _ = x.shape
+        v = self.arena.variables
+        t8 = self.thresh8 if training else 0
+        if t8 and dropout_seeds is None:
+            raise B200GanError("training-mode forward needs dropout_seeds")
+        seeds = dropout_seeds if t8 else [0] * 7
+        c1 = self._buf("c1", (B, H, W, 64), torch.bfloat16)
+        check(lib.b2g_conv3x3_c3_to_c64(_p(x), _p(v[0]), _p(self._inv_sigma(0)), _p(v[1]), _p(c1), B, H, W,
+                                         ACT_LEAKY, LEAKY_ALPHA, t8, seeds[0] & _MASK64, None, ACT_NONE, _stream()),
+              "b2g_conv3x3_c3_to_c64")
+        acts = [c1]
+        cur = c1
+        for i in range(1, 7):
+            _name, k, s, _ci, cout = D_CONVS[i]
+            out = self._buf(f"c{i + 1}", (B, cur.shape[1] // s, cur.shape[2] // s, cout), torch.bfloat16)
+            ops.conv_igemm(CONV_K3S1 if s == 1 else CONV_K4S2, cur, self._wp_f[i], out, bias=v[2 * i + 1],
+                           act=ACT_LEAKY, alpha=LEAKY_ALPHA, dropout_thresh8=t8, dropout_seed=seeds[i])
+            acts.append(out)
+            cur = out
+        self._x = x
+        self._acts = acts
+        self._train_fwd = bool(t8)
+        self._B = B
+        self.logits = self._buf("logits", (B, 1), torch.float32)
+        self._dlogit = self._buf("dlogit", (B,), torch.float32)
+        self._loss = torch.empty(2, dtype=torch.float32, device=self.device)  # fresh: returned to the caller
+        self._ws = self._buf("head_ws", (64 * B,), torch.float32)
+        self._head_pending = True
+        return self
+
+    def head_loss(self, loss_kind: int, label: float, inv_batch: float):
+        """Dense(1) + loss.  Returns (loss scalar tensor, logits [B,1])."""
+        v = self.arena.variables
+        check(_lib.load().b2g_dhead_fwd_loss(_p(self._acts[6]), _p(v[14]), _p(self._inv_sigma(7)), _p(v[15]),
+                                             self._B, self.F, loss_kind, label, inv_batch, _p(self._ws),
+                                             self._ws.numel(), _p(self.logits), _p(self._dlogit), _p(self._loss),
+                                             _stream()), "b2g_dhead_fwd_loss", 2)
+        return self._loss[0], self.logits
+
+    def backward(self, need_wgrad: bool, need_input_grad: bool, g_out=None):
+        """Backward from the dlogit of the last head_loss.  need_wgrad fills arena.g (zeroed first);
+        need_input_grad returns dL/d(pre-tanh generator output) fp32 [B,H,W,3] (uses tanh'(g_out))."""
+        lib = _lib.load()
+        v, g = self.arena.variables, self.arena.grads
+        acts = self._acts
+        B = self._B
+        dscale = self.keep_scale if self._train_fwd else 1.0
+        dzero = 0.0 if self._train_fwd else LEAKY_ALPHA
+        if need_wgrad:
+            self.arena.g.zero_()
+        c7 = acts[6]
+        dpre = self._buf("dpre7", tuple(c7.shape), torch.bfloat16)
+        check(lib.b2g_dhead_bwd(_p(c7), _p(v[14]), _p(self._inv_sigma(7)), _p(self._dlogit), B, self.F, LEAKY_ALPHA,
+                                dscale, dzero, _p(dpre), _p(g[14]) if need_wgrad else None,
+                                _p(g[15]) if need_wgrad else None, _stream()), "b2g_dhead_bwd")
+        for i in range(6, 0, -1):
+            _name, k, s, _ci, cout = D_CONVS[i]
+            x_in = acts[i - 1]
+            if need_wgrad:
+                check(lib.b2g_colsum_bf16(_p(dpre), _p(g[2 * i + 1]), dpre.numel() // cout, cout, _stream()),
+                      "b2g_colsum_bf16")
+                ops.conv_wgrad(CONV_K3S1 if s == 1 else CONV_K4S2, x_in, dpre, g[2 * i])
+            dprev = self._buf(f"dpre{i}", tuple(x_in.shape), torch.bfloat16)
+            ops.conv_igemm(CONV_K3S1 if s == 1 else CONVT_K4S2, dpre, self._wp_d[i], dprev, yprev=x_in,
+                           dact=ACT_LEAKY, dact_alpha=LEAKY_ALPHA, dact_scale=dscale, dact_zero=dzero)
+            dpre = dprev
+        H, W = self.input_size[0], self.input_size[1]
+        if need_wgrad:
+            check(lib.b2g_wgrad3x3_c3_c64(_p(self._x), _p(dpre), _p(g[0]), _p(g[1]), B, H, W, _stream()),
+                  "b2g_wgrad3x3_c3_c64")
+            if self.spectral_norm:
+                for i in range(8):
+                    check(lib.b2g_sn_grad_finalize(_p(v[2 * i]), _p(g[2 * i]), _p(self.sn_u[i]), _p(self.sn_vraw[i]),
+                                                   _p(self.sn_scal[i]), _p(self._sn_dot), self._sn_K[i],
+                                                   self._sn_C[i], _stream()), "b2g_sn_grad_finalize", 3)
+        d_in = None
+        if need_input_grad:
+            d_in = self._buf("d_in", (B, H, W, 3), torch.float32)
+            check(lib.b2g_conv3x3_c64_to_c3(_p(dpre), _p(v[0]), _p(self._inv_sigma(0)), _p(d_in), B, H, W, ACT_NONE,
+                                             _p(g_out), ACT_TANH if g_out is not None else ACT_NONE, _stream()),
+                  "b2g_conv3x3_c64_to_c3")
+        return d_in
+
+
+def make_dcgan_generator(output_size, device="cuda", seed=62) -> Generator:
+    """sndcgan/SNDCGAN.py:25."""
+    return Generator(output_size, device=device, seed=seed)
+
+
+def make_dcgan_discriminator(dropout_rate, input_size, device="cuda", seed=63, spectral_norm=False) -> Discriminator:
+    """sndcgan/SNDCGAN.py:69."""
+    return Discriminator(dropout_rate, input_size, device=device, seed=seed, spectral_norm=spectral_norm)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# SNDCGAN: state + train_step  (SNDCGAN.py:148-269)
+# ----------------------------------------------------------------------------------------------------------
+LOSS_BCE, LOSS_HINGE_D, LOSS_HINGE_G = 0, 1, 2
+
+
+class SNDCGANEngine:
+    """Models, optimizers and the exact step ordering of SNDCGAN.train_step (SNDCGAN.py:241-269), without the
+    reference's filesystem / dataset side effects (those live in trainer.SNDCGAN, which subclasses this)."""
+
+    def __init__(self, batch_size, dropout=0.5, learning_rate_disc=2e-4, learning_rate_gen=2e-4,
+                 image_size=(144, 256, 3), z_size=Z_SIZE, device="cuda", seed=62, spectral_norm=False, loss="bce",
+                 process_group=None):
+        if z_size != Z_SIZE:
+            raise B200GanError("z_size must be 128 (sndcgan/Trainer.py:8)")
+        if loss not in ("bce", "hinge"):
+            raise B200GanError("loss must be 'bce' (reference) or 'hinge'")
+        _lib.load()
+        self.batch_size = batch_size
+        self.z_size = z_size
+        self.image_size = tuple(image_size)
+        self.device = torch.device(device)
+        self.loss = loss
+        self.gen_model = make_dcgan_generator(output_size=image_size, device=device, seed=seed)          # :164
+        self.g_optimizer = Adam(learning_rate=learning_rate_gen)                                         # :165
+        self.disc_model = make_dcgan_discriminator(dropout, input_size=image_size, device=device, seed=seed + 1,
+                                                   spectral_norm=spectral_norm)                          # :167
+        self.d_optimizer = Adam(learning_rate=learning_rate_disc)                                        # :168
+        self.seed = seed
+        self.step_count = 0
+        self.pg = process_group
+        self.world = 1
+        self.rank = 0
+        if process_group is not None:
+            import torch.distributed as dist
+            self.world = dist.get_world_size(process_group)
+            self.rank = dist.get_rank(process_group)
+            # identical initial weights on every rank
+            dist.broadcast(self.gen_model.arena.w, src=0, group=process_group)
+            dist.broadcast(self.disc_model.arena.w, src=0, group=process_group)
+            self.gen_model._packed_dirty = True
+            self.disc_model._packed_dirty = True
+        self.gpu_launches = 0
+
+    def _dropout_seeds(self, pass_idx: int):
+        base = (self.seed * 0x1000003 + self.rank * 0x10001 + 1) & _MASK64
+        return [_splitmix64(base ^ ((self.step_count * 3 + pass_idx) * 8 + layer)) for layer in range(7)]
+
+    def _allreduce(self, flat, async_op=False):
+        if self.world == 1:
+            return None
+        import torch.distributed as dist
+        return dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.pg, async_op=async_op)
+
+    def train_step(self, input_real, input_z, dropout_seeds=None):
+        """One G update + two D updates, in the reference's order (SNDCGAN.py:241-269).
+
+        Returns (g_loss, d_loss, d_loss_real, d_loss_fake, d_logits_real, d_logits_fake) as CUDA tensors.
+        dropout_seeds: optional (seeds_a, seeds_b, seeds_c), 7 ints each, for reproducible masks."""
+        G, D = self.gen_model, self.disc_model
+        B = input_real.shape[0]
+        inv_b = 1.0 / B
+        gs = 1.0 / self.world
+        sa, sb, sc = dropout_seeds if dropout_seeds is not None else [self._dropout_seeds(i) for i in range(3)]
+        g_kind = LOSS_BCE if self.loss == "bce" else LOSS_HINGE_G
+        d_kind = LOSS_BCE if self.loss == "bce" else LOSS_HINGE_D
+
+        # (1) generator step (:242-249)
+        g_output = G.forward(input_z)                                               # :243
+        D.forward(g_output, training=True, dropout_seeds=sa)                        # :244
+        g_loss, _ = D.head_loss(g_kind, 1.0, inv_b)                                 # :245-246
+        d_gout = D.backward(need_wgrad=False, need_input_grad=True, g_out=g_output)
+        G.backward(d_gout)                                                          # :248
+        g_work = self._allreduce(G.arena.g, async_op=True)
+        # G's Adam (:249) is issued at the end of the step: nothing below reads the generator's weights, so the
+        # result is identical and its gradient all-reduce overlaps both discriminator steps.
+
+        # (2) discriminator step on the real batch (:251-257)
+        D.forward(input_real, training=True, dropout_seeds=sb)                      # :252
+        d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b)                # :253-254
+        d_logits_real = d_logits_real.clone()
+        D.backward(need_wgrad=True, need_input_grad=False)                          # :256
+        self._allreduce(D.arena.g)
+        self.d_optimizer.apply_arena(D.arena, gs)                                   # :257
+        D._packed_dirty = True
+
+        # (3) discriminator step on the stale fake batch (:259-267)
+        D.forward(g_output, training=True, dropout_seeds=sc)                        # :260
+        d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)                # :261-262
+        D.backward(need_wgrad=True, need_input_grad=False)                          # :266
+        self._allreduce(D.arena.g)
+        self.d_optimizer.apply_arena(D.arena, gs)                                   # :267
+        D._packed_dirty = True
+
+        if g_work is not None:
+            g_work.wait()
+        self.g_optimizer.apply_arena(G.arena, gs)                                   # :249 (deferred)
+        G._packed_dirty = True
+
+        d_loss = d_loss_fake + d_loss_real                                          # :264
+        self.step_count += 1
+        return (g_loss, d_loss, d_loss_real, d_loss_fake, d_logits_real, d_logits_fake)
+
+
+def create_samples(g_model: Generator, input_z, batch_size):
+    """sndcgan/generator_output.py:25-28: G(z, training=False) -> reshape (B,H,W,3) -> (x+1)/2."""
+    g_output = g_model(input_z, training=False)
+    images = g_output.reshape(batch_size, *g_model.output_size)
+    return (images + 1) / 2.0
+
+
+class DeviceFeeder:
+    """Double-buffered host -> device staging of (input_real, input_z) batches on a copy stream — the analogue of
+    the reference's `train_ds.prefetch(AUTOTUNE)` (SNDCGAN.py:143): batch i+1 is copied while step i computes."""
+
+    def __init__(self, batch_size, image_size=(144, 256, 3), z_size=Z_SIZE, device="cuda"):
+        self.device = torch.device(device)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.real = [torch.empty((batch_size, *image_size), dtype=torch.float32, device=self.device) for _ in range(2)]
+        self.z = [torch.empty((batch_size, z_size), dtype=torch.float32, device=self.device) for _ in range(2)]
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.free = [torch.cuda.Event(), torch.cuda.Event()]
+        self.put_idx = 0
+        self.get_idx = 0
+        self.bytes_per_batch = self.real[0].numel() * 4 + self.z[0].numel() * 4
+
+    def put(self, real_host: torch.Tensor, z_host: torch.Tensor) -> None:
+        """Start the asynchronous copy of one (pinned) host batch into the next staging slot."""
+        i = self.put_idx
+        self.put_idx ^= 1
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.free[i])      # the step that last used this slot has been issued
+            self.real[i].copy_(real_host, non_blocking=True)
+            self.z[i].copy_(z_host, non_blocking=True)
+            self.ready[i].record(self.copy_stream)
+
+    def get(self):
+        """Device tensors of the oldest pending batch; the compute stream waits for its copy."""
+        i = self.get_idx
+        self.get_idx ^= 1
+        torch.cuda.current_stream().wait_event(self.ready[i])
+        return self.real[i], self.z[i], i
+
+    def release(self, i: int) -> None:
+        self.free[i].record(torch.cuda.current_stream())

@@ -107,6 +107,64 @@ typedef struct b2g_wgrad_args {
 
 int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream);
 
+/* ---- 3-channel edge layers (direct convolutions; HBM / CUDA-core bound) ---------------------------------
+ * w is the fp32 Keras kernel [3][3][3][64] of either D.conv1 (Conv2D HWIO, SNDCGAN.py:73-76) or G.convT4
+ * (Conv2DTranspose HWOI with 3 filters, :57-61); wscale (device scalar or NULL) multiplies it (1/sigma).
+ *   c3_to_c64 : out bf16 [N,H,W,64] = act(conv3x3(in fp32 [N,H,W,3]) + bias) [dropout] [* relu'(yprev)]
+ *               -> D.conv1 forward (act=LEAKY, dropout) and G.convT4 input-gradient (dact=RELU, yprev=a3).
+ *   c64_to_c3 : out fp32 [N,H,W,3] = act(flipped conv3x3(in bf16 [N,H,W,64])) [* tanh'(yprev fp32)]
+ *               -> G.convT4 forward (act=TANH) and D.conv1 input-gradient (dact=TANH, yprev=g_output).
+ *   wgrad     : dw[27][64] += sum_pix t3[pix+tap][c3] * t64[pix][c64]; dbias[64] += sum_pix t64 (or NULL)
+ *               -> D.conv1 (t3 = images, t64 = dY) and G.convT4 (t3 = dY fp32, t64 = layer input a3). */
+int b2g_conv3x3_c3_to_c64(const float* in, const float* w, const float* wscale, const float* bias, void* out, int N,
+                          int H, int W, int act, float alpha, int dropout_thresh8, unsigned long long dropout_seed,
+                          const void* yprev, int dact, b2g_stream_t stream);
+int b2g_conv3x3_c64_to_c3(const void* in, const float* w, const float* wscale, float* out, int N, int H, int W,
+                          int act, const float* yprev, int dact, b2g_stream_t stream);
+int b2g_wgrad3x3_c3_c64(const float* t3, const void* t64, float* dw, float* dbias, int N, int H, int W,
+                        b2g_stream_t stream);
+
+/* ---- generator stem: Dense(128->F, no bias) + inference BatchNorm + ReLU (SNDCGAN.py:31-34) ------------
+ * fwd: out bf16 [B,F] = relu(gamma*inv_std * (z W) + beta).   bwd: from dq bf16 [B,F] (= dL/d(BN output),
+ * ReLU' already applied) computes dW [128,F], dgamma [F], dbeta [F] (overwritten). */
+int b2g_dense_g_fwd(const float* z, const float* W, const float* gamma, const float* beta, float inv_std, void* out,
+                    int B, int F, b2g_stream_t stream);
+int b2g_dense_g_bwd(const float* z, const float* W, const float* gamma, float inv_std, const void* dq, float* dW,
+                    float* dgamma, float* dbeta, int B, int F, b2g_stream_t stream);
+
+/* ---- discriminator head: Flatten + Dense(1) (SNDCGAN.py:122-123) fused with the loss (:170) ------------
+ * fwd_loss: logits[b] = wscale * <x[b,:], w> + bias; loss_kind 0 = BCE-with-logits vs `label`,
+ *           1 = D hinge, 2 = G hinge; loss_out[0] = inv_batch*sum loss, loss_out[1] = inv_batch*sum sigmoid(x);
+ *           dlogit[b] = inv_batch * dloss/dlogit.  workspace: >= 64*B floats.
+ * bwd:      dx bf16 [B,F] = dlogit[b]*wscale*w[j]*act'(x[b,j]) (LeakyReLU/Dropout derivative of conv7 from its
+ *           saved output x); dw[j] += sum_b dlogit[b]*x[b,j]; db += sum_b dlogit[b]  (dw/db may be NULL). */
+int b2g_dhead_fwd_loss(const void* x, const float* w, const float* wscale, const float* bias, int B, int F,
+                       int loss_kind, float label, float inv_batch, float* workspace, int workspace_floats,
+                       float* logits, float* dlogit, float* loss_out, b2g_stream_t stream);
+int b2g_dhead_bwd(const void* x, const float* w, const float* wscale, const float* dlogit, int B, int F, float alpha,
+                  float dscale, float dzero, void* dx, float* dw, float* db, b2g_stream_t stream);
+
+/* ---- parameter-side kernels -------------------------------------------------------------------------------
+ * adam: Keras-2 Adam on a flat fp32 arena (all variables of one network): one launch per apply_gradients
+ *       (SNDCGAN.py:249,:257,:267).  lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is computed by the caller; g is
+ *       multiplied by gscale first (1/world_size after a sum all-reduce).
+ * colsum_bf16: out[c] += sum_p x[p][c] (BiasAddGrad / BatchNorm-beta gradient).
+ * bn_fold_finalize: Conv2DTranspose kernel W[taps][Co][Ci] whose forward used W*gamma[co]*inv_std:
+ *       dgamma[co] = inv_std*sum W*G, then G *= gamma[co]*inv_std in place.
+ * spectral_norm_multi: one power iteration for up to 8 matrices W_l [K_l][C_l] reading each W once;
+ *       scal_l = {scratch, sigma, 1/sigma, |W u|}; t_raw_l / scal_l[0] must be zero on first use.
+ * sn_grad_finalize: G <- G/sigma - (<G,W>/sigma^2) v u^T in place (gradient through W/sigma). */
+int b2g_adam(float* w, const float* g, float* m, float* v, long n, float lr_t, float beta1, float beta2, float eps,
+             float gscale, b2g_stream_t stream);
+int b2g_colsum_bf16(const void* x, float* out, long P, int C, b2g_stream_t stream);
+int b2g_bn_fold_finalize(const float* W, float* G, const float* gamma, float inv_std, float* dgamma, int taps, int Co,
+                         int Ci, b2g_stream_t stream);
+int b2g_spectral_norm_multi(int n_layers, const float* const* W, float* const* u, float* const* v_raw,
+                            float* const* t_raw, float* const* scal, const int* K, const int* C,
+                            b2g_stream_t stream);
+int b2g_sn_grad_finalize(const float* W, float* G, const float* u, const float* v_raw, const float* scal,
+                         float* dot_scratch, int K, int C, b2g_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,20 +73,63 @@ def init_vars(shapes, seed: int, dtype=torch.float32) -> list[torch.Tensor]:
 
 
 # ----------------------------------------------------------------------------------------------------------
+# optional emulation of the CUDA path's storage precision (bf16 activations / activation gradients, bf16
+# packed conv weights with the BatchNorm / spectral-norm scale folded in, fp32 accumulation and master weights).
+# With emu=False (default) the oracle is the plain fp32/fp64 restatement of the reference.
+# ----------------------------------------------------------------------------------------------------------
+class _QAct(torch.autograd.Function):
+    """round to bf16 in forward (stored activation) and in backward (stored activation gradient)"""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(g.dtype)
+
+
+class _QW(torch.autograd.Function):
+    """round a (folded) weight to bf16 in forward; straight-through in backward (fp32 weight gradients)"""
+
+    @staticmethod
+    def forward(ctx, w):
+        return w.to(torch.bfloat16).to(w.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def _qa(x, emu):
+    return _QAct.apply(x) if emu else x
+
+
+def _qw(w, emu):
+    return _QW.apply(w) if emu else w
+
+
+# ----------------------------------------------------------------------------------------------------------
 # forward passes
 # ----------------------------------------------------------------------------------------------------------
-def generator_forward(gv: list[torch.Tensor], z: torch.Tensor, image_size=(144, 256, 3), collect: dict | None = None):
+def generator_forward(gv: list[torch.Tensor], z: torch.Tensor, image_size=(144, 256, 3), collect: dict | None = None,
+                      emu: bool = False):
     """SNDCGAN.py:28-61 with BatchNorm in INFERENCE mode (moving mean 0 / var 1): train_step calls
     self.gen_model(input_z) without training=True (:243) and create_samples passes training=False."""
     h, w = image_size[0] // 8, image_size[1] // 8
     x = K.dense(z, gv[0])
-    x = torch.relu(K.batchnorm_inference(x, gv[1], gv[2]))
+    x = _qa(torch.relu(K.batchnorm_inference(x, gv[1], gv[2])), emu)
     x = x.reshape(-1, h, w, 512)                                        # :34 row-major NHWC
     if collect is not None:
         collect["g_a0"] = x
     for i, (kidx, stride) in enumerate([(3, 2), (6, 2), (9, 2)]):
-        x = K.conv2d_transpose_same(x, gv[kidx], stride)
-        x = torch.relu(K.batchnorm_inference(x, gv[kidx + 1], gv[kidx + 2]))
+        if emu:  # same math, BatchNorm scale folded into the bf16 weight like the CUDA path
+            gs = gv[kidx + 1] / math.sqrt(1.0 + K.BN_EPS)
+            x = K.conv2d_transpose_same(x, _qw(gv[kidx] * gs[None, None, :, None], True), stride) + gv[kidx + 2]
+            x = _qa(torch.relu(x), True)
+        else:
+            x = K.conv2d_transpose_same(x, gv[kidx], stride)
+            x = torch.relu(K.batchnorm_inference(x, gv[kidx + 1], gv[kidx + 2]))
         if collect is not None:
             collect[f"g_a{i + 1}"] = x
     x = torch.tanh(K.conv2d_transpose_same(x, gv[12], 1))              # :57-61
@@ -96,7 +139,8 @@ def generator_forward(gv: list[torch.Tensor], z: torch.Tensor, image_size=(144, 
 
 
 def discriminator_forward(dv: list[torch.Tensor], x: torch.Tensor, rate: float, masks: list | None,
-                          collect: dict | None = None, sn_state: list | None = None, tag: str = "d"):
+                          collect: dict | None = None, sn_state: list | None = None, tag: str = "d",
+                          emu: bool = False):
     """SNDCGAN.py:70-124 with training=True dropout given as explicit keep masks (one per conv, or None).
 
     sn_state (optional, NOT in the reference): list of 8 persistent `u` vectors; when given, every kernel is
@@ -114,9 +158,9 @@ def discriminator_forward(dv: list[torch.Tensor], x: torch.Tensor, rate: float, 
         return wt / sigma
 
     for i, (_name, _k, stride, _ci, _co) in enumerate(D_CONVS):
-        x = K.conv2d_same(x, eff(i, dv[2 * i]), dv[2 * i + 1], stride)
+        x = K.conv2d_same(x, _qw(eff(i, dv[2 * i]), emu and i > 0), dv[2 * i + 1], stride)
         x = K.leaky_relu(x)
-        x = K.dropout(x, None if masks is None else masks[i], rate)
+        x = _qa(K.dropout(x, None if masks is None else masks[i], rate), emu)
         if collect is not None:
             collect[f"{tag}_c{i + 1}"] = x
     x = x.reshape(x.shape[0], -1)                                       # Flatten :122
@@ -169,7 +213,8 @@ class OracleSNDCGAN:
     """State + train_step of the reference's SNDCGAN class (model/optimizer part of SNDCGAN.py:149-170)."""
 
     def __init__(self, image_size=(144, 256, 3), dropout=0.5, lr_d=2e-4, lr_g=2e-4, seed=62,
-                 dtype=torch.float32, loss="bce", spectral_norm=False):
+                 dtype=torch.float32, loss="bce", spectral_norm=False, emu=False):
+        self.emu = emu
         self.image_size = tuple(image_size)
         self.dropout = dropout
         self.loss = loss
@@ -193,8 +238,9 @@ class OracleSNDCGAN:
         for p in gv + dv:
             p.requires_grad_(True)
         # (1) generator step, :242-249
-        g_output = generator_forward(gv, input_z, self.image_size, collect)
-        d_logits_fake = discriminator_forward(dv, g_output, self.dropout, masks_a, collect, self.sn_state, "da")
+        g_output = generator_forward(gv, input_z, self.image_size, collect, self.emu)
+        d_logits_fake = discriminator_forward(dv, g_output, self.dropout, masks_a, collect, self.sn_state, "da",
+                                              self.emu)
         g_loss = g_loss_fn(self.loss, d_logits_fake)
         g_grads = torch.autograd.grad(g_loss, gv)
         g_output = g_output.detach()
@@ -202,14 +248,16 @@ class OracleSNDCGAN:
             collect["g_grads"] = [g.clone() for g in g_grads]
         self.g_opt.apply(gv, g_grads)
         # (2) discriminator step on real, :251-257
-        d_logits_real = discriminator_forward(dv, input_real, self.dropout, masks_b, collect, self.sn_state, "db")
+        d_logits_real = discriminator_forward(dv, input_real, self.dropout, masks_b, collect, self.sn_state, "db",
+                                              self.emu)
         d_loss_real = d_loss_fn(self.loss, d_logits_real, 1.0)
         d_grads1 = torch.autograd.grad(d_loss_real, dv)
         if collect is not None:
             collect["d_grads1"] = [g.clone() for g in d_grads1]
         self.d_opt.apply(dv, d_grads1)
         # (3) discriminator step on the stale fake batch, :259-267
-        d_logits_fake2 = discriminator_forward(dv, g_output, self.dropout, masks_c, collect, self.sn_state, "dc")
+        d_logits_fake2 = discriminator_forward(dv, g_output, self.dropout, masks_c, collect, self.sn_state, "dc",
+                                               self.emu)
         d_loss_fake = d_loss_fn(self.loss, d_logits_fake2, 0.0)
         d_loss = d_loss_fake + d_loss_real                               # :264
         d_grads2 = torch.autograd.grad(d_loss_fake, dv)
