@@ -35,16 +35,21 @@ int num_sms() {
 }
 
 // One thread per packed element: wpacked[ph][n][tap*Ck + c] (bf16) <- w[ky][kx][d2][d3] (fp32) * scales.
-__global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip,
+__global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
                                         const float* __restrict__ w, const float* __restrict__ scale_scalar,
                                         const float* __restrict__ scale_d2, const float* __restrict__ scale_d3,
                                         __nv_bfloat16* __restrict__ out, int phases, int taps, long total) {
   const int Cn = n_is_d3 ? D3 : D2;  // GEMM-N channels
-  const int Ck = n_is_d3 ? D2 : D3;  // GEMM-K channels per tap
+  const int Ckr = n_is_d3 ? D2 : D3;      // real GEMM-K channels per tap
+  const int Ck = ck_pad > Ckr ? ck_pad : Ckr;  // stored (zero padded) extent
   const float s0 = scale_scalar ? *scale_scalar : 1.f;
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int c = (int)(i % Ck);
     long r = i / Ck;
+    if (c >= Ckr) {
+      out[i] = __float2bfloat16_rn(0.f);
+      continue;
+    }
     const int tap = (int)(r % taps);
     r /= taps;
     const int n = (int)(r % Cn);
@@ -78,7 +83,8 @@ using namespace b2g;
 extern "C" int b2g_version(void) { return 100; }
 extern "C" const char* b2g_last_error(void) { return error_buffer(); }
 
-extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, const float* w,
+extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
+                                    const float* w,
                                     const float* scale_scalar, const float* scale_d2, const float* scale_d3,
                                     void* wpacked, b2g_stream_t stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -87,6 +93,9 @@ extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, in
   if (kind == B2G_CONV_K3S1) {
     if (kh != 3 || kw != 3) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: K3S1 needs a 3x3 kernel");
     phases = 1; taps = 9;
+  } else if (kind == B2G_CONV_K1S1) {
+    if (kh != 1 || kw != 1 || flip) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: K1S1 needs 1x1, no flip");
+    phases = 1; taps = 1;
   } else if (kind == B2G_CONV_K4S2) {
     if (kh != 4 || kw != 4 || flip) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: K4S2 needs 4x4, no flip");
     phases = 1; taps = 16;
@@ -96,11 +105,13 @@ extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, in
   } else {
     return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: unknown kind %d", kind);
   }
-  const long total = (long)phases * taps * D2 * D3;
+  const int ckr = n_is_d3 ? D2 : D3, cn = n_is_d3 ? D3 : D2;
+  const int ck = ck_pad > ckr ? ck_pad : ckr;
+  const long total = (long)phases * taps * cn * ck;
   const int threads = 256;
   long blocks = (total + threads - 1) / threads;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  pack_conv_weight_kernel<<<(int)blocks, threads, 0, stream>>>(kind, kh, kw, D2, D3, n_is_d3, flip, w, scale_scalar,
+  pack_conv_weight_kernel<<<(int)blocks, threads, 0, stream>>>(kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, w, scale_scalar,
                                                                 scale_d2, scale_d3,
                                                                 static_cast<__nv_bfloat16*>(wpacked), phases, taps, total);
   B2G_LAUNCH_CHECK();

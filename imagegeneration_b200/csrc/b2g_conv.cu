@@ -30,6 +30,9 @@ struct alignas(64) ConvKernelParams {
   uint32_t seed_lo, seed_hi;
   int dact;
   float dact_alpha, dact_scale, dact_zero;
+  int out_f32;     // narrow fp32 output: `cs` real channels, out/yprev are float [pixels][cs]
+  int cs;          // channel stride of the output tensor (== plan.Cout unless out_f32)
+  int brows;       // rows of the packed weight matrix per phase
 };
 
 template <int BLOCK_N>
@@ -39,7 +42,7 @@ struct ConvCfg {
   static constexpr int kBBytes = BLOCK_N * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8);
-  static constexpr int kTmemCols = 2 * BLOCK_N;  // 128 / 256 / 512: powers of two >= 32
+  static constexpr int kTmemCols = 2 * BLOCK_N;  // 64 / 128 / 256 / 512: powers of two >= 32
   static constexpr int kBarBytes = 256;
   static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // +1024: manual alignment
 };
@@ -108,7 +111,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const TileCoord tc = decode_tile(pl, p.n_tiles, tile);
         const int w0 = tc.tw * pl.bw, h0 = tc.th * pl.bh, n0 = tc.tn * pl.bn;
-        const int brow = tc.phase * pl.Cout + tc.n_tile * BLOCK_N;
+        const int brow = tc.phase * p.brows + tc.n_tile * BLOCK_N;
         for (int ks = 0; ks < k_steps; ++ks) {
           const int tap = ks / p.cin_chunks;
           const int chunk = ks - tap * p.cin_chunks;
@@ -175,9 +178,30 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t r[32];
+        __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
         const int cb = col0 + c * 32;
+        if (p.out_f32) {  // narrow fp32 output (3 real channels): tanh / tanh' epilogues of the generator's last layer
+          if (valid && cb < p.cs) {
+            float* of = reinterpret_cast<float*>(p.out) + pix * p.cs + cb;
+            const float* yf = reinterpret_cast<const float*>(p.yprev) + pix * p.cs + cb;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (cb + j < p.cs) {
+                float o = __uint_as_float(r[j]);
+                if (p.bias) o += __ldg(p.bias + cb + j);
+                if (p.act == B2G_ACT_TANH) o = tanhf(o);
+                if (p.dact == B2G_ACT_TANH) {
+                  const float y = __ldg(yf + j);
+                  o *= 1.f - y * y;
+                }
+                of[j] = o;
+              }
+            }
+          }
+          continue;
+        }
         const size_t off = pix * pl.Cout + cb;  // element offset of this thread's 32 outputs
         float v[32];
 #pragma unroll
@@ -283,7 +307,15 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!a || !a->in || !a->wpacked || !a->out) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: null pointer");
   if (a->Cin % 64 || a->Cin <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cin=%d not a multiple of 64", a->Cin);
-  if (a->Cout % 64 || a->Cout <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cout=%d not a multiple of 64", a->Cout);
+  if (a->out_f32) {
+    if (a->Cout != 32 || a->cout_store < 1 || a->cout_store > 8 || a->kind == B2G_CONVT_K4S2)
+      return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: fp32 narrow output needs Cout=32, 1<=cout_store<=8, 1 phase");
+    if (a->dropout_thresh8 || (a->act != B2G_ACT_NONE && a->act != B2G_ACT_TANH) ||
+        (a->dact != B2G_ACT_NONE && a->dact != B2G_ACT_TANH))
+      return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: fp32 narrow output supports bias/tanh/tanh' epilogues only");
+  } else if (a->Cout % 64 || a->Cout <= 0) {
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cout=%d not a multiple of 64", a->Cout);
+  }
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
 
@@ -292,7 +324,10 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   if (!build_conv_plan(a->kind, a->N, a->Hin, a->Win, a->Cin, a->Cout, 128, &kp.plan))
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: kind %d cannot tile N=%d H=%d W=%d", a->kind, a->N, a->Hin, a->Win);
   const ConvPlan& pl = kp.plan;
-  const int block_n = a->Cout % 256 == 0 ? 256 : (a->Cout % 128 == 0 ? 128 : 64);
+  const int block_n = a->out_f32 ? 32 : (a->Cout % 256 == 0 ? 256 : (a->Cout % 128 == 0 ? 128 : 64));
+  kp.out_f32 = a->out_f32;
+  kp.cs = a->out_f32 ? a->cout_store : a->Cout;
+  kp.brows = a->out_f32 ? a->cout_store : a->Cout;
   kp.cin_chunks = a->Cin / 64;
   kp.n_tiles = a->Cout / block_n;
 
@@ -318,7 +353,7 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   }
   {
     const uint64_t ktot = (uint64_t)pl.taps * a->Cin;
-    const uint64_t dims[2] = {ktot, (uint64_t)pl.phases * a->Cout};
+    const uint64_t dims[2] = {ktot, (uint64_t)pl.phases * kp.brows};
     const uint64_t str[1] = {ktot * es};
     const uint32_t bbox[2] = {64u, (uint32_t)block_n};
     int rc = make_tmap(&kp.bmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a->wpacked, dims, str, bbox);
@@ -342,6 +377,7 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   switch (block_n) {
     case 256: return launch_conv<256>(kp, total_tiles, stream);
     case 128: return launch_conv<128>(kp, total_tiles, stream);
+    case 32: return launch_conv<32>(kp, total_tiles, stream);
     default: return launch_conv<64>(kp, total_tiles, stream);
   }
 }

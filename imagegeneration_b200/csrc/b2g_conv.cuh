@@ -6,6 +6,7 @@
 //   K3S1   : 1 phase, 9 taps, grid = input = output.                       in(y+ky-1, x+kx-1)
 //   K4S2   : 1 phase, 16 taps, grid = output; the input is seen as 4 parity sub-grids (one tensor map each):
 //            in(2y+ky-1, 2x+kx-1) = sub[(ky+1)&1][(kx+1)&1](y + floor((ky-1)/2), x + floor((kx-1)/2))
+//   K1S1   : 1 phase, 1 tap, no shift (plain GEMM over pixels; edge layers after im2col27)
 //   CONVT  : 4 phases (py,px) x 4 taps (jy,jx), grid = input, output pixel (2y+py, 2x+px):
 //            py=0: ky = 1 (dy 0), 3 (dy -1);  py=1: ky = 0 (dy +1), 2 (dy 0)   [Y = 2*iy + ky - 1]
 #pragma once
@@ -90,6 +91,10 @@ inline bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout
         int t = ky * 3 + kx;
         p->tap_map[t] = 0; p->tap_dy[t] = (int8_t)(ky - 1); p->tap_dx[t] = (int8_t)(kx - 1);
       }
+  } else if (kind == B2G_CONV_K1S1) {
+    p->phases = 1; p->taps = 1; p->n_amaps = 1;
+    p->Hg = Hin; p->Wg = Win; p->Hout = Hin; p->Wout = Win; p->os = 1;
+    p->tap_map[0] = 0; p->tap_dy[0] = 0; p->tap_dx[0] = 0;
   } else if (kind == B2G_CONV_K4S2) {
     if ((Hin & 1) || (Win & 1)) return false;
     p->phases = 1; p->taps = 16; p->n_amaps = 4;

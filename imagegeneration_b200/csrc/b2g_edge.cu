@@ -307,3 +307,54 @@ extern "C" int b2g_wgrad3x3_c3_c64(const float* t3, const void* t64, float* dw, 
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// im2col-27: fp32 [N,H,W,3] -> bf16 [N,H,W,64] so that the 3-channel 3x3 layers run as K=64 GEMMs on the
+// tcgen05 kernels (conv_igemm K1S1 forward / input-gradient, conv_wgrad K1S1 weight gradient).
+// One thread per (pixel, 8-channel group); groups 4..7 are zero padding.
+// ---------------------------------------------------------------------------------------------------------
+namespace b2g {
+__global__ void __launch_bounds__(256) im2col27_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                       int N, int H, int W) {
+  const long total = (long)N * H * W * 8;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += gridDim.x * 256L) {
+    const int g = (int)(i & 7);
+    const long pix = i >> 3;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (g < 4) {
+      const int x = (int)(pix % W);
+      const int y = (int)((pix / W) % H);
+      const long nb = (pix / ((long)W * H)) * H * W;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int col = g * 8 + k;
+        if (col < 27) {
+          const int tap = col / 3, c3 = col - tap * 3;
+          const int xx = x + tap % 3 - 1, yy = y + tap / 3 - 1;
+          if (xx >= 0 && xx < W && yy >= 0 && yy < H) v[k] = __ldg(in + (nb + (long)yy * W + xx) * 3 + c3);
+        } else if (col == 27) {
+          v[k] = 1.f;
+        }
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    reinterpret_cast<uint4*>(out)[i] = o;
+  }
+}
+}  // namespace b2g
+
+extern "C" int b2g_im2col27(const float* in, void* out, int N, int H, int W, b2g_stream_t stream_) {
+  if (!in || !out) return fail(B2G_E_INVALID_ARG, "b2g_im2col27: null pointer");
+  const long total = (long)N * H * W * 8;
+  long blocks = (total + 255) / 256;
+  const long cap = (long)num_sms() * 32;
+  if (blocks > cap) blocks = cap;
+  b2g::im2col27_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      in, static_cast<__nv_bfloat16*>(out), N, H, W);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}

@@ -26,7 +26,9 @@ struct alignas(64) WgradKernelParams {
   int Cm, Cn;           // channels on the M / N side
   int m_tiles, n_tiles, splits, ptiles;
   int Ca, Cb;           // output is [taps][Ca][Cb]
+  int ca_valid;         // rows a < ca_valid are stored; row a == ca_valid goes to dbias (edge layers), else == Ca
   float* out;
+  float* dbias;
 };
 
 template <int BLOCK_N>
@@ -177,26 +179,35 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const int m = wi.m_tile * 128 + row;
-      float* obase = p.out + (size_t)wi.tap * p.Ca * p.Cb;
+      float* obase = p.out + (size_t)wi.tap * p.ca_valid * p.Cb;
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t r[32];
+        __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
         if (nonempty) {
           const int n = wi.n_tile * BLOCK_N + c * 32;
           if (p.m_is_shifted) {  // out[a = m][b = n..n+31]: contiguous per thread
             float* dst = obase + (size_t)m * p.Cb + n;
+            bool store = true;
+            if (m >= p.ca_valid) {  // padded rows: nothing, except the all-ones row = bias gradient
+              store = (m == p.ca_valid) && (p.dbias != nullptr);
+              dst = p.dbias + n;
+            }
+            if (store) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(__uint_as_float(r[j])),
-                           "f"(__uint_as_float(r[j + 1])), "f"(__uint_as_float(r[j + 2])),
-                           "f"(__uint_as_float(r[j + 3]))
-                           : "memory");
+              for (int j = 0; j < 32; j += 4) {
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j),
+                             "f"(__uint_as_float(r[j])), "f"(__uint_as_float(r[j + 1])),
+                             "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
+                             : "memory");
+              }
             }
           } else {  // out[a = n + j][b = m]: coalesced across the warp's lanes
 #pragma unroll
-            for (int j = 0; j < 32; ++j) atomicAdd(obase + (size_t)(n + j) * p.Cb + m, __uint_as_float(r[j]));
+            for (int j = 0; j < 32; ++j)
+              if (n + j < p.ca_valid) atomicAdd(obase + (size_t)(n + j) * p.Cb + m, __uint_as_float(r[j]));
           }
         }
       }
@@ -236,12 +247,12 @@ using namespace b2g;
 extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!a || !a->shifted || !a->unshifted || !a->dw) return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: null pointer");
-  if (a->kind != B2G_CONV_K3S1 && a->kind != B2G_CONV_K4S2)
-    return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: kind must be K3S1 or K4S2 (tap plan of the shifted operand)");
+  if (a->kind != B2G_CONV_K3S1 && a->kind != B2G_CONV_K4S2 && a->kind != B2G_CONV_K1S1)
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: kind must be K3S1, K4S2 or K1S1 (tap plan of the shifted operand)");
   if (a->Ca % 64 || a->Cb % 64 || a->Ca <= 0 || a->Cb <= 0)
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: channels (%d,%d) must be multiples of 64", a->Ca, a->Cb);
-  if (a->Ca % 128 && a->Cb % 128)
-    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: one of Ca=%d, Cb=%d must be a multiple of 128", a->Ca, a->Cb);
+  if (a->ca_valid < 0 || a->ca_valid > a->Ca || (a->dbias && (a->ca_valid <= 0 || a->ca_valid >= a->Ca)))
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: bad ca_valid=%d for Ca=%d", a->ca_valid, a->Ca);
 
   WgradKernelParams kp;
   memset(&kp, 0, sizeof(kp));
@@ -249,11 +260,17 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   if (!build_conv_plan(a->kind, a->N, a->Hs, a->Ws, a->Ca, a->Cb, 64, &kp.plan))
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: cannot tile N=%d Hs=%d Ws=%d", a->N, a->Hs, a->Ws);
   const ConvPlan& pl = kp.plan;
-  kp.m_is_shifted = (a->Ca % 128 == 0) ? 1 : 0;
+  // M side needs 128-channel tiles: prefer the operand with a multiple of 128 channels; when neither has one
+  // (64 x 64 edge layers) the shifted operand goes on M and its upper 64 rows are TMA zero fill (box beyond C).
+  kp.m_is_shifted = (a->Ca % 128 == 0 || a->Cb % 128 != 0) ? 1 : 0;
   kp.Cm = kp.m_is_shifted ? a->Ca : a->Cb;
   kp.Cn = kp.m_is_shifted ? a->Cb : a->Ca;
   const int block_n = kp.Cn % 256 == 0 ? 256 : (kp.Cn % 128 == 0 ? 128 : 64);
-  kp.m_tiles = kp.Cm / 128;
+  kp.m_tiles = (kp.Cm + 127) / 128;
+  kp.ca_valid = a->ca_valid > 0 ? a->ca_valid : a->Ca;
+  kp.dbias = a->dbias;
+  if (kp.ca_valid != a->Ca && !kp.m_is_shifted)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: ca_valid needs the shifted operand on the M side");
   kp.n_tiles = kp.Cn / block_n;
   kp.ptiles = pl.m_tiles;
   kp.Ca = a->Ca;

@@ -12,7 +12,7 @@ PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200gan.so"
 
 # enums mirrored from include/b200gan.h
-CONV_K3S1, CONV_K4S2, CONVT_K4S2 = 0, 1, 2
+CONV_K3S1, CONV_K4S2, CONVT_K4S2, CONV_K1S1 = 0, 1, 2, 3
 ACT_NONE, ACT_LEAKY, ACT_RELU, ACT_TANH = 0, 1, 2, 3
 
 
@@ -36,6 +36,7 @@ class ConvArgs(C.Structure):
         ("yprev", C.c_void_p),
         ("dact", C.c_int),
         ("dact_alpha", C.c_float), ("dact_scale", C.c_float), ("dact_zero", C.c_float),
+        ("out_f32", C.c_int), ("cout_store", C.c_int),
     ]
 
 
@@ -47,6 +48,8 @@ class WgradArgs(C.Structure):
         ("shifted", C.c_void_p),
         ("unshifted", C.c_void_p),
         ("dw", C.c_void_p),
+        ("ca_valid", C.c_int),
+        ("dbias", C.c_void_p),
     ]
 
 
@@ -68,7 +71,7 @@ def load() -> C.CDLL:
     lib.b2g_conv_igemm.restype = C.c_int
     lib.b2g_conv_igemm.argtypes = [C.POINTER(ConvArgs), C.c_void_p]
     lib.b2g_pack_conv_weight.restype = C.c_int
-    lib.b2g_pack_conv_weight.argtypes = [C.c_int] * 7 + [C.c_void_p] * 5 + [C.c_void_p]
+    lib.b2g_pack_conv_weight.argtypes = [C.c_int] * 8 + [C.c_void_p] * 5 + [C.c_void_p]
     _declare_rest(lib)
     _lib = lib
     return lib
@@ -87,6 +90,8 @@ def _declare_rest(lib: C.CDLL) -> None:
 _P, _I, _F, _L, _U64 = C.c_void_p, C.c_int, C.c_float, C.c_long, C.c_ulonglong
 _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_conv_wgrad": [C.POINTER(WgradArgs), _P],
+    # in, out, N, H, W, stream
+    "b2g_im2col27": [_P, _P, _I, _I, _I, _P],
     # in, w, wscale, bias, out, N, H, W, act, alpha, thresh8, seed, yprev, dact, stream
     "b2g_conv3x3_c3_to_c64": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _I, _U64, _P, _I, _P],
     # in, w, wscale, out, N, H, W, act, yprev, dact, stream

@@ -9,13 +9,13 @@ import torch
 
 from . import lib as _lib
 from .lib import WgradArgs
-from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K3S1, CONV_K4S2, CONVT_K4S2, ConvArgs,
+from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K1S1, CONV_K3S1, CONV_K4S2, CONVT_K4S2, ConvArgs,
                   B200GanError, check)
 
-__all__ = ["pack_conv_weight", "conv_igemm", "conv_wgrad", "CONV_K3S1", "CONV_K4S2", "CONVT_K4S2", "ACT_NONE", "ACT_LEAKY",
+__all__ = ["pack_conv_weight", "conv_igemm", "conv_wgrad", "im2col27", "CONV_K1S1", "CONV_K3S1", "CONV_K4S2", "CONVT_K4S2", "ACT_NONE", "ACT_LEAKY",
            "ACT_RELU", "ACT_TANH"]
 
-_KIND_GEOM = {CONV_K3S1: (3, 1, 9), CONV_K4S2: (4, 1, 16), CONVT_K4S2: (4, 4, 4)}  # k, phases, taps
+_KIND_GEOM = {CONV_K3S1: (3, 1, 9), CONV_K4S2: (4, 1, 16), CONVT_K4S2: (4, 4, 4), CONV_K1S1: (1, 1, 1)}  # k, phases, taps
 
 
 def _ptr(t: torch.Tensor | None):
@@ -52,7 +52,8 @@ def _need_cuda(*ts: torch.Tensor | None) -> None:
 
 def pack_conv_weight(kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = False,
                      scale_scalar: torch.Tensor | None = None, scale_d2: torch.Tensor | None = None,
-                     scale_d3: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+                     scale_d3: torch.Tensor | None = None, out: torch.Tensor | None = None,
+                     ck_pad: int = 0) -> torch.Tensor:
     """fp32 Keras-layout conv weight [kh,kw,d2,d3] -> bf16 packed [phases, Cn, taps*Ck] for conv_igemm."""
     _need_cuda(w, scale_scalar, scale_d2, scale_d3, out)
     k, phases, taps = _KIND_GEOM[kind]
@@ -60,9 +61,10 @@ def pack_conv_weight(kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = Fal
     if w.dtype != torch.float32 or kh != k or kw != k:
         raise B200GanError(f"pack_conv_weight: expected fp32 [{k},{k},d2,d3], got {tuple(w.shape)} {w.dtype}")
     cn, ck = (d3, d2) if n_is_d3 else (d2, d3)
+    ck = max(ck, ck_pad)
     if out is None:
         out = torch.empty((phases, cn, taps * ck), dtype=torch.bfloat16, device=w.device)
-    check(_lib.load().b2g_pack_conv_weight(kind, kh, kw, d2, d3, int(n_is_d3), int(flip), _ptr(w),
+    check(_lib.load().b2g_pack_conv_weight(kind, kh, kw, d2, d3, int(n_is_d3), int(flip), ck_pad, _ptr(w),
                                            _ptr(scale_scalar), _ptr(scale_d2), _ptr(scale_d3), _ptr(out),
                                            _stream()), "b2g_pack_conv_weight")
     return out
@@ -72,8 +74,10 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                bias: torch.Tensor | None = None, act: int = ACT_NONE, alpha: float = 0.0,
                dropout_thresh8: int = 0, dropout_seed: int = 0, yprev: torch.Tensor | None = None,
                dact: int = ACT_NONE, dact_alpha: float = 0.0, dact_scale: float = 1.0,
-               dact_zero: float = 0.0) -> torch.Tensor:
-    """Tensor-core implicit-GEMM conv / transposed conv with fused epilogue (see include/b200gan.h)."""
+               dact_zero: float = 0.0, out_f32: bool = False) -> torch.Tensor:
+    """Tensor-core implicit-GEMM conv / transposed conv with fused epilogue (see include/b200gan.h).
+
+    out_f32=True: narrow fp32 output — wpacked has `cout_store` (<= 8) rows and out is fp32 [N,Ho,Wo,cout_store]."""
     _need_cuda(x, wpacked, out, bias, yprev)
     n, h, w, cin = x.shape
     k, phases, taps = _KIND_GEOM[kind]
@@ -82,45 +86,64 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
     if wpacked.shape[0] != phases or wpacked.shape[2] != taps * cin:
         raise B200GanError(f"conv_igemm: packed weight {tuple(wpacked.shape)} does not match kind/Cin={cin}")
     cout = wpacked.shape[1]
-    ho, wo = {CONV_K3S1: (h, w), CONV_K4S2: (h // 2, w // 2), CONVT_K4S2: (h * 2, w * 2)}[kind]
+    ho, wo = {CONV_K3S1: (h, w), CONV_K4S2: (h // 2, w // 2), CONVT_K4S2: (h * 2, w * 2), CONV_K1S1: (h, w)}[kind]
+    odt = torch.float32 if out_f32 else torch.bfloat16
     if out is None:
-        out = torch.empty((n, ho, wo, cout), dtype=torch.bfloat16, device=x.device)
-    elif tuple(out.shape) != (n, ho, wo, cout) or out.dtype != torch.bfloat16:
+        out = torch.empty((n, ho, wo, cout), dtype=odt, device=x.device)
+    elif tuple(out.shape) != (n, ho, wo, cout) or out.dtype != odt:
         raise B200GanError("conv_igemm: bad output tensor")
-    if yprev is not None and (tuple(yprev.shape) != tuple(out.shape) or yprev.dtype != torch.bfloat16):
+    if yprev is not None and (tuple(yprev.shape) != tuple(out.shape) or yprev.dtype != odt):
         raise B200GanError("conv_igemm: yprev must match the output")
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout):
         raise B200GanError("conv_igemm: bias must be fp32 [Cout]")
+    cout_store = 0
+    if out_f32:
+        cout_store, cout = cout, 32
     a = ConvArgs(kind=kind, N=n, Hin=h, Win=w, Cin=cin, Cout=cout, inp=x.data_ptr(), wpacked=wpacked.data_ptr(),
                  out=out.data_ptr(), bias=None if bias is None else bias.data_ptr(), act=act, alpha=alpha,
                  dropout_thresh8=dropout_thresh8, dropout_seed=dropout_seed & 0xFFFFFFFFFFFFFFFF,
                  yprev=None if yprev is None else yprev.data_ptr(), dact=dact, dact_alpha=dact_alpha,
-                 dact_scale=dact_scale, dact_zero=dact_zero)
+                 dact_scale=dact_scale, dact_zero=dact_zero, out_f32=int(out_f32), cout_store=cout_store)
     ev = _prof_begin()
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
-    _prof_end(ev, "conv_igemm", 2.0 * n * h * w * cin * cout * (16 if kind == CONVT_K4S2 else taps) /
-              (4 if kind == CONV_K4S2 else 1))
+    cin_alg = 27 if kind == CONV_K1S1 else cin   # K1S1 is only used on im2col27 operands (27 real channels)
+    _prof_end(ev, "conv_igemm", 2.0 * n * h * w * cin_alg * (cout_store or cout) *
+              (16 if kind == CONVT_K4S2 else taps) / (4 if kind == CONV_K4S2 else 1))
     return out
 
 
-def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
+def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: torch.Tensor, ca_valid: int = 0,
+               dbias: torch.Tensor | None = None) -> torch.Tensor:
     """dw[tap][a][b] += sum_pixels shifted[tap-shifted pixel, a] * unshifted[pixel, b] (see include/b200gan.h).
 
     dw is fp32 [k,k,Ca,Cb] and is accumulated into (zero it first for a fresh gradient)."""
     _need_cuda(shifted, unshifted, dw)
     n, hs, ws, ca = shifted.shape
     cb = unshifted.shape[3]
-    k = 3 if kind == CONV_K3S1 else 4
-    hg, wg = (hs, ws) if kind == CONV_K3S1 else (hs // 2, ws // 2)
+    k = {CONV_K3S1: 3, CONV_K4S2: 4, CONV_K1S1: 1}[kind]
+    hg, wg = (hs // 2, ws // 2) if kind == CONV_K4S2 else (hs, ws)
     if tuple(unshifted.shape) != (n, hg, wg, cb):
         raise B200GanError(f"conv_wgrad: unshifted operand {tuple(unshifted.shape)} != {(n, hg, wg, cb)}")
     if shifted.dtype != torch.bfloat16 or unshifted.dtype != torch.bfloat16 or dw.dtype != torch.float32:
         raise B200GanError("conv_wgrad: operands must be bf16 and dw fp32")
-    if dw.numel() != k * k * ca * cb:
+    if dw.numel() != k * k * (ca_valid or ca) * cb:
         raise B200GanError("conv_wgrad: bad dw size")
     a = WgradArgs(kind=kind, N=n, Hs=hs, Ws=ws, Ca=ca, Cb=cb, shifted=shifted.data_ptr(),
-                  unshifted=unshifted.data_ptr(), dw=dw.data_ptr())
+                  unshifted=unshifted.data_ptr(), dw=dw.data_ptr(), ca_valid=ca_valid,
+                  dbias=None if dbias is None else dbias.data_ptr())
     ev = _prof_begin()
     check(_lib.load().b2g_conv_wgrad(C.byref(a), _stream()), "b2g_conv_wgrad")
-    _prof_end(ev, "conv_wgrad", 2.0 * n * hg * wg * ca * cb * k * k)
+    _prof_end(ev, "conv_wgrad", 2.0 * n * hg * wg * (ca_valid or ca) * cb * k * k)
     return dw
+
+
+def im2col27(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fp32 [N,H,W,3] -> bf16 [N,H,W,64]: the 27 taps*channels of a 3x3 window, a ones channel, zero padding."""
+    _need_cuda(x, out)
+    n, h, w, c = x.shape
+    if c != 3 or x.dtype != torch.float32:
+        raise B200GanError("im2col27: expected fp32 [N,H,W,3]")
+    if out is None:
+        out = torch.empty((n, h, w, 64), dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().b2g_im2col27(_ptr(x), _ptr(out), n, h, w, _stream()), "b2g_im2col27")
+    return out

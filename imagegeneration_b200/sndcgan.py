@@ -19,7 +19,8 @@ import torch
 
 from . import lib as _lib
 from . import ops
-from .lib import ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K3S1, CONV_K4S2, CONVT_K4S2, B200GanError, check
+from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K1S1, CONV_K3S1, CONV_K4S2, CONVT_K4S2,
+                  B200GanError, check)
 
 BN_EPS = 1e-3                    # Keras BatchNormalization default epsilon
 INV_STD = 1.0 / math.sqrt(1.0 + BN_EPS)   # inference BN with moving_var = 1
@@ -145,6 +146,8 @@ class Generator:
         self._inv_std = torch.full((1,), INV_STD, dtype=torch.float32, device=self.device)
         self._wp_f = [None] * 3           # packed fprop weights
         self._wp_d = [None] * 3           # packed dgrad weights
+        self._wp4_f = None                # convT4 forward  (64 -> 3, flipped 3x3 taps), [1][3][576]
+        self._wp4_d = None                # convT4 input-gradient (im2col27 -> 64), [1][64][64]
         self._packed_dirty = True
         self._bufs = {}
         self._z = None
@@ -180,6 +183,9 @@ class Generator:
                                                  scale_d2=gamma, out=self._wp_f[i])
             self._wp_d[i] = ops.pack_conv_weight(CONV_K4S2, v[k], n_is_d3=True, scale_scalar=self._inv_std,
                                                  scale_d2=gamma, out=self._wp_d[i])
+        self._wp4_f = ops.pack_conv_weight(CONV_K3S1, v[12], n_is_d3=False, flip=True, out=self._wp4_f)
+        self._wp4_d = ops.pack_conv_weight(CONV_K1S1, v[12].view(1, 1, 27, 64), n_is_d3=True, ck_pad=64,
+                                           out=self._wp4_d)
         self._packed_dirty = False
 
     def forward(self, z):
@@ -205,8 +211,7 @@ class Generator:
             x = out
         H, W, _ = self.output_size
         g_out = self._buf("g_out", (B, H, W, 3), torch.float32)
-        check(lib.b2g_conv3x3_c64_to_c3(_p(x), _p(v[12]), None, _p(g_out), B, H, W, ACT_TANH, None, ACT_NONE,
-                                         _stream()), "b2g_conv3x3_c64_to_c3")
+        ops.conv_igemm(CONV_K3S1, x, self._wp4_f, g_out, act=ACT_TANH, out_f32=True)
         self._acts = acts
         self._z = z
         self.g_out = g_out
@@ -224,12 +229,12 @@ class Generator:
         a0, a1, a2, a3 = self._acts
         B, H, W, _ = d_pre_tanh.shape
         self.zero_grads()
-        # convT4 (64 -> 3, k3 s1): wgrad + input gradient with ReLU' of a3
-        check(lib.b2g_wgrad3x3_c3_c64(_p(d_pre_tanh), _p(a3), _p(g[12]), None, B, H, W, _stream()),
-              "b2g_wgrad3x3_c3_c64")
+        # convT4 (64 -> 3, k3 s1) on tensor cores through the 27-channel im2col of dY: wgrad + input gradient
+        # (ReLU' of a3 in the epilogue)
+        x27 = ops.im2col27(d_pre_tanh, self._buf("dy27", (B, H, W, 64), torch.bfloat16))
+        ops.conv_wgrad(CONV_K1S1, x27, a3, g[12], ca_valid=27)
         dq = self._buf("dq3", tuple(a3.shape), torch.bfloat16)
-        check(lib.b2g_conv3x3_c3_to_c64(_p(d_pre_tanh), _p(v[12]), None, None, _p(dq), B, H, W, ACT_NONE, 0.0, 0, 0,
-                                         _p(a3), ACT_RELU, _stream()), "b2g_conv3x3_c3_to_c64")
+        ops.conv_igemm(CONV_K1S1, x27, self._wp4_d, dq, yprev=a3, dact=ACT_RELU)
         acts_in = [a0, a1, a2]
         for i in (2, 1, 0):
             k = (3, 6, 9)[i]
@@ -344,6 +349,11 @@ class Discriminator:
 
     def repack(self):
         v = self.arena.variables
+        sc0 = self._inv_sigma(0)
+        self._wp_f[0] = ops.pack_conv_weight(CONV_K1S1, v[0].view(1, 1, 27, 64), n_is_d3=True, ck_pad=64,
+                                             scale_scalar=sc0, out=self._wp_f[0])           # im2col27 -> 64
+        self._wp_d[0] = ops.pack_conv_weight(CONV_K3S1, v[0], n_is_d3=False, flip=True, scale_scalar=sc0,
+                                             out=self._wp_d[0])                               # 64 -> 3
         for i in range(1, 7):
             _name, k, s, _ci, _co = D_CONVS[i]
             sc = self._inv_sigma(i)
@@ -359,9 +369,10 @@ class Discriminator:
                                                      out=self._wp_d[i])
         self._packed_dirty = False
 
-    def forward(self, x, training=False, dropout_seeds=None):
+    def forward(self, x, training=False, dropout_seeds=None, x27=None):
         """x: fp32 CUDA [B,H,W,3].  With training=True dropout is active; `dropout_seeds` (7 ints) makes the
-        masks reproducible (tests regenerate them with oracle/dropout_hash.py)."""
+        masks reproducible (tests regenerate them with oracle/dropout_hash.py).  x27: optional cached
+        ops.im2col27(x) (train_step feeds the same generated batch to two passes)."""
         lib = _lib.load()
         if x.dtype != torch.float32 or not x.is_cuda or tuple(x.shape[1:]) != self.input_size:
             raise B200GanError(f"discriminator input must be a CUDA fp32 tensor [B,{self.input_size}]")
@@ -376,10 +387,12 @@ class Discriminator:
         if t8 and dropout_seeds is None:
             raise B200GanError("training-mode forward needs dropout_seeds")
         seeds = dropout_seeds if t8 else [0] * 7
+        if x27 is None:
+            x27 = ops.im2col27(x, self._buf("x27", (B, H, W, 64), torch.bfloat16))
         c1 = self._buf("c1", (B, H, W, 64), torch.bfloat16)
-        check(lib.b2g_conv3x3_c3_to_c64(_p(x), _p(v[0]), _p(self._inv_sigma(0)), _p(v[1]), _p(c1), B, H, W,
-                                         ACT_LEAKY, LEAKY_ALPHA, t8, seeds[0] & _MASK64, None, ACT_NONE, _stream()),
-              "b2g_conv3x3_c3_to_c64")
+        ops.conv_igemm(CONV_K1S1, x27, self._wp_f[0], c1, bias=v[1], act=ACT_LEAKY, alpha=LEAKY_ALPHA,
+                       dropout_thresh8=t8, dropout_seed=seeds[0])
+        self._x27 = x27
         acts = [c1]
         cur = c1
         for i in range(1, 7):
@@ -438,8 +451,7 @@ class Discriminator:
             dpre = dprev
         H, W = self.input_size[0], self.input_size[1]
         if need_wgrad:
-            check(lib.b2g_wgrad3x3_c3_c64(_p(self._x), _p(dpre), _p(g[0]), _p(g[1]), B, H, W, _stream()),
-                  "b2g_wgrad3x3_c3_c64")
+            ops.conv_wgrad(CONV_K1S1, self._x27, dpre, g[0], ca_valid=27, dbias=g[1])
             if self.spectral_norm:
                 for i in range(8):
                     check(lib.b2g_sn_grad_finalize(_p(v[2 * i]), _p(g[2 * i]), _p(self.sn_u[i]), _p(self.sn_vraw[i]),
@@ -448,9 +460,8 @@ class Discriminator:
         d_in = None
         if need_input_grad:
             d_in = self._buf("d_in", (B, H, W, 3), torch.float32)
-            check(lib.b2g_conv3x3_c64_to_c3(_p(dpre), _p(v[0]), _p(self._inv_sigma(0)), _p(d_in), B, H, W, ACT_NONE,
-                                             _p(g_out), ACT_TANH if g_out is not None else ACT_NONE, _stream()),
-                  "b2g_conv3x3_c64_to_c3")
+            ops.conv_igemm(CONV_K3S1, dpre, self._wp_d[0], d_in, yprev=g_out,
+                           dact=ACT_TANH if g_out is not None else ACT_NONE, out_f32=True)
         return d_in
 
 
@@ -533,7 +544,8 @@ class SNDCGANEngine:
 
         # (1) generator step (:242-249)
         g_output = G.forward(input_z)                                               # :243
-        D.forward(g_output, training=True, dropout_seeds=sa)                        # :244
+        g27 = ops.im2col27(g_output, D._buf("g27", (B, *self.image_size[:2], 64), torch.bfloat16))
+        D.forward(g_output, training=True, dropout_seeds=sa, x27=g27)               # :244
         g_loss, _ = D.head_loss(g_kind, 1.0, inv_b)                                 # :245-246
         d_gout = D.backward(need_wgrad=False, need_input_grad=True, g_out=g_output)
         G.backward(d_gout)                                                          # :248
@@ -551,7 +563,7 @@ class SNDCGANEngine:
         D._packed_dirty = True
 
         # (3) discriminator step on the stale fake batch (:259-267)
-        D.forward(g_output, training=True, dropout_seeds=sc)                        # :260
+        D.forward(g_output, training=True, dropout_seeds=sc, x27=g27)               # :260
         d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)                # :261-262
         D.backward(need_wgrad=True, need_input_grad=False)                          # :266
         self._allreduce(D.arena.g)

@@ -46,8 +46,11 @@ const char* b2g_last_error(void); /* thread-local, valid until the next failing 
  *   B2G_CONVT_K4S2  4x4 stride-2 SAME transposed conv as 4 sub-pixel phases of 2x2 taps. Hout=2Hin, Wout=2Win
  *       replaces Conv2DTranspose k4 s2 fwd (SNDCGAN.py:36-39,43-46,50-53) and the input-gradient of
  *       Conv2D k4 s2 (discriminator backward).
+ *   B2G_CONV_K1S1   1x1 conv (1 tap, no shift) = plain GEMM over pixels. Used for the 3-channel edge layers
+ *       after b2g_im2col27 has expanded [N,H,W,3] into 27(+1) bf16 channels: D.conv1 forward
+ *       (SNDCGAN.py:73-76) and the input-gradient of G.convT4 (:57-61).
  */
-enum { B2G_CONV_K3S1 = 0, B2G_CONV_K4S2 = 1, B2G_CONVT_K4S2 = 2 };
+enum { B2G_CONV_K3S1 = 0, B2G_CONV_K4S2 = 1, B2G_CONVT_K4S2 = 2, B2G_CONV_K1S1 = 3 };
 enum { B2G_ACT_NONE = 0, B2G_ACT_LEAKY = 1, B2G_ACT_RELU = 2, B2G_ACT_TANH = 3 };
 
 typedef struct b2g_conv_args {
@@ -67,9 +70,14 @@ typedef struct b2g_conv_args {
   /* backward use: multiply by the activation derivative recovered from the saved forward output `yprev`
      (same shape as out): dact=LEAKY: y>0 -> dscale, y<0 -> alpha*dscale, y==0 -> dzero (dropped element);
      dact=RELU: y>0 -> 1 else 0; dact=TANH: (1-y^2). */
-  const void* yprev; /* bf16 or NULL */
+  const void* yprev; /* same dtype/shape as out, or NULL */
   int dact;
   float dact_alpha, dact_scale, dact_zero;
+  /* narrow fp32 outputs (G.convT4 forward + tanh, D.conv1 input-gradient): out_f32 = 1 stores fp32 and
+     cout_store (> 0, phases == 1 only) is the number of REAL output channels: wpacked then has cout_store
+     rows, `out`/`yprev` are [N,Hout,Wout,cout_store] and Cout is only the MMA N tile (32). */
+  int out_f32;
+  int cout_store;
 } b2g_conv_args;
 
 int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
@@ -83,10 +91,15 @@ int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
  *   flip    = 1: spatially flipped taps (dgrad of a stride-1 conv)
  *   scale_scalar (device ptr to one float, may be NULL) multiplies everything (use 1/sigma);
  *   scale_d2 / scale_d3 (device ptr to per-d2 / per-d3 floats, may be NULL).
+ *   ck_pad (0 = none): pad the per-tap GEMM-K extent with zeros up to ck_pad (K1S1 edge layers: 27 -> 64).
  */
-int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, const float* w,
+int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad, const float* w,
                          const float* scale_scalar, const float* scale_d2, const float* scale_d3, void* wpacked,
                          b2g_stream_t stream);
+
+/* fp32 [N,H,W,3] -> bf16 [N,H,W,64]: channel tap*3+c (tap = ky*3+kx) holds in[y+ky-1, x+kx-1, c] (zero outside),
+ * channel 27 holds 1.0 (its wgrad row is the bias gradient), channels 28..63 are zero. */
+int b2g_im2col27(const float* in, void* out, int N, int H, int W, b2g_stream_t stream);
 
 /* ---- conv / convT weight gradient on tensor cores ---------------------------------------------------------
  *   dw[tap][a][b] += sum_{n,y,x} shifted[n, tap(y,x), a] * unshifted[n, y, x, b]      (fp32 atomics; the
@@ -94,6 +107,7 @@ int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, 
  *     Conv2D k3 s1  [3,3,Cin,Cout]:  kind=K3S1, shifted = layer input x   (Ca=Cin),  unshifted = dY (Cb=Cout)
  *     Conv2D k4 s2  [4,4,Cin,Cout]:  kind=K4S2, shifted = layer input x   (Ca=Cin),  unshifted = dY (Cb=Cout)
  *     Conv2DTranspose k4 s2 [4,4,Cout,Cin]: kind=K4S2, shifted = dY (Ca=Cout), unshifted = layer input (Cb=Cin)
+ *     3-channel edge layers [3,3,3,64]:     kind=K1S1, shifted = im2col27(3-channel tensor), unshifted = 64-ch tensor
  *   Hs, Ws = spatial size of the shifted operand; the unshifted one is (Hs,Ws) for K3S1, (Hs/2,Ws/2) for K4S2.
  *   Replaces Conv2DBackpropFilter behind tape.gradient (sndcgan/SNDCGAN.py:248,:256,:266). */
 typedef struct b2g_wgrad_args {
@@ -103,6 +117,11 @@ typedef struct b2g_wgrad_args {
   const void* shifted;   /* bf16 [N,Hs,Ws,Ca] */
   const void* unshifted; /* bf16 [N,Hg,Wg,Cb] */
   float* dw;             /* fp32 [taps][Ca][Cb], accumulated into */
+  /* K1S1 edge layers (shifted = b2g_im2col27 output, Ca = 64): only rows a < ca_valid are real weights
+     (dw is [ca_valid][Cb]); row a == ca_valid (the all-ones channel) is added to dbias[Cb] when non-NULL.
+     ca_valid = 0 means Ca. */
+  int ca_valid;
+  float* dbias;
 } b2g_wgrad_args;
 
 int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream);
