@@ -246,7 +246,7 @@ def run_b200(args):
     eng.train_step(real_dev[0], z_dev[0])
     torch.cuda.synchronize()
     agg = {}
-    for name, flops, a, b in lib.profile_sink:
+    for name, flops, a, b, _label in lib.profile_sink:
         d = agg.setdefault(name, [0.0, 0.0, 0])
         d[0] += flops
         d[1] += a.elapsed_time(b) * 1e-3

@@ -47,7 +47,12 @@ struct ConvCfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // +1024: manual alignment
 };
 
-constexpr int kConvThreads = 192;
+// epilogue warp groups: each group is 4 warps (one per TMEM lane quarter); groups interleave over the 32-column
+// chunks of a tile so that several chunks are in flight (the epilogue is latency-bound with one warp per SMSP)
+template <int BLOCK_N>
+constexpr int epi_groups() { return BLOCK_N >= 128 ? 4 : BLOCK_N / 32; }
+template <int BLOCK_N>
+constexpr int conv_threads() { return 64 + 128 * epi_groups<BLOCK_N>(); }
 
 struct TileCoord {
   int phase, n_tile, tn, th, tw;
@@ -66,8 +71,11 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvPlan& pl, int n_tiles
 }
 
 template <int BLOCK_N>
-__global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvKernelParams p) {
+__global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
+    conv_igemm_kernel(const __grid_constant__ ConvKernelParams p) {
   using Cfg = ConvCfg<BLOCK_N>;
+  constexpr int kEpiGroups = epi_groups<BLOCK_N>();
+  __shared__ float sbias[512];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
@@ -89,13 +97,17 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], 4);
+      mbar_init(&tempty_bar[a], 4 * kEpiGroups);
     }
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < pl.n_amaps; ++i) tma_prefetch_desc(&p.amap[i]);
     tma_prefetch_desc(&p.bmap);
+  }
+  if (p.bias) {
+    const int nb = p.out_f32 ? p.cs : pl.Cout;
+    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.bias[i];
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
@@ -157,8 +169,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       }
     }
   } else {
-    // ------------------------------------------------ epilogue (4 warps; warp w owns TMEM lanes 32*(w%4)..+31)
+    // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
     const int q = warp & 3;
+    const int grp = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     const int wl = row % pl.bw;
     const int hl = (row / pl.bw) % pl.bh;
@@ -176,7 +189,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
+      for (int c = grp; c < BLOCK_N / 32; c += kEpiGroups) {
         uint32_t r[32];
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
@@ -190,7 +203,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             for (int j = 0; j < 8; ++j) {
               if (cb + j < p.cs) {
                 float o = __uint_as_float(r[j]);
-                if (p.bias) o += __ldg(p.bias + cb + j);
+                if (p.bias) o += sbias[cb + j];
                 if (p.act == B2G_ACT_TANH) o = tanhf(o);
                 if (p.dact == B2G_ACT_TANH) {
                   const float y = __ldg(yf + j);
@@ -208,7 +221,10 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
         if (p.bias) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + cb + j);
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(&sbias[cb + j4 * 4]);
+            v[j4 * 4 + 0] += b4.x; v[j4 * 4 + 1] += b4.y; v[j4 * 4 + 2] += b4.z; v[j4 * 4 + 3] += b4.w;
+          }
         }
         if (p.act == B2G_ACT_LEAKY) {
 #pragma unroll
@@ -294,7 +310,7 @@ static int launch_conv(const ConvKernelParams& kp, int total_tiles, cudaStream_t
     attr_set = true;
   }
   int grid = total_tiles < num_sms() ? total_tiles : num_sms();
-  conv_igemm_kernel<BLOCK_N><<<grid, kConvThreads, Cfg::kSmemBytes, stream>>>(kp);
+  conv_igemm_kernel<BLOCK_N><<<grid, conv_threads<BLOCK_N>(), Cfg::kSmemBytes, stream>>>(kp);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
@@ -317,6 +333,7 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cout=%d not a multiple of 64", a->Cout);
   }
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
+  if (a->Cout > 512) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cout=%d > 512", a->Cout);
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
 
   ConvKernelParams kp;

@@ -169,9 +169,17 @@ __host__ __device__ __forceinline__ uint32_t b2g_mix32(uint32_t x) {
   x ^= x >> 16;
   return x;
 }
-// group = (flat element index) >> 2 ; returns 4 random bytes (element i uses byte i & 3)
+// group = (flat element index) >> 2 ; returns 4 random bytes (element i uses byte i & 3).
+// One multiply-xorshift hash (lowbias32) of (group ^ seed_lo) with seed_hi injected between its two rounds.
 __host__ __device__ __forceinline__ uint32_t b2g_dropout_bits(uint32_t group, uint32_t seed_lo, uint32_t seed_hi) {
-  return b2g_mix32(b2g_mix32(group ^ seed_lo) + seed_hi);
+  uint32_t x = group ^ seed_lo;
+  x ^= x >> 16;
+  x *= 0x7feb352du;
+  x ^= x >> 15;
+  x += seed_hi;
+  x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {

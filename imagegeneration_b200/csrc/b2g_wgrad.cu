@@ -12,6 +12,8 @@
 //
 // Replaces Conv2DBackpropFilter (tape.gradient at sndcgan/SNDCGAN.py:248,:256,:266) for the Conv2D layers
 // :80-118 and the Conv2DTranspose layers :36-53.
+#include <stdlib.h>
+
 #include "b2g_conv.cuh"
 #include "b2g_host.h"
 #include "b2g_ptx.cuh"
@@ -240,6 +242,235 @@ static int launch_wgrad(const WgradKernelParams& kp, int total_items, cudaStream
   return B2G_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// Tap-grouped variant (the default for the 128+-channel layers): M side = 128 channels of the UNSHIFTED operand,
+// N side = up to 256 columns made of `T` taps x `cc` channels of the shifted operand (cc = min(Ca, 256),
+// T = 256 / cc).  One unshifted tile feeds T taps, every MMA is N=256 wide (MMA-bound instead of smem-bound for
+// the 64/128-channel layers), and the accumulator is stored transposed: out[tap][a][b = M row].
+// ------------------------------------------------------------------------------------------------------------
+struct alignas(64) WgradTapsParams {
+  CUtensorMap smap[4];
+  CUtensorMap umap;
+  ConvPlan plan;
+  int Ca, Cb;
+  int cc;          // shifted channels per tap inside one N tile
+  int T;           // taps per group
+  int groups;      // ceil(taps / T)
+  int a_chunks;    // Ca / cc
+  int m_tiles;     // Cb / 128
+  int splits, ptiles;
+  float* out;
+};
+
+struct WgradTapsCfg {
+  static constexpr int kBoxBytes = 64 * 128;
+  static constexpr int kMBytes = 2 * kBoxBytes;
+  static constexpr int kNBytes = 4 * kBoxBytes;
+  static constexpr int kStageBytes = kMBytes + kNBytes;  // 48 KB
+  static constexpr int kStages = 4;
+  static constexpr int kTmemCols = 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;
+};
+
+struct WgradTapsItem {
+  int tg, ac, m_tile, nt, p_begin, p_end;
+};
+__device__ __forceinline__ WgradTapsItem decode_taps_item(const WgradTapsParams& p, int item) {
+  WgradTapsItem w;
+  w.tg = item % p.groups;
+  int r = item / p.groups;
+  w.ac = r % p.a_chunks;
+  r /= p.a_chunks;
+  w.m_tile = r % p.m_tiles;
+  const int split = r / p.m_tiles;
+  const int left = p.plan.taps - w.tg * p.T;
+  w.nt = left < p.T ? left : p.T;
+  w.p_begin = (int)((long)split * p.ptiles / p.splits);
+  w.p_end = (int)((long)(split + 1) * p.ptiles / p.splits);
+  return w;
+}
+
+__global__ void __launch_bounds__(kWgradThreads, 1) wgrad_taps_kernel(const __grid_constant__ WgradTapsParams p) {
+  using Cfg = WgradTapsCfg;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const ConvPlan& pl = p.plan;
+  const int total_items = p.groups * p.a_chunks * p.m_tiles * p.splits;
+  const int boxes_per_tap = p.cc / 64;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < pl.n_amaps; ++i) tma_prefetch_desc(&p.smap[i]);
+    tma_prefetch_desc(&p.umap);
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        const WgradTapsItem wi = decode_taps_item(p, item);
+        const int m_c0 = wi.m_tile * 128, a_c0 = wi.ac * p.cc;
+        const uint32_t bytes = Cfg::kMBytes + wi.nt * boxes_per_tap * Cfg::kBoxBytes;
+        for (int pt = wi.p_begin; pt < wi.p_end; ++pt) {
+          const int tw = pt % pl.tiles_w;
+          const int r2 = pt / pl.tiles_w;
+          const int th = r2 % pl.tiles_h;
+          const int tn = r2 / pl.tiles_h;
+          const int w0 = tw * pl.bw, h0 = th * pl.bh, n0 = tn * pl.bn;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* m_dst = smem + stage * Cfg::kStageBytes;
+          uint8_t* n_dst = m_dst + Cfg::kMBytes;
+          mbar_expect_tx(&full_bar[stage], bytes);
+          tma_load_4d(m_dst, &p.umap, &full_bar[stage], m_c0, w0, h0, n0);
+          tma_load_4d(m_dst + Cfg::kBoxBytes, &p.umap, &full_bar[stage], m_c0 + 64, w0, h0, n0);
+          for (int t = 0; t < wi.nt; ++t) {
+            const int tap = wi.tg * p.T + t;
+            const CUtensorMap* sm = &p.smap[pl.tap_map[tap]];
+            const int dy = pl.tap_dy[tap], dx = pl.tap_dx[tap];
+            for (int g = 0; g < boxes_per_tap; ++g)
+              tma_load_4d(n_dst + (t * boxes_per_tap + g) * Cfg::kBoxBytes, sm, &full_bar[stage], a_c0 + g * 64,
+                          w0 + dx, h0 + dy, n0);
+          }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
+        const WgradTapsItem wi = decode_taps_item(p, item);
+        const uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, wi.nt * p.cc);
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(&tempty_bar[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * 256;
+        const int k_steps = wi.p_end - wi.p_begin;
+        for (int ks = 0; ks < k_steps; ++ks) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t m_addr = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t n_addr = m_addr + Cfg::kMBytes;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            umma_f16(d_tmem, umma_smem_desc(m_addr + k * 2048, Cfg::kBoxBytes, 1024),
+                     umma_smem_desc(n_addr + k * 2048, Cfg::kBoxBytes, 1024), idesc, (ks | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[as]);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    int it = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
+      const WgradTapsItem wi = decode_taps_item(p, item);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      const bool nonempty = wi.p_end > wi.p_begin;
+      mbar_wait(&tfull_bar[as], aphase);
+      tc_fence_after();
+      const int b = wi.m_tile * 128 + row;
+      const int n_chunks = wi.nt * p.cc / 32;
+#pragma unroll 1
+      for (int c = 0; c < n_chunks; ++c) {
+        uint32_t r[32];
+        __syncwarp();
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * 256 + c * 32, r);
+        tmem_ld_wait();
+        if (nonempty) {
+          const int n = c * 32;
+          const int tap = wi.tg * p.T + n / p.cc;
+          const int a0 = wi.ac * p.cc + n % p.cc;
+          float* dst = p.out + ((size_t)tap * p.Ca + a0) * p.Cb + b;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) atomicAdd(dst + (size_t)j * p.Cb, __uint_as_float(r[j]));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+static int launch_wgrad_taps(const WgradTapsParams& kp, int total_items, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(wgrad_taps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        WgradTapsCfg::kSmemBytes));
+    attr_set = true;
+  }
+  int grid = total_items < num_sms() ? total_items : num_sms();
+  wgrad_taps_kernel<<<grid, kWgradThreads, WgradTapsCfg::kSmemBytes, stream>>>(kp);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+// tensor maps of both operands ([64 pixel][64 channel] boxes) shared by the two kernel variants
+static int make_wgrad_maps(const b2g_wgrad_args* a, const ConvPlan& pl, CUtensorMap* smap, CUtensorMap* umap) {
+  const size_t es = 2;
+  const uint32_t box[4] = {64u, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bn};
+  const char* sbase = static_cast<const char*>(a->shifted);
+  if (pl.n_amaps == 1) {
+    const uint64_t dims[4] = {(uint64_t)a->Ca, (uint64_t)a->Ws, (uint64_t)a->Hs, (uint64_t)a->N};
+    const uint64_t str[3] = {(uint64_t)a->Ca * es, (uint64_t)a->Ws * a->Ca * es, (uint64_t)a->Hs * a->Ws * a->Ca * es};
+    int rc = make_tmap(&smap[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, sbase, dims, str, box);
+    if (rc) return rc;
+  } else {
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px) {
+        const uint64_t dims[4] = {(uint64_t)a->Ca, (uint64_t)a->Ws / 2, (uint64_t)a->Hs / 2, (uint64_t)a->N};
+        const uint64_t str[3] = {(uint64_t)2 * a->Ca * es, (uint64_t)2 * a->Ws * a->Ca * es,
+                                 (uint64_t)a->Hs * a->Ws * a->Ca * es};
+        int rc = make_tmap(&smap[py * 2 + px], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                           sbase + ((size_t)py * a->Ws + px) * a->Ca * es, dims, str, box);
+        if (rc) return rc;
+      }
+  }
+  const uint64_t dims[4] = {(uint64_t)a->Cb, (uint64_t)pl.Wg, (uint64_t)pl.Hg, (uint64_t)a->N};
+  const uint64_t str[3] = {(uint64_t)a->Cb * es, (uint64_t)pl.Wg * a->Cb * es, (uint64_t)pl.Hg * pl.Wg * a->Cb * es};
+  return make_tmap(umap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a->unshifted, dims, str, box);
+}
+
 }  // namespace b2g
 
 using namespace b2g;
@@ -253,6 +484,40 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: channels (%d,%d) must be multiples of 64", a->Ca, a->Cb);
   if (a->ca_valid < 0 || a->ca_valid > a->Ca || (a->dbias && (a->ca_valid <= 0 || a->ca_valid >= a->Ca)))
     return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: bad ca_valid=%d for Ca=%d", a->ca_valid, a->Ca);
+
+  static int force_taps = []() { const char* e = getenv("B2G_WGRAD_TAPS"); return e ? atoi(e) : -1; }();
+  const bool taps_ok = a->Cb % 128 == 0 && (a->ca_valid == 0 || a->ca_valid == a->Ca) && !a->dbias;
+  // Measured on B200 (profiles/r1_wgrad_variants.md): grouping taps wins when the other kernel's N tile would be
+  // narrow (Cb == 128: 64->128 and 128->128 layers); for Cb >= 256 the per-tap kernel with vector reds is faster.
+  const bool use_taps = taps_ok && (force_taps < 0 ? a->Cb == 128 : force_taps != 0);
+  if (use_taps) {
+    // tap-grouped kernel (M = unshifted operand, N = taps x shifted channels)
+    WgradTapsParams tp;
+    memset(&tp, 0, sizeof(tp));
+    if (!build_conv_plan(a->kind, a->N, a->Hs, a->Ws, a->Ca, a->Cb, 64, &tp.plan))
+      return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: cannot tile N=%d Hs=%d Ws=%d", a->N, a->Hs, a->Ws);
+    const ConvPlan& tpl = tp.plan;
+    tp.Ca = a->Ca;
+    tp.Cb = a->Cb;
+    tp.cc = a->Ca < 256 ? a->Ca : 256;
+    if (a->Ca % tp.cc) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: Ca=%d unsupported", a->Ca);
+    tp.T = 256 / tp.cc;
+    tp.groups = (tpl.taps + tp.T - 1) / tp.T;
+    tp.a_chunks = a->Ca / tp.cc;
+    tp.m_tiles = a->Cb / 128;
+    tp.ptiles = tpl.m_tiles;
+    tp.out = a->dw;
+    const int base = tp.groups * tp.a_chunks * tp.m_tiles;
+    // equal-length work items: keep their count just below a whole number of rounds over the SMs (no ragged tail)
+    static int rounds = []() { const char* e = getenv("B2G_WGRAD_ROUNDS"); int r = e ? atoi(e) : 2; return r > 0 ? r : 2; }();
+    int sp = rounds * num_sms() / base;
+    if (sp > tp.ptiles / 8) sp = tp.ptiles / 8;
+    if (sp < 1) sp = 1;
+    tp.splits = sp;
+    int rc = make_wgrad_maps(a, tpl, tp.smap, &tp.umap);
+    if (rc) return rc;
+    return launch_wgrad_taps(tp, base * sp, stream);
+  }
 
   WgradKernelParams kp;
   memset(&kp, 0, sizeof(kp));
@@ -276,9 +541,10 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   kp.Ca = a->Ca;
   kp.Cb = a->Cb;
   kp.out = a->dw;
-  // split-K: aim for ~4 work items per SM, at least 8 k-steps each
+  // split-K: equal-length work items, just under 4 whole rounds over the SMs (no ragged last round)
   const int base_items = pl.taps * kp.m_tiles * kp.n_tiles;
-  int splits = (4 * num_sms() + base_items - 1) / base_items;
+  static int rounds1 = []() { const char* e = getenv("B2G_WGRAD_ROUNDS1"); int r = e ? atoi(e) : 4; return r > 0 ? r : 4; }();
+  int splits = rounds1 * num_sms() / base_items;
   if (splits > kp.ptiles / 8) splits = kp.ptiles / 8;
   if (splits < 1) splits = 1;
   kp.splits = splits;

@@ -34,12 +34,12 @@ def _prof_begin():
     return ev
 
 
-def _prof_end(ev, name, flops):
+def _prof_end(ev, name, flops, label=""):
     if ev is None:
         return
     end = torch.cuda.Event(enable_timing=True)
     end.record()
-    _lib.profile_sink.append((name, flops, ev, end))
+    _lib.profile_sink.append((name, flops, ev, end, label))
 
 
 def _need_cuda(*ts: torch.Tensor | None) -> None:
@@ -108,7 +108,8 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
     cin_alg = 27 if kind == CONV_K1S1 else cin   # K1S1 is only used on im2col27 operands (27 real channels)
     _prof_end(ev, "conv_igemm", 2.0 * n * h * w * cin_alg * (cout_store or cout) *
-              (16 if kind == CONVT_K4S2 else taps) / (4 if kind == CONV_K4S2 else 1))
+              (16 if kind == CONVT_K4S2 else taps) / (4 if kind == CONV_K4S2 else 1),
+              f"kind{kind} {n}x{h}x{w}x{cin}->{cout_store or cout}")
     return out
 
 
@@ -133,7 +134,8 @@ def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: to
                   dbias=None if dbias is None else dbias.data_ptr())
     ev = _prof_begin()
     check(_lib.load().b2g_conv_wgrad(C.byref(a), _stream()), "b2g_conv_wgrad")
-    _prof_end(ev, "conv_wgrad", 2.0 * n * hg * wg * (ca_valid or ca) * cb * k * k)
+    _prof_end(ev, "conv_wgrad", 2.0 * n * hg * wg * (ca_valid or ca) * cb * k * k,
+              f"kind{kind} {n}x{hs}x{ws} Ca{ca} Cb{cb}")
     return dw
 
 

@@ -25,10 +25,18 @@ def mix32(x: np.ndarray) -> np.ndarray:
 
 
 def dropout_bits(group: np.ndarray, seed: int) -> np.ndarray:
+    """b2g_dropout_bits: lowbias32 of (group ^ seed_lo) with seed_hi added between its two multiply rounds."""
     seed_lo = np.uint32(seed & 0xFFFFFFFF)
     seed_hi = np.uint32((seed >> 32) & 0xFFFFFFFF)
     with np.errstate(over="ignore"):
-        return mix32(mix32(group.astype(np.uint32) ^ seed_lo) + seed_hi)
+        x = group.astype(np.uint32) ^ seed_lo
+        x ^= x >> np.uint32(16)
+        x *= _M1
+        x ^= x >> np.uint32(15)
+        x += seed_hi
+        x *= _M2
+        x ^= x >> np.uint32(16)
+        return x
 
 
 def keep_mask(numel: int, seed: int, thresh8: int) -> np.ndarray:
