@@ -130,7 +130,7 @@ def run_reference(args):
     probe()
     t1 = time.perf_counter() - t0
     total = args.steps + args.warmup
-    batch = 16
+    batch = int(os.environ.get("B2G_REF_MAX_BATCH", "16"))
     while batch > 1 and t1 * batch * total > 150.0:
         batch //= 2
     step = _oracle_step_factory(batch)

@@ -39,39 +39,16 @@ __global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3
                                         const float* __restrict__ w, const float* __restrict__ scale_scalar,
                                         const float* __restrict__ scale_d2, const float* __restrict__ scale_d3,
                                         __nv_bfloat16* __restrict__ out, int phases, int taps, long total) {
-  const int Cn = n_is_d3 ? D3 : D2;  // GEMM-N channels
-  const int Ckr = n_is_d3 ? D2 : D3;      // real GEMM-K channels per tap
-  const int Ck = ck_pad > Ckr ? ck_pad : Ckr;  // stored (zero padded) extent
   const float s0 = scale_scalar ? *scale_scalar : 1.f;
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % Ck);
-    long r = i / Ck;
-    if (c >= Ckr) {
-      out[i] = __float2bfloat16_rn(0.f);
-      continue;
+    int d2, d3;
+    const long src = pack_source_index(kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, taps, i, &d2, &d3);
+    float v = 0.f;
+    if (src >= 0) {
+      v = w[src] * s0;
+      if (scale_d2) v *= scale_d2[d2];
+      if (scale_d3) v *= scale_d3[d3];
     }
-    const int tap = (int)(r % taps);
-    r /= taps;
-    const int n = (int)(r % Cn);
-    const int ph = (int)(r / Cn);
-    int ky, kx;
-    if (kind == B2G_CONVT_K4S2) {
-      int d;
-      convt_tap(ph >> 1, tap >> 1, &ky, &d);
-      convt_tap(ph & 1, tap & 1, &kx, &d);
-    } else {
-      ky = tap / kw;
-      kx = tap % kw;
-      if (flip) {
-        ky = kh - 1 - ky;
-        kx = kw - 1 - kx;
-      }
-    }
-    const int d2 = n_is_d3 ? c : n;
-    const int d3 = n_is_d3 ? n : c;
-    float v = w[(((long)ky * kw + kx) * D2 + d2) * D3 + d3] * s0;
-    if (scale_d2) v *= scale_d2[d2];
-    if (scale_d3) v *= scale_d3[d3];
     out[i] = __float2bfloat16_rn(v);
   }
 }
@@ -116,4 +93,33 @@ extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, in
                                                                 static_cast<__nv_bfloat16*>(wpacked), phases, taps, total);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
+}
+
+// ---- host-only introspection (no CUDA calls): lets the CPU test-suite check the tiling / tap / packing logic ----
+extern "C" int b2g_conv_plan_query(int kind, int N, int Hin, int Win, int tile_pixels, int* out, int out_len) {
+  ConvPlan p;
+  memset(&p, 0, sizeof(p));
+  if (out_len < 80) return fail(B2G_E_INVALID_ARG, "b2g_conv_plan_query: out needs 80 ints");
+  if (!build_conv_plan(kind, N, Hin, Win, 64, 64, tile_pixels, &p))
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_plan_query: cannot tile kind %d N=%d H=%d W=%d", kind, N, Hin, Win);
+  const int hdr[16] = {p.phases, p.taps, p.Hg, p.Wg, p.bw, p.bh, p.bn, p.tiles_w, p.tiles_h, p.tiles_n, p.m_tiles,
+                       p.Hout, p.Wout, p.os, p.n_amaps, 0};
+  for (int i = 0; i < 16; ++i) out[i] = hdr[i];
+  for (int i = 0; i < 16; ++i) {
+    out[16 + i] = p.tap_map[i];
+    out[32 + i] = p.tap_dy[i];
+    out[48 + i] = p.tap_dx[i];
+  }
+  for (int i = 0; i < 4; ++i) {
+    out[64 + i] = p.ph_y[i];
+    out[68 + i] = p.ph_x[i];
+  }
+  return B2G_OK;
+}
+
+extern "C" long b2g_pack_source_index(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
+                                      long i) {
+  const int taps = kind == B2G_CONV_K3S1 ? 9 : (kind == B2G_CONV_K4S2 ? 16 : (kind == B2G_CONVT_K4S2 ? 4 : 1));
+  int d2, d3;
+  return pack_source_index(kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, taps, i, &d2, &d3);
 }

@@ -46,6 +46,41 @@ __host__ __device__ inline void convt_tap(int p, int j, int* k, int* d) {
   else        { *k = j == 0 ? 0 : 2; *d = j == 0 ? 1 : 0; }
 }
 
+// Source element of packed weight element i (layout [phase][n][tap*Ck + c], Ck zero-padded to ck_pad) inside the
+// fp32 Keras kernel w[kh][kw][D2][D3]; returns -1 for a padding element.  *d2 / *d3 receive the channel indices
+// (for the per-channel scales).  Shared by the pack kernel and the host-side plan tests.
+__host__ __device__ inline long pack_source_index(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip,
+                                                  int ck_pad, int taps, long i, int* d2_out, int* d3_out) {
+  const int Cn = n_is_d3 ? D3 : D2;
+  const int Ckr = n_is_d3 ? D2 : D3;
+  const int Ck = ck_pad > Ckr ? ck_pad : Ckr;
+  const int c = (int)(i % Ck);
+  long r = i / Ck;
+  if (c >= Ckr) return -1;
+  const int tap = (int)(r % taps);
+  r /= taps;
+  const int n = (int)(r % Cn);
+  const int ph = (int)(r / Cn);
+  int ky, kx;
+  if (kind == B2G_CONVT_K4S2) {
+    int d;
+    convt_tap(ph >> 1, tap >> 1, &ky, &d);
+    convt_tap(ph & 1, tap & 1, &kx, &d);
+  } else {
+    ky = tap / kw;
+    kx = tap % kw;
+    if (flip) {
+      ky = kh - 1 - ky;
+      kx = kw - 1 - kx;
+    }
+  }
+  const int d2 = n_is_d3 ? c : n;
+  const int d3 = n_is_d3 ? n : c;
+  *d2_out = d2;
+  *d3_out = d3;
+  return (((long)ky * kw + kx) * D2 + d2) * D3 + d3;
+}
+
 inline bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 // Chooses the pixel tile (bw, bh, bn) with bw*bh*bn == tile_pixels that wastes the fewest rows.

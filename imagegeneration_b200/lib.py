@@ -72,6 +72,10 @@ def load() -> C.CDLL:
     lib.b2g_conv_igemm.argtypes = [C.POINTER(ConvArgs), C.c_void_p]
     lib.b2g_pack_conv_weight.restype = C.c_int
     lib.b2g_pack_conv_weight.argtypes = [C.c_int] * 8 + [C.c_void_p] * 5 + [C.c_void_p]
+    lib.b2g_conv_plan_query.restype = C.c_int
+    lib.b2g_conv_plan_query.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.c_int]
+    lib.b2g_pack_source_index.restype = C.c_long
+    lib.b2g_pack_source_index.argtypes = [C.c_int] * 8 + [C.c_long]
     _declare_rest(lib)
     _lib = lib
     return lib
@@ -133,4 +137,5 @@ def check(rc: int, what: str, launches: int = 1) -> None:
 
 # Names every build of the library must export (tests/test_abi.py checks them against include/b200gan.h).
 def exported_symbols() -> list[str]:
-    return ["b2g_version", "b2g_last_error", "b2g_conv_igemm", "b2g_pack_conv_weight", *_EXTRA_SIGNATURES]
+    return ["b2g_version", "b2g_last_error", "b2g_conv_igemm", "b2g_pack_conv_weight", "b2g_conv_plan_query",
+            "b2g_pack_source_index", *_EXTRA_SIGNATURES]

@@ -526,8 +526,8 @@ class SNDCGANEngine:
     def _allreduce(self, flat, async_op=False):
         if self.world == 1:
             return None
-        import torch.distributed as dist
-        return dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.pg, async_op=async_op)
+        from .dp import allreduce_sum_
+        return allreduce_sum_(flat, self.pg, async_op)
 
     def train_step(self, input_real, input_z, dropout_seeds=None):
         """One G update + two D updates, in the reference's order (SNDCGAN.py:241-269).

@@ -184,6 +184,14 @@ int b2g_spectral_norm_multi(int n_layers, const float* const* W, float* const* u
 int b2g_sn_grad_finalize(const float* W, float* G, const float* u, const float* v_raw, const float* scal,
                          float* dot_scratch, int K, int C, b2g_stream_t stream);
 
+/* ---- host-only introspection (no CUDA calls; used by the CPU test-suite) ---------------------------------
+ * conv_plan_query: tiling + tap tables of a conv role -> out[0..15] = {phases, taps, Hg, Wg, bw, bh, bn, tiles_w,
+ *   tiles_h, tiles_n, m_tiles, Hout, Wout, out_stride, n_input_maps, 0}; out[16+i] = input map of tap entry i,
+ *   out[32+i] = dy, out[48+i] = dx (entry = phase*taps + tap); out[64+p] / out[68+p] = output phase offsets.
+ * pack_source_index: flat index into the fp32 Keras kernel that packed element i is taken from (-1 = padding). */
+int b2g_conv_plan_query(int kind, int N, int Hin, int Win, int tile_pixels, int* out, int out_len);
+long b2g_pack_source_index(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad, long i);
+
 #ifdef __cplusplus
 }
 #endif

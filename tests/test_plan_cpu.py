@@ -1,0 +1,127 @@
+"""CPU: the tiling / tap-table / weight-packing logic of the implicit-GEMM kernels (host code shared with the CUDA
+kernels through b2g_conv_plan_query / b2g_pack_source_index) reproduces the oracle's Keras-semantics convolutions
+when the GEMM itself is emulated with numpy."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import keras_ops as K
+
+K3S1, K4S2, CONVT, K1S1 = 0, 1, 2, 3
+
+
+def _plan(kind, n, h, w, tile=128):
+    from imagegeneration_b200 import lib
+    out = (C.c_int * 80)()
+    rc = lib.load().b2g_conv_plan_query(kind, n, h, w, tile, out, 80)
+    assert rc == 0, lib.load().b2g_last_error()
+    v = list(out)
+    keys = ["phases", "taps", "Hg", "Wg", "bw", "bh", "bn", "tiles_w", "tiles_h", "tiles_n", "m_tiles", "Hout", "Wout",
+            "os", "n_amaps"]
+    p = dict(zip(keys, v[:15]))
+    p["tap_map"], p["tap_dy"], p["tap_dx"] = v[16:32], v[32:48], v[48:64]
+    p["ph_y"], p["ph_x"] = v[64:68], v[68:72]
+    return p
+
+
+def _pack(kind, w, n_is_d3, flip, ck_pad=0):
+    from imagegeneration_b200 import lib
+    l = lib.load()
+    kh, kw, d2, d3 = w.shape
+    phases, taps = {K3S1: (1, 9), K4S2: (1, 16), CONVT: (4, 4), K1S1: (1, 1)}[kind]
+    cn, ck = (d3, d2) if n_is_d3 else (d2, d3)
+    ck = max(ck, ck_pad)
+    flat = w.reshape(-1)
+    out = np.zeros(phases * cn * taps * ck)
+    for i in range(out.size):
+        s = l.b2g_pack_source_index(kind, kh, kw, d2, d3, int(n_is_d3), int(flip), ck_pad, i)
+        out[i] = 0.0 if s < 0 else flat[s]
+    return out.reshape(phases, cn, taps * ck)
+
+
+def _emulate(kind, x, packed, plan):
+    """out[n, Y, X, :] accumulated tap by tap exactly as the kernel's TMA loads + MMAs do (zero fill outside)."""
+    n, h, w, c = x.shape
+    cn = packed.shape[1]
+    out = np.zeros((n, plan["Hout"], plan["Wout"], cn))
+    hg, wg = plan["Hg"], plan["Wg"]
+    for ph in range(plan["phases"]):
+        acc = np.zeros((n, hg, wg, cn))
+        for t in range(plan["taps"]):
+            e = ph * plan["taps"] + t
+            m, dy, dx = plan["tap_map"][e], plan["tap_dy"][e], plan["tap_dx"][e]
+            src = x[:, (m // 2)::2, (m % 2)::2, :] if plan["n_amaps"] == 4 else x
+            sh = np.zeros((n, hg, wg, c))
+            ys = np.arange(hg) + dy
+            xs = np.arange(wg) + dx
+            vy = (ys >= 0) & (ys < src.shape[1])
+            vx = (xs >= 0) & (xs < src.shape[2])
+            sh[np.ix_(np.arange(n), np.nonzero(vy)[0], np.nonzero(vx)[0])] = src[np.ix_(np.arange(n), ys[vy], xs[vx])]
+            acc += sh @ packed[ph][:, t * c:(t + 1) * c].T
+        out[:, plan["ph_y"][ph]::plan["os"], plan["ph_x"][ph]::plan["os"], :] = acc
+    return out
+
+
+def _rand(shape, seed):
+    return np.random.default_rng(seed).uniform(-1, 1, shape)
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 4, 8), (1, 6, 4), (3, 2, 16)])
+def test_k3s1_forward_and_dgrad(n, h, w):
+    x, wt = _rand((n, h, w, 5), 1), _rand((3, 3, 5, 7), 2)
+    ref = K.conv2d_same(torch.from_numpy(x), torch.from_numpy(wt), None, 1).numpy()
+    plan = _plan(K3S1, n, h, w)
+    assert np.allclose(_emulate(K3S1, x, _pack(K3S1, wt, True, False), plan), ref, atol=1e-10)
+    dy = _rand((n, h, w, 7), 3)
+    xt = torch.zeros((n, h, w, 5), dtype=torch.float64, requires_grad=True)
+    K.conv2d_same(xt, torch.from_numpy(wt), None, 1).backward(torch.from_numpy(dy))
+    assert np.allclose(_emulate(K3S1, dy, _pack(K3S1, wt, False, True), plan), xt.grad.numpy(), atol=1e-10)
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 4, 8), (1, 6, 4)])
+def test_k4s2_forward_and_convt_dgrad(n, h, w):
+    x, wt = _rand((n, 2 * h, 2 * w, 5), 4), _rand((4, 4, 5, 7), 5)
+    ref = K.conv2d_same(torch.from_numpy(x), torch.from_numpy(wt), None, 2).numpy()
+    assert np.allclose(_emulate(K4S2, x, _pack(K4S2, wt, True, False), _plan(K4S2, n, 2 * h, 2 * w)), ref, atol=1e-10)
+    # input-gradient of the stride-2 conv = CONVT role with (n = Cin, k = Cout) packing
+    dy = _rand((n, h, w, 7), 6)
+    xt = torch.zeros((n, 2 * h, 2 * w, 5), dtype=torch.float64, requires_grad=True)
+    K.conv2d_same(xt, torch.from_numpy(wt), None, 2).backward(torch.from_numpy(dy))
+    got = _emulate(CONVT, dy, _pack(CONVT, wt, False, False), _plan(CONVT, n, h, w))
+    assert np.allclose(got, xt.grad.numpy(), atol=1e-10)
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 4, 8), (1, 2, 4)])
+def test_convt_forward_and_its_dgrad(n, h, w):
+    x, wt = _rand((n, h, w, 5), 7), _rand((4, 4, 7, 5), 8)      # Conv2DTranspose kernel [kh,kw,Cout,Cin]
+    xt = torch.from_numpy(x).requires_grad_(True)
+    y = K.conv2d_transpose_same(xt, torch.from_numpy(wt), 2)
+    assert np.allclose(_emulate(CONVT, x, _pack(CONVT, wt, False, False), _plan(CONVT, n, h, w)), y.detach().numpy(),
+                       atol=1e-10)
+    dy = _rand((n, 2 * h, 2 * w, 7), 9)
+    y.backward(torch.from_numpy(dy))
+    got = _emulate(K4S2, dy, _pack(K4S2, wt, True, False), _plan(K4S2, n, 2 * h, 2 * w))
+    assert np.allclose(got, xt.grad.numpy(), atol=1e-10)
+
+
+def test_k1s1_padding_of_the_edge_layer_weights():
+    wt = _rand((3, 3, 3, 64), 10)
+    p = _pack(K1S1, wt.reshape(1, 1, 27, 64), True, False, ck_pad=64)
+    assert p.shape == (1, 64, 64)
+    assert np.array_equal(p[0][:, :27], wt.reshape(27, 64).T) and not p[0][:, 27:].any()
+
+
+@pytest.mark.parametrize("kind,h,w", [(K3S1, 144, 256), (K3S1, 72, 128), (K3S1, 36, 64), (K3S1, 18, 32), (K4S2, 144, 256),
+                                      (CONVT, 18, 32), (CONVT, 72, 128), (K3S1, 2, 4), (K1S1, 144, 256)])
+@pytest.mark.parametrize("n", [1, 3, 64])
+@pytest.mark.parametrize("tile", [128, 64])
+def test_tiles_cover_the_grid(kind, h, w, n, tile):
+    p = _plan(kind, n, h, w, tile)
+    assert p["bw"] * p["bh"] * p["bn"] == tile
+    assert p["tiles_w"] * p["bw"] == p["Wg"]
+    assert p["tiles_h"] * p["bh"] >= p["Hg"] and (p["tiles_h"] - 1) * p["bh"] < p["Hg"]
+    assert p["tiles_n"] * p["bn"] >= n and (p["tiles_n"] - 1) * p["bn"] < n
+    assert p["m_tiles"] == p["tiles_w"] * p["tiles_h"] * p["tiles_n"]
+    assert max(p["bw"], p["bh"], p["bn"]) <= 256                      # TMA box limit

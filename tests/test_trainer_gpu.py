@@ -1,0 +1,72 @@
+"""GPU: the Trainer-level drop-in (sndcgan/SNDCGAN.py:148-212, :272-335): directory handling, epoch loop, losses
+pickle, checkpoint cadence, --continue resume; plus hinge / spectral-norm options against the oracle."""
+import os
+import pickle
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import sndcgan_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def test_train_loop_checkpoint_and_resume(tmp_path):
+    from imagegeneration_b200.trainer import SNDCGAN
+    d = str(tmp_path / "training")
+    live = str(tmp_path / "live")
+    size = (16, 32, 3)
+    m = SNDCGAN(d, "synthetic:12", 4, 0.5, 2e-4, 2e-4, live, False, size, 128)
+    m.train(2 + 1, 2)                                  # epochs 0,1,2 -> checkpoints at 0 and 2 (:317)
+    ck = sorted(os.listdir(os.path.join(d, "checkpoints")))
+    assert ck == ["ckpt-0.pt", "ckpt-2.pt"]
+    losses = pickle.load(open(os.path.join(d, "losses.pickle"), "rb"))
+    assert losses["epoch"] == [0, 1, 2] and len(losses["avg_g_loss"]) == 3
+    assert all(np.isfinite(v) for v in losses["avg_d_loss"])
+    assert m.d_optimizer.iterations == 2 * m.g_optimizer.iterations == 2 * 9
+    assert os.path.exists(live + ".png")
+    w_before = m.gen_model.arena.w.clone()
+    m2 = SNDCGAN(d, "synthetic:12", 4, 0.5, 2e-4, 2e-4, live, True, size, 128)      # --continue
+    assert m2.start_epoch == 3
+    assert torch.equal(m2.gen_model.arena.w, w_before)
+    assert m2.g_optimizer.iterations == 9
+    m3 = SNDCGAN(d, "synthetic:12", 4, 0.5, 2e-4, 2e-4, live, False, size, 128)     # fresh start wipes the dir (:152)
+    assert m3.start_epoch == 0 and os.listdir(os.path.join(d, "checkpoints")) == []
+
+
+@pytest.mark.parametrize("loss,sn", [("hinge", False), ("bce", True), ("hinge", True)])
+def test_hinge_and_spectral_norm_options(loss, sn):
+    """north_star options that the reference lacks: losses vs the oracle <= 2e-2, sigma <= 1e-5."""
+    from imagegeneration_b200.sndcgan import SNDCGANEngine
+    size, B = (16, 32, 3), 4
+    eng = SNDCGANEngine(B, dropout=0.0, image_size=size, seed=62, loss=loss, spectral_norm=sn)
+    orc = O.OracleSNDCGAN(size, dropout=0.0, seed=62, loss=loss, spectral_norm=sn)
+    orc.gv = [v.detach().cpu().clone() for v in eng.gen_model.trainable_variables]
+    orc.dv = [v.detach().cpu().clone() for v in eng.disc_model.trainable_variables]
+    if sn:
+        orc.sn_state = [u.detach().cpu().clone() for u in eng.disc_model.sn_u]
+    g = torch.Generator().manual_seed(3)
+    real = torch.rand((B, *size), generator=g) * 2 - 1
+    z = torch.rand((B, 128), generator=g) * 2 - 1
+    col = {}
+    ref = orc.train_step(real, z, collect=col)
+    out = eng.train_step(real.cuda(), z.cuda())
+    torch.cuda.synchronize()
+    for a, b in zip(out[:4], ref[:4]):
+        assert abs(float(a) - float(b)) <= 2e-2 * max(1.0, abs(float(b)))
+    if sn:
+        for i in range(8):      # sigma of the last D pass
+            s_ref = float(col[f"dc_sigma{i}"])
+            assert abs(float(eng.disc_model.sn_scal[i][1]) - s_ref) / s_ref < 2e-4, i
+        from oracle import keras_ops as K
+        # identical u0: re-create the engine's initial vectors
+        eng3 = SNDCGANEngine(B, dropout=0.0, image_size=size, seed=62, loss=loss, spectral_norm=True)
+        u0s = [u.detach().cpu().double() for u in eng3.disc_model.sn_u]
+        eng3.disc_model.sn_power_iteration()
+        torch.cuda.synchronize()
+        for i in range(8):
+            w2d = eng3.disc_model.trainable_variables[2 * i].detach().cpu().double()
+            w2d = w2d.reshape(-1, w2d.shape[-1])
+            sigma, _u, _v = K.spectral_norm_power_iteration(w2d, u0s[i], 1)
+            assert abs(float(eng3.disc_model.sn_scal[i][1]) - float(sigma)) / float(sigma) < 1e-5, i
