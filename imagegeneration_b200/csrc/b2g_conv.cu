@@ -9,6 +9,8 @@
 // Replaces the cuDNN convolutions TensorFlow dispatches for sndcgan/SNDCGAN.py:36-53 (Conv2DTranspose),
 // :80-118 (Conv2D) and their gradients w.r.t. the input (tape.gradient at :248,:256,:266).
 #include "b2g_conv.cuh"
+#include "b2g_conv_epi.cuh"
+#include "b2g_conv_rows.cuh"
 #include "b2g_host.h"
 #include "b2g_ptx.cuh"
 
@@ -20,18 +22,7 @@ struct alignas(64) ConvKernelParams {
   ConvPlan plan;
   int cin_chunks;  // Cin / 64
   int n_tiles;     // Cout / BLOCK_N
-  __nv_bfloat16* out;
-  const float* bias;
-  const __nv_bfloat16* yprev;
-  int act;
-  float alpha;
-  int drop_thresh8;
-  float drop_scale;
-  uint32_t seed_lo, seed_hi;
-  int dact;
-  float dact_alpha, dact_scale, dact_zero;
-  int out_f32;     // narrow fp32 output: `cs` real channels, out/yprev are float [pixels][cs]
-  int cs;          // channel stride of the output tensor (== plan.Cout unless out_f32)
+  EpiParams e;     // fused epilogue (b2g_conv_epi.cuh)
   int brows;       // rows of the packed weight matrix per phase
 };
 
@@ -105,9 +96,9 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     for (int i = 0; i < pl.n_amaps; ++i) tma_prefetch_desc(&p.amap[i]);
     tma_prefetch_desc(&p.bmap);
   }
-  if (p.bias) {
-    const int nb = p.out_f32 ? p.cs : pl.Cout;
-    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.bias[i];
+  if (p.e.bias) {
+    const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
+    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i];
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
@@ -116,57 +107,60 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ------------------------------------------------ TMA producer
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord tc = decode_tile(pl, p.n_tiles, tile);
-        const int w0 = tc.tw * pl.bw, h0 = tc.th * pl.bh, n0 = tc.tn * pl.bn;
-        const int brow = tc.phase * p.brows + tc.n_tile * BLOCK_N;
-        for (int ks = 0; ks < k_steps; ++ks) {
-          const int tap = ks / p.cin_chunks;
-          const int chunk = ks - tap * p.cin_chunks;
-          const int e = tc.phase * pl.taps + tap;
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+    // ------------------------------------------------ TMA producer (whole warp converged; one elected lane issues)
+    const uint32_t leader = elect_one_sync();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const TileCoord tc = decode_tile(pl, p.n_tiles, tile);
+      const int w0 = tc.tw * pl.bw, h0 = tc.th * pl.bh, n0 = tc.tn * pl.bn;
+      const int brow = tc.phase * p.brows + tc.n_tile * BLOCK_N;
+      int tap = 0, chunk = 0;
+      for (int ks = 0; ks < k_steps; ++ks) {
+        const int e = tc.phase * pl.taps + tap;
+        const int amap = pl.tap_map[e], dx = pl.tap_dx[e], dy = pl.tap_dy[e];
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (leader) {
           uint8_t* a_dst = smem + stage * Cfg::kStageBytes;
-          uint8_t* b_dst = a_dst + Cfg::kABytes;
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_4d(a_dst, &p.amap[pl.tap_map[e]], &full_bar[stage], chunk * 64, w0 + pl.tap_dx[e],
-                      h0 + pl.tap_dy[e], n0);
-          tma_load_2d(b_dst, &p.bmap, &full_bar[stage], (tap * p.cin_chunks + chunk) * 64, brow);
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+          tma_load_4d(a_dst, &p.amap[amap], &full_bar[stage], chunk * 64, w0 + dx, h0 + dy, n0);
+          tma_load_2d(a_dst + Cfg::kABytes, &p.bmap, &full_bar[stage], ks * 64, brow);
         }
+        __syncwarp();
+        if (++chunk == p.cin_chunks) { chunk = 0; ++tap; }
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(&tempty_bar[as], aphase ^ 1);
+    // ------------------------------------------------ MMA issuer (whole warp converged; one elected lane issues)
+    const uint32_t leader = elect_one_sync();
+    constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
+    const uint32_t smem_base = smem_u32(smem);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(&tempty_bar[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+      for (int ks = 0; ks < k_steps; ++ks) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
-        for (int ks = 0; ks < k_steps; ++ks) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * Cfg::kStageBytes);
-          const uint32_t b_addr = a_addr + Cfg::kABytes;
+        const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
+        const uint64_t adesc = umma_desc_kmajor(a_addr);
+        const uint64_t bdesc = umma_desc_kmajor(a_addr + Cfg::kABytes);
+        if (leader) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            umma_f16(d_tmem, umma_smem_desc(a_addr + k * 32, 16, 1024), umma_smem_desc(b_addr + k * 32, 16, 1024),
-                     idesc, (ks | k) != 0);
-          }
+          for (int k = 0; k < 4; ++k) umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
           umma_commit(&empty_bar[stage]);
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);
+        __syncwarp();
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
+      if (leader) umma_commit(&tfull_bar[as]);
+      __syncwarp();
     }
   } else {
     // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
@@ -194,94 +188,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
-        const int cb = col0 + c * 32;
-        if (p.out_f32) {  // narrow fp32 output (3 real channels): tanh / tanh' epilogues of the generator's last layer
-          if (valid && cb < p.cs) {
-            float* of = reinterpret_cast<float*>(p.out) + pix * p.cs + cb;
-            const float* yf = reinterpret_cast<const float*>(p.yprev) + pix * p.cs + cb;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              if (cb + j < p.cs) {
-                float o = __uint_as_float(r[j]);
-                if (p.bias) o += sbias[cb + j];
-                if (p.act == B2G_ACT_TANH) o = tanhf(o);
-                if (p.dact == B2G_ACT_TANH) {
-                  const float y = __ldg(yf + j);
-                  o *= 1.f - y * y;
-                }
-                of[j] = o;
-              }
-            }
-          }
-          continue;
-        }
-        const size_t off = pix * pl.Cout + cb;  // element offset of this thread's 32 outputs
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        if (p.bias) {
-#pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 b4 = *reinterpret_cast<const float4*>(&sbias[cb + j4 * 4]);
-            v[j4 * 4 + 0] += b4.x; v[j4 * 4 + 1] += b4.y; v[j4 * 4 + 2] += b4.z; v[j4 * 4 + 3] += b4.w;
-          }
-        }
-        if (p.act == B2G_ACT_LEAKY) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * p.alpha;
-        } else if (p.act == B2G_ACT_RELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-        }
-        if (p.drop_thresh8 > 0 && valid) {
-          const uint32_t g0 = static_cast<uint32_t>(off >> 2);
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            const uint32_t bits = b2g_dropout_bits(g0 + g, p.seed_lo, p.seed_hi);
-#pragma unroll
-            for (int b = 0; b < 4; ++b) {
-              const int byte = (bits >> (8 * b)) & 0xFF;
-              v[g * 4 + b] = byte < p.drop_thresh8 ? 0.f : v[g * 4 + b] * p.drop_scale;
-            }
-          }
-        }
-        if (p.dact != B2G_ACT_NONE && valid) {
-          const uint4* yp = reinterpret_cast<const uint4*>(p.yprev + off);
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const uint4 yv = __ldg(yp + g);
-            const uint32_t w4[4] = {yv.x, yv.y, yv.z, yv.w};
-#pragma unroll
-            for (int b = 0; b < 4; ++b) {
-              const float y0 = bf16_lo(w4[b]), y1 = bf16_hi(w4[b]);
-              float f0, f1;
-              if (p.dact == B2G_ACT_LEAKY) {
-                f0 = y0 > 0.f ? p.dact_scale : (y0 < 0.f ? p.dact_alpha * p.dact_scale : p.dact_zero);
-                f1 = y1 > 0.f ? p.dact_scale : (y1 < 0.f ? p.dact_alpha * p.dact_scale : p.dact_zero);
-              } else if (p.dact == B2G_ACT_RELU) {
-                f0 = y0 > 0.f ? 1.f : 0.f;
-                f1 = y1 > 0.f ? 1.f : 0.f;
-              } else {  // tanh
-                f0 = 1.f - y0 * y0;
-                f1 = 1.f - y1 * y1;
-              }
-              v[g * 8 + b * 2] *= f0;
-              v[g * 8 + b * 2 + 1] *= f1;
-            }
-          }
-        }
-        if (valid) {
-          uint4* op = reinterpret_cast<uint4*>(p.out + off);
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            uint4 o;
-            o.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
-            o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
-            o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
-            o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
-            op[g] = o;
-          }
-        }
+        conv_epilogue_chunk(p.e, sbias, r, pix, col0 + c * 32, valid);
       }
       tc_fence_before();
       __syncwarp();
@@ -342,8 +249,12 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: kind %d cannot tile N=%d H=%d W=%d", a->kind, a->N, a->Hin, a->Win);
   const ConvPlan& pl = kp.plan;
   const int block_n = a->out_f32 ? 32 : (a->Cout % 256 == 0 ? 256 : (a->Cout % 128 == 0 ? 128 : 64));
-  kp.out_f32 = a->out_f32;
-  kp.cs = a->out_f32 ? a->cout_store : a->Cout;
+  {  // wide layers with Cout <= 128: row-slab kernel (b2g_conv_rows.cu) re-uses each input row across taps
+    bool handled = false;
+    const int rc = launch_conv_rows(a, pl, block_n, stream_, &handled);
+    if (rc != B2G_OK || handled) return rc;
+  }
+  fill_epi_params(a, &kp.e);
   kp.brows = a->out_f32 ? a->cout_store : a->Cout;
   kp.cin_chunks = a->Cin / 64;
   kp.n_tiles = a->Cout / block_n;
@@ -376,20 +287,6 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
     int rc = make_tmap(&kp.bmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a->wpacked, dims, str, bbox);
     if (rc) return rc;
   }
-  kp.out = static_cast<__nv_bfloat16*>(a->out);
-  kp.bias = a->bias;
-  kp.yprev = static_cast<const __nv_bfloat16*>(a->yprev);
-  kp.act = a->act;
-  kp.alpha = a->alpha;
-  kp.drop_thresh8 = a->dropout_thresh8;
-  kp.drop_scale = 256.f / (256.f - (float)a->dropout_thresh8);
-  kp.seed_lo = (uint32_t)(a->dropout_seed & 0xFFFFFFFFull);
-  kp.seed_hi = (uint32_t)(a->dropout_seed >> 32);
-  kp.dact = a->dact;
-  kp.dact_alpha = a->dact_alpha;
-  kp.dact_scale = a->dact_scale;
-  kp.dact_zero = a->dact_zero;
-
   const int total_tiles = pl.phases * pl.m_tiles * kp.n_tiles;
   switch (block_n) {
     case 256: return launch_conv<256>(kp, total_tiles, stream);

@@ -1,0 +1,363 @@
+// b2g_conv_rows.cu — row-slab implicit-GEMM convolution for sm_100a (layers >= 128 pixels wide, Cout <= 128).
+//
+//   warp 0      : slab producer (one lane) — per needed input row ONE TMA box of 130 pixels x 64 channels
+//   warp 1      : TMEM allocator + MMA issuer (one lane) — walks the static schedule of b2g_conv_rows.cuh:
+//                 per step one weight tile and R tcgen05.mma groups (one per row of the super-tile), the dx tap
+//                 selected by offsetting the SW128 smem descriptor by dx*128 bytes inside the slab
+//   warp 2      : weight-tile producer (one lane) — its own ring, so neither producer can starve the other
+//   warps 3..18 : epilogue (4 groups x 4 TMEM lane quarters) over the R*P accumulators, double-buffered in TMEM
+//
+// Same roles, arguments and fused epilogues as conv_igemm_kernel (b2g_conv.cu); replaces the cuDNN convolutions
+// behind sndcgan/SNDCGAN.py:50-61 (G.convT3, G.convT4), :80-90 (D.conv2, D.conv3) and their input gradients.
+#include <stdlib.h>
+#include <string.h>
+
+#include "b2g_conv_epi.cuh"
+#include "b2g_conv_rows.cuh"
+#include "b2g_host.h"
+#include "b2g_ptx.cuh"
+
+namespace b2g {
+
+struct alignas(64) RowsKernelParams {
+  CUtensorMap amap[4];
+  CUtensorMap bmap;
+  ConvPlan plan;
+  EpiParams e;
+  RowsGeom geom;
+  RowsSched sched[2];
+  int n_tiles;       // Cout / BLOCK_N
+  int brows;         // rows of the packed weight matrix per phase
+  int total_tiles;   // PG * n_tiles * N * row_blocks * tiles_w
+};
+
+template <int BLOCK_N>
+struct RowsCfg {
+  static constexpr int kSlabBytes = 17 * 1024;                       // 130 px * 128 B = 16640, padded to 1 KiB
+  static constexpr int kSlabTx = kRowsSlabPixels * 128;              // bytes one slab TMA delivers
+  static constexpr int kSlabs = BLOCK_N == 128 ? 7 : 8;
+  static constexpr int kBBytes = BLOCK_N * 128;
+  static constexpr int kBStages = BLOCK_N == 128 ? 6 : 8;
+  static constexpr int kBarBytes = 512;
+  static constexpr int kSmemBytes = kSlabs * kSlabBytes + kBStages * kBBytes + kBarBytes + 1024;
+  static constexpr int kEpiGroups = 4;
+  static constexpr int kThreads = 96 + 128 * kEpiGroups;
+};
+
+struct RowsTile {
+  int pg, n_tile, n, y0, w0;
+};
+__device__ __forceinline__ RowsTile decode_rows_tile(const RowsKernelParams& p, int tile) {
+  RowsTile t;
+  const int tw = tile % p.plan.tiles_w;
+  tile /= p.plan.tiles_w;
+  t.w0 = tw * 128;
+  t.y0 = (tile % p.geom.row_blocks) * p.geom.R;
+  tile /= p.geom.row_blocks;
+  t.n = tile % p.plan.N;
+  tile /= p.plan.N;
+  t.n_tile = tile % p.n_tiles;
+  t.pg = tile / p.n_tiles;
+  return t;
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(RowsCfg<BLOCK_N>::kThreads, 1)
+    conv_rows_kernel(const __grid_constant__ RowsKernelParams p) {
+  using Cfg = RowsCfg<BLOCK_N>;
+  __shared__ float sbias[512];
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* bsm = smem + Cfg::kSlabs * Cfg::kSlabBytes;
+  uint64_t* sfull = reinterpret_cast<uint64_t*>(bsm + Cfg::kBStages * Cfg::kBBytes);
+  uint64_t* sempty = sfull + Cfg::kSlabs;
+  uint64_t* bfull = sempty + Cfg::kSlabs;
+  uint64_t* bempty = bfull + Cfg::kBStages;
+  uint64_t* tfull = bempty + Cfg::kBStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const ConvPlan& pl = p.plan;
+  const int R = p.geom.R, P = p.geom.P, n_acc = p.geom.n_acc;
+  const uint32_t tmem_cols = 2u * n_acc * BLOCK_N;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kSlabs; ++s) {
+      mbar_init(&sfull[s], 1);
+      mbar_init(&sempty[s], 1);
+    }
+    for (int s = 0; s < Cfg::kBStages; ++s) {
+      mbar_init(&bfull[s], 1);
+      mbar_init(&bempty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 4 * Cfg::kEpiGroups);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < pl.n_amaps; ++i) tma_prefetch_desc(&p.amap[i]);
+  }
+  if (warp == 2 && lane == 0) tma_prefetch_desc(&p.bmap);
+  if (p.e.bias) {
+    const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
+    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i];
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------ slab producer (whole warp converged; one elected lane issues)
+    const uint32_t leader = elect_one_sync();
+    uint32_t stage = 0, par = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      const RowsTile t = decode_rows_tile(p, tile);
+      const RowsSched& sc = p.sched[t.pg];
+      const int n_slabs = sc.n_slabs;
+      for (int i = 0; i < n_slabs; ++i) {
+        const int amap = sc.slab_map[i], chunk = sc.slab_chunk[i], dy = sc.slab_dy[i];
+        mbar_wait(&sempty[stage], par ^ 1);
+        if (leader) {
+          mbar_expect_tx(&sfull[stage], Cfg::kSlabTx);
+          tma_load_4d(smem + stage * Cfg::kSlabBytes, &p.amap[amap], &sfull[stage], chunk * 64, t.w0 - 1, t.y0 + dy,
+                      t.n);
+        }
+        __syncwarp();
+        if (++stage == Cfg::kSlabs) { stage = 0; par ^= 1; }
+      }
+    }
+  } else if (warp == 2) {
+    // ------------------------------------------------ weight-tile producer
+    const uint32_t leader = elect_one_sync();
+    uint32_t stage = 0, par = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      const RowsTile t = decode_rows_tile(p, tile);
+      const RowsSched& sc = p.sched[t.pg];
+      const int n_steps = sc.n_steps;
+      const int brow0 = t.pg * P * p.brows + t.n_tile * BLOCK_N;
+      for (int j = 0; j < n_steps; ++j) {
+        const RowsStep st = sc.steps[j];
+        mbar_wait(&bempty[stage], par ^ 1);
+        if (leader) {
+          mbar_expect_tx(&bfull[stage], Cfg::kBBytes);
+          tma_load_2d(bsm + stage * Cfg::kBBytes, &p.bmap, &bfull[stage], st.bcol * 64, brow0 + st.phase_l * p.brows);
+        }
+        __syncwarp();
+        if (++stage == Cfg::kBStages) { stage = 0; par ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------ MMA issuer (whole warp converged; one elected lane issues)
+    const uint32_t leader = elect_one_sync();
+    constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
+    const uint32_t slab_base = smem_u32(smem), b_base = smem_u32(bsm);
+    uint32_t s_head = 0, s_head_par = 0;  // ring position / parity of slab 0 of the current tile
+    uint32_t b_stage = 0, b_par = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const RowsTile t = decode_rows_tile(p, tile);
+      const RowsSched& sc = p.sched[t.pg];
+      const int as = it & 1;
+      mbar_wait(&tempty[as], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t d_base = tmem_base + as * (n_acc * BLOCK_N);
+      uint32_t written = 0;
+      int waited = 0;
+      uint32_t w_stage = s_head, w_par = s_head_par;  // next slab to wait for
+      uint32_t r_stage = s_head;                      // next slab to release
+      const int n_steps = sc.n_steps;
+      for (int j = 0; j < n_steps; ++j) {
+        const RowsStep st = sc.steps[j];
+        mbar_wait(&bfull[b_stage], b_par);
+        for (; waited <= st.slab0 + R - 1; ++waited) {
+          mbar_wait(&sfull[w_stage], w_par);
+          if (++w_stage == Cfg::kSlabs) { w_stage = 0; w_par ^= 1; }
+        }
+        tc_fence_after();
+        const uint64_t bdesc = umma_desc_kmajor(b_base + b_stage * Cfg::kBBytes);
+        uint32_t sstage = s_head + st.slab0;
+        if (sstage >= Cfg::kSlabs) sstage -= Cfg::kSlabs;
+        if (sstage >= Cfg::kSlabs) sstage -= Cfg::kSlabs;
+        if (sstage >= Cfg::kSlabs) sstage -= Cfg::kSlabs;
+        for (int r = 0; r < R; ++r) {
+          const uint64_t adesc = umma_desc_kmajor(slab_base + sstage * Cfg::kSlabBytes + st.dxi * 128);
+          const int acc = st.acc0 + r * P;
+          const uint32_t d_tmem = d_base + acc * BLOCK_N;
+          const uint32_t have = (written >> acc) & 1;
+          if (leader) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, have | (k != 0));
+          }
+          __syncwarp();
+          written |= 1u << acc;
+          if (++sstage == Cfg::kSlabs) sstage = 0;
+        }
+        if (leader) {
+          umma_commit(&bempty[b_stage]);
+          for (int q = 0; q < st.rel; ++q) {
+            uint32_t rs = r_stage + q;
+            if (rs >= Cfg::kSlabs) rs -= Cfg::kSlabs;
+            umma_commit(&sempty[rs]);
+          }
+        }
+        __syncwarp();
+        r_stage += st.rel;
+        if (r_stage >= Cfg::kSlabs) r_stage -= Cfg::kSlabs;
+        if (++b_stage == Cfg::kBStages) { b_stage = 0; b_par ^= 1; }
+      }
+      s_head = w_stage;  // every slab of the tile has been waited for by its last step
+      s_head_par = w_par;
+      if (leader) umma_commit(&tfull[as]);
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
+    const int q = warp & 3;
+    const int grp = (warp - 3) >> 2;
+    const int row = q * 32 + lane;
+    constexpr int kChunks = BLOCK_N / 32;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const RowsTile t = decode_rows_tile(p, tile);
+      mbar_wait(&tfull[as], (it >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int idx = grp; idx < n_acc * kChunks; idx += Cfg::kEpiGroups) {
+        const int acc = idx / kChunks, c = idx % kChunks;
+        const int r = acc / P, phase = t.pg * P + acc % P;
+        const int gy = t.y0 + r;
+        const bool valid = gy < pl.Hg;
+        const int oy = gy * pl.os + pl.ph_y[phase], ox = (t.w0 + row) * pl.os + pl.ph_x[phase];
+        const size_t pix = (static_cast<size_t>(t.n) * pl.Hout + oy) * pl.Wout + ox;
+        uint32_t v[32];
+        __syncwarp();
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * (n_acc * BLOCK_N) + acc * BLOCK_N + c * 32,
+                      v);
+        tmem_ld_wait();
+        conv_epilogue_chunk(p.e, sbias, v, pix, t.n_tile * BLOCK_N + c * 32, valid);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+template <int BLOCK_N>
+static int launch_rows(const RowsKernelParams& kp, cudaStream_t stream) {
+  using Cfg = RowsCfg<BLOCK_N>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(conv_rows_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int grid = kp.total_tiles < num_sms() ? kp.total_tiles : num_sms();
+  conv_rows_kernel<BLOCK_N><<<grid, Cfg::kThreads, Cfg::kSmemBytes, stream>>>(kp);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+static int rows_ring(int block_n) { return block_n == 128 ? RowsCfg<128>::kSlabs : RowsCfg<64>::kSlabs; }
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
+int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream_, bool* handled) {
+  *handled = false;
+  const int enabled = env_int("B2G_CONV_ROWS", 1);  // read per call: tests switch kernels
+  if (!enabled) return B2G_OK;
+  if (block_n != 32 && block_n != 64 && block_n != 128) return B2G_OK;
+  RowsKernelParams kp;
+  memset(&kp, 0, sizeof(kp));
+  if (!build_rows_sched(pl, block_n, rows_ring(block_n), &kp.geom, kp.sched)) return B2G_OK;
+  kp.plan = pl;
+  fill_epi_params(a, &kp.e);
+  kp.brows = a->out_f32 ? a->cout_store : a->Cout;
+  kp.n_tiles = a->Cout / block_n;
+  kp.total_tiles = kp.geom.PG * kp.n_tiles * pl.N * kp.geom.row_blocks * pl.tiles_w;
+
+  const size_t es = 2;
+  const char* base = static_cast<const char*>(a->in);
+  const uint32_t box[4] = {64u, (uint32_t)kRowsSlabPixels, 1u, 1u};
+  if (pl.n_amaps == 1) {
+    const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->Win, (uint64_t)a->Hin, (uint64_t)a->N};
+    const uint64_t str[3] = {(uint64_t)a->Cin * es, (uint64_t)a->Win * a->Cin * es,
+                             (uint64_t)a->Hin * a->Win * a->Cin * es};
+    int rc = make_tmap(&kp.amap[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, str, box);
+    if (rc) return rc;
+  } else {
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px) {
+        const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->Win / 2, (uint64_t)a->Hin / 2, (uint64_t)a->N};
+        const uint64_t str[3] = {(uint64_t)2 * a->Cin * es, (uint64_t)2 * a->Win * a->Cin * es,
+                                 (uint64_t)a->Hin * a->Win * a->Cin * es};
+        const char* b = base + ((size_t)py * a->Win + px) * a->Cin * es;
+        int rc = make_tmap(&kp.amap[py * 2 + px], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, b, dims, str, box);
+        if (rc) return rc;
+      }
+  }
+  {
+    const uint64_t ktot = (uint64_t)pl.taps * a->Cin;
+    const uint64_t dims[2] = {ktot, (uint64_t)pl.phases * kp.brows};
+    const uint64_t str[1] = {ktot * es};
+    const uint32_t bbox[2] = {64u, (uint32_t)block_n};
+    int rc = make_tmap(&kp.bmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a->wpacked, dims, str, bbox);
+    if (rc) return rc;
+  }
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  int rc;
+  switch (block_n) {
+    case 128: rc = launch_rows<128>(kp, stream); break;
+    case 64: rc = launch_rows<64>(kp, stream); break;
+    default: rc = launch_rows<32>(kp, stream); break;
+  }
+  if (rc == B2G_OK) *handled = true;
+  return rc;
+}
+
+}  // namespace b2g
+
+// host-only introspection for the CPU test-suite: the row-slab schedule of a conv role.
+//   out[0..7] = {handled, R, P, PG, n_acc, row_blocks, n_slabs(pg), n_steps(pg)};
+//   out[8 + 3*i + {0,1,2}] = slab i {map, dy, chunk};  out[8 + 72 + 6*j + {0..5}] = step j {bcol, phase_l, slab0, dxi, acc0, rel}
+extern "C" int b2g_conv_rows_plan_query(int kind, int N, int Hin, int Win, int Cin, int block_n, int pg, int* out,
+                                        int out_len) {
+  using namespace b2g;
+  if (!out || out_len < 8 + 3 * kRowsMaxSlabs + 6 * kRowsMaxSteps) return fail(B2G_E_INVALID_ARG, "rows_plan_query: out too small");
+  memset(out, 0, sizeof(int) * out_len);
+  ConvPlan pl;
+  if (!build_conv_plan(kind, N, Hin, Win, Cin, block_n, 128, &pl)) return B2G_OK;
+  RowsGeom g;
+  RowsSched sc[2];
+  if (block_n != 32 && block_n != 64 && block_n != 128) return B2G_OK;
+  if (!build_rows_sched(pl, block_n, rows_ring(block_n), &g, sc)) return B2G_OK;
+  if (pg < 0 || pg >= g.PG) return fail(B2G_E_INVALID_ARG, "rows_plan_query: phase group %d out of range", pg);
+  out[0] = 1; out[1] = g.R; out[2] = g.P; out[3] = g.PG; out[4] = g.n_acc; out[5] = g.row_blocks;
+  out[6] = sc[pg].n_slabs; out[7] = sc[pg].n_steps;
+  for (int i = 0; i < sc[pg].n_slabs; ++i) {
+    out[8 + 3 * i] = sc[pg].slab_map[i]; out[9 + 3 * i] = sc[pg].slab_dy[i]; out[10 + 3 * i] = sc[pg].slab_chunk[i];
+  }
+  for (int j = 0; j < sc[pg].n_steps; ++j) {
+    const RowsStep& st = sc[pg].steps[j];
+    int* o = out + 8 + 3 * kRowsMaxSlabs + 6 * j;
+    o[0] = st.bcol; o[1] = st.phase_l; o[2] = st.slab0; o[3] = st.dxi; o[4] = st.acc0; o[5] = st.rel;
+  }
+  return B2G_OK;
+}

@@ -1,0 +1,137 @@
+// b2g_conv_rows.cuh — schedule of the row-slab implicit-GEMM conv kernel (b2g_conv_rows.cu).
+//
+// For layers whose phase grid is >= 128 pixels wide, an M tile is 128 consecutive pixels of ONE image row.  The
+// activation operand of tap (dy, dx) is then the input row y+dy shifted by dx pixels, so instead of one TMA box
+// per tap the kernel loads each needed input row ONCE as a "slab" of 130 pixels x 64 channels (1 halo pixel each
+// side, zero-filled outside the image) and addresses the dx taps by moving the UMMA smem descriptor by
+// dx * 128 bytes.  A super-tile is R consecutive rows x P output phases (R*P accumulators in TMEM), so a slab is
+// shared by up to 3 (dx) x R (rows) x P (phases) MMAs and a weight tile by R MMAs: L2->SM traffic per MMA drops
+// 2.3-4x against the per-tap kernel, which is what bounds the Cout <= 128 layers.
+//
+// The schedule is a static program (identical for every super-tile of a phase group) built on the host:
+//   slabs[i] : input map, row offset relative to the first row of the super-tile, channel chunk — loaded in order
+//   steps[j] : one weight tile (k-block `bcol`, local phase) + R MMAs: row r uses slab slab0 + r at pixel shift
+//              dxi and accumulator acc0 + r*P; after the step the oldest `rel` slabs are released (FIFO).
+#pragma once
+#include "b2g_conv.cuh"
+
+namespace b2g {
+
+constexpr int kRowsMaxSlabs = 24;
+constexpr int kRowsMaxSteps = 64;
+constexpr int kRowsSlabPixels = 130;
+
+struct RowsStep {
+  int16_t bcol;    // k-block (64 columns) of the packed weight matrix
+  int8_t phase_l;  // local phase inside the phase group
+  int8_t slab0;    // slab used by row r = 0
+  int8_t dxi;      // pixel shift inside the slab: dx + 1
+  int8_t acc0;     // accumulator of row r = 0
+  int8_t rel;      // slabs released after this step
+  int8_t pad;
+};
+
+struct RowsSched {
+  int n_slabs, n_steps;
+  int8_t slab_map[kRowsMaxSlabs], slab_dy[kRowsMaxSlabs], slab_chunk[kRowsMaxSlabs];
+  RowsStep steps[kRowsMaxSteps];
+};
+
+struct RowsGeom {
+  int R, P, PG, n_acc;  // rows per super-tile, phases per phase group, phase groups, accumulators
+  int row_blocks;       // ceil(Hg / R)
+};
+
+// One attempt with a fixed number of rows per super-tile.
+inline bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGeom* g, RowsSched* sched /*[2]*/) {
+  const int chunks = pl.Cin / 64;
+  g->R = R;
+  g->P = P;
+  g->PG = pl.phases / P;
+  g->n_acc = R * P;
+  g->row_blocks = (pl.Hg + R - 1) / R;
+  if (g->PG > 2) return false;
+  for (int pg = 0; pg < g->PG; ++pg) {
+    RowsSched& s = sched[pg];
+    s.n_slabs = 0;
+    s.n_steps = 0;
+    int last_use[kRowsMaxSlabs];
+    for (int c = 0; c < chunks; ++c) {
+      for (int m = 0; m < pl.n_amaps; ++m) {
+        int dmin = 127, dmax = -128;
+        for (int pl_ = 0; pl_ < P; ++pl_)
+          for (int t = 0; t < pl.taps; ++t) {
+            const int e = (pg * P + pl_) * pl.taps + t;
+            if (pl.tap_map[e] != m) continue;
+            if (pl.tap_dx[e] < -1 || pl.tap_dx[e] > 1) return false;
+            if (pl.tap_dy[e] < dmin) dmin = pl.tap_dy[e];
+            if (pl.tap_dy[e] > dmax) dmax = pl.tap_dy[e];
+          }
+        if (dmin > dmax) continue;
+        const int base = s.n_slabs;
+        const int cnt = dmax - dmin + R;
+        if (base + cnt > kRowsMaxSlabs) return false;
+        for (int i = 0; i < cnt; ++i) {
+          s.slab_map[base + i] = (int8_t)m;
+          s.slab_dy[base + i] = (int8_t)(dmin + i);
+          s.slab_chunk[base + i] = (int8_t)c;
+          last_use[base + i] = -1;
+        }
+        s.n_slabs += cnt;
+        for (int dy = dmin; dy <= dmax; ++dy)
+          for (int pl_ = 0; pl_ < P; ++pl_)
+            for (int t = 0; t < pl.taps; ++t) {
+              const int e = (pg * P + pl_) * pl.taps + t;
+              if (pl.tap_map[e] != m || pl.tap_dy[e] != dy) continue;
+              if (s.n_steps >= kRowsMaxSteps) return false;
+              RowsStep& st = s.steps[s.n_steps];
+              st.bcol = (int16_t)(t * chunks + c);
+              st.phase_l = (int8_t)pl_;
+              st.slab0 = (int8_t)(base + dy - dmin);
+              st.dxi = (int8_t)(pl.tap_dx[e] + 1);
+              st.acc0 = (int8_t)pl_;
+              st.rel = 0;
+              st.pad = 0;
+              for (int r = 0; r < R; ++r) last_use[st.slab0 + r] = s.n_steps;
+              ++s.n_steps;
+            }
+      }
+    }
+    // FIFO release counts; the live span (needed slab - released slabs) must fit the ring
+    int released = 0;
+    for (int i = 0; i + 1 < s.n_slabs; ++i)
+      if (last_use[i] > last_use[i + 1]) return false;
+    for (int j = 0; j < s.n_steps; ++j) {
+      const int need = s.steps[j].slab0 + R - 1;
+      if (need + 1 - released > ring) return false;
+      int rel = 0;
+      while (released + rel < s.n_slabs && last_use[released + rel] == j) ++rel;
+      s.steps[j].rel = (int8_t)rel;
+      released += rel;
+    }
+    if (released != s.n_slabs) return false;
+  }
+  return true;
+}
+
+// Builds the geometry and one schedule per phase group: the largest R in {4, 2, 1} whose accumulators fit 256 TMEM
+// columns (x2 buffers) and whose schedule fits the tables and the slab ring.  `ring` = slab stages the kernel owns.
+// Returns false when the role does not fit (the caller falls back to the per-tap kernel).
+inline bool build_rows_sched(const ConvPlan& pl, int block_n, int ring, RowsGeom* g, RowsSched* sched /*[2]*/) {
+  if (pl.kind == B2G_CONV_K1S1) return false;
+  if (pl.bw != 128 || pl.bh != 1 || pl.bn != 1) return false;
+  if (pl.Cin % 64 || block_n > 256) return false;
+  int P = pl.kind == B2G_CONVT_K4S2 ? 2 : 1;
+  if (P * block_n > 256) P = 1;
+  int R = 256 / (P * block_n);
+  if (R > 4) R = 4;
+  while (R > 1 && R > pl.Hg) R /= 2;
+  for (; R >= 1; R /= 2)
+    if (try_rows_sched(pl, ring, R, P, g, sched)) return true;
+  return false;
+}
+
+// Launches the row-slab kernel when the role fits it; *handled tells the caller whether it did.
+int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream, bool* handled);
+
+}  // namespace b2g

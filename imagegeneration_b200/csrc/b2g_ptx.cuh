@@ -16,6 +16,20 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One lane of a fully converged warp gets 1, the others 0.  Issue loops run warp-wide on uniform values and guard
+// only the tcgen05 / TMA instruction itself with this predicate: inside `if (lane == 0)` the compiler cannot prove
+// that operands are warp-uniform and wraps every UTCHMMA / UTCBAR in an ELECT..BRA.U.ANY waterfall loop, which
+// makes the single issuing thread (not the tensor pipe) the bottleneck of the N <= 128 tiles.
+__device__ __forceinline__ uint32_t elect_one_sync() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred;
+}
+
 // ---------------------------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------------------------
@@ -147,6 +161,13 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_
   d |= static_cast<uint64_t>(1) << 46;
   d |= static_cast<uint64_t>(2) << 61;
   return d;
+}
+// Constant upper part of a K-major SW128 descriptor (LBO = 16, SBO = 1024, version 1): OR in (saddr & 0x3FFFF) >> 4.
+// Advancing K by 16 bf16 (32 bytes) inside the 128-byte swizzle row adds 2 to the descriptor.
+constexpr uint64_t kDescKMajorSW128 =
+    (static_cast<uint64_t>(16 >> 4) << 16) | (static_cast<uint64_t>(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+__device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t saddr) {
+  return kDescKMajorSW128 | static_cast<uint64_t>((saddr & 0x3FFFFu) >> 4);
 }
 // Instruction descriptor for kind::f16 / kind::tf32 with fp32 accumulation.
 //   [4,6) D format (1 = f32)  [7,10) A format  [10,13) B format (1 = bf16, 2 = tf32)

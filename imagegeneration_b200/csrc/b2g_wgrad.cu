@@ -102,7 +102,8 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {  // whole warp converged on uniform values; one elected lane issues the TMA loads
+      const uint32_t leader = elect_one_sync();
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
@@ -119,6 +120,7 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* m_dst = smem + stage * Cfg::kStageBytes;
           uint8_t* n_dst = m_dst + Cfg::kMBytes;
+          if (leader) {
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           if (p.m_is_shifted) {
 #pragma unroll
@@ -135,39 +137,45 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
             for (int g = 0; g < BLOCK_N / 64; ++g)
               tma_load_4d(n_dst + g * Cfg::kBoxBytes, sm, &full_bar[stage], n_c0 + g * 64, w0 + dx, h0 + dy, n0);
           }
+          }
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, BLOCK_N);
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
-        const WgradItem wi = decode_item(p, item);
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(&tempty_bar[as], aphase ^ 1);
+    // whole warp converged on uniform values; one elected lane issues (see elect_one_sync in b2g_ptx.cuh)
+    const uint32_t leader = elect_one_sync();
+    constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, BLOCK_N);
+    const uint32_t smem_base = smem_u32(smem);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
+      const WgradItem wi = decode_item(p, item);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(&tempty_bar[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+      const int k_steps = wi.p_end - wi.p_begin;
+      for (int ks = 0; ks < k_steps; ++ks) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
-        const int k_steps = wi.p_end - wi.p_begin;
-        for (int ks = 0; ks < k_steps; ++ks) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t m_addr = smem_u32(smem + stage * Cfg::kStageBytes);
-          const uint32_t n_addr = m_addr + Cfg::kMBytes;
+        const uint32_t m_addr = smem_base + stage * Cfg::kStageBytes;
+        const uint64_t mdesc = umma_smem_desc(m_addr, Cfg::kBoxBytes, 1024);
+        const uint64_t ndesc = umma_smem_desc(m_addr + Cfg::kMBytes, Cfg::kBoxBytes, 1024);
+        if (leader) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {  // 16 pixels per MMA = two 8-line swizzle groups = 2048 bytes
-            umma_f16(d_tmem, umma_smem_desc(m_addr + k * 2048, Cfg::kBoxBytes, 1024),
-                     umma_smem_desc(n_addr + k * 2048, Cfg::kBoxBytes, 1024), idesc, (ks | k) != 0);
-          }
+          for (int k = 0; k < 4; ++k)  // 16 pixels per MMA = two 8-line swizzle groups = 2048 bytes (>> 4 = 128)
+            umma_f16(d_tmem, mdesc + 128 * k, ndesc + 128 * k, idesc, (ks | k) != 0);
           umma_commit(&empty_bar[stage]);
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);
+        __syncwarp();
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
+      if (leader) umma_commit(&tfull_bar[as]);
+      __syncwarp();
     }
   } else {
     const int q = warp & 3;
@@ -329,7 +337,8 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_taps_kernel(const __gr
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
+      const uint32_t leader = elect_one_sync();
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
@@ -345,6 +354,7 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_taps_kernel(const __gr
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* m_dst = smem + stage * Cfg::kStageBytes;
           uint8_t* n_dst = m_dst + Cfg::kMBytes;
+          if (leader) {
           mbar_expect_tx(&full_bar[stage], bytes);
           tma_load_4d(m_dst, &p.umap, &full_bar[stage], m_c0, w0, h0, n0);
           tma_load_4d(m_dst + Cfg::kBoxBytes, &p.umap, &full_bar[stage], m_c0 + 64, w0, h0, n0);
@@ -356,39 +366,43 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_taps_kernel(const __gr
               tma_load_4d(n_dst + (t * boxes_per_tap + g) * Cfg::kBoxBytes, sm, &full_bar[stage], a_c0 + g * 64,
                           w0 + dx, h0 + dy, n0);
           }
+          }
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
-        const WgradTapsItem wi = decode_taps_item(p, item);
-        const uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, wi.nt * p.cc);
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(&tempty_bar[as], aphase ^ 1);
+    const uint32_t leader = elect_one_sync();
+    const uint32_t smem_base = smem_u32(smem);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++it) {
+      const WgradTapsItem wi = decode_taps_item(p, item);
+      const uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, wi.nt * p.cc);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(&tempty_bar[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * 256;
+      const int k_steps = wi.p_end - wi.p_begin;
+      for (int ks = 0; ks < k_steps; ++ks) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * 256;
-        const int k_steps = wi.p_end - wi.p_begin;
-        for (int ks = 0; ks < k_steps; ++ks) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t m_addr = smem_u32(smem + stage * Cfg::kStageBytes);
-          const uint32_t n_addr = m_addr + Cfg::kMBytes;
+        const uint32_t m_addr = smem_base + stage * Cfg::kStageBytes;
+        const uint64_t mdesc = umma_smem_desc(m_addr, Cfg::kBoxBytes, 1024);
+        const uint64_t ndesc = umma_smem_desc(m_addr + Cfg::kMBytes, Cfg::kBoxBytes, 1024);
+        if (leader) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            umma_f16(d_tmem, umma_smem_desc(m_addr + k * 2048, Cfg::kBoxBytes, 1024),
-                     umma_smem_desc(n_addr + k * 2048, Cfg::kBoxBytes, 1024), idesc, (ks | k) != 0);
-          }
+          for (int k = 0; k < 4; ++k) umma_f16(d_tmem, mdesc + 128 * k, ndesc + 128 * k, idesc, (ks | k) != 0);
           umma_commit(&empty_bar[stage]);
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);
+        __syncwarp();
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
+      if (leader) umma_commit(&tfull_bar[as]);
+      __syncwarp();
     }
   } else {
     const int q = warp & 3;

@@ -120,6 +120,8 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_spectral_norm_multi": [_I, _P, _P, _P, _P, _P, _P, _P, _P],
     # W, G, u, v_raw, scal, dot_scratch, K, C, stream
     "b2g_sn_grad_finalize": [_P, _P, _P, _P, _P, _P, _I, _I, _P],
+    # kind, N, Hin, Win, Cin, block_n, phase_group, out, out_len   (host-only)
+    "b2g_conv_rows_plan_query": [_I, _I, _I, _I, _I, _I, _I, C.POINTER(C.c_int), _I],
 }
 
 

@@ -188,7 +188,13 @@ int b2g_sn_grad_finalize(const float* W, float* G, const float* u, const float* 
  * conv_plan_query: tiling + tap tables of a conv role -> out[0..15] = {phases, taps, Hg, Wg, bw, bh, bn, tiles_w,
  *   tiles_h, tiles_n, m_tiles, Hout, Wout, out_stride, n_input_maps, 0}; out[16+i] = input map of tap entry i,
  *   out[32+i] = dy, out[48+i] = dx (entry = phase*taps + tap); out[64+p] / out[68+p] = output phase offsets.
- * pack_source_index: flat index into the fp32 Keras kernel that packed element i is taken from (-1 = padding). */
+ * pack_source_index: flat index into the fp32 Keras kernel that packed element i is taken from (-1 = padding).
+ * conv_rows_plan_query: the row-slab schedule (csrc/b2g_conv_rows.cuh) b2g_conv_igemm uses for layers >= 128 pixels
+ *   wide with Cout <= 128, for phase group pg: out[0..7] = {handled, R, P, PG, n_acc, row_blocks, n_slabs, n_steps};
+ *   out[8+3i..] = slab i {input map, dy, channel chunk}; out[80+6j..] = step j {k-block, local phase, slab of row 0,
+ *   dx+1, accumulator of row 0, slabs released after the step}.  out_len >= 464.
+ */
+int b2g_conv_rows_plan_query(int kind, int N, int Hin, int Win, int Cin, int block_n, int pg, int* out, int out_len);
 int b2g_conv_plan_query(int kind, int N, int Hin, int Win, int tile_pixels, int* out, int out_len);
 long b2g_pack_source_index(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad, long i);
 

@@ -125,3 +125,103 @@ def test_tiles_cover_the_grid(kind, h, w, n, tile):
     assert p["tiles_n"] * p["bn"] >= n and (p["tiles_n"] - 1) * p["bn"] < n
     assert p["m_tiles"] == p["tiles_w"] * p["tiles_h"] * p["tiles_n"]
     assert max(p["bw"], p["bh"], p["bn"]) <= 256                      # TMA box limit
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# row-slab schedule (csrc/b2g_conv_rows.cuh): slabs with a 1-pixel halo, dx taps as shifted views, R rows x P phases
+# ---------------------------------------------------------------------------------------------------------------
+def _rows_plan(kind, n, h, w, cin, block_n, pg):
+    from imagegeneration_b200 import lib
+    out = (C.c_int * 464)()
+    rc = lib.load().b2g_conv_rows_plan_query(kind, n, h, w, cin, block_n, pg, out, 464)
+    assert rc == 0, lib.load().b2g_last_error()
+    v = list(out)
+    d = dict(zip(["handled", "R", "P", "PG", "n_acc", "row_blocks", "n_slabs", "n_steps"], v[:8]))
+    d["slabs"] = [tuple(v[8 + 3 * i:11 + 3 * i]) for i in range(d["n_slabs"])]
+    d["steps"] = [tuple(v[80 + 6 * j:86 + 6 * j]) for j in range(d["n_steps"])]
+    return d
+
+
+def _emulate_rows(kind, x, packed, plan, block_n, ring):
+    """Walks the schedule exactly like the kernel: slabs are 130-pixel rows (zero outside the image), MMA row m of
+    tap dx reads slab pixel m + dxi, the slab ring is FIFO with `ring` stages."""
+    n, h, w, cin = x.shape
+    cn = packed.shape[1]
+    assert cn <= block_n
+    out = np.full((n, plan["Hout"], plan["Wout"], cn), np.nan)
+    hg, wg = plan["Hg"], plan["Wg"]
+    pg0 = _rows_plan(kind, n, h, w, cin, block_n, 0)
+    assert pg0["handled"] == 1
+    for pg in range(pg0["PG"]):
+        rp = _rows_plan(kind, n, h, w, cin, block_n, pg)
+        R, P = rp["R"], rp["P"]
+        assert rp["row_blocks"] * R >= hg
+        for img in range(n):
+            for yb in range(rp["row_blocks"]):
+                for tw in range(wg // 128):
+                    y0, w0 = yb * R, tw * 128
+                    slabs = []
+                    for (m, dy, ch) in rp["slabs"]:
+                        src = x[img, (m // 2)::2, (m % 2)::2, :] if plan["n_amaps"] == 4 else x[img]
+                        sl = np.zeros((130, 64))
+                        yy = y0 + dy
+                        if 0 <= yy < src.shape[0]:
+                            xs = np.arange(130) + w0 - 1
+                            ok = (xs >= 0) & (xs < src.shape[1])
+                            sl[ok] = src[yy, xs[ok], ch * 64:(ch + 1) * 64]
+                        slabs.append(sl)
+                    acc = np.zeros((R * P, 128, cn))
+                    released = 0
+                    for (bcol, phl, slab0, dxi, acc0, rel) in rp["steps"]:
+                        bt = packed[pg * P + phl][:, bcol * 64:(bcol + 1) * 64]
+                        for r in range(R):
+                            s = slab0 + r
+                            assert released <= s < released + ring          # still resident in the ring
+                            acc[acc0 + r * P] += slabs[s][dxi:dxi + 128] @ bt.T
+                        released += rel
+                    assert released == len(slabs)
+                    for a in range(R * P):
+                        r, ph = a // P, pg * P + a % P
+                        if y0 + r < hg:
+                            oy = (y0 + r) * plan["os"] + plan["ph_y"][ph]
+                            ox = (w0 + np.arange(128)) * plan["os"] + plan["ph_x"][ph]
+                            out[img, oy, ox, :] = acc[a]
+    return out
+
+
+@pytest.mark.parametrize("kind,h,w,cin,cout,bn", [(K3S1, 5, 128, 128, 7, 128), (K3S1, 4, 256, 64, 3, 32),
+                                                  (K3S1, 3, 128, 64, 9, 64), (K4S2, 6, 256, 64, 5, 128),
+                                                  (CONVT, 3, 128, 128, 6, 64), (CONVT, 4, 128, 64, 5, 128)])
+def test_row_slab_schedule_matches_the_tap_plan(kind, h, w, cin, cout, bn):
+    n = 2
+    ks = 3 if kind == K3S1 else 4
+    x = _rand((n, h, w, cin), 11)
+    if kind == CONVT:
+        wt = _rand((ks, ks, cout, cin), 12)
+        packed = _pack(CONVT, wt, False, False)
+    else:
+        wt = _rand((ks, ks, cin, cout), 12)
+        packed = _pack(kind, wt, True, False)
+    plan = _plan(kind, n, h, w)
+    ref = _emulate(kind, x, packed, plan)
+    got = _emulate_rows(kind, x, packed, plan, bn, ring=7 if bn == 128 else 8)
+    assert not np.isnan(got).any()
+    assert np.allclose(got, ref, atol=1e-9)
+
+
+def test_row_slab_schedule_geometry_of_the_model_layers():
+    # D.conv3 (k3s1 128->128 @72x128): 2 rows per super-tile, 4 slabs per channel chunk, 18 weight tiles
+    p = _rows_plan(K3S1, 64, 72, 128, 128, 128, 0)
+    assert (p["handled"], p["R"], p["P"], p["PG"], p["n_slabs"], p["n_steps"]) == (1, 2, 1, 1, 8, 18)
+    # G.convT3 / D.conv2 dgrad (convT 128->64 @72x128): 2 rows x 2 phases, phase group = output row parity
+    p = _rows_plan(CONVT, 64, 72, 128, 128, 64, 1)
+    assert (p["handled"], p["R"], p["P"], p["PG"], p["n_slabs"], p["n_steps"]) == (1, 2, 2, 2, 6, 16)
+    # G.convT4 (k3s1 64->3, N tile 32): 4 rows per super-tile share 6 slabs
+    p = _rows_plan(K3S1, 64, 144, 256, 64, 32, 0)
+    assert (p["handled"], p["R"], p["n_slabs"], p["n_steps"]) == (1, 4, 6, 9)
+    # D.conv2 forward (k4s2 64->128): 4 parity maps x 3 slabs
+    p = _rows_plan(K4S2, 64, 144, 256, 64, 128, 0)
+    assert (p["handled"], p["R"], p["n_slabs"], p["n_steps"]) == (1, 2, 12, 16)
+    # narrow layers stay on the per-tap kernel
+    assert _rows_plan(K3S1, 64, 36, 64, 256, 128, 0)["handled"] == 0
+    assert _rows_plan(K1S1, 64, 144, 256, 64, 64, 0)["handled"] == 0
