@@ -33,7 +33,10 @@ struct ConvCfg {
   static constexpr int kBBytes = BLOCK_N * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8);
-  static constexpr int kTmemCols = 2 * BLOCK_N;  // 64 / 128 / 256 / 512: powers of two >= 32
+  // accumulator buffers in TMEM: 2 for the wide tiles; 4 for N <= 64, whose tiles have only 1-2 column chunks, so that
+  // the 4 epilogue groups work on 2-4 consecutive tiles at once (a K1S1 tile is one MMA step: epilogue-latency bound)
+  static constexpr int kAccBufs = BLOCK_N <= 64 ? 4 : 2;
+  static constexpr int kTmemCols = kAccBufs * BLOCK_N;  // 128 / 256 / 256 / 512: powers of two >= 32
   static constexpr int kBarBytes = 256;
   static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // +1024: manual alignment
 };
@@ -41,7 +44,7 @@ struct ConvCfg {
 // epilogue warp groups: each group is 4 warps (one per TMEM lane quarter); groups interleave over the 32-column
 // chunks of a tile so that several chunks are in flight (the epilogue is latency-bound with one warp per SMSP)
 template <int BLOCK_N>
-constexpr int epi_groups() { return BLOCK_N >= 128 ? 4 : BLOCK_N / 32; }
+constexpr int epi_groups() { return 4; }
 template <int BLOCK_N>
 constexpr int conv_threads() { return 64 + 128 * epi_groups<BLOCK_N>(); }
 
@@ -66,14 +69,16 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     conv_igemm_kernel(const __grid_constant__ ConvKernelParams p) {
   using Cfg = ConvCfg<BLOCK_N>;
   constexpr int kEpiGroups = epi_groups<BLOCK_N>();
+  constexpr int kChunks = BLOCK_N / 32;
+  constexpr int kGroupsPerTile = kChunks < kEpiGroups ? kChunks : kEpiGroups;  // groups that work on one tile
   __shared__ float sbias[512];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
-  uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* tempty_bar = tfull_bar + Cfg::kAccBufs;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + Cfg::kAccBufs);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -86,9 +91,9 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < Cfg::kAccBufs; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], 4 * kEpiGroups);
+      mbar_init(&tempty_bar[a], 4 * kGroupsPerTile);
     }
     fence_barrier_init();
   }
@@ -140,8 +145,8 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     uint32_t phase = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
+      const int as = it % Cfg::kAccBufs;
+      const uint32_t aphase = (it / Cfg::kAccBufs) & 1;
       mbar_wait(&tempty_bar[as], aphase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BLOCK_N;
@@ -172,8 +177,15 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     const int nl = row / (pl.bw * pl.bh);
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
+      const int as = it % Cfg::kAccBufs;
+      const uint32_t aphase = (it / Cfg::kAccBufs) & 1;
+      // wide tiles: every group takes the chunks c = grp (mod 4); narrow tiles (1-2 chunks): chunk c of tile `it`
+      // belongs to group (it * kChunks + c) mod 4, so consecutive tiles are drained by different groups
+      int c_first = grp;
+      if (kChunks < kEpiGroups) {
+        c_first = (grp - it * kChunks) & (kEpiGroups - 1);
+        if (c_first >= kChunks) continue;
+      }
       const TileCoord tc = decode_tile(pl, p.n_tiles, tile);
       const int gw = tc.tw * pl.bw + wl, gh = tc.th * pl.bh + hl, gn = tc.tn * pl.bn + nl;
       const bool valid = (gh < pl.Hg) && (gn < pl.N);
@@ -183,7 +195,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = grp; c < BLOCK_N / 32; c += kEpiGroups) {
+      for (int c = c_first; c < kChunks; c += kEpiGroups) {
         uint32_t r[32];
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);

@@ -29,6 +29,7 @@ struct alignas(64) RowsKernelParams {
   int n_tiles;       // Cout / BLOCK_N
   int brows;         // rows of the packed weight matrix per phase
   int total_tiles;   // PG * n_tiles * N * row_blocks * tiles_w
+  int tiles_per_pg;  // n_tiles * N * row_blocks * tiles_w
 };
 
 template <int BLOCK_N>
@@ -59,6 +60,35 @@ __device__ __forceinline__ RowsTile decode_rows_tile(const RowsKernelParams& p, 
   t.n_tile = tile % p.n_tiles;
   t.pg = tile / p.n_tiles;
   return t;
+}
+
+// Division-free tile iterator for the single-lane issue warps: integer division is a vector-ALU sequence, and
+// anything derived from it leaves the uniform datapath (R2UR before every TMA / MMA operand).  The mixed-radix
+// coordinate (tw, yb, n, n_tile, pg) of tile blockIdx.x is found by repeated subtraction once, then advanced by the
+// digits of gridDim.x with carries.
+struct RowsCoord {
+  int tw, yb, n, nt, pg;
+};
+__device__ __forceinline__ void rows_coord_normalise(const RowsKernelParams& p, RowsCoord& c) {
+  while (c.tw >= p.plan.tiles_w) { c.tw -= p.plan.tiles_w; ++c.yb; }
+  while (c.yb >= p.geom.row_blocks) { c.yb -= p.geom.row_blocks; ++c.n; }
+  while (c.n >= p.plan.N) { c.n -= p.plan.N; ++c.nt; }
+  while (c.nt >= p.n_tiles) { c.nt -= p.n_tiles; ++c.pg; }
+}
+__device__ __forceinline__ void rows_coord_advance(const RowsKernelParams& p, RowsCoord& c, const RowsCoord& d) {
+  c.tw += d.tw;
+  int cy = 0;
+  if (c.tw >= p.plan.tiles_w) { c.tw -= p.plan.tiles_w; cy = 1; }
+  c.yb += d.yb + cy;
+  cy = 0;
+  if (c.yb >= p.geom.row_blocks) { c.yb -= p.geom.row_blocks; cy = 1; }
+  c.n += d.n + cy;
+  cy = 0;
+  if (c.n >= p.plan.N) { c.n -= p.plan.N; cy = 1; }
+  c.nt += d.nt + cy;
+  cy = 0;
+  if (c.nt >= p.n_tiles) { c.nt -= p.n_tiles; cy = 1; }
+  c.pg += d.pg + cy;
 }
 
 template <int BLOCK_N>
@@ -115,54 +145,60 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N>::kThreads, 1)
   if (warp == 0) {
     // ------------------------------------------------ slab producer (whole warp converged; one elected lane issues)
     const uint32_t leader = elect_one_sync();
+    RowsCoord c = {static_cast<int>(blockIdx.x), 0, 0, 0, 0}, d = {static_cast<int>(gridDim.x), 0, 0, 0, 0};
+    rows_coord_normalise(p, c);
+    rows_coord_normalise(p, d);
     uint32_t stage = 0, par = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      const RowsTile t = decode_rows_tile(p, tile);
-      const RowsSched& sc = p.sched[t.pg];
+      const RowsSched& sc = p.sched[c.pg];
       const int n_slabs = sc.n_slabs;
+      const int w0 = c.tw * 128 - 1, y0 = c.yb * R;
       for (int i = 0; i < n_slabs; ++i) {
         const int amap = sc.slab_map[i], chunk = sc.slab_chunk[i], dy = sc.slab_dy[i];
         mbar_wait(&sempty[stage], par ^ 1);
         if (leader) {
           mbar_expect_tx(&sfull[stage], Cfg::kSlabTx);
-          tma_load_4d(smem + stage * Cfg::kSlabBytes, &p.amap[amap], &sfull[stage], chunk * 64, t.w0 - 1, t.y0 + dy,
-                      t.n);
+          tma_load_4d(smem + stage * Cfg::kSlabBytes, &p.amap[amap], &sfull[stage], chunk * 64, w0, y0 + dy, c.n);
         }
         __syncwarp();
         if (++stage == Cfg::kSlabs) { stage = 0; par ^= 1; }
       }
+      rows_coord_advance(p, c, d);
     }
   } else if (warp == 2) {
     // ------------------------------------------------ weight-tile producer
     const uint32_t leader = elect_one_sync();
+    RowsCoord c = {static_cast<int>(blockIdx.x), 0, 0, 0, 0}, d = {static_cast<int>(gridDim.x), 0, 0, 0, 0};
+    rows_coord_normalise(p, c);
+    rows_coord_normalise(p, d);
     uint32_t stage = 0, par = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      const RowsTile t = decode_rows_tile(p, tile);
-      const RowsSched& sc = p.sched[t.pg];
+      const RowsSched& sc = p.sched[c.pg];
       const int n_steps = sc.n_steps;
-      const int brow0 = t.pg * P * p.brows + t.n_tile * BLOCK_N;
+      const int brow0 = c.pg * P * p.brows + c.nt * BLOCK_N;
       for (int j = 0; j < n_steps; ++j) {
-        const RowsStep st = sc.steps[j];
+        const int bcol = sc.steps[j].bcol, phl = sc.steps[j].phase_l;
         mbar_wait(&bempty[stage], par ^ 1);
         if (leader) {
           mbar_expect_tx(&bfull[stage], Cfg::kBBytes);
-          tma_load_2d(bsm + stage * Cfg::kBBytes, &p.bmap, &bfull[stage], st.bcol * 64, brow0 + st.phase_l * p.brows);
+          tma_load_2d(bsm + stage * Cfg::kBBytes, &p.bmap, &bfull[stage], bcol * 64, brow0 + phl * p.brows);
         }
         __syncwarp();
         if (++stage == Cfg::kBStages) { stage = 0; par ^= 1; }
       }
+      rows_coord_advance(p, c, d);
     }
   } else if (warp == 1) {
     // ------------------------------------------------ MMA issuer (whole warp converged; one elected lane issues)
     const uint32_t leader = elect_one_sync();
     constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
-    const uint32_t slab_base = smem_u32(smem), b_base = smem_u32(bsm);
+    constexpr uint32_t kSlabD = Cfg::kSlabBytes >> 4, kBD = Cfg::kBBytes >> 4;  // stage strides in descriptor units
+    const uint32_t slab_lo0 = (smem_u32(smem) & 0x3FFFFu) >> 4, b_lo0 = (smem_u32(bsm) & 0x3FFFFu) >> 4;
     uint32_t s_head = 0, s_head_par = 0;  // ring position / parity of slab 0 of the current tile
     uint32_t b_stage = 0, b_par = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const RowsTile t = decode_rows_tile(p, tile);
-      const RowsSched& sc = p.sched[t.pg];
+      const RowsSched& sc = p.sched[tile >= p.tiles_per_pg ? 1 : 0];
       const int as = it & 1;
       mbar_wait(&tempty[as], ((it >> 1) & 1) ^ 1);
       tc_fence_after();
@@ -173,41 +209,39 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N>::kThreads, 1)
       uint32_t r_stage = s_head;                      // next slab to release
       const int n_steps = sc.n_steps;
       for (int j = 0; j < n_steps; ++j) {
-        const RowsStep st = sc.steps[j];
+        const int slab0 = sc.steps[j].slab0, dxi = sc.steps[j].dxi, acc0 = sc.steps[j].acc0, rel = sc.steps[j].rel;
         mbar_wait(&bfull[b_stage], b_par);
-        for (; waited <= st.slab0 + R - 1; ++waited) {
+        for (; waited < slab0 + R; ++waited) {
           mbar_wait(&sfull[w_stage], w_par);
           if (++w_stage == Cfg::kSlabs) { w_stage = 0; w_par ^= 1; }
         }
         tc_fence_after();
-        const uint64_t bdesc = umma_desc_kmajor(b_base + b_stage * Cfg::kBBytes);
-        uint32_t sstage = s_head + st.slab0;
+        const uint32_t b_lo = b_lo0 + b_stage * kBD;
+        uint32_t sstage = s_head + slab0;  // slab0 < 3 * kSlabs (kRowsMaxSlabs = 24, ring >= 7)
+        if (sstage >= 2 * Cfg::kSlabs) sstage -= 2 * Cfg::kSlabs;
         if (sstage >= Cfg::kSlabs) sstage -= Cfg::kSlabs;
         if (sstage >= Cfg::kSlabs) sstage -= Cfg::kSlabs;
-        if (sstage >= Cfg::kSlabs) sstage -= Cfg::kSlabs;
+#pragma unroll 1
         for (int r = 0; r < R; ++r) {
-          const uint64_t adesc = umma_desc_kmajor(slab_base + sstage * Cfg::kSlabBytes + st.dxi * 128);
-          const int acc = st.acc0 + r * P;
+          const uint32_t a_lo = slab_lo0 + sstage * kSlabD + dxi * 8;
+          const int acc = acc0 + r * P;
           const uint32_t d_tmem = d_base + acc * BLOCK_N;
           const uint32_t have = (written >> acc) & 1;
-          if (leader) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, have | (k != 0));
-          }
+          if (leader) umma_f16_k64(d_tmem, a_lo, b_lo, idesc, have);
           __syncwarp();
           written |= 1u << acc;
           if (++sstage == Cfg::kSlabs) sstage = 0;
         }
         if (leader) {
           umma_commit(&bempty[b_stage]);
-          for (int q = 0; q < st.rel; ++q) {
+          for (int q = 0; q < rel; ++q) {
             uint32_t rs = r_stage + q;
             if (rs >= Cfg::kSlabs) rs -= Cfg::kSlabs;
             umma_commit(&sempty[rs]);
           }
         }
         __syncwarp();
-        r_stage += st.rel;
+        r_stage += rel;
         if (r_stage >= Cfg::kSlabs) r_stage -= Cfg::kSlabs;
         if (++b_stage == Cfg::kBStages) { b_stage = 0; b_par ^= 1; }
       }
@@ -291,7 +325,8 @@ int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   fill_epi_params(a, &kp.e);
   kp.brows = a->out_f32 ? a->cout_store : a->Cout;
   kp.n_tiles = a->Cout / block_n;
-  kp.total_tiles = kp.geom.PG * kp.n_tiles * pl.N * kp.geom.row_blocks * pl.tiles_w;
+  kp.tiles_per_pg = kp.n_tiles * pl.N * kp.geom.row_blocks * pl.tiles_w;
+  kp.total_tiles = kp.geom.PG * kp.tiles_per_pg;
 
   const size_t es = 2;
   const char* base = static_cast<const char*>(a->in);

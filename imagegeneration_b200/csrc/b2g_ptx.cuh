@@ -123,6 +123,26 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Four K=16 MMAs over one 64-element (128-byte) K block of K-major SW128 operands: descriptors are built inside the
+// asm block from their low words (start address >> 4, +2 per K=16 step) and the constant high word, so the issuing
+// warp only has to move three 32-bit values into uniform registers per call.
+__device__ __forceinline__ void umma_f16_k64(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, t;\n\t.reg .b64 da, db;\n\t.reg .b32 al, bl;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.b32 t, 0, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t"
+      "add.u32 al, %1, 2;\n\tadd.u32 bl, %2, 2;\n\tmov.b64 da, {al, %5};\n\tmov.b64 db, {bl, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, t;\n\t"
+      "add.u32 al, %1, 4;\n\tadd.u32 bl, %2, 4;\n\tmov.b64 da, {al, %5};\n\tmov.b64 db, {bl, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, t;\n\t"
+      "add.u32 al, %1, 6;\n\tadd.u32 bl, %2, 6;\n\tmov.b64 da, {al, %5};\n\tmov.b64 db, {bl, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, t;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(0x40004040u)
+      : "memory");
+}
 // mbarrier arrives once all previously issued tcgen05.mma of this thread have completed.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
