@@ -314,46 +314,54 @@ extern "C" int b2g_wgrad3x3_c3_c64(const float* t3, const void* t64, float* dw, 
 // One thread per (pixel, 8-channel group); groups 4..7 are zero padding.
 // ---------------------------------------------------------------------------------------------------------
 namespace b2g {
+// One block per image row (n, y): the three input rows y-1..y+1 are staged in shared memory with a zero halo, then
+// every thread emits 16-byte groups of 8 output channels (coalesced stores; the 27 taps*channels of a pixel are three
+// contiguous runs of 9 floats in the staged rows).  HBM-bound: 12 B read + 128 B written per pixel.
+constexpr int kIm2colMaxW = 1024;
 __global__ void __launch_bounds__(256) im2col27_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
                                                        int N, int H, int W) {
-  const long total = (long)N * H * W * 8;
-  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += gridDim.x * 256L) {
-    const int g = (int)(i & 7);
-    const long pix = i >> 3;
-    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  extern __shared__ float rows[];  // [3][(W + 2) * 3]
+  const int row = blockIdx.x;      // n * H + y
+  const int n = row / H, y = row - n * H;
+  const int rs = (W + 2) * 3;
+  for (int i = threadIdx.x; i < 3 * rs; i += 256) {
+    const int ky = i / rs, j = i - ky * rs;  // j = (x + 1) * 3 + c
+    const int yy = y + ky - 1;
+    float v = 0.f;
+    if (yy >= 0 && yy < H && j >= 3 && j < rs - 3) v = __ldg(in + ((size_t)(n * H + yy) * W) * 3 + (j - 3));
+    rows[i] = v;
+  }
+  __syncthreads();
+  uint4* orow = reinterpret_cast<uint4*>(out) + (size_t)row * W * 8;
+  for (int idx = threadIdx.x; idx < W * 8; idx += 256) {
+    const int x = idx >> 3, g = idx & 7;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
     if (g < 4) {
-      const int x = (int)(pix % W);
-      const int y = (int)((pix / W) % H);
-      const long nb = (pix / ((long)W * H)) * H * W;
+      float v[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const int col = g * 8 + k;
-        if (col < 27) {
-          const int tap = col / 3, c3 = col - tap * 3;
-          const int xx = x + tap % 3 - 1, yy = y + tap / 3 - 1;
-          if (xx >= 0 && xx < W && yy >= 0 && yy < H) v[k] = __ldg(in + (nb + (long)yy * W + xx) * 3 + c3);
-        } else if (col == 27) {
-          v[k] = 1.f;
-        }
+        const int col = g * 8 + k;         // < 32
+        const int ky = (col * 57) >> 9;    // col / 9 for col < 32
+        const int ky_c = ky > 2 ? 2 : ky;
+        const float t = rows[ky_c * rs + x * 3 + (col - ky_c * 9)];
+        v[k] = col < 27 ? t : (col == 27 ? 1.f : 0.f);
       }
+      o.x = pack_bf16x2(v[0], v[1]);
+      o.y = pack_bf16x2(v[2], v[3]);
+      o.z = pack_bf16x2(v[4], v[5]);
+      o.w = pack_bf16x2(v[6], v[7]);
     }
-    uint4 o;
-    o.x = pack_bf16x2(v[0], v[1]);
-    o.y = pack_bf16x2(v[2], v[3]);
-    o.z = pack_bf16x2(v[4], v[5]);
-    o.w = pack_bf16x2(v[6], v[7]);
-    reinterpret_cast<uint4*>(out)[i] = o;
+    orow[idx] = o;
   }
 }
 }  // namespace b2g
 
 extern "C" int b2g_im2col27(const float* in, void* out, int N, int H, int W, b2g_stream_t stream_) {
   if (!in || !out) return fail(B2G_E_INVALID_ARG, "b2g_im2col27: null pointer");
-  const long total = (long)N * H * W * 8;
-  long blocks = (total + 255) / 256;
-  const long cap = (long)num_sms() * 32;
-  if (blocks > cap) blocks = cap;
-  b2g::im2col27_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+  if (N <= 0 || H <= 0 || W <= 0 || W > b2g::kIm2colMaxW)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_im2col27: bad shape N=%d H=%d W=%d (W <= %d)", N, H, W, b2g::kIm2colMaxW);
+  const size_t smem = (size_t)3 * (W + 2) * 3 * sizeof(float);
+  b2g::im2col27_kernel<<<(unsigned)(N * H), 256, smem, static_cast<cudaStream_t>(stream_)>>>(
       in, static_cast<__nv_bfloat16*>(out), N, H, W);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
