@@ -48,22 +48,6 @@ constexpr int epi_groups() { return 4; }
 template <int BLOCK_N>
 constexpr int conv_threads() { return 64 + 128 * epi_groups<BLOCK_N>(); }
 
-struct TileCoord {
-  int phase, n_tile, tn, th, tw;
-};
-__device__ __forceinline__ TileCoord decode_tile(const ConvPlan& pl, int n_tiles, int tile) {
-  TileCoord c;
-  c.n_tile = tile % n_tiles;
-  int rest = tile / n_tiles;
-  int m = rest % pl.m_tiles;
-  c.phase = rest / pl.m_tiles;
-  c.tw = m % pl.tiles_w;
-  int r2 = m / pl.tiles_w;
-  c.th = r2 % pl.tiles_h;
-  c.tn = r2 / pl.tiles_h;
-  return c;
-}
-
 template <int BLOCK_N>
 __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     conv_igemm_kernel(const __grid_constant__ ConvKernelParams p) {
@@ -241,6 +225,7 @@ using namespace b2g;
 extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!a || !a->in || !a->wpacked || !a->out) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: null pointer");
+  if (a->kind == B2G_CONV_K3S1_C3) return launch_conv_c3(a, stream_);
   if (a->Cin % 64 || a->Cin <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cin=%d not a multiple of 64", a->Cin);
   if (a->out_f32) {
     if (a->Cout != 32 || a->cout_store < 1 || a->cout_store > 8 || a->kind == B2G_CONVT_K4S2)

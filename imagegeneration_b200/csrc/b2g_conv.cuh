@@ -126,7 +126,7 @@ inline bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout
         int t = ky * 3 + kx;
         p->tap_map[t] = 0; p->tap_dy[t] = (int8_t)(ky - 1); p->tap_dx[t] = (int8_t)(kx - 1);
       }
-  } else if (kind == B2G_CONV_K1S1) {
+  } else if (kind == B2G_CONV_K1S1 || kind == B2G_CONV_K3S1_C3) {
     p->phases = 1; p->taps = 1; p->n_amaps = 1;
     p->Hg = Hin; p->Wg = Win; p->Hout = Hin; p->Wout = Win; p->os = 1;
     p->tap_map[0] = 0; p->tap_dy[0] = 0; p->tap_dx[0] = 0;
@@ -168,5 +168,26 @@ inline bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout
   p->m_tiles = p->tiles_w * p->tiles_h * p->tiles_n;
   return true;
 }
+
+// Tile index -> (phase, N tile, pixel box) for the per-tap kernels; device code only.
+struct TileCoord {
+  int phase, n_tile, tn, th, tw;
+};
+__device__ __forceinline__ TileCoord decode_tile(const ConvPlan& pl, int n_tiles, int tile) {
+  TileCoord c;
+  c.n_tile = tile % n_tiles;
+  int rest = tile / n_tiles;
+  int m = rest % pl.m_tiles;
+  c.phase = rest / pl.m_tiles;
+  c.tw = m % pl.tiles_w;
+  int r2 = m / pl.tiles_w;
+  c.th = r2 % pl.tiles_h;
+  c.tn = r2 / pl.tiles_h;
+  return c;
+}
+
+
+// 3-channel 3x3 conv with the im2col patch built in shared memory (b2g_conv_c3.cu)
+int launch_conv_c3(const b2g_conv_args* a, void* stream);
 
 }  // namespace b2g

@@ -12,7 +12,7 @@ PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200gan.so"
 
 # enums mirrored from include/b200gan.h
-CONV_K3S1, CONV_K4S2, CONVT_K4S2, CONV_K1S1 = 0, 1, 2, 3
+CONV_K3S1, CONV_K4S2, CONVT_K4S2, CONV_K1S1, CONV_K3S1_C3 = 0, 1, 2, 3, 4
 ACT_NONE, ACT_LEAKY, ACT_RELU, ACT_TANH = 0, 1, 2, 3
 
 

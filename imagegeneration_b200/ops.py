@@ -9,13 +9,15 @@ import torch
 
 from . import lib as _lib
 from .lib import WgradArgs
-from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K1S1, CONV_K3S1, CONV_K4S2, CONVT_K4S2, ConvArgs,
+from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K1S1, CONV_K3S1, CONV_K3S1_C3, CONV_K4S2, CONVT_K4S2,
+                  ConvArgs,
                   B200GanError, check)
 
-__all__ = ["pack_conv_weight", "conv_igemm", "conv_wgrad", "im2col27", "CONV_K1S1", "CONV_K3S1", "CONV_K4S2", "CONVT_K4S2", "ACT_NONE", "ACT_LEAKY",
+__all__ = ["pack_conv_weight", "conv_igemm", "conv_wgrad", "im2col27", "CONV_K1S1", "CONV_K3S1_C3", "CONV_K3S1", "CONV_K4S2", "CONVT_K4S2", "ACT_NONE", "ACT_LEAKY",
            "ACT_RELU", "ACT_TANH"]
 
-_KIND_GEOM = {CONV_K3S1: (3, 1, 9), CONV_K4S2: (4, 1, 16), CONVT_K4S2: (4, 4, 4), CONV_K1S1: (1, 1, 1)}  # k, phases, taps
+_KIND_GEOM = {CONV_K3S1: (3, 1, 9), CONV_K4S2: (4, 1, 16), CONVT_K4S2: (4, 4, 4), CONV_K1S1: (1, 1, 1),
+              CONV_K3S1_C3: (1, 1, 1)}  # k, phases, taps (K3S1_C3 takes the K1S1 packing of the [27][Cout] matrix)
 
 
 def _ptr(t: torch.Tensor | None):
@@ -81,12 +83,17 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
     _need_cuda(x, wpacked, out, bias, yprev)
     n, h, w, cin = x.shape
     k, phases, taps = _KIND_GEOM[kind]
-    if x.dtype != torch.bfloat16 or wpacked.dtype != torch.bfloat16:
+    if kind == CONV_K3S1_C3:
+        # 3-channel fp32 input, im2col patch built inside the kernel; weights = K1S1 packing of [27][Cout], ck_pad 64
+        if x.dtype != torch.float32 or cin != 3 or wpacked.dtype != torch.bfloat16 or tuple(wpacked.shape[::2]) != (1, 64):
+            raise B200GanError("conv_igemm(K3S1_C3): expected fp32 [N,H,W,3] and packed bf16 weights [1,Cout,64]")
+    elif x.dtype != torch.bfloat16 or wpacked.dtype != torch.bfloat16:
         raise B200GanError("conv_igemm: activations and packed weights must be bf16")
-    if wpacked.shape[0] != phases or wpacked.shape[2] != taps * cin:
+    elif wpacked.shape[0] != phases or wpacked.shape[2] != taps * cin:
         raise B200GanError(f"conv_igemm: packed weight {tuple(wpacked.shape)} does not match kind/Cin={cin}")
     cout = wpacked.shape[1]
-    ho, wo = {CONV_K3S1: (h, w), CONV_K4S2: (h // 2, w // 2), CONVT_K4S2: (h * 2, w * 2), CONV_K1S1: (h, w)}[kind]
+    ho, wo = {CONV_K3S1: (h, w), CONV_K4S2: (h // 2, w // 2), CONVT_K4S2: (h * 2, w * 2), CONV_K1S1: (h, w),
+              CONV_K3S1_C3: (h, w)}[kind]
     odt = torch.float32 if out_f32 else torch.bfloat16
     if out is None:
         out = torch.empty((n, ho, wo, cout), dtype=odt, device=x.device)
@@ -106,7 +113,7 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                  dact_scale=dact_scale, dact_zero=dact_zero, out_f32=int(out_f32), cout_store=cout_store)
     ev = _prof_begin()
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
-    cin_alg = 27 if kind == CONV_K1S1 else cin   # K1S1 is only used on im2col27 operands (27 real channels)
+    cin_alg = 27 if kind in (CONV_K1S1, CONV_K3S1_C3) else cin   # edge layers: 27 real taps*channels
     _prof_end(ev, "conv_igemm", 2.0 * n * h * w * cin_alg * (cout_store or cout) *
               (16 if kind == CONVT_K4S2 else taps) / (4 if kind == CONV_K4S2 else 1),
               f"kind{kind} {n}x{h}x{w}x{cin}->{cout_store or cout}")

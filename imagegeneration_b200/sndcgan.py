@@ -19,7 +19,7 @@ import torch
 
 from . import lib as _lib
 from . import ops
-from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K1S1, CONV_K3S1, CONV_K4S2, CONVT_K4S2,
+from .lib import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_TANH, CONV_K1S1, CONV_K3S1, CONV_K3S1_C3, CONV_K4S2, CONVT_K4S2,
                   B200GanError, check)
 
 BN_EPS = 1e-3                    # Keras BatchNormalization default epsilon
@@ -234,7 +234,7 @@ class Generator:
         x27 = ops.im2col27(d_pre_tanh, self._buf("dy27", (B, H, W, 64), torch.bfloat16))
         ops.conv_wgrad(CONV_K1S1, x27, a3, g[12], ca_valid=27)
         dq = self._buf("dq3", tuple(a3.shape), torch.bfloat16)
-        ops.conv_igemm(CONV_K1S1, x27, self._wp4_d, dq, yprev=a3, dact=ACT_RELU)
+        ops.conv_igemm(CONV_K3S1_C3, d_pre_tanh, self._wp4_d, dq, yprev=a3, dact=ACT_RELU)
         acts_in = [a0, a1, a2]
         for i in (2, 1, 0):
             k = (3, 6, 9)[i]
@@ -387,12 +387,12 @@ class Discriminator:
         if t8 and dropout_seeds is None:
             raise B200GanError("training-mode forward needs dropout_seeds")
         seeds = dropout_seeds if t8 else [0] * 7
-        if x27 is None:
-            x27 = ops.im2col27(x, self._buf("x27", (B, H, W, 64), torch.bfloat16))
+        # conv1 (3 -> 64): the 27-wide im2col patch is built inside the kernel (B2G_CONV_K3S1_C3); the im2col27 tensor
+        # is only materialised in backward(), for the weight gradient
         c1 = self._buf("c1", (B, H, W, 64), torch.bfloat16)
-        ops.conv_igemm(CONV_K1S1, x27, self._wp_f[0], c1, bias=v[1], act=ACT_LEAKY, alpha=LEAKY_ALPHA,
+        ops.conv_igemm(CONV_K3S1_C3, x, self._wp_f[0], c1, bias=v[1], act=ACT_LEAKY, alpha=LEAKY_ALPHA,
                        dropout_thresh8=t8, dropout_seed=seeds[0])
-        self._x27 = x27
+        self._x_in, self._x27 = x, x27
         acts = [c1]
         cur = c1
         for i in range(1, 7):
@@ -451,7 +451,10 @@ class Discriminator:
             dpre = dprev
         H, W = self.input_size[0], self.input_size[1]
         if need_wgrad:
-            ops.conv_wgrad(CONV_K1S1, self._x27, dpre, g[0], ca_valid=27, dbias=g[1])
+            x27 = self._x27
+            if x27 is None:
+                x27 = ops.im2col27(self._x_in, self._buf("x27", (B, H, W, 64), torch.bfloat16))
+            ops.conv_wgrad(CONV_K1S1, x27, dpre, g[0], ca_valid=27, dbias=g[1])
             if self.spectral_norm:
                 for i in range(8):
                     check(lib.b2g_sn_grad_finalize(_p(v[2 * i]), _p(g[2 * i]), _p(self.sn_u[i]), _p(self.sn_vraw[i]),
@@ -544,8 +547,7 @@ class SNDCGANEngine:
 
         # (1) generator step (:242-249)
         g_output = G.forward(input_z)                                               # :243
-        g27 = ops.im2col27(g_output, D._buf("g27", (B, *self.image_size[:2], 64), torch.bfloat16))
-        D.forward(g_output, training=True, dropout_seeds=sa, x27=g27)               # :244
+        D.forward(g_output, training=True, dropout_seeds=sa)                        # :244
         g_loss, _ = D.head_loss(g_kind, 1.0, inv_b)                                 # :245-246
         d_gout = D.backward(need_wgrad=False, need_input_grad=True, g_out=g_output)
         G.backward(d_gout)                                                          # :248
@@ -563,7 +565,7 @@ class SNDCGANEngine:
         D._packed_dirty = True
 
         # (3) discriminator step on the stale fake batch (:259-267)
-        D.forward(g_output, training=True, dropout_seeds=sc, x27=g27)               # :260
+        D.forward(g_output, training=True, dropout_seeds=sc)                        # :260
         d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)                # :261-262
         D.backward(need_wgrad=True, need_input_grad=False)                          # :266
         self._allreduce(D.arena.g)

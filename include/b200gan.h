@@ -49,8 +49,12 @@ const char* b2g_last_error(void); /* thread-local, valid until the next failing 
  *   B2G_CONV_K1S1   1x1 conv (1 tap, no shift) = plain GEMM over pixels. Used for the 3-channel edge layers
  *       after b2g_im2col27 has expanded [N,H,W,3] into 27(+1) bf16 channels: D.conv1 forward
  *       (SNDCGAN.py:73-76) and the input-gradient of G.convT4 (:57-61).
+ *   B2G_CONV_K3S1_C3  3x3 stride-1 SAME conv over a 3-CHANNEL fp32 tensor: `in` is fp32 [N,H,W,3], Cin = 3, and the
+ *       27(+1 ones)-wide im2col patch of every pixel is built in shared memory by the kernel itself (no im2col27
+ *       tensor in HBM).  wpacked is the K1S1 packing of the [27][Cout] matrix with ck_pad = 64; Cout = 64.
+ *       Same layers as K1S1: D.conv1 forward (SNDCGAN.py:73-76) and the input-gradient of G.convT4 (:57-61).
  */
-enum { B2G_CONV_K3S1 = 0, B2G_CONV_K4S2 = 1, B2G_CONVT_K4S2 = 2, B2G_CONV_K1S1 = 3 };
+enum { B2G_CONV_K3S1 = 0, B2G_CONV_K4S2 = 1, B2G_CONVT_K4S2 = 2, B2G_CONV_K1S1 = 3, B2G_CONV_K3S1_C3 = 4 };
 enum { B2G_ACT_NONE = 0, B2G_ACT_LEAKY = 1, B2G_ACT_RELU = 2, B2G_ACT_TANH = 3 };
 
 typedef struct b2g_conv_args {

@@ -298,3 +298,36 @@ def test_spectral_norm_power_iteration_and_grad():
     for i in range(7):
         s0 = float(torch.linalg.svdvals(Ws[i].double())[0])
         assert abs(float(sc[i][1]) - s0) / s0 < 1e-3, f"layer {i}"
+
+
+@pytest.mark.parametrize("n,h,w", EDGE + [(2, 5, 128), (5, 3, 8)])
+def test_edge_c3_fused_patch_kernel(n, h, w):
+    """B2G_CONV_K3S1_C3: the im2col patch is built in shared memory; must equal the im2col27 + K1S1 route bit for bit
+    (same bf16 operands, same fp32 accumulation order is not guaranteed -> tiny tolerance) and match the oracle."""
+    from imagegeneration_b200 import ops
+    x = _rand((n, h, w, 3), 21)
+    wt = _rand((3, 3, 3, 64), 22, 0.2)
+    b = _rand((64,), 23, 0.1)
+    wp = ops.pack_conv_weight(ops.CONV_K1S1, wt.cuda().view(1, 1, 27, 64), n_is_d3=True, ck_pad=64)
+    seed = 0x0BAD_5EED_1234
+    y = ops.conv_igemm(ops.CONV_K3S1_C3, x.cuda(), wp, bias=b.cuda(), act=ops.ACT_LEAKY, alpha=0.1,
+                       dropout_thresh8=128, dropout_seed=seed)
+    y2 = ops.conv_igemm(ops.CONV_K1S1, ops.im2col27(x.cuda()), wp, bias=b.cuda(), act=ops.ACT_LEAKY, alpha=0.1,
+                        dropout_thresh8=128, dropout_seed=seed)
+    torch.cuda.synchronize()
+    assert _rel_l2(y.float(), y2.float()) < 1e-3
+    pre = K.leaky_relu(K.conv2d_same(_bf(x), _bf(wt), b, 1))
+    from oracle.dropout_hash import keep_mask
+    import numpy as np
+    mask = torch.from_numpy(keep_mask(pre.numel(), seed, 128).astype(np.float32)).reshape(pre.shape)
+    assert _rel_l2(y.float().cpu(), K.dropout(pre, mask, 0.5)) < 6e-3
+    # G.convT4 input gradient: 3-channel fp32 dY -> 64 channels, ReLU' of the saved layer input in the epilogue
+    dy = _rand((n, h, w, 3), 24)
+    wg = _rand((3, 3, 3, 64), 25, 0.2)                     # Conv2DTranspose kernel [kh,kw,Cout=3,Cin=64]
+    a3 = torch.relu(_rand((n, h, w, 64), 26))
+    xin = a3.clone().requires_grad_(True)
+    K.conv2d_transpose_same(xin, _bf(wg), 1).backward(_bf(dy))
+    wpd = ops.pack_conv_weight(ops.CONV_K1S1, wg.cuda().view(1, 1, 27, 64), n_is_d3=True, ck_pad=64)
+    dq = ops.conv_igemm(ops.CONV_K3S1_C3, dy.cuda(), wpd, yprev=a3.cuda().to(torch.bfloat16), dact=ops.ACT_RELU)
+    torch.cuda.synchronize()
+    assert _rel_l2(dq.float().cpu(), xin.grad * (a3 > 0).float()) < 6e-3

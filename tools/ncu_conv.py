@@ -17,6 +17,11 @@ def rnd(*shape, dtype=torch.bfloat16):
 
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 for _ in range(reps):
+    # 0. D.conv1 forward with the im2col patch built in shared memory (B2G_CONV_K3S1_C3)
+    img = rnd(B, 144, 256, 3, dtype=torch.float32)
+    wc3 = ops.pack_conv_weight(ops.CONV_K1S1, rnd(1, 1, 27, 64, dtype=torch.float32), n_is_d3=True, ck_pad=64)
+    ops.conv_igemm(ops.CONV_K3S1_C3, img, wc3, bias=rnd(64, dtype=torch.float32), act=ops.ACT_LEAKY, alpha=0.1,
+                   dropout_thresh8=128, dropout_seed=4)
     # 1. D.conv1 forward as K1S1 GEMM (im2col27 operand): bias + leaky + dropout
     x27 = rnd(B, 144, 256, 64)
     w = ops.pack_conv_weight(ops.CONV_K1S1, rnd(1, 1, 27, 64, dtype=torch.float32), n_is_d3=True, ck_pad=64)
