@@ -157,6 +157,56 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------------------
 # our arm
 # ----------------------------------------------------------------------------------------------------------
+def _hbm_kernel_rooflines(eng, peaks, peak_kind):
+    """Achieved HBM GB/s of the memory-bound parameter kernels, each timed alone with CUDA events on torch's current
+    stream (the stream they are launched on), L2 flushed between repetitions by a 512 MB fill.
+      adam (G arena): 28 B per parameter (read w, g, m, v; write w, m, v)            SURVEY.md section 8(d)
+      spectral_norm_multi (all 8 D matrices, one power iteration): 4 B per weight (W read once)"""
+    import torch
+    from imagegeneration_b200.sndcgan import SNDCGANEngine
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    flush = torch.empty(128 * 1024 * 1024, dtype=torch.float32, device="cuda")
+    out = {}
+
+    def timed(fn, reps=5):
+        ts = []
+        for _ in range(reps):
+            flush.fill_(1.0)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b) * 1e-3)
+        ts.sort()
+        return ts[len(ts) // 2]
+
+    G = eng.gen_model.arena
+    it0 = eng.g_optimizer.iterations
+    g_saved = G.g.clone()
+    G.g.zero_()                       # zero gradients with m = v as left by training: weights barely move
+    sec = timed(lambda: eng.g_optimizer.apply_arena(G, 0.0))
+    eng.g_optimizer.iterations = it0
+    G.g.copy_(g_saved)
+    byt = 28.0 * G.numel
+    out["adam_generator_arena"] = {"bound": "hbm", "achieved": byt / sec / 1e9, "peak": peak, "unit": "GB/s",
+                                   "frac": byt / sec / 1e9 / peak, "bytes_per_launch": byt, "us": sec * 1e6,
+                                   "peak_kind": f"{peak_kind} copy bandwidth"}
+    try:
+        sn = SNDCGANEngine(4, dropout=0.0, image_size=IMAGE_SIZE, seed=62, spectral_norm=True)
+        D = sn.disc_model
+        sec = timed(D.sn_power_iteration)
+        byt = 4.0 * sum(k * c for k, c in zip(D._sn_K, D._sn_C))
+        out["spectral_norm_multi"] = {"bound": "hbm", "achieved": byt / sec / 1e9, "peak": peak, "unit": "GB/s",
+                                      "frac": byt / sec / 1e9 / peak, "bytes_per_launch": byt, "us": sec * 1e6,
+                                      "note": "8 matrices, 24.6 MB in 2 launches: latency-bound at this size",
+                                      "peak_kind": f"{peak_kind} copy bandwidth"}
+        del sn
+    except Exception as e:  # the option is not on the reference path; never fail the bench line for it
+        out["spectral_norm_multi"] = {"error": str(e)[:200]}
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -260,6 +310,7 @@ def run_b200(args):
                       "frac": fl / sec / 1e12 / peak_tf, "traffic": None, "launches_per_step": cnt,
                       "ms_per_step": sec * 1e3, "peak_kind": f"{peak_kind} sustained bf16"}
     tc_ms = sum(v["ms_per_step"] for v in roof.values())
+    hbm_roof = _hbm_kernel_rooflines(eng, peaks, peak_kind) if rank == 0 else None
 
     if rank != 0:
         if world > 1:
@@ -280,6 +331,7 @@ def run_b200(args):
         "clocks": clocks,
         "roofline": roof.get("conv_igemm"),
         "roofline_wgrad": roof.get("conv_wgrad"),
+        "roofline_hbm": hbm_roof,
         "step_model": {"tflops_per_gpu_whole_step": FLOP_PER_IMAGE * B / (ms_per_step * 1e-3) / 1e12,
                        "frac_of_peak_whole_step": FLOP_PER_IMAGE * B / (ms_per_step * 1e-3) / 1e12 / peak_tf,
                        "tensor_core_kernels_ms": tc_ms, "other_ms": ms_per_step - tc_ms},

@@ -158,3 +158,63 @@ def test_rows_narrow_fp32_output_with_tanh(n, h, w):
     assert tuple(y.shape) == (n, h, w, 3)
     assert _rel_l2(y.cpu(), ref) < 2e-3
     assert _rel_l2(y, y_tap) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CTA-pair kernel (csrc/b2g_conv_pair.cu, tcgen05 cta_group::2): same results as the one-CTA kernels
+# ---------------------------------------------------------------------------------------------------------------
+def _pair_vs_single(fn):
+    os.environ["B2G_CONV_PAIR"] = "1"
+    a = fn()
+    os.environ["B2G_CONV_PAIR"] = "0"
+    try:
+        b = fn()
+    finally:
+        os.environ["B2G_CONV_PAIR"] = "1"
+    torch.cuda.synchronize()
+    return a, b
+
+
+PAIR = [
+    # (kind, N, H, W, Cin, Cout): even number of 128-pixel tiles; Cout 64 / 128 / 256 / 512 (two N tiles)
+    ("k3s1", 2, 8, 16, 64, 64),
+    ("k3s1", 4, 18, 32, 128, 256),
+    ("k3s1", 2, 18, 32, 256, 512),
+    ("k4s2", 2, 16, 32, 64, 128),
+    ("k4s2", 2, 36, 64, 128, 256),
+    ("convt", 2, 8, 16, 128, 64),
+    ("convt", 4, 18, 32, 256, 256),
+    ("k3s1", 3, 36, 64, 64, 128),      # 3*36*64/128 = 54 tiles
+]
+
+
+@pytest.mark.parametrize("kind,n,h,w,cin,cout", PAIR)
+def test_pair_kernel_matches_single_cta_and_oracle(kind, n, h, w, cin, cout):
+    from imagegeneration_b200 import ops
+    b = _rand((cout,), 33, 0.1)
+    seed = 0x77_1234_5678
+    if kind == "k3s1":
+        x = _bf16_round(_rand((n, h, w, cin), 31))
+        wt = _rand((3, 3, cin, cout), 32, 0.05)
+        wp = ops.pack_conv_weight(ops.CONV_K3S1, wt.cuda(), n_is_d3=True)
+        k, ref = ops.CONV_K3S1, K.leaky_relu(K.conv2d_same(x, _bf16_round(wt), b, 1))
+    elif kind == "k4s2":
+        x = _bf16_round(_rand((n, 2 * h, 2 * w, cin), 31))
+        wt = _rand((4, 4, cin, cout), 32, 0.05)
+        wp = ops.pack_conv_weight(ops.CONV_K4S2, wt.cuda(), n_is_d3=True)
+        k, ref = ops.CONV_K4S2, K.leaky_relu(K.conv2d_same(x, _bf16_round(wt), b, 2))
+    else:
+        x = _bf16_round(_rand((n, h, w, cin), 31))
+        wt = _rand((4, 4, cout, cin), 32, 0.05)
+        wp = ops.pack_conv_weight(ops.CONVT_K4S2, wt.cuda(), n_is_d3=False)
+        k, ref = ops.CONVT_K4S2, K.leaky_relu(K.conv2d_transpose_same(x, _bf16_round(wt), 2) + b)
+    xg = x.cuda().to(torch.bfloat16)
+    os.environ["B2G_CONV_ROWS"] = "0"
+    try:
+        y, y1 = _pair_vs_single(lambda: ops.conv_igemm(k, xg, wp, bias=b.cuda(), act=ops.ACT_LEAKY, alpha=0.1,
+                                                       dropout_thresh8=64, dropout_seed=seed))
+    finally:
+        os.environ["B2G_CONV_ROWS"] = "1"
+    assert torch.equal(y, y1)            # same taps in the same order into fp32 accumulators: bit-identical
+    mask = torch.from_numpy(keep_mask(ref.numel(), seed, 64).astype(np.float32)).reshape(ref.shape)
+    assert _rel_l2(y.float().cpu(), K.dropout(ref, mask, 0.25)) < 6e-3

@@ -53,12 +53,13 @@ def test_hinge_and_spectral_norm_options(loss, sn):
     ref = orc.train_step(real, z, collect=col)
     out = eng.train_step(real.cuda(), z.cuda())
     torch.cuda.synchronize()
-    for a, b in zip(out[:4], ref[:4]):
-        assert abs(float(a) - float(b)) <= 2e-2 * max(1.0, abs(float(b)))
+    for name, a, b in zip(("g_loss", "d_loss", "d_loss_real", "d_loss_fake"), out[:4], ref[:4]):
+        assert abs(float(a) - float(b)) <= 2e-2 * max(1.0, abs(float(b))), (name, float(a), float(b))
     if sn:
         for i in range(8):      # sigma of the last D pass
             s_ref = float(col[f"dc_sigma{i}"])
-            assert abs(float(eng.disc_model.sn_scal[i][1]) - s_ref) / s_ref < 2e-4, i
+            assert abs(float(eng.disc_model.sn_scal[i][1]) - s_ref) / s_ref < 2e-4, (
+                i, float(eng.disc_model.sn_scal[i][1]), s_ref)
         from oracle import keras_ops as K
         # identical u0: re-create the engine's initial vectors
         eng3 = SNDCGANEngine(B, dropout=0.0, image_size=size, seed=62, loss=loss, spectral_norm=True)
