@@ -246,6 +246,11 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: kind %d cannot tile N=%d H=%d W=%d", a->kind, a->N, a->Hin, a->Win);
   const ConvPlan& pl = kp.plan;
   const int block_n = a->out_f32 ? 32 : (a->Cout % 256 == 0 ? 256 : (a->Cout % 128 == 0 ? 128 : 64));
+  {  // wide layers of the model (>= 128 pixels per row, Cout <= 128): row-slab kernel with a compile-time schedule
+    bool handled = false;
+    const int rc = launch_conv_rows(a, pl, block_n, stream_, &handled, /*static_only=*/true);
+    if (rc != B2G_OK || handled) return rc;
+  }
   {  // CTA-pair tiles (cta_group::2) whenever the number of pixel tiles is even
     bool handled = false;
     const int rc = launch_conv_pair(a, pl, block_n, stream_, &handled);
@@ -253,7 +258,7 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   }
   {  // wide layers with Cout <= 128: row-slab kernel (b2g_conv_rows.cu) re-uses each input row across taps
     bool handled = false;
-    const int rc = launch_conv_rows(a, pl, block_n, stream_, &handled);
+    const int rc = launch_conv_rows(a, pl, block_n, stream_, &handled, /*static_only=*/false);
     if (rc != B2G_OK || handled) return rc;
   }
   fill_epi_params(a, &kp.e);

@@ -35,13 +35,13 @@ struct ConvPlan {
 };
 
 // ky (0..3) of a 4x4 stride-2 conv -> (parity sub-grid row, row offset inside the sub-grid)
-__host__ __device__ inline void k4s2_tap(int k, int* parity, int* off) {
+__host__ __device__ constexpr void k4s2_tap(int k, int* parity, int* off) {
   // input coordinate 2*o + k - 1:  k=0 -> 2(o-1)+1 ; k=1 -> 2o ; k=2 -> 2o+1 ; k=3 -> 2(o+1)
   *parity = (k + 1) & 1;
   *off = (k == 0) ? -1 : (k == 3 ? 1 : 0);
 }
 // convT phase p (0/1), tap j (0/1) -> (kernel index k, input offset d) with Y = 2*iy + k - 1, Y = 2*y + p
-__host__ __device__ inline void convt_tap(int p, int j, int* k, int* d) {
+__host__ __device__ constexpr void convt_tap(int p, int j, int* k, int* d) {
   if (p == 0) { *k = j == 0 ? 1 : 3; *d = j == 0 ? 0 : -1; }
   else        { *k = j == 0 ? 0 : 2; *d = j == 0 ? 1 : 0; }
 }
@@ -81,12 +81,12 @@ __host__ __device__ inline long pack_source_index(int kind, int kh, int kw, int 
   return (((long)ky * kw + kx) * D2 + d2) * D3 + d3;
 }
 
-inline bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+constexpr bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 // Chooses the pixel tile (bw, bh, bn) with bw*bh*bn == tile_pixels that wastes the fewest rows.
 // Returns false when the grid width cannot be tiled (Wg must divide tile_pixels or be a multiple of it).
-inline bool choose_tile(int tile_pixels, int N, int Hg, int Wg, int* bw, int* bh, int* bn) {
-  int w;
+constexpr bool choose_tile(int tile_pixels, int N, int Hg, int Wg, int* bw, int* bh, int* bn) {
+  int w = 0;
   if (Wg >= tile_pixels) {
     if (Wg % tile_pixels) return false;
     w = tile_pixels;
@@ -112,7 +112,7 @@ inline bool choose_tile(int tile_pixels, int N, int Hg, int Wg, int* bw, int* bh
 }
 
 // Fills the geometry + tap tables for a conv role. Returns false on unsupported shapes.
-inline bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout, int tile_pixels, ConvPlan* p) {
+constexpr bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout, int tile_pixels, ConvPlan* p) {
   p->kind = kind;
   p->N = N;
   p->Cin = Cin;
@@ -136,7 +136,7 @@ inline bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout
     p->Hg = Hin / 2; p->Wg = Win / 2; p->Hout = Hin / 2; p->Wout = Win / 2; p->os = 1;
     for (int ky = 0; ky < 4; ++ky)
       for (int kx = 0; kx < 4; ++kx) {
-        int py, dy, px, dx;
+        int py = 0, dy = 0, px = 0, dx = 0;
         k4s2_tap(ky, &py, &dy);
         k4s2_tap(kx, &px, &dx);
         int t = ky * 4 + kx;
@@ -151,7 +151,7 @@ inline bool build_conv_plan(int kind, int N, int Hin, int Win, int Cin, int Cout
         p->ph_y[ph] = (int8_t)py; p->ph_x[ph] = (int8_t)px;
         for (int jy = 0; jy < 2; ++jy)
           for (int jx = 0; jx < 2; ++jx) {
-            int ky, dy, kx, dx;
+            int ky = 0, dy = 0, kx = 0, dx = 0;
             convt_tap(py, jy, &ky, &dy);
             convt_tap(px, jx, &kx, &dx);
             int e = ph * 4 + jy * 2 + jx;

@@ -12,6 +12,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <utility>
+
 #include "b2g_conv_epi.cuh"
 #include "b2g_conv_rows.cuh"
 #include "b2g_host.h"
@@ -32,15 +34,17 @@ struct alignas(64) RowsKernelParams {
   int tiles_per_pg;  // n_tiles * N * row_blocks * tiles_w
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, class SS = RowsDyn>
 struct RowsCfg {
   static constexpr int kSlabBytes = 17 * 1024;                       // 130 px * 128 B = 16640, padded to 1 KiB
   static constexpr int kSlabTx = kRowsSlabPixels * 128;              // bytes one slab TMA delivers
-  static constexpr int kSlabs = BLOCK_N == 128 ? 7 : 8;
+  static constexpr int kSlabs = SS::kStatic ? SS::kS : (BLOCK_N == 128 ? 7 : 8);
   static constexpr int kBBytes = BLOCK_N * 128;
-  static constexpr int kBStages = BLOCK_N == 128 ? 6 : 8;
+  static constexpr int kBStages = SS::kStatic ? SS::kSB : (BLOCK_N == 128 ? 6 : 8);
   static constexpr int kBarBytes = 512;
   static constexpr int kSmemBytes = kSlabs * kSlabBytes + kBStages * kBBytes + kBarBytes + 1024;
+  static_assert(2 * (kSlabs + kBStages) * 8 + 4 * 8 + 8 <= kBarBytes, "barrier area");
+  static_assert(kSmemBytes + 2048 <= 227 * 1024, "shared memory budget (incl. the static bias table)");
   static constexpr int kEpiGroups = 4;
   static constexpr int kThreads = 96 + 128 * kEpiGroups;
 };
@@ -91,10 +95,47 @@ __device__ __forceinline__ void rows_coord_advance(const RowsKernelParams& p, Ro
   c.pg += d.pg + cy;
 }
 
-template <int BLOCK_N>
-__global__ void __launch_bounds__(RowsCfg<BLOCK_N>::kThreads, 1)
+// One step of a compile-time schedule: every stage, barrier, parity bit and accumulator is an immediate.
+template <class SS, int BLOCK_N, int J>
+__device__ __forceinline__ void rows_static_step(uint32_t leader, uint32_t slab_lo0, uint32_t b_lo0, uint32_t d_base,
+                                                 uint64_t* sfull, uint64_t* sempty, uint64_t* bfull, uint64_t* bempty,
+                                                 uint32_t par_s0, uint32_t par_b0) {
+  using Cfg = RowsCfg<BLOCK_N, SS>;
+  constexpr RowsStep st = SS::step(J);
+  constexpr int S = SS::kS, SB = SS::kSB, R = SS::kR, P = SS::kP;
+  constexpr int bst = J % SB;
+  constexpr int need = st.slab0 + R - 1, prev = SS::need_before(J), rel0 = SS::released_before(J);
+  constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
+  mbar_wait(&bfull[bst], par_b0 ^ ((J / SB) & 1));
+#pragma unroll
+  for (int i = prev + 1; i <= need; ++i) mbar_wait(&sfull[i % S], par_s0 ^ ((i / S) & 1));
+  tc_fence_after();
+  if (leader) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int acc = st.acc0 + r * P;
+      umma_f16_k64(d_base + acc * BLOCK_N,
+                   slab_lo0 + ((st.slab0 + r) % S) * (Cfg::kSlabBytes >> 4) + st.dxi * 8,
+                   b_lo0 + bst * (Cfg::kBBytes >> 4), idesc, SS::written_before(J, acc) ? 1u : 0u);
+    }
+    umma_commit(&bempty[bst]);
+#pragma unroll
+    for (int q = 0; q < st.rel; ++q) umma_commit(&sempty[(rel0 + q) % S]);
+  }
+  __syncwarp();
+}
+template <class SS, int BLOCK_N, int... Js>
+__device__ __forceinline__ void rows_static_tile(std::integer_sequence<int, Js...>, uint32_t leader, uint32_t slab_lo0,
+                                                 uint32_t b_lo0, uint32_t d_base, uint64_t* sfull, uint64_t* sempty,
+                                                 uint64_t* bfull, uint64_t* bempty, uint32_t par_s0, uint32_t par_b0) {
+  (rows_static_step<SS, BLOCK_N, Js>(leader, slab_lo0, b_lo0, d_base, sfull, sempty, bfull, bempty, par_s0, par_b0),
+   ...);
+}
+
+template <int BLOCK_N, class SS>
+__global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     conv_rows_kernel(const __grid_constant__ RowsKernelParams p) {
-  using Cfg = RowsCfg<BLOCK_N>;
+  using Cfg = RowsCfg<BLOCK_N, SS>;
   __shared__ float sbias[512];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -194,6 +235,26 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N>::kThreads, 1)
     constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
     constexpr uint32_t kSlabD = Cfg::kSlabBytes >> 4, kBD = Cfg::kBBytes >> 4;  // stage strides in descriptor units
     const uint32_t slab_lo0 = (smem_u32(smem) & 0x3FFFFu) >> 4, b_lo0 = (smem_u32(bsm) & 0x3FFFFu) >> 4;
+    if constexpr (SS::kStatic) {
+      // compile-time schedule: the rings divide the slabs / weight tiles of a super-tile, so only one parity bit
+      // per ring changes from tile to tile
+      static_assert(SS::ok(), "schedule does not fit");
+      static_assert(SS::n_slabs() % SS::kS == 0 && SS::n_steps() % SS::kSB == 0, "rings must divide the schedule");
+      constexpr uint32_t us = SS::n_slabs() / SS::kS, ub = SS::n_steps() / SS::kSB;  // uses of a stage per tile
+      uint32_t cs = 0, cb = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        mbar_wait(&tempty[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        rows_static_tile<SS, BLOCK_N>(std::make_integer_sequence<int, SS::n_steps()>{}, leader, slab_lo0, b_lo0,
+                                      tmem_base + as * (n_acc * BLOCK_N), sfull, sempty, bfull, bempty, cs & 1, cb & 1);
+        cs += us;
+        cb += ub;
+        if (leader) umma_commit(&tfull[as]);
+        __syncwarp();
+      }
+    } else {
     uint32_t s_head = 0, s_head_par = 0;  // ring position / parity of slab 0 of the current tile
     uint32_t b_stage = 0, b_par = 0;
     int it = 0;
@@ -250,6 +311,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N>::kThreads, 1)
       if (leader) umma_commit(&tfull[as]);
       __syncwarp();
     }
+    }
   } else {
     // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
     const int q = warp & 3;
@@ -291,36 +353,66 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N>::kThreads, 1)
   }
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, class SS = RowsDyn>
 static int launch_rows(const RowsKernelParams& kp, cudaStream_t stream) {
-  using Cfg = RowsCfg<BLOCK_N>;
+  using Cfg = RowsCfg<BLOCK_N, SS>;
   static bool attr_set = false;
   if (!attr_set) {
-    B2G_CUDA_CHECK(cudaFuncSetAttribute(conv_rows_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(conv_rows_kernel<BLOCK_N, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         Cfg::kSmemBytes));
     attr_set = true;
   }
   const int grid = kp.total_tiles < num_sms() ? kp.total_tiles : num_sms();
-  conv_rows_kernel<BLOCK_N><<<grid, Cfg::kThreads, Cfg::kSmemBytes, stream>>>(kp);
+  conv_rows_kernel<BLOCK_N, SS><<<grid, Cfg::kThreads, Cfg::kSmemBytes, stream>>>(kp);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
 
 static int rows_ring(int block_n) { return block_n == 128 ? RowsCfg<128>::kSlabs : RowsCfg<64>::kSlabs; }
 
+// compile-time schedules of the model's four wide roles: <kind, Cin/64, R, P, N tile, slab ring, weight-tile ring>
+using RowsConv3 = RowsStatic<B2G_CONV_K3S1, 2, 2, 1, 128, 4, 9>;    // D.conv3 fwd / dgrad (128 -> 128 @72x128)
+using RowsConv2 = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 8>;    // D.conv2 fwd (64 -> 128, 144x256 -> 72x128)
+using RowsConvT3 = RowsStatic<B2G_CONVT_K4S2, 2, 2, 2, 64, 6, 8>;   // G.convT3 fwd / D.conv2 dgrad (128 -> 64)
+using RowsConvT4 = RowsStatic<B2G_CONV_K3S1, 1, 4, 1, 32, 6, 9>;    // G.convT4 fwd / D.conv1 dgrad (64 -> 3)
+
+// Tries the compile-time kernel SS for this role: the host schedule is rebuilt with SS's slab ring and must equal
+// the compile-time one step for step.
+template <int BLOCK_N, class SS>
+static bool try_static(const ConvPlan& pl, int block_n, RowsKernelParams* kp) {
+  if (block_n != BLOCK_N || pl.kind != SS::kKind || pl.Cin != SS::kCh * 64) return false;
+  RowsGeom g;
+  RowsSched sc[2];
+  if (!build_rows_sched(pl, block_n, SS::kS, &g, sc)) return false;
+  if (!rows_static_matches<SS>(g, sc)) return false;
+  kp->geom = g;
+  kp->sched[0] = sc[0];
+  kp->sched[1] = sc[1];
+  return true;
+}
+
 static int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
 }
 
-int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream_, bool* handled) {
+int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream_, bool* handled,
+                     bool static_only) {
   *handled = false;
   const int enabled = env_int("B2G_CONV_ROWS", 1);  // read per call: tests switch kernels
   if (!enabled) return B2G_OK;
   if (block_n != 32 && block_n != 64 && block_n != 128) return B2G_OK;
   RowsKernelParams kp;
   memset(&kp, 0, sizeof(kp));
-  if (!build_rows_sched(pl, block_n, rows_ring(block_n), &kp.geom, kp.sched)) return B2G_OK;
+  int which = 0;  // 0 = generic table-driven kernel, 1..4 = compile-time schedule
+  if (env_int("B2G_ROWS_STATIC", 1)) {
+    if (try_static<128, RowsConv3>(pl, block_n, &kp)) which = 1;
+    else if (try_static<128, RowsConv2>(pl, block_n, &kp)) which = 2;
+    else if (try_static<64, RowsConvT3>(pl, block_n, &kp)) which = 3;
+    else if (try_static<32, RowsConvT4>(pl, block_n, &kp)) which = 4;
+  }
+  if (!which && static_only) return B2G_OK;
+  if (!which && !build_rows_sched(pl, block_n, rows_ring(block_n), &kp.geom, kp.sched)) return B2G_OK;
   kp.plan = pl;
   fill_epi_params(a, &kp.e);
   kp.brows = a->out_f32 ? a->cout_store : a->Cout;
@@ -358,10 +450,17 @@ int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   }
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   int rc;
-  switch (block_n) {
-    case 128: rc = launch_rows<128>(kp, stream); break;
-    case 64: rc = launch_rows<64>(kp, stream); break;
-    default: rc = launch_rows<32>(kp, stream); break;
+  switch (which) {
+    case 1: rc = launch_rows<128, RowsConv3>(kp, stream); break;
+    case 2: rc = launch_rows<128, RowsConv2>(kp, stream); break;
+    case 3: rc = launch_rows<64, RowsConvT3>(kp, stream); break;
+    case 4: rc = launch_rows<32, RowsConvT4>(kp, stream); break;
+    default:
+      switch (block_n) {
+        case 128: rc = launch_rows<128>(kp, stream); break;
+        case 64: rc = launch_rows<64>(kp, stream); break;
+        default: rc = launch_rows<32>(kp, stream); break;
+      }
   }
   if (rc == B2G_OK) *handled = true;
   return rc;

@@ -43,7 +43,7 @@ struct RowsGeom {
 };
 
 // One attempt with a fixed number of rows per super-tile.
-inline bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGeom* g, RowsSched* sched /*[2]*/) {
+constexpr bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGeom* g, RowsSched* sched /*[2]*/) {
   const int chunks = pl.Cin / 64;
   g->R = R;
   g->P = P;
@@ -55,7 +55,7 @@ inline bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGeom*
     RowsSched& s = sched[pg];
     s.n_slabs = 0;
     s.n_steps = 0;
-    int last_use[kRowsMaxSlabs];
+    int last_use[kRowsMaxSlabs] = {};
     for (int c = 0; c < chunks; ++c) {
       for (int m = 0; m < pl.n_amaps; ++m) {
         int dmin = 127, dmax = -128;
@@ -117,7 +117,7 @@ inline bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGeom*
 // Builds the geometry and one schedule per phase group: the largest R in {4, 2, 1} whose accumulators fit 256 TMEM
 // columns (x2 buffers) and whose schedule fits the tables and the slab ring.  `ring` = slab stages the kernel owns.
 // Returns false when the role does not fit (the caller falls back to the per-tap kernel).
-inline bool build_rows_sched(const ConvPlan& pl, int block_n, int ring, RowsGeom* g, RowsSched* sched /*[2]*/) {
+constexpr bool build_rows_sched(const ConvPlan& pl, int block_n, int ring, RowsGeom* g, RowsSched* sched /*[2]*/) {
   if (pl.kind == B2G_CONV_K1S1) return false;
   if (pl.bw != 128 || pl.bh != 1 || pl.bn != 1) return false;
   if (pl.Cin % 64 || block_n > 256) return false;
@@ -131,7 +131,83 @@ inline bool build_rows_sched(const ConvPlan& pl, int block_n, int ring, RowsGeom
   return false;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Compile-time schedules for the model's own roles.  The generic kernel walks the schedule as a table, which costs
+// the single issuing thread ~130 instructions per step (ring arithmetic, table loads, R2UR moves) — more than the
+// 2 x 256 tensor-core cycles a step is worth.  For a fixed (kind, Cin/64, R, P) and ring sizes that DIVIDE the number
+// of slabs / weight tiles per super-tile, every smem address, barrier and accumulator of every step is a constant:
+// the MMA warp's loop is fully unrolled into waits, UTCHMMA groups and commits with immediate operands.
+// ---------------------------------------------------------------------------------------------------------------
+struct RowsSchedPair {
+  RowsGeom g;
+  RowsSched s[2];
+  bool ok;
+};
+
+struct RowsDyn {  // generic kernel: table-driven issue loop, default ring sizes
+  static constexpr bool kStatic = false;
+  static constexpr int kS = 0, kSB = 0;
+};
+
+template <int KIND, int CH, int R_, int P_, int BN, int S_, int SB_>
+struct RowsStatic {
+  static constexpr bool kStatic = true;
+  static constexpr int kKind = KIND, kCh = CH, kR = R_, kP = P_, kS = S_, kSB = SB_;
+  static constexpr RowsSchedPair make() {
+    ConvPlan pl{};
+    // any geometry whose phase grid is 128 pixels wide yields the same schedule
+    const bool ok_plan = build_conv_plan(KIND, 1, KIND == B2G_CONV_K4S2 ? 16 : 8, KIND == B2G_CONV_K4S2 ? 256 : 128,
+                                         CH * 64, BN, 128, &pl);
+    RowsSchedPair sp{};
+    sp.ok = ok_plan && try_rows_sched(pl, S_, R_, P_, &sp.g, sp.s);
+    return sp;
+  }
+  static constexpr bool ok() { return make().ok; }
+  static constexpr int n_steps() { return make().s[0].n_steps; }
+  static constexpr int n_slabs() { return make().s[0].n_slabs; }
+  static constexpr RowsStep step(int j) { return make().s[0].steps[j]; }
+  static constexpr int need_before(int J) {  // highest slab index any step j < J has waited for
+    const RowsSchedPair sp = make();
+    int m = -1;
+    for (int j = 0; j < J; ++j)
+      if (sp.s[0].steps[j].slab0 + R_ - 1 > m) m = sp.s[0].steps[j].slab0 + R_ - 1;
+    return m;
+  }
+  static constexpr int released_before(int J) {
+    const RowsSchedPair sp = make();
+    int n = 0;
+    for (int j = 0; j < J; ++j) n += sp.s[0].steps[j].rel;
+    return n;
+  }
+  static constexpr bool written_before(int J, int acc) {
+    const RowsSchedPair sp = make();
+    for (int j = 0; j < J; ++j)
+      for (int r = 0; r < R_; ++r)
+        if (sp.s[0].steps[j].acc0 + r * P_ == acc) return true;
+    return false;
+  }
+  static_assert(S_ >= 1 && SB_ >= 1, "ring sizes");
+};
+
+// true when the host-built schedule (both phase groups) equals the compile-time one on the MMA side
+template <class SS>
+inline bool rows_static_matches(const RowsGeom& g, const RowsSched* sched) {
+  constexpr RowsSchedPair sp = SS::make();
+  if (!sp.ok || g.R != SS::kR || g.P != SS::kP) return false;
+  for (int pg = 0; pg < g.PG; ++pg) {
+    if (sched[pg].n_slabs != sp.s[0].n_slabs || sched[pg].n_steps != sp.s[0].n_steps) return false;
+    for (int j = 0; j < sp.s[0].n_steps; ++j) {
+      const RowsStep &a = sched[pg].steps[j], &b = sp.s[0].steps[j];
+      if (a.slab0 != b.slab0 || a.dxi != b.dxi || a.acc0 != b.acc0 || a.rel != b.rel) return false;
+    }
+  }
+  return true;
+}
+
 // Launches the row-slab kernel when the role fits it; *handled tells the caller whether it did.
-int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream, bool* handled);
+// static_only: only the compile-time-scheduled variants (tried before the CTA-pair kernel; the generic table-driven
+// variant is tried after it).
+int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream, bool* handled,
+                     bool static_only);
 
 }  // namespace b2g
