@@ -35,10 +35,11 @@ int num_sms() {
 }
 
 // One thread per packed element: wpacked[ph][n][tap*Ck + c] (bf16) <- w[ky][kx][d2][d3] (fp32) * scales.
+template <typename OutT>
 __global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
                                         const float* __restrict__ w, const float* __restrict__ scale_scalar,
                                         const float* __restrict__ scale_d2, const float* __restrict__ scale_d3,
-                                        __nv_bfloat16* __restrict__ out, int phases, int taps, long total) {
+                                        OutT* __restrict__ out, int phases, int taps, long total) {
   const float s0 = scale_scalar ? *scale_scalar : 1.f;
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     int d2, d3;
@@ -49,7 +50,8 @@ __global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3
       if (scale_d2) v *= scale_d2[d2];
       if (scale_d3) v *= scale_d3[d3];
     }
-    out[i] = __float2bfloat16_rn(v);
+    if constexpr (sizeof(OutT) == 4) out[i] = v;
+    else out[i] = __float2bfloat16_rn(v);
   }
 }
 
@@ -60,10 +62,9 @@ using namespace b2g;
 extern "C" int b2g_version(void) { return 100; }
 extern "C" const char* b2g_last_error(void) { return error_buffer(); }
 
-extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
-                                    const float* w,
-                                    const float* scale_scalar, const float* scale_d2, const float* scale_d3,
-                                    void* wpacked, b2g_stream_t stream_) {
+static int pack_conv_weight_any(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
+                                const float* w, const float* scale_scalar, const float* scale_d2,
+                                const float* scale_d3, void* wpacked, b2g_stream_t stream_, bool f32) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!w || !wpacked) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: null pointer");
   int phases, taps;
@@ -88,11 +89,29 @@ extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, in
   const int threads = 256;
   long blocks = (total + threads - 1) / threads;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  pack_conv_weight_kernel<<<(int)blocks, threads, 0, stream>>>(kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, w, scale_scalar,
-                                                                scale_d2, scale_d3,
-                                                                static_cast<__nv_bfloat16*>(wpacked), phases, taps, total);
+  if (f32)
+    pack_conv_weight_kernel<float><<<(int)blocks, threads, 0, stream>>>(
+        kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, w, scale_scalar, scale_d2, scale_d3, static_cast<float*>(wpacked),
+        phases, taps, total);
+  else
+    pack_conv_weight_kernel<__nv_bfloat16><<<(int)blocks, threads, 0, stream>>>(
+        kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, w, scale_scalar, scale_d2, scale_d3,
+        static_cast<__nv_bfloat16*>(wpacked), phases, taps, total);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
+}
+
+extern "C" int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
+                                    const float* w, const float* scale_scalar, const float* scale_d2,
+                                    const float* scale_d3, void* wpacked, b2g_stream_t stream) {
+  return pack_conv_weight_any(kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, w, scale_scalar, scale_d2, scale_d3, wpacked,
+                              stream, false);
+}
+extern "C" int b2g_pack_conv_weight_f32(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
+                                        const float* w, const float* scale_scalar, const float* scale_d2,
+                                        const float* scale_d3, void* wpacked, b2g_stream_t stream) {
+  return pack_conv_weight_any(kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, w, scale_scalar, scale_d2, scale_d3, wpacked,
+                              stream, true);
 }
 
 // ---- host-only introspection (no CUDA calls): lets the CPU test-suite check the tiling / tap / packing logic ----

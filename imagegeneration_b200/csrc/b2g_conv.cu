@@ -48,9 +48,12 @@ constexpr int epi_groups() { return 4; }
 template <int BLOCK_N>
 constexpr int conv_threads() { return 64 + 128 * epi_groups<BLOCK_N>(); }
 
-template <int BLOCK_N>
+// kTf32: fp32 activations / weights (32 channels per 128-byte k-step row), tcgen05.mma kind::tf32 (K = 8 per
+// instruction = the same 32 bytes as K = 16 bf16, so tiles, swizzle and descriptors are byte-identical).
+template <int BLOCK_N, bool kTf32 = false>
 __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     conv_igemm_kernel(const __grid_constant__ ConvKernelParams p) {
+  constexpr int kChunk = kTf32 ? 32 : 64;  // channels per k-step
   using Cfg = ConvCfg<BLOCK_N>;
   constexpr int kEpiGroups = epi_groups<BLOCK_N>();
   constexpr int kChunks = BLOCK_N / 32;
@@ -112,8 +115,8 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
         if (leader) {
           uint8_t* a_dst = smem + stage * Cfg::kStageBytes;
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_4d(a_dst, &p.amap[amap], &full_bar[stage], chunk * 64, w0 + dx, h0 + dy, n0);
-          tma_load_2d(a_dst + Cfg::kABytes, &p.bmap, &full_bar[stage], ks * 64, brow);
+          tma_load_4d(a_dst, &p.amap[amap], &full_bar[stage], chunk * kChunk, w0 + dx, h0 + dy, n0);
+          tma_load_2d(a_dst + Cfg::kABytes, &p.bmap, &full_bar[stage], ks * kChunk, brow);
         }
         __syncwarp();
         if (++chunk == p.cin_chunks) { chunk = 0; ++tap; }
@@ -123,7 +126,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
   } else if (warp == 1) {
     // ------------------------------------------------ MMA issuer (whole warp converged; one elected lane issues)
     const uint32_t leader = elect_one_sync();
-    constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
+    constexpr uint32_t idesc = umma_idesc(/*bf16 = 1, tf32 = 2*/ kTf32 ? 2 : 1, 0, 0, 128, BLOCK_N);
     const uint32_t smem_base = smem_u32(smem);
     int stage = 0;
     uint32_t phase = 0;
@@ -142,7 +145,10 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
         const uint64_t bdesc = umma_desc_kmajor(a_addr + Cfg::kABytes);
         if (leader) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+          for (int k = 0; k < 4; ++k) {
+            if constexpr (kTf32) umma_tf32(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+            else umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+          }
           umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
@@ -203,17 +209,17 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
 // ------------------------------------------------------------------------------------------------------------
 // host launcher
 // ------------------------------------------------------------------------------------------------------------
-template <int BLOCK_N>
+template <int BLOCK_N, bool kTf32 = false>
 static int launch_conv(const ConvKernelParams& kp, int total_tiles, cudaStream_t stream) {
   using Cfg = ConvCfg<BLOCK_N>;
   static bool attr_set = false;
   if (!attr_set) {
-    B2G_CUDA_CHECK(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(conv_igemm_kernel<BLOCK_N, kTf32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         Cfg::kSmemBytes));
     attr_set = true;
   }
   int grid = total_tiles < num_sms() ? total_tiles : num_sms();
-  conv_igemm_kernel<BLOCK_N><<<grid, conv_threads<BLOCK_N>(), Cfg::kSmemBytes, stream>>>(kp);
+  conv_igemm_kernel<BLOCK_N, kTf32><<<grid, conv_threads<BLOCK_N>(), Cfg::kSmemBytes, stream>>>(kp);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
@@ -226,7 +232,12 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!a || !a->in || !a->wpacked || !a->out) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: null pointer");
   if (a->kind == B2G_CONV_K3S1_C3) return launch_conv_c3(a, stream_);
-  if (a->Cin % 64 || a->Cin <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cin=%d not a multiple of 64", a->Cin);
+  const int tf32 = a->tf32 ? 1 : 0;
+  const int kchunk = tf32 ? 32 : 64;  // channels per 128-byte k-step row
+  if (a->Cin % kchunk || a->Cin <= 0)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cin=%d not a multiple of %d", a->Cin, kchunk);
+  if (tf32 && (a->out_f32 || a->kind == B2G_CONV_K1S1))
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: the tf32 path covers K3S1 / K4S2 / CONVT with full-width output");
   if (a->out_f32) {
     if (a->Cout != 32 || a->cout_store < 1 || a->cout_store > 8 || a->kind == B2G_CONVT_K4S2)
       return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: fp32 narrow output needs Cout=32, 1<=cout_store<=8, 1 phase");
@@ -246,34 +257,35 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: kind %d cannot tile N=%d H=%d W=%d", a->kind, a->N, a->Hin, a->Win);
   const ConvPlan& pl = kp.plan;
   const int block_n = a->out_f32 ? 32 : (a->Cout % 256 == 0 ? 256 : (a->Cout % 128 == 0 ? 128 : 64));
-  {  // wide layers of the model (>= 128 pixels per row, Cout <= 128): row-slab kernel with a compile-time schedule
+  if (!tf32) {  // wide layers of the model (>= 128 pixels per row, Cout <= 128): row-slab kernel, compile-time schedule
     bool handled = false;
     const int rc = launch_conv_rows(a, pl, block_n, stream_, &handled, /*static_only=*/true);
     if (rc != B2G_OK || handled) return rc;
   }
-  {  // CTA-pair tiles (cta_group::2) whenever the number of pixel tiles is even
+  if (!tf32) {  // CTA-pair tiles (cta_group::2) whenever the number of pixel tiles is even
     bool handled = false;
     const int rc = launch_conv_pair(a, pl, block_n, stream_, &handled);
     if (rc != B2G_OK || handled) return rc;
   }
-  {  // wide layers with Cout <= 128: row-slab kernel (b2g_conv_rows.cu) re-uses each input row across taps
+  if (!tf32) {  // wide layers with Cout <= 128: row-slab kernel (b2g_conv_rows.cu) re-uses each input row across taps
     bool handled = false;
     const int rc = launch_conv_rows(a, pl, block_n, stream_, &handled, /*static_only=*/false);
     if (rc != B2G_OK || handled) return rc;
   }
   fill_epi_params(a, &kp.e);
   kp.brows = a->out_f32 ? a->cout_store : a->Cout;
-  kp.cin_chunks = a->Cin / 64;
+  kp.cin_chunks = a->Cin / kchunk;
   kp.n_tiles = a->Cout / block_n;
 
   // A tensor maps (innermost first: C, W, H, N)
-  const size_t es = 2;
+  const size_t es = tf32 ? 4 : 2;
+  const CUtensorMapDataType dt = tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   const char* base = static_cast<const char*>(a->in);
-  const uint32_t box[4] = {64u, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bn};
+  const uint32_t box[4] = {(uint32_t)kchunk, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bn};
   if (pl.n_amaps == 1) {
     const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->Win, (uint64_t)a->Hin, (uint64_t)a->N};
     const uint64_t str[3] = {(uint64_t)a->Cin * es, (uint64_t)a->Win * a->Cin * es, (uint64_t)a->Hin * a->Win * a->Cin * es};
-    int rc = make_tmap(&kp.amap[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, str, box);
+    int rc = make_tmap(&kp.amap[0], dt, 4, base, dims, str, box);
     if (rc) return rc;
   } else {
     for (int py = 0; py < 2; ++py)
@@ -282,7 +294,7 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
         const uint64_t str[3] = {(uint64_t)2 * a->Cin * es, (uint64_t)2 * a->Win * a->Cin * es,
                                  (uint64_t)a->Hin * a->Win * a->Cin * es};
         const char* b = base + ((size_t)py * a->Win + px) * a->Cin * es;
-        int rc = make_tmap(&kp.amap[py * 2 + px], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, b, dims, str, box);
+        int rc = make_tmap(&kp.amap[py * 2 + px], dt, 4, b, dims, str, box);
         if (rc) return rc;
       }
   }
@@ -290,11 +302,18 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
     const uint64_t ktot = (uint64_t)pl.taps * a->Cin;
     const uint64_t dims[2] = {ktot, (uint64_t)pl.phases * kp.brows};
     const uint64_t str[1] = {ktot * es};
-    const uint32_t bbox[2] = {64u, (uint32_t)block_n};
-    int rc = make_tmap(&kp.bmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a->wpacked, dims, str, bbox);
+    const uint32_t bbox[2] = {(uint32_t)kchunk, (uint32_t)block_n};
+    int rc = make_tmap(&kp.bmap, dt, 2, a->wpacked, dims, str, bbox);
     if (rc) return rc;
   }
   const int total_tiles = pl.phases * pl.m_tiles * kp.n_tiles;
+  if (tf32) {
+    switch (block_n) {
+      case 256: return launch_conv<256, true>(kp, total_tiles, stream);
+      case 128: return launch_conv<128, true>(kp, total_tiles, stream);
+      default: return launch_conv<64, true>(kp, total_tiles, stream);
+    }
+  }
   switch (block_n) {
     case 256: return launch_conv<256>(kp, total_tiles, stream);
     case 128: return launch_conv<128>(kp, total_tiles, stream);

@@ -25,6 +25,7 @@ struct EpiParams {
   int out_f32;  // narrow fp32 output: `cs` real channels, out/yprev are float [pixels][cs]
   int cs;       // channel stride of the output tensor (== Cout unless out_f32)
   int Cout;
+  int f32_io;   // tf32 path: out / yprev are full-width fp32 [pixels][Cout]
 };
 
 // r: 32 accumulator columns [cb, cb+32) of output pixel `pix` (flat N*H*W index); `valid` = pixel inside the tensor.
@@ -80,7 +81,23 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
       }
     }
   }
-  if (p.dact != B2G_ACT_NONE && valid) {
+  if (p.dact != B2G_ACT_NONE && valid && p.f32_io) {
+    const float4* yp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.yprev) + off);
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+      const float4 yv = __ldg(yp + g);
+      const float y4[4] = {yv.x, yv.y, yv.z, yv.w};
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const float y0 = y4[b];
+        float f0;
+        if (p.dact == B2G_ACT_LEAKY) f0 = y0 > 0.f ? p.dact_scale : (y0 < 0.f ? p.dact_alpha * p.dact_scale : p.dact_zero);
+        else if (p.dact == B2G_ACT_RELU) f0 = y0 > 0.f ? 1.f : 0.f;
+        else f0 = 1.f - y0 * y0;
+        v[g * 4 + b] *= f0;
+      }
+    }
+  } else if (p.dact != B2G_ACT_NONE && valid) {
     const uint4* yp = reinterpret_cast<const uint4*>(p.yprev + off);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
@@ -105,7 +122,11 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
       }
     }
   }
-  if (valid) {
+  if (valid && p.f32_io) {
+    float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off);
+#pragma unroll
+    for (int g = 0; g < 8; ++g) op[g] = make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+  } else if (valid) {
     uint4* op = reinterpret_cast<uint4*>(p.out + off);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
@@ -137,6 +158,7 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->out_f32 = a->out_f32;
   e->cs = a->out_f32 ? a->cout_store : a->Cout;
   e->Cout = a->Cout;
+  e->f32_io = a->tf32;
 }
 
 }  // namespace b2g

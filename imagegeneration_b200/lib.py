@@ -37,6 +37,7 @@ class ConvArgs(C.Structure):
         ("dact", C.c_int),
         ("dact_alpha", C.c_float), ("dact_scale", C.c_float), ("dact_zero", C.c_float),
         ("out_f32", C.c_int), ("cout_store", C.c_int),
+        ("tf32", C.c_int),
     ]
 
 
@@ -72,6 +73,8 @@ def load() -> C.CDLL:
     lib.b2g_conv_igemm.argtypes = [C.POINTER(ConvArgs), C.c_void_p]
     lib.b2g_pack_conv_weight.restype = C.c_int
     lib.b2g_pack_conv_weight.argtypes = [C.c_int] * 8 + [C.c_void_p] * 5 + [C.c_void_p]
+    lib.b2g_pack_conv_weight_f32.restype = C.c_int
+    lib.b2g_pack_conv_weight_f32.argtypes = [C.c_int] * 8 + [C.c_void_p] * 5 + [C.c_void_p]
     lib.b2g_conv_plan_query.restype = C.c_int
     lib.b2g_conv_plan_query.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.c_int]
     lib.b2g_pack_source_index.restype = C.c_long
@@ -139,5 +142,6 @@ def check(rc: int, what: str, launches: int = 1) -> None:
 
 # Names every build of the library must export (tests/test_abi.py checks them against include/b200gan.h).
 def exported_symbols() -> list[str]:
-    return ["b2g_version", "b2g_last_error", "b2g_conv_igemm", "b2g_pack_conv_weight", "b2g_conv_plan_query",
+    return ["b2g_version", "b2g_last_error", "b2g_conv_igemm", "b2g_pack_conv_weight", "b2g_pack_conv_weight_f32",
+            "b2g_conv_plan_query",
             "b2g_pack_source_index", *_EXTRA_SIGNATURES]

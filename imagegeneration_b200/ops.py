@@ -55,8 +55,9 @@ def _need_cuda(*ts: torch.Tensor | None) -> None:
 def pack_conv_weight(kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = False,
                      scale_scalar: torch.Tensor | None = None, scale_d2: torch.Tensor | None = None,
                      scale_d3: torch.Tensor | None = None, out: torch.Tensor | None = None,
-                     ck_pad: int = 0) -> torch.Tensor:
-    """fp32 Keras-layout conv weight [kh,kw,d2,d3] -> bf16 packed [phases, Cn, taps*Ck] for conv_igemm."""
+                     ck_pad: int = 0, tf32: bool = False) -> torch.Tensor:
+    """fp32 Keras-layout conv weight [kh,kw,d2,d3] -> bf16 packed [phases, Cn, taps*Ck] for conv_igemm
+    (tf32=True: fp32 packing for the kind::tf32 path)."""
     _need_cuda(w, scale_scalar, scale_d2, scale_d3, out)
     k, phases, taps = _KIND_GEOM[kind]
     kh, kw, d2, d3 = w.shape
@@ -64,11 +65,14 @@ def pack_conv_weight(kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = Fal
         raise B200GanError(f"pack_conv_weight: expected fp32 [{k},{k},d2,d3], got {tuple(w.shape)} {w.dtype}")
     cn, ck = (d3, d2) if n_is_d3 else (d2, d3)
     ck = max(ck, ck_pad)
+    odt = torch.float32 if tf32 else torch.bfloat16
     if out is None:
-        out = torch.empty((phases, cn, taps * ck), dtype=torch.bfloat16, device=w.device)
-    check(_lib.load().b2g_pack_conv_weight(kind, kh, kw, d2, d3, int(n_is_d3), int(flip), ck_pad, _ptr(w),
-                                           _ptr(scale_scalar), _ptr(scale_d2), _ptr(scale_d3), _ptr(out),
-                                           _stream()), "b2g_pack_conv_weight")
+        out = torch.empty((phases, cn, taps * ck), dtype=odt, device=w.device)
+    elif out.dtype != odt:
+        raise B200GanError("pack_conv_weight: output dtype does not match the path")
+    fn = _lib.load().b2g_pack_conv_weight_f32 if tf32 else _lib.load().b2g_pack_conv_weight
+    check(fn(kind, kh, kw, d2, d3, int(n_is_d3), int(flip), ck_pad, _ptr(w), _ptr(scale_scalar), _ptr(scale_d2),
+             _ptr(scale_d3), _ptr(out), _stream()), "b2g_pack_conv_weight")
     return out
 
 
@@ -76,7 +80,7 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                bias: torch.Tensor | None = None, act: int = ACT_NONE, alpha: float = 0.0,
                dropout_thresh8: int = 0, dropout_seed: int = 0, yprev: torch.Tensor | None = None,
                dact: int = ACT_NONE, dact_alpha: float = 0.0, dact_scale: float = 1.0,
-               dact_zero: float = 0.0, out_f32: bool = False) -> torch.Tensor:
+               dact_zero: float = 0.0, out_f32: bool = False, tf32: bool = False) -> torch.Tensor:
     """Tensor-core implicit-GEMM conv / transposed conv with fused epilogue (see include/b200gan.h).
 
     out_f32=True: narrow fp32 output — wpacked has `cout_store` (<= 8) rows and out is fp32 [N,Ho,Wo,cout_store]."""
@@ -87,6 +91,11 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
         # 3-channel fp32 input, im2col patch built inside the kernel; weights = K1S1 packing of [27][Cout], ck_pad 64
         if x.dtype != torch.float32 or cin != 3 or wpacked.dtype != torch.bfloat16 or tuple(wpacked.shape[::2]) != (1, 64):
             raise B200GanError("conv_igemm(K3S1_C3): expected fp32 [N,H,W,3] and packed bf16 weights [1,Cout,64]")
+    elif tf32:
+        if x.dtype != torch.float32 or wpacked.dtype != torch.float32 or out_f32 or cin % 32:
+            raise B200GanError("conv_igemm(tf32): fp32 activations / fp32 packed weights, Cin % 32 == 0")
+        if wpacked.shape[0] != phases or wpacked.shape[2] != taps * cin:
+            raise B200GanError(f"conv_igemm: packed weight {tuple(wpacked.shape)} does not match kind/Cin={cin}")
     elif x.dtype != torch.bfloat16 or wpacked.dtype != torch.bfloat16:
         raise B200GanError("conv_igemm: activations and packed weights must be bf16")
     elif wpacked.shape[0] != phases or wpacked.shape[2] != taps * cin:
@@ -94,7 +103,7 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
     cout = wpacked.shape[1]
     ho, wo = {CONV_K3S1: (h, w), CONV_K4S2: (h // 2, w // 2), CONVT_K4S2: (h * 2, w * 2), CONV_K1S1: (h, w),
               CONV_K3S1_C3: (h, w)}[kind]
-    odt = torch.float32 if out_f32 else torch.bfloat16
+    odt = torch.float32 if (out_f32 or tf32) else torch.bfloat16
     if out is None:
         out = torch.empty((n, ho, wo, cout), dtype=odt, device=x.device)
     elif tuple(out.shape) != (n, ho, wo, cout) or out.dtype != odt:
@@ -110,7 +119,8 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                  out=out.data_ptr(), bias=None if bias is None else bias.data_ptr(), act=act, alpha=alpha,
                  dropout_thresh8=dropout_thresh8, dropout_seed=dropout_seed & 0xFFFFFFFFFFFFFFFF,
                  yprev=None if yprev is None else yprev.data_ptr(), dact=dact, dact_alpha=dact_alpha,
-                 dact_scale=dact_scale, dact_zero=dact_zero, out_f32=int(out_f32), cout_store=cout_store)
+                 dact_scale=dact_scale, dact_zero=dact_zero, out_f32=int(out_f32), cout_store=cout_store,
+                 tf32=int(tf32))
     ev = _prof_begin()
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
     cin_alg = 27 if kind in (CONV_K1S1, CONV_K3S1_C3) else cin   # edge layers: 27 real taps*channels

@@ -82,6 +82,9 @@ typedef struct b2g_conv_args {
      rows, `out`/`yprev` are [N,Hout,Wout,cout_store] and Cout is only the MMA N tile (32). */
   int out_f32;
   int cout_store;
+  /* tf32 = 1: the fp32 / tf32 path of north_star: `in`, `out`, `yprev` are fp32 NHWC (Cin % 32 == 0), wpacked is the
+     fp32 packing produced by b2g_pack_conv_weight_f32, the MMAs are tcgen05 kind::tf32 (fp32 accumulate). */
+  int tf32;
 } b2g_conv_args;
 
 int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
@@ -100,6 +103,11 @@ int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
 int b2g_pack_conv_weight(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad, const float* w,
                          const float* scale_scalar, const float* scale_d2, const float* scale_d3, void* wpacked,
                          b2g_stream_t stream);
+
+/* Same packing with fp32 output (tf32 path; the tensor core reads the top 19 bits of every fp32 operand). */
+int b2g_pack_conv_weight_f32(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
+                             const float* w, const float* scale_scalar, const float* scale_d2, const float* scale_d3,
+                             void* wpacked, b2g_stream_t stream);
 
 /* fp32 [N,H,W,3] -> bf16 [N,H,W,64]: channel tap*3+c (tap = ky*3+kx) holds in[y+ky-1, x+kx-1, c] (zero outside),
  * channel 27 holds 1.0 (its wgrad row is the bias gradient), channels 28..63 are zero. */
