@@ -50,8 +50,14 @@ __global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3
       if (scale_d2) v *= scale_d2[d2];
       if (scale_d3) v *= scale_d3[d3];
     }
-    if constexpr (sizeof(OutT) == 4) out[i] = v;
-    else out[i] = __float2bfloat16_rn(v);
+    if constexpr (sizeof(OutT) == 4) {
+      // round to nearest tf32 here: tcgen05 kind::tf32 truncates the low 13 mantissa bits of what it reads
+      uint32_t t;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(v));
+      out[i] = __uint_as_float(t);
+    } else {
+      out[i] = __float2bfloat16_rn(v);
+    }
   }
 }
 

@@ -39,7 +39,8 @@ EncodeTiledFn encode_tiled_fn();  // defined in b2g_api.cu; NULL when the driver
 // Tiled tensor map with 128-byte swizzle and zero fill for out-of-bounds elements.
 // dims/box are innermost-first; strides_bytes has rank-1 entries (dimension 0 is contiguous).
 inline int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
-                     const uint64_t* strides_bytes, const uint32_t* box) {
+                     const uint64_t* strides_bytes, const uint32_t* box,
+                     CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return fail(B2G_E_DRIVER, "cuTensorMapEncodeTiled unavailable (no CUDA driver)");
   cuuint64_t d[5], s[4];
@@ -51,7 +52,7 @@ inline int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int rank, const voi
   }
   for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
   CUresult r = fn(m, dt, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     return fail(B2G_E_DRIVER,
                 "cuTensorMapEncodeTiled failed (%d): rank %d base %p dims [%llu,%llu,%llu,%llu] box [%u,%u,%u,%u]",

@@ -249,6 +249,17 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+// MN-major 32-bit (tf32) operands: the only layout tcgen05 accepts is the 128-byte swizzle with 32-byte atoms
+// (layout type 1; TMA: CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) whose pattern repeats every 4 k-lines (512 bytes).
+__device__ __forceinline__ uint64_t umma_smem_desc_sw128_32b(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(1) << 61;
+  return d;
+}
 // Constant upper part of a K-major SW128 descriptor (LBO = 16, SBO = 1024, version 1): OR in (saddr & 0x3FFFF) >> 4.
 // Advancing K by 16 bf16 (32 bytes) inside the 128-byte swizzle row adds 2 to the descriptor.
 constexpr uint64_t kDescKMajorSW128 =

@@ -33,14 +33,18 @@ struct alignas(64) WgradKernelParams {
   float* dbias;
 };
 
-template <int BLOCK_N>
+// kTf32: fp32 operands (32 channels per 128-byte line), tcgen05.mma kind::tf32 with K = 8 pixels per instruction.
+template <int BLOCK_N, bool kTf32 = false>
 struct WgradCfg {
   static constexpr int kTileK = 64;                 // pixels per k-step
-  static constexpr int kBoxBytes = kTileK * 128;    // one [64 pix][64 ch] box
-  static constexpr int kMBytes = 2 * kBoxBytes;     // 128 channels
-  static constexpr int kNBytes = (BLOCK_N / 64) * kBoxBytes;
+  static constexpr int kBoxCh = kTf32 ? 32 : 64;    // channels per 128-byte line of a box
+  static constexpr int kBoxBytes = kTileK * 128;    // one [64 pix][kBoxCh ch] box
+  static constexpr int kMBoxes = 128 / kBoxCh;      // 128 channels on the M side
+  static constexpr int kNBoxes = BLOCK_N / kBoxCh;
+  static constexpr int kMBytes = kMBoxes * kBoxBytes;
+  static constexpr int kNBytes = kNBoxes * kBoxBytes;
   static constexpr int kStageBytes = kMBytes + kNBytes;
-  static constexpr int kStages = BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8);
+  static constexpr int kStages = kTf32 ? (BLOCK_N == 128 ? 3 : 4) : (BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8));
   static constexpr int kTmemCols = 2 * BLOCK_N;
   static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;
 };
@@ -64,9 +68,9 @@ __device__ __forceinline__ WgradItem decode_item(const WgradKernelParams& p, int
   return w;
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool kTf32 = false>
 __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_constant__ WgradKernelParams p) {
-  using Cfg = WgradCfg<BLOCK_N>;
+  using Cfg = WgradCfg<BLOCK_N, kTf32>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
@@ -124,18 +128,18 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           if (p.m_is_shifted) {
 #pragma unroll
-            for (int g = 0; g < 2; ++g)
-              tma_load_4d(m_dst + g * Cfg::kBoxBytes, sm, &full_bar[stage], m_c0 + g * 64, w0 + dx, h0 + dy, n0);
+            for (int g = 0; g < Cfg::kMBoxes; ++g)
+              tma_load_4d(m_dst + g * Cfg::kBoxBytes, sm, &full_bar[stage], m_c0 + g * Cfg::kBoxCh, w0 + dx, h0 + dy, n0);
 #pragma unroll
-            for (int g = 0; g < BLOCK_N / 64; ++g)
-              tma_load_4d(n_dst + g * Cfg::kBoxBytes, &p.umap, &full_bar[stage], n_c0 + g * 64, w0, h0, n0);
+            for (int g = 0; g < Cfg::kNBoxes; ++g)
+              tma_load_4d(n_dst + g * Cfg::kBoxBytes, &p.umap, &full_bar[stage], n_c0 + g * Cfg::kBoxCh, w0, h0, n0);
           } else {
 #pragma unroll
-            for (int g = 0; g < 2; ++g)
-              tma_load_4d(m_dst + g * Cfg::kBoxBytes, &p.umap, &full_bar[stage], m_c0 + g * 64, w0, h0, n0);
+            for (int g = 0; g < Cfg::kMBoxes; ++g)
+              tma_load_4d(m_dst + g * Cfg::kBoxBytes, &p.umap, &full_bar[stage], m_c0 + g * Cfg::kBoxCh, w0, h0, n0);
 #pragma unroll
-            for (int g = 0; g < BLOCK_N / 64; ++g)
-              tma_load_4d(n_dst + g * Cfg::kBoxBytes, sm, &full_bar[stage], n_c0 + g * 64, w0 + dx, h0 + dy, n0);
+            for (int g = 0; g < Cfg::kNBoxes; ++g)
+              tma_load_4d(n_dst + g * Cfg::kBoxBytes, sm, &full_bar[stage], n_c0 + g * Cfg::kBoxCh, w0 + dx, h0 + dy, n0);
           }
           }
           __syncwarp();
@@ -146,7 +150,7 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
   } else if (warp == 1) {
     // whole warp converged on uniform values; one elected lane issues (see elect_one_sync in b2g_ptx.cuh)
     const uint32_t leader = elect_one_sync();
-    constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, BLOCK_N);
+    constexpr uint32_t idesc = umma_idesc(/*bf16 = 1, tf32 = 2*/ kTf32 ? 2 : 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, BLOCK_N);
     const uint32_t smem_base = smem_u32(smem);
     int stage = 0;
     uint32_t phase = 0;
@@ -163,12 +167,20 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         const uint32_t m_addr = smem_base + stage * Cfg::kStageBytes;
-        const uint64_t mdesc = umma_smem_desc(m_addr, Cfg::kBoxBytes, 1024);
-        const uint64_t ndesc = umma_smem_desc(m_addr + Cfg::kMBytes, Cfg::kBoxBytes, 1024);
+        const uint64_t mdesc = kTf32 ? umma_smem_desc_sw128_32b(m_addr, Cfg::kBoxBytes, 512)
+                                     : umma_smem_desc(m_addr, Cfg::kBoxBytes, 1024);
+        const uint64_t ndesc = kTf32 ? umma_smem_desc_sw128_32b(m_addr + Cfg::kMBytes, Cfg::kBoxBytes, 512)
+                                     : umma_smem_desc(m_addr + Cfg::kMBytes, Cfg::kBoxBytes, 1024);
         if (leader) {
+          if constexpr (kTf32) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)  // 16 pixels per MMA = two 8-line swizzle groups = 2048 bytes (>> 4 = 128)
-            umma_f16(d_tmem, mdesc + 128 * k, ndesc + 128 * k, idesc, (ks | k) != 0);
+            for (int k = 0; k < 8; ++k)  // 8 pixels per MMA = two 4-line swizzle groups = 1024 bytes (>> 4 = 64)
+              umma_tf32(d_tmem, mdesc + 64 * k, ndesc + 64 * k, idesc, (ks | k) != 0);
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)  // 16 pixels per MMA = two 8-line swizzle groups = 2048 bytes (>> 4 = 128)
+              umma_f16(d_tmem, mdesc + 128 * k, ndesc + 128 * k, idesc, (ks | k) != 0);
+          }
           umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
@@ -235,17 +247,17 @@ __global__ void __launch_bounds__(kWgradThreads, 1) wgrad_kernel(const __grid_co
   }
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool kTf32 = false>
 static int launch_wgrad(const WgradKernelParams& kp, int total_items, cudaStream_t stream) {
-  using Cfg = WgradCfg<BLOCK_N>;
+  using Cfg = WgradCfg<BLOCK_N, kTf32>;
   static bool attr_set = false;
   if (!attr_set) {
-    B2G_CUDA_CHECK(cudaFuncSetAttribute(wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(wgrad_kernel<BLOCK_N, kTf32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         Cfg::kSmemBytes));
     attr_set = true;
   }
   int grid = total_items < num_sms() ? total_items : num_sms();
-  wgrad_kernel<BLOCK_N><<<grid, kWgradThreads, Cfg::kSmemBytes, stream>>>(kp);
+  wgrad_kernel<BLOCK_N, kTf32><<<grid, kWgradThreads, Cfg::kSmemBytes, stream>>>(kp);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
@@ -500,7 +512,10 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
     return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: bad ca_valid=%d for Ca=%d", a->ca_valid, a->Ca);
 
   static int force_taps = []() { const char* e = getenv("B2G_WGRAD_TAPS"); return e ? atoi(e) : -1; }();
-  const bool taps_ok = a->Cb % 128 == 0 && (a->ca_valid == 0 || a->ca_valid == a->Ca) && !a->dbias;
+  const int tf32 = a->tf32 ? 1 : 0;  // fp32 operands, kind::tf32 (the per-layer parity path)
+  if (tf32 && a->kind == B2G_CONV_K1S1)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: the tf32 path covers K3S1 / K4S2");
+  const bool taps_ok = !tf32 && a->Cb % 128 == 0 && (a->ca_valid == 0 || a->ca_valid == a->Ca) && !a->dbias;
   // Measured on B200 (profiles/r1_wgrad_variants.md): grouping taps wins when the other kernel's N tile would be
   // narrow (Cb == 128: 64->128 and 128->128 layers); for Cb >= 256 the per-tap kernel with vector reds is faster.
   const bool use_taps = taps_ok && (force_taps < 0 ? a->Cb == 128 : force_taps != 0);
@@ -544,7 +559,7 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   kp.m_is_shifted = (a->Ca % 128 == 0 || a->Cb % 128 != 0) ? 1 : 0;
   kp.Cm = kp.m_is_shifted ? a->Ca : a->Cb;
   kp.Cn = kp.m_is_shifted ? a->Cb : a->Ca;
-  const int block_n = kp.Cn % 256 == 0 ? 256 : (kp.Cn % 128 == 0 ? 128 : 64);
+  const int block_n = (kp.Cn % 256 == 0 && !tf32) ? 256 : (kp.Cn % 128 == 0 ? 128 : 64);
   kp.m_tiles = (kp.Cm + 127) / 128;
   kp.ca_valid = a->ca_valid > 0 ? a->ca_valid : a->Ca;
   kp.dbias = a->dbias;
@@ -563,13 +578,16 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   if (splits < 1) splits = 1;
   kp.splits = splits;
 
-  const size_t es = 2;
-  const uint32_t box[4] = {64u, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bn};
+  const size_t es = tf32 ? 4 : 2;
+  const CUtensorMapDataType dt = tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  // MN-major 32-bit operands must use the 32-byte-atom flavour of the 128-byte swizzle (see umma_smem_desc_sw128_32b)
+  const CUtensorMapSwizzle sw = tf32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  const uint32_t box[4] = {tf32 ? 32u : 64u, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bn};
   const char* sbase = static_cast<const char*>(a->shifted);
   if (pl.n_amaps == 1) {
     const uint64_t dims[4] = {(uint64_t)a->Ca, (uint64_t)a->Ws, (uint64_t)a->Hs, (uint64_t)a->N};
     const uint64_t str[3] = {(uint64_t)a->Ca * es, (uint64_t)a->Ws * a->Ca * es, (uint64_t)a->Hs * a->Ws * a->Ca * es};
-    int rc = make_tmap(&kp.smap[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, sbase, dims, str, box);
+    int rc = make_tmap(&kp.smap[0], dt, 4, sbase, dims, str, box, sw);
     if (rc) return rc;
   } else {
     for (int py = 0; py < 2; ++py)
@@ -577,18 +595,20 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
         const uint64_t dims[4] = {(uint64_t)a->Ca, (uint64_t)a->Ws / 2, (uint64_t)a->Hs / 2, (uint64_t)a->N};
         const uint64_t str[3] = {(uint64_t)2 * a->Ca * es, (uint64_t)2 * a->Ws * a->Ca * es,
                                  (uint64_t)a->Hs * a->Ws * a->Ca * es};
-        int rc = make_tmap(&kp.smap[py * 2 + px], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
-                           sbase + ((size_t)py * a->Ws + px) * a->Ca * es, dims, str, box);
+        int rc = make_tmap(&kp.smap[py * 2 + px], dt, 4,
+                           sbase + ((size_t)py * a->Ws + px) * a->Ca * es, dims, str, box, sw);
         if (rc) return rc;
       }
   }
   {
     const uint64_t dims[4] = {(uint64_t)a->Cb, (uint64_t)pl.Wg, (uint64_t)pl.Hg, (uint64_t)a->N};
     const uint64_t str[3] = {(uint64_t)a->Cb * es, (uint64_t)pl.Wg * a->Cb * es, (uint64_t)pl.Hg * pl.Wg * a->Cb * es};
-    int rc = make_tmap(&kp.umap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a->unshifted, dims, str, box);
+    int rc = make_tmap(&kp.umap, dt, 4, a->unshifted, dims, str, box, sw);
     if (rc) return rc;
   }
   const int total_items = base_items * kp.splits;
+  if (tf32) return block_n == 128 ? launch_wgrad<128, true>(kp, total_items, stream)
+                                  : launch_wgrad<64, true>(kp, total_items, stream);
   switch (block_n) {
     case 256: return launch_wgrad<256>(kp, total_items, stream);
     case 128: return launch_wgrad<128>(kp, total_items, stream);

@@ -51,6 +51,7 @@ class WgradArgs(C.Structure):
         ("dw", C.c_void_p),
         ("ca_valid", C.c_int),
         ("dbias", C.c_void_p),
+        ("tf32", C.c_int),
     ]
 
 

@@ -131,10 +131,11 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
 
 
 def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: torch.Tensor, ca_valid: int = 0,
-               dbias: torch.Tensor | None = None) -> torch.Tensor:
+               dbias: torch.Tensor | None = None, tf32: bool = False) -> torch.Tensor:
     """dw[tap][a][b] += sum_pixels shifted[tap-shifted pixel, a] * unshifted[pixel, b] (see include/b200gan.h).
 
-    dw is fp32 [k,k,Ca,Cb] and is accumulated into (zero it first for a fresh gradient)."""
+    dw is fp32 [k,k,Ca,Cb] and is accumulated into (zero it first for a fresh gradient).  tf32=True takes fp32
+    operands (kind::tf32 products, the per-layer 1e-3 parity path); the training step uses bf16 operands."""
     _need_cuda(shifted, unshifted, dw)
     n, hs, ws, ca = shifted.shape
     cb = unshifted.shape[3]
@@ -142,13 +143,14 @@ def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: to
     hg, wg = (hs // 2, ws // 2) if kind == CONV_K4S2 else (hs, ws)
     if tuple(unshifted.shape) != (n, hg, wg, cb):
         raise B200GanError(f"conv_wgrad: unshifted operand {tuple(unshifted.shape)} != {(n, hg, wg, cb)}")
-    if shifted.dtype != torch.bfloat16 or unshifted.dtype != torch.bfloat16 or dw.dtype != torch.float32:
-        raise B200GanError("conv_wgrad: operands must be bf16 and dw fp32")
+    want = torch.float32 if tf32 else torch.bfloat16
+    if shifted.dtype != want or unshifted.dtype != want or dw.dtype != torch.float32:
+        raise B200GanError(f"conv_wgrad: operands must be {want} and dw fp32")
     if dw.numel() != k * k * (ca_valid or ca) * cb:
         raise B200GanError("conv_wgrad: bad dw size")
     a = WgradArgs(kind=kind, N=n, Hs=hs, Ws=ws, Ca=ca, Cb=cb, shifted=shifted.data_ptr(),
                   unshifted=unshifted.data_ptr(), dw=dw.data_ptr(), ca_valid=ca_valid,
-                  dbias=None if dbias is None else dbias.data_ptr())
+                  dbias=None if dbias is None else dbias.data_ptr(), tf32=1 if tf32 else 0)
     ev = _prof_begin()
     check(_lib.load().b2g_conv_wgrad(C.byref(a), _stream()), "b2g_conv_wgrad")
     _prof_end(ev, "conv_wgrad", 2.0 * n * hg * wg * (ca_valid or ca) * cb * k * k,

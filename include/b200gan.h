@@ -134,6 +134,9 @@ typedef struct b2g_wgrad_args {
      ca_valid = 0 means Ca. */
   int ca_valid;
   float* dbias;
+  /* 1: shifted / unshifted are fp32 and the products run as tcgen05 kind::tf32 (K3S1 / K4S2 only) — the
+     fp32/tf32 per-layer parity path, see b2g_conv_args.tf32. */
+  int tf32;
 } b2g_wgrad_args;
 
 int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream);

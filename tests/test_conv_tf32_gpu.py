@@ -95,3 +95,59 @@ def test_tf32_convt_fprop(n, h, w, cin, cout):
     y = ops.conv_igemm(ops.CONVT_K4S2, x.cuda(), wp, bias=beta.cuda(), act=ops.ACT_RELU, tf32=True)
     torch.cuda.synchronize()
     assert _rel_l2(y.cpu(), torch.relu(K.conv2d_transpose_same(x, wt, 2) + beta)) < TOL
+
+
+WGRAD_CASES = [
+    # (N, H(grid), W(grid), Cin, Cout): 64x64 (zero-filled M half), transposed store (Cin=64), N tiles of 64 and 128
+    (2, 8, 16, 64, 64),
+    (2, 8, 16, 64, 128),
+    (3, 18, 32, 128, 128),
+    (2, 36, 64, 128, 256),
+    (1, 72, 128, 128, 64),
+    (2, 18, 32, 256, 512),
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout", WGRAD_CASES)
+def test_tf32_wgrad_k3s1(n, h, w, cin, cout):
+    """Weight gradient of a stride-1 3x3 conv from UNROUNDED fp32 operands (kind::tf32, MN-major) at 1e-3."""
+    from imagegeneration_b200 import ops
+    x = _rand((n, h, w, cin), 21)
+    dy = _rand((n, h, w, cout), 22)
+    wt = torch.zeros((3, 3, cin, cout), requires_grad=True)
+    K.conv2d_same(x, wt, None, 1).backward(dy)
+    dw = torch.zeros((3, 3, cin, cout), device="cuda")
+    ops.conv_wgrad(ops.CONV_K3S1, x.cuda(), dy.cuda(), dw, tf32=True)
+    torch.cuda.synchronize()
+    assert _rel_l2(dw.cpu(), wt.grad) < TOL
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout", WGRAD_CASES)
+def test_tf32_wgrad_k4s2_conv_and_convt(n, h, w, cin, cout):
+    from imagegeneration_b200 import ops
+    x = _rand((n, 2 * h, 2 * w, cin), 23)
+    dy = _rand((n, h, w, cout), 24)
+    wt = torch.zeros((4, 4, cin, cout), requires_grad=True)
+    K.conv2d_same(x, wt, None, 2).backward(dy)
+    dw = torch.zeros((4, 4, cin, cout), device="cuda")
+    ops.conv_wgrad(ops.CONV_K4S2, x.cuda(), dy.cuda(), dw, tf32=True)
+    torch.cuda.synchronize()
+    assert _rel_l2(dw.cpu(), wt.grad) < TOL
+    # Conv2DTranspose kernel [4,4,Cout,Cin]: shifted operand = dY, unshifted = the layer input
+    xt_in = _rand((n, h, w, cin), 25)
+    dyt = _rand((n, 2 * h, 2 * w, cout), 26)
+    wtt = torch.zeros((4, 4, cout, cin), requires_grad=True)
+    K.conv2d_transpose_same(xt_in, wtt, 2).backward(dyt)
+    dwt = torch.zeros((4, 4, cout, cin), device="cuda")
+    ops.conv_wgrad(ops.CONV_K4S2, dyt.cuda(), xt_in.cuda(), dwt, tf32=True)
+    torch.cuda.synchronize()
+    assert _rel_l2(dwt.cpu(), wtt.grad) < TOL
+
+
+def test_tf32_wgrad_rejects_bf16_operands():
+    from imagegeneration_b200 import ops
+    from imagegeneration_b200.lib import B200GanError
+    x = torch.zeros((1, 8, 16, 64), device="cuda", dtype=torch.bfloat16)
+    dw = torch.zeros((3, 3, 64, 64), device="cuda")
+    with pytest.raises(B200GanError):
+        ops.conv_wgrad(ops.CONV_K3S1, x, x, dw, tf32=True)
