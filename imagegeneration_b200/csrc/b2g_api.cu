@@ -61,6 +61,43 @@ __global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3
   }
 }
 
+// All packings of one model in ONE launch (the train step re-packs every conv weight after each optimizer update):
+// the jobs travel as kernel parameters, block b works on job j with first_block[j] <= b < first_block[j + 1].
+constexpr int kMaxPackJobs = 24;
+constexpr int kPackElemsPerBlock = 2048;
+struct PackJobDev {
+  int kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, taps, first_block;
+  long total;
+  const float *w, *scale_scalar, *scale_d2, *scale_d3;
+  __nv_bfloat16* out;
+};
+struct alignas(16) PackMultiParams {
+  PackJobDev job[kMaxPackJobs];
+  int n_jobs;
+};
+
+__global__ void __launch_bounds__(256) pack_conv_weight_multi_kernel(const __grid_constant__ PackMultiParams p) {
+  int j = 0;
+  while (j + 1 < p.n_jobs && (int)blockIdx.x >= p.job[j + 1].first_block) ++j;
+  const PackJobDev& q = p.job[j];
+  const float s0 = q.scale_scalar ? *q.scale_scalar : 1.f;
+  const long base = (long)(blockIdx.x - q.first_block) * kPackElemsPerBlock;
+#pragma unroll 1
+  for (int e = threadIdx.x; e < kPackElemsPerBlock; e += 256) {
+    const long i = base + e;
+    if (i >= q.total) break;
+    int d2, d3;
+    const long src = pack_source_index(q.kind, q.kh, q.kw, q.D2, q.D3, q.n_is_d3, q.flip, q.ck_pad, q.taps, i, &d2, &d3);
+    float v = 0.f;
+    if (src >= 0) {
+      v = q.w[src] * s0;
+      if (q.scale_d2) v *= q.scale_d2[d2];
+      if (q.scale_d3) v *= q.scale_d3[d3];
+    }
+    q.out[i] = __float2bfloat16_rn(v);
+  }
+}
+
 }  // namespace b2g
 
 using namespace b2g;
@@ -68,11 +105,8 @@ using namespace b2g;
 extern "C" int b2g_version(void) { return 100; }
 extern "C" const char* b2g_last_error(void) { return error_buffer(); }
 
-static int pack_conv_weight_any(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
-                                const float* w, const float* scale_scalar, const float* scale_d2,
-                                const float* scale_d3, void* wpacked, b2g_stream_t stream_, bool f32) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (!w || !wpacked) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: null pointer");
+// phases / taps of a packing kind; rejects kernel sizes and flips the kind does not define
+static int pack_geometry(int kind, int kh, int kw, int flip, int* phases_out, int* taps_out) {
   int phases, taps;
   if (kind == B2G_CONV_K3S1) {
     if (kh != 3 || kw != 3) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: K3S1 needs a 3x3 kernel");
@@ -89,6 +123,19 @@ static int pack_conv_weight_any(int kind, int kh, int kw, int D2, int D3, int n_
   } else {
     return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: unknown kind %d", kind);
   }
+  *phases_out = phases;
+  *taps_out = taps;
+  return B2G_OK;
+}
+
+static int pack_conv_weight_any(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad,
+                                const float* w, const float* scale_scalar, const float* scale_d2,
+                                const float* scale_d3, void* wpacked, b2g_stream_t stream_, bool f32) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!w || !wpacked) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight: null pointer");
+  int phases, taps;
+  int rc = pack_geometry(kind, kh, kw, flip, &phases, &taps);
+  if (rc) return rc;
   const int ckr = n_is_d3 ? D2 : D3, cn = n_is_d3 ? D3 : D2;
   const int ck = ck_pad > ckr ? ck_pad : ckr;
   const long total = (long)phases * taps * cn * ck;
@@ -118,6 +165,35 @@ extern "C" int b2g_pack_conv_weight_f32(int kind, int kh, int kw, int D2, int D3
                                         const float* scale_d3, void* wpacked, b2g_stream_t stream) {
   return pack_conv_weight_any(kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, w, scale_scalar, scale_d2, scale_d3, wpacked,
                               stream, true);
+}
+
+extern "C" int b2g_pack_conv_weight_multi(const b2g_pack_job* jobs, int n_jobs, b2g_stream_t stream_) {
+  if (!jobs || n_jobs <= 0 || n_jobs > kMaxPackJobs)
+    return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight_multi: 1..%d jobs", kMaxPackJobs);
+  PackMultiParams p;
+  memset(&p, 0, sizeof(p));
+  int blocks = 0;
+  for (int j = 0; j < n_jobs; ++j) {
+    const b2g_pack_job& s = jobs[j];
+    if (!s.w || !s.wpacked) return fail(B2G_E_INVALID_ARG, "b2g_pack_conv_weight_multi: null pointer in job %d", j);
+    int phases, taps;
+    int rc = pack_geometry(s.kind, s.kh, s.kw, s.flip, &phases, &taps);
+    if (rc) return rc;
+    const int ckr = s.n_is_d3 ? s.D2 : s.D3, cn = s.n_is_d3 ? s.D3 : s.D2;
+    const int ck = s.ck_pad > ckr ? s.ck_pad : ckr;
+    PackJobDev& d = p.job[j];
+    d.kind = s.kind; d.kh = s.kh; d.kw = s.kw; d.D2 = s.D2; d.D3 = s.D3;
+    d.n_is_d3 = s.n_is_d3; d.flip = s.flip; d.ck_pad = s.ck_pad; d.taps = taps;
+    d.total = (long)phases * taps * cn * ck;
+    d.first_block = blocks;
+    d.w = s.w; d.scale_scalar = s.scale_scalar; d.scale_d2 = s.scale_d2; d.scale_d3 = s.scale_d3;
+    d.out = static_cast<__nv_bfloat16*>(s.wpacked);
+    blocks += (int)((d.total + kPackElemsPerBlock - 1) / kPackElemsPerBlock);
+  }
+  p.n_jobs = n_jobs;
+  pack_conv_weight_multi_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
 }
 
 // ---- host-only introspection (no CUDA calls): lets the CPU test-suite check the tiling / tap / packing logic ----

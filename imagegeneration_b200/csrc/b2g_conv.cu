@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
   }
   if (p.e.bias) {
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
-    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i];
+    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
@@ -250,6 +250,8 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
   if (a->Cout > 512) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cout=%d > 512", a->Cout);
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
+  if (a->dropout_thresh8 > 0 && a->act == B2G_ACT_TANH)  // the dropout scale is applied before the activation
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout needs a positively homogeneous activation (none/leaky/relu)");
 
   ConvKernelParams kp;
   memset(&kp, 0, sizeof(kp));

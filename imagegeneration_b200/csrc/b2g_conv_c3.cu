@@ -1,11 +1,16 @@
 // b2g_conv_c3.cu — 3x3 stride-1 SAME convolution over a 3-channel fp32 tensor (3 -> 64 channels) on tcgen05, with
 // the im2col operand built IN SHARED MEMORY instead of in HBM.
 //
-//   warp 0      : loads the packed [64][64] weight tile once (TMA); it stays resident for the whole kernel
+//   warp 0      : loads the packed [64][64] weight tile once (TMA; resident for the whole kernel), then streams the
+//                 fp32 input: per 128-pixel tile ONE TMA box = the tile's pixels plus a one-pixel halo
+//                 ((bw+8)*3 floats x (bh+2) rows x bn images; out-of-image parts arrive as zeros = SAME padding;
+//                 the box starts 4 pixels left of the tile because TMA wants a 16-byte aligned start offset)
+//                 through an 8-stage ring — the HBM/L2 latency is hidden by the ring, not by the builder threads
 //   warp 1      : TMEM allocator + MMA issuer — one K=32 step (two K=16 MMAs, M=128, N=64) per 128-pixel tile
-//   warps 2..5  : patch builders, one pixel per thread: 27 fp32 loads (zero outside the image) + a ones column ->
-//                 32 bf16 = 4 x 16 B written at the SW128-swizzled position of the pixel's row, fence.proxy.async,
-//                 mbarrier arrive.  This is the im2col27 tensor of b2g_edge.cu, never leaving the SM.
+//   warps 2..5  : patch builders, one pixel per thread: 27 conflict-free LDS.32 from the staged box + a ones
+//                 column -> 32 bf16 = 4 x 16 B written at the SW128-swizzled position of the pixel's row,
+//                 fence.proxy.async, mbarrier arrive.  This is the im2col27 tensor of b2g_edge.cu, never leaving
+//                 the SM.
 //   warps 6..21 : epilogue (4 groups x 4 TMEM lane quarters, 4 accumulator buffers): bias / LeakyReLU / dropout or
 //                 ReLU' from the saved output, bf16 NHWC stores (b2g_conv_epi.cuh)
 //
@@ -23,22 +28,28 @@ namespace b2g {
 
 struct alignas(64) C3KernelParams {
   CUtensorMap bmap;
-  ConvPlan plan;  // K1S1 geometry: 128-pixel boxes (bw, bh, bn) over the N x H x W grid
+  CUtensorMap imap;  // fp32 input seen as 8-byte elements: dims {W*3/2, H, N}, box {(bw+8)*3/2, bh+2, bn}
+  ConvPlan plan;     // K1S1 geometry: 128-pixel boxes (bw, bh, bn) over the N x H x W grid
   EpiParams e;
-  const float* in;  // fp32 [N, H, W, 3]
+  EpiTmaMaps em;     // TMA epilogue (used when e.tma)
+  int in_box_bytes;  // bytes one input box delivers
 };
 
 struct C3Cfg {
   static constexpr int kBlockN = 64;
   static constexpr int kABytes = 128 * 128;  // 128 pixel rows of 128 B; only the first 64 B (K = 32) are used
   static constexpr int kStages = 6;
+  static constexpr int kInStages = 8;           // staged fp32 input boxes
+  static constexpr int kInStageBytes = 8192;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896)
   static constexpr int kBBytes = kBlockN * 128;
   static constexpr int kAccBufs = 4;
   static constexpr int kTmemCols = kAccBufs * kBlockN;
   static constexpr int kBuilderWarps = 4;
   static constexpr int kEpiGroups = 4;
   static constexpr int kThreads = 64 + 32 * kBuilderWarps + 128 * kEpiGroups;
-  static constexpr int kSmemBytes = kStages * kABytes + kBBytes + 256 + 1024;
+  static constexpr int kMainBytes = kStages * kABytes + kBBytes + kInStages * kInStageBytes;  // multiple of 1 KiB
+  static constexpr int kEpiWarps = 4 * kEpiGroups;
+  static constexpr int kSmemBytes = kMainBytes + epi_tma_smem_bytes(kEpiWarps) + 512 + 1024;
 };
 
 __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __grid_constant__ C3KernelParams p) {
@@ -49,12 +60,16 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* bsm = smem + Cfg::kStages * Cfg::kABytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bsm + Cfg::kBBytes);
+  uint8_t* insm = bsm + Cfg::kBBytes;
+  uint8_t* epism = smem + Cfg::kMainBytes;  // per-warp boxes of the TMA epilogue
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epism + epi_tma_smem_bytes(Cfg::kEpiWarps));
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint64_t* tempty_bar = tfull_bar + Cfg::kAccBufs;
   uint64_t* bfull_bar = tempty_bar + Cfg::kAccBufs;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull_bar + 1);
+  uint64_t* in_full = bfull_bar + 1;
+  uint64_t* in_empty = in_full + Cfg::kInStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(in_empty + Cfg::kInStages);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -71,9 +86,14 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       mbar_init(&tempty_bar[a], 4 * kChunks);
     }
     mbar_init(bfull_bar, 1);
+    for (int s = 0; s < Cfg::kInStages; ++s) {
+      mbar_init(&in_full[s], 1);
+      mbar_init(&in_empty[s], Cfg::kBuilderWarps);
+    }
+    if (p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps);
     fence_barrier_init();
   }
-  if (p.e.bias && threadIdx.x < BLOCK_N) sbias[threadIdx.x] = p.e.bias[threadIdx.x];
+  epi_load_bias(p.e, sbias, BLOCK_N);
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -81,13 +101,30 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ------------------------------------------------ weight tile: loaded once, resident
-    if (elect_one_sync()) {
+    // ------------------------------------------------ weight tile: loaded once, resident; then the input stream
+    const uint32_t leader = elect_one_sync();
+    if (leader) {
       tma_prefetch_desc(&p.bmap);
+      tma_prefetch_desc(&p.imap);
       mbar_expect_tx(bfull_bar, Cfg::kBBytes);
       tma_load_2d(bsm, &p.bmap, bfull_bar, 0, 0);
     }
     __syncwarp();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const TileCoord tc = decode_tile(pl, 1, tile);
+      mbar_wait(&in_empty[stage], phase ^ 1);
+      if (leader) {
+        mbar_expect_tx(&in_full[stage], p.in_box_bytes);
+        // box origin: pixel (w0 - 4, h0 - 1) of image n0; 3 floats per pixel, 2 floats per 8-byte element.
+        // (Measured: a start offset that is not a multiple of 16 bytes is an illegal-instruction fault.)
+        tma_load_3d(insm + stage * Cfg::kInStageBytes, &p.imap, &in_full[stage], (tc.tw * pl.bw - 4) * 3 / 2,
+                    tc.th * pl.bh - 1, tc.tn * pl.bn);
+      }
+      __syncwarp();
+      if (++stage == Cfg::kInStages) { stage = 0; phase ^= 1; }
+    }
   } else if (warp == 1) {
     // ------------------------------------------------ MMA issuer (whole warp converged; one elected lane issues)
     const uint32_t leader = elect_one_sync();
@@ -118,66 +155,43 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     // ------------------------------------------------ patch builders: thread m owns pixel row m of the A tile
     const int m = threadIdx.x - 64;
     const int wl = m % pl.bw, hl = (m / pl.bw) % pl.bh, nl = m / (pl.bw * pl.bh);
-    const int H = pl.Hg, W = pl.Wg;
     const uint32_t row_off = m * 128, sw = m & 7;
-    // gathers the 27 taps*channels of this thread's pixel of `tile` (zeros outside the image, ones column at 27).
-    // The loads are volatile asm so that the compiler keeps them BEFORE the mbarrier wait / pack of the previous
-    // tile (it otherwise sinks them behind the pack and the whole L2 latency is exposed once per tile).
-    auto gather = [&](int tile, float (&v)[28]) {
-      const TileCoord tc = decode_tile(pl, 1, tile);
-      const int x = tc.tw * pl.bw + wl, y = tc.th * pl.bh + hl, n = tc.tn * pl.bn + nl;
+    // this thread's window inside a staged box [bn][bh + 2][(bw + 8) * 3 floats]: rows hl..hl+2, nine consecutive
+    // floats from pixel wl + 3 (= image pixel x - 1).  Consecutive lanes are 3 words apart: conflict-free LDS.32.
+    const int pitch = (pl.bw + 8) * 3;
+    const int win_off = ((nl * (pl.bh + 2) + hl) * (pl.bw + 8) + wl + 3) * 3;
+    int stage = 0, istage = 0;
+    uint32_t phase = 0, iphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      float v[32];
+      mbar_wait_parked(&in_full[istage], iphase);
+      const float* src = reinterpret_cast<const float*>(insm + istage * Cfg::kInStageBytes) + win_off;
 #pragma unroll
-      for (int k = 0; k < 28; ++k) v[k] = 0.f;
-      if (y < H && n < pl.N) {
-        const float* img = p.in + (size_t)n * H * W * 3;
+      for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-        for (int ky = 0; ky < 3; ++ky) {
-          const int yy = y + ky - 1;
-          if (yy < 0 || yy >= H) continue;
-          const float* rowp = img + ((size_t)yy * W + x) * 3;
+        for (int j = 0; j < 9; ++j) v[ky * 9 + j] = src[ky * pitch + j];  // j = kx * 3 + c
+      v[27] = 1.f;
 #pragma unroll
-          for (int j = 0; j < 9; ++j) {  // j = kx * 3 + c: nine consecutive floats starting at pixel x - 1
-            const int xx = x + j / 3 - 1;
-            if (xx >= 0 && xx < W)
-              asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v[ky * 9 + j]) : "l"(rowp + j - 3));
-          }
-        }
-        v[27] = 1.f;
-      }
-    };
-    int stage = 0;
-    uint32_t phase = 0;
-    // packs one gathered pixel into its swizzled 64 bytes of the A stage and hands the stage to the MMA warp
-    auto emit = [&](const float (&v)[28]) {
-      mbar_wait(&empty_bar[stage], phase ^ 1);
+      for (int k = 28; k < 32; ++k) v[k] = 0.f;
+      mbar_wait_parked(&empty_bar[stage], phase ^ 1);
       uint8_t* dst = smem + stage * Cfg::kABytes + row_off;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         uint4 o;
         o.x = pack_bf16x2(v[j * 8 + 0], v[j * 8 + 1]);
         o.y = pack_bf16x2(v[j * 8 + 2], v[j * 8 + 3]);
-        o.z = j < 3 ? pack_bf16x2(v[j < 3 ? j * 8 + 4 : 0], v[j < 3 ? j * 8 + 5 : 0]) : 0u;  // columns 28..31 = 0
-        o.w = j < 3 ? pack_bf16x2(v[j < 3 ? j * 8 + 6 : 0], v[j < 3 ? j * 8 + 7 : 0]) : 0u;
+        o.z = pack_bf16x2(v[j * 8 + 4], v[j * 8 + 5]);
+        o.w = pack_bf16x2(v[j * 8 + 6], v[j * 8 + 7]);
         *reinterpret_cast<uint4*>(dst + ((j ^ sw) << 4)) = o;  // 128-byte swizzle: 16-byte chunk j of row m -> j ^ (m & 7)
       }
       fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's async-proxy reads
       __syncwarp();
-      if (lane == 0) mbar_arrive(&full_bar[stage]);
+      if (lane == 0) {
+        mbar_arrive(&in_empty[istage]);  // the box was consumed into registers before the stores above
+        mbar_arrive(&full_bar[stage]);
+      }
       if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-    };
-    // software pipeline, two register sets: the next tile's loads are in flight while this tile is packed
-    float va[28], vb[28];
-    const int step = gridDim.x;
-    int tile = blockIdx.x;
-    if (tile < total_tiles) gather(tile, va);
-    while (tile < total_tiles) {
-      if (tile + step < total_tiles) gather(tile + step, vb);
-      emit(va);
-      tile += step;
-      if (tile >= total_tiles) break;
-      if (tile + step < total_tiles) gather(tile + step, va);
-      emit(vb);
-      tile += step;
+      if (++istage == Cfg::kInStages) { istage = 0; iphase ^= 1; }
     }
   } else {
     // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
@@ -185,6 +199,10 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     const int grp = (warp - 2 - Cfg::kBuilderWarps) >> 2;
     const int row = q * 32 + lane;
     const int wl = row % pl.bw, hl = (row / pl.bw) % pl.bh, nl = row / (pl.bw * pl.bh);
+    // origin of this warp's 32-pixel box inside a tile (TMA epilogue)
+    const int wl0 = (q * 32) % pl.bw, hl0 = ((q * 32) / pl.bw) % pl.bh, nl0 = (q * 32) / (pl.bw * pl.bh);
+    EpiWarpStage st = epi_tma_stage(epism, Cfg::kEpiWarps, warp - 2 - Cfg::kBuilderWarps);
+    const bool use_tma = p.e.tma != 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int c = (grp - it * kChunks) & (Cfg::kEpiGroups - 1);  // chunk c of tile `it` belongs to group (2*it + c) % 4
@@ -194,17 +212,21 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       const int gw = tc.tw * pl.bw + wl, gh = tc.th * pl.bh + hl, gn = tc.tn * pl.bn + nl;
       const bool valid = (gh < pl.Hg) && (gn < pl.N);
       const size_t pix = (static_cast<size_t>(gn) * pl.Hout + gh) * pl.Wout + gw;
-      mbar_wait(&tfull_bar[as], (it / Cfg::kAccBufs) & 1);
+      const int bx = tc.tw * pl.bw + wl0, by = tc.th * pl.bh + hl0, bn = tc.tn * pl.bn + nl0;
+      if (use_tma) epi_tma_begin(p.e, &p.em.ymap[0], st, c * 32, bx, by, bn);
+      mbar_wait_parked(&tfull_bar[as], (it / Cfg::kAccBufs) & 1);
       tc_fence_after();
       uint32_t r[32];
       __syncwarp();
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
       tmem_ld_wait();
-      conv_epilogue_chunk(p.e, sbias, r, pix, c * 32, valid);
+      if (use_tma) epi_tma_chunk(p.e, &p.em.omap[0], st, sbias, r, pix, c * 32, lane, bx, by, bn);
+      else conv_epilogue_chunk(p.e, sbias, r, pix, c * 32, valid);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[as]);
     }
+    if (use_tma) epi_tma_end();
   }
 
   tc_fence_before();
@@ -222,12 +244,30 @@ int launch_conv_c3(const b2g_conv_args* a, void* stream_) {
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255)
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
+  if (a->dropout_thresh8 > 0 && a->act == B2G_ACT_TANH)
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout needs a positively homogeneous activation (none/leaky/relu)");
   C3KernelParams kp;
   memset(&kp, 0, sizeof(kp));
   if (!build_conv_plan(a->kind, a->N, a->Hin, a->Win, 64, a->Cout, 128, &kp.plan))
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm(K3S1_C3): cannot tile N=%d H=%d W=%d", a->N, a->Hin, a->Win);
   fill_epi_params(a, &kp.e);
-  kp.in = static_cast<const float*>(a->in);
+  {
+    int rc = fill_epi_tma(a, kp.plan, true, &kp.e, &kp.em);
+    if (rc) return rc;
+  }
+  {
+    const ConvPlan& pl = kp.plan;
+    kp.in_box_bytes = pl.bn * (pl.bh + 2) * (pl.bw + 8) * 12;
+    if (pl.bw % 4 || a->Win % 4 || kp.in_box_bytes > C3Cfg::kInStageBytes)
+      return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm(K3S1_C3): cannot stage N=%d H=%d W=%d (box %d bytes)", a->N,
+                  a->Hin, a->Win, kp.in_box_bytes);
+    // 8-byte elements (two floats): the 3-float pixels cannot be a TMA dimension (12 bytes), 2-float units can
+    const uint64_t dims[3] = {(uint64_t)a->Win * 3 / 2, (uint64_t)a->Hin, (uint64_t)a->N};
+    const uint64_t str[2] = {(uint64_t)a->Win * 12, (uint64_t)a->Hin * a->Win * 12};
+    const uint32_t ibox[3] = {(uint32_t)(pl.bw + 8) * 3 / 2, (uint32_t)pl.bh + 2, (uint32_t)pl.bn};
+    int rc = make_tmap(&kp.imap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, a->in, dims, str, ibox, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
+  }
   {
     const uint64_t dims[2] = {64u, (uint64_t)a->Cout};
     const uint64_t str[1] = {64u * 2u};

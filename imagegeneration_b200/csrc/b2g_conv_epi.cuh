@@ -6,6 +6,10 @@
 // Replaces the BiasAdd / LeakyRelu / Relu / Tanh / Dropout ops and their gradients that TensorFlow runs as
 // separate kernels after each convolution (sndcgan/SNDCGAN.py:40-41,:61,:77-78).
 #pragma once
+#include <stdlib.h>
+
+#include "b2g_conv.cuh"
+#include "b2g_host.h"
 #include "b2g_ptx.cuh"
 #include "../../include/b200gan.h"
 
@@ -19,6 +23,9 @@ struct EpiParams {
   float alpha;
   int drop_thresh8;
   float drop_scale;
+  float pre_scale;  // dropout scale 1/(1-rate) applied BEFORE the (positively homogeneous) activation, folded into
+                    // the bias FFMA; the kernels' shared bias tables hold bias * pre_scale (epi_load_bias)
+  int leaky_max;    // 0 <= alpha <= 1: LeakyReLU(v) = max(v, alpha * v)
   uint32_t seed_lo, seed_hi;
   int dact;
   float dact_alpha, dact_scale, dact_zero;
@@ -26,43 +33,44 @@ struct EpiParams {
   int cs;       // channel stride of the output tensor (== Cout unless out_f32)
   int Cout;
   int f32_io;   // tf32 path: out / yprev are full-width fp32 [pixels][Cout]
+  int tma;      // 1: bf16 output (and yprev) move through per-warp shared-memory boxes and TMA (EpiTmaMaps)
+  int qw, qh, qn;  // the 32 pixels one epilogue warp owns, as a box of the tile (qw * qh * qn == 32)
 };
 
-// r: 32 accumulator columns [cb, cb+32) of output pixel `pix` (flat N*H*W index); `valid` = pixel inside the tensor.
-__device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
-                                                    size_t pix, int cb, bool valid) {
-  if (p.out_f32) {  // narrow fp32 output (3 real channels): tanh / tanh' epilogues of the generator's last layer
-    if (valid && cb < p.cs) {
-      float* of = reinterpret_cast<float*>(p.out) + pix * p.cs + cb;
-      const float* yf = reinterpret_cast<const float*>(p.yprev) + pix * p.cs + cb;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (cb + j < p.cs) {
-          float o = __uint_as_float(r[j]);
-          if (p.bias) o += sbias[cb + j];
-          if (p.act == B2G_ACT_TANH) o = tanhf(o);
-          if (p.dact == B2G_ACT_TANH) {
-            const float y = __ldg(yf + j);
-            o *= 1.f - y * y;
-          }
-          of[j] = o;
-        }
-      }
-    }
-    return;
-  }
+// Tensor maps of the TMA epilogue: bf16 NHWC output / saved forward output, one map per output phase (transposed
+// conv: phase (py, px) is the stride-2 sub-grid starting at (py, px)); box {32 channels, qw, qh, qn}, 64-byte swizzle.
+struct alignas(64) EpiTmaMaps {
+  CUtensorMap omap[4];
+  CUtensorMap ymap[4];
+};
+constexpr int kEpiStageBytes = 2048;  // one warp's [32 pixels][32 channels] bf16 box
+
+// bias -> activation -> dropout -> activation derivative -> bf16 (or full-width fp32) store for 32 channels of one
+// pixel.  yload(g) returns 16-byte group g (8 bf16) of the saved forward output, ostore(g, o) stores output group g;
+// both are only called for bf16 tensors and valid pixels.
+template <class YLoad, class OStore>
+__device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
+                                                   size_t pix, int cb, bool valid, YLoad yload, OStore ostore) {
   const size_t off = pix * p.Cout + cb;  // element offset of this thread's 32 outputs
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-  if (p.bias) {
+  if (p.bias) {  // (acc + bias) * pre_scale as one FFMA per element
+    const float ps = p.pre_scale;
 #pragma unroll
     for (int j4 = 0; j4 < 8; ++j4) {
       const float4 b4 = *reinterpret_cast<const float4*>(&sbias[cb + j4 * 4]);
-      v[j4 * 4 + 0] += b4.x; v[j4 * 4 + 1] += b4.y; v[j4 * 4 + 2] += b4.z; v[j4 * 4 + 3] += b4.w;
+      v[j4 * 4 + 0] = fmaf(v[j4 * 4 + 0], ps, b4.x); v[j4 * 4 + 1] = fmaf(v[j4 * 4 + 1], ps, b4.y);
+      v[j4 * 4 + 2] = fmaf(v[j4 * 4 + 2], ps, b4.z); v[j4 * 4 + 3] = fmaf(v[j4 * 4 + 3], ps, b4.w);
     }
+  } else if (p.pre_scale != 1.f) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] *= p.pre_scale;
   }
-  if (p.act == B2G_ACT_LEAKY) {
+  if (p.act == B2G_ACT_LEAKY && p.leaky_max) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], v[j] * p.alpha);
+  } else if (p.act == B2G_ACT_LEAKY) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * p.alpha;
   } else if (p.act == B2G_ACT_RELU) {
@@ -70,15 +78,18 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
     for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
   }
   if (p.drop_thresh8 > 0 && valid) {
+    // element i keeps its value iff byte (i & 3) of the group's hash >= thresh8: the byte is moved to the top of
+    // the word and compared with thresh8 << 24 (the junk below it cannot change the outcome); the 1/(1-rate)
+    // scale was applied before the activation (pre_scale)
     const uint32_t g0 = static_cast<uint32_t>(off >> 2);
+    const uint32_t t24 = static_cast<uint32_t>(p.drop_thresh8) << 24;
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
       const uint32_t bits = b2g_dropout_bits(g0 + g, p.seed_lo, p.seed_hi);
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const int byte = (bits >> (8 * b)) & 0xFF;
-        v[g * 4 + b] = byte < p.drop_thresh8 ? 0.f : v[g * 4 + b] * p.drop_scale;
-      }
+      v[g * 4 + 0] = (bits << 24) >= t24 ? v[g * 4 + 0] : 0.f;
+      v[g * 4 + 1] = (bits << 16) >= t24 ? v[g * 4 + 1] : 0.f;
+      v[g * 4 + 2] = (bits << 8) >= t24 ? v[g * 4 + 2] : 0.f;
+      v[g * 4 + 3] = bits >= t24 ? v[g * 4 + 3] : 0.f;
     }
   }
   if (p.dact != B2G_ACT_NONE && valid && p.f32_io) {
@@ -98,10 +109,9 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
       }
     }
   } else if (p.dact != B2G_ACT_NONE && valid) {
-    const uint4* yp = reinterpret_cast<const uint4*>(p.yprev + off);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
-      const uint4 yv = __ldg(yp + g);
+      const uint4 yv = yload(g);
       const uint32_t w4[4] = {yv.x, yv.y, yv.z, yv.w};
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
@@ -127,7 +137,6 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
 #pragma unroll
     for (int g = 0; g < 8; ++g) op[g] = make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
   } else if (valid) {
-    uint4* op = reinterpret_cast<uint4*>(p.out + off);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       uint4 o;
@@ -135,9 +144,113 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
       o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
       o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
       o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
-      op[g] = o;
+      ostore(g, o);
     }
   }
+}
+
+// r: 32 accumulator columns [cb, cb+32) of output pixel `pix` (flat N*H*W index); `valid` = pixel inside the tensor.
+__device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
+                                                    size_t pix, int cb, bool valid) {
+  if (p.out_f32) {  // narrow fp32 output (3 real channels): tanh / tanh' epilogues of the generator's last layer
+    if (valid && cb < p.cs) {
+      float* of = reinterpret_cast<float*>(p.out) + pix * p.cs + cb;
+      const float* yf = reinterpret_cast<const float*>(p.yprev) + pix * p.cs + cb;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (cb + j < p.cs) {
+          float o = __uint_as_float(r[j]);
+          if (p.bias) o += sbias[cb + j];
+          if (p.act == B2G_ACT_TANH) o = tanhf(o);
+          if (p.dact == B2G_ACT_TANH) {
+            const float y = __ldg(yf + j);
+            o *= 1.f - y * y;
+          }
+          of[j] = o;
+        }
+      }
+    }
+    return;
+  }
+  conv_epilogue_math(
+      p, sbias, r, pix, cb, valid,
+      [&](int g) { return __ldg(reinterpret_cast<const uint4*>(p.yprev + pix * p.Cout + cb) + g); },
+      [&](int g, const uint4& o) { reinterpret_cast<uint4*>(p.out + pix * p.Cout + cb)[g] = o; });
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// TMA-staged variant.  A thread-per-pixel epilogue writes 16 bytes per lane into 32 different 128-byte lines per
+// store instruction: 32 LSU wavefronts each, 128 per 32x32 chunk (and as many again for the saved-output loads of a
+// backward epilogue) — measured as THE bottleneck of the layers with <= 128 output channels (profiles/r1_v6_*).
+// Here each epilogue warp owns one 2 KiB shared-memory box [32 pixels][32 channels] (64-byte swizzle, conflict
+// free 16-byte accesses): the saved output arrives in it by TMA, the results leave from it by TMA.
+// ---------------------------------------------------------------------------------------------------------------
+struct EpiWarpStage {
+  uint8_t* buf;     // this warp's box (1 KiB aligned)
+  uint64_t* ybar;   // mbarrier of the saved-output loads into buf
+  uint32_t yphase;
+};
+
+// Shared memory the TMA epilogue needs behind a kernel's own buffers (1 KiB aligned): boxes, then mbarriers.
+__host__ __device__ constexpr int epi_tma_smem_bytes(int warps) { return warps * kEpiStageBytes + 256; }
+
+__device__ __forceinline__ EpiWarpStage epi_tma_stage(uint8_t* base, int warps, int w) {
+  EpiWarpStage st;
+  st.buf = base + w * kEpiStageBytes;
+  st.ybar = reinterpret_cast<uint64_t*>(base + warps * kEpiStageBytes) + w;
+  st.yphase = 0;
+  return st;
+}
+// by one thread, before fence_barrier_init() and the block-wide sync
+__device__ __forceinline__ void epi_tma_init(uint8_t* base, int warps) {
+  for (int w = 0; w < warps; ++w) mbar_init(reinterpret_cast<uint64_t*>(base + warps * kEpiStageBytes) + w, 1);
+}
+
+// Whole warp, as early as possible (before waiting for the accumulator): frees the box (the previous store has read
+// it) and starts loading the saved forward output of channels [cb, cb+32) of the warp's pixels (box origin bx, by, bn
+// in the phase grid).
+__device__ __forceinline__ void epi_tma_begin(const EpiParams& p, const CUtensorMap* ymap, const EpiWarpStage& st,
+                                              int cb, int bx, int by, int bn) {
+  if (elect_one_sync()) {  // elect.sync picks the same lane for the same mask: the bulk groups stay with one thread
+    tma_store_wait_read();
+    if (p.dact != B2G_ACT_NONE) {
+      mbar_expect_tx(st.ybar, kEpiStageBytes);
+      tma_load_4d(st.buf, ymap, st.ybar, cb, bx, by, bn);
+    }
+  }
+  __syncwarp();
+}
+
+// Whole warp: epilogue math of one chunk (lane = pixel) through the box, then the TMA store.
+__device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensorMap* omap, EpiWarpStage& st,
+                                              const float* sbias, const uint32_t (&r)[32], size_t pix, int cb, int lane,
+                                              int bx, int by, int bn) {
+  uint8_t* row = st.buf + lane * 64;
+  const uint32_t sw = (lane >> 1) & 3;  // 64-byte swizzle: 16-byte group g of row i lives at g ^ ((i >> 1) & 3)
+  if (p.dact != B2G_ACT_NONE) {
+    mbar_wait(st.ybar, st.yphase);
+    st.yphase ^= 1;
+  }
+  conv_epilogue_math(
+      p, sbias, r, pix, cb, true,
+      [&](int g) { return *reinterpret_cast<const uint4*>(row + ((g ^ sw) << 4)); },
+      [&](int g, const uint4& o) { *reinterpret_cast<uint4*>(row + ((g ^ sw) << 4)) = o; });
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (elect_one_sync()) tma_store_4d(omap, st.buf, cb, bx, by, bn);
+  __syncwarp();
+}
+
+// Whole warp, before the kernel's final block-wide sync: the last store must have read the box.
+__device__ __forceinline__ void epi_tma_end() {
+  if (elect_one_sync()) tma_store_wait_read();
+  __syncwarp();
+}
+
+// Block-wide: shared bias table = bias[0..n) * pre_scale (see EpiParams::pre_scale); call before the block sync.
+__device__ __forceinline__ void epi_load_bias(const EpiParams& p, float* sbias, int n) {
+  if (p.bias)
+    for (int i = threadIdx.x; i < n; i += blockDim.x) sbias[i] = p.bias[i] * p.pre_scale;
 }
 
 // Fills the epilogue parameters from the C-ABI arguments.
@@ -149,6 +262,8 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->alpha = a->alpha;
   e->drop_thresh8 = a->dropout_thresh8;
   e->drop_scale = 256.f / (256.f - (float)a->dropout_thresh8);
+  e->pre_scale = a->dropout_thresh8 > 0 ? e->drop_scale : 1.f;  // act is NONE / LEAKY / RELU here (validated)
+  e->leaky_max = (a->alpha >= 0.f && a->alpha <= 1.f) ? 1 : 0;
   e->seed_lo = (uint32_t)(a->dropout_seed & 0xFFFFFFFFull);
   e->seed_hi = (uint32_t)(a->dropout_seed >> 32);
   e->dact = a->dact;
@@ -159,6 +274,39 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->cs = a->out_f32 ? a->cout_store : a->Cout;
   e->Cout = a->Cout;
   e->f32_io = a->tf32;
+  e->tma = 0;
+}
+
+// Host: decides whether the TMA epilogue applies and builds its tensor maps (b2g_conv_epi_host.cu-free: inline).
+// `enabled` lets a kernel without shared-memory room opt out.
+inline int fill_epi_tma(const b2g_conv_args* a, const ConvPlan& pl, bool enabled, EpiParams* e, EpiTmaMaps* m) {
+  static int env = []() { const char* s = getenv("B2G_EPI_TMA"); return s ? atoi(s) : 1; }();
+  e->tma = 0;
+  if (!enabled || !env || a->out_f32 || a->tf32 || a->Cout % 32) return B2G_OK;
+  const int qw = pl.bw < 32 ? pl.bw : 32;
+  const int qh = pl.bh < 32 / qw ? pl.bh : 32 / qw;
+  const int qn = 32 / (qw * qh);
+  if (qw * qh * qn != 32 || qn > pl.bn) return B2G_OK;
+  const int os = pl.os;
+  const size_t es = 2;
+  for (int ph = 0; ph < pl.phases; ++ph) {
+    const size_t boff = ((size_t)pl.ph_y[ph] * pl.Wout + pl.ph_x[ph]) * a->Cout * es;
+    const uint64_t dims[4] = {(uint64_t)a->Cout, (uint64_t)pl.Wout / os, (uint64_t)pl.Hout / os, (uint64_t)pl.N};
+    const uint64_t str[3] = {(uint64_t)os * a->Cout * es, (uint64_t)os * pl.Wout * a->Cout * es,
+                             (uint64_t)pl.Hout * pl.Wout * a->Cout * es};
+    const uint32_t box[4] = {32u, (uint32_t)qw, (uint32_t)qh, (uint32_t)qn};
+    int rc = make_tmap(&m->omap[ph], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, static_cast<char*>(a->out) + boff, dims, str,
+                       box, CU_TENSOR_MAP_SWIZZLE_64B);
+    if (rc) return rc;
+    if (a->dact != B2G_ACT_NONE) {
+      rc = make_tmap(&m->ymap[ph], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, static_cast<const char*>(a->yprev) + boff, dims,
+                     str, box, CU_TENSOR_MAP_SWIZZLE_64B);
+      if (rc) return rc;
+    }
+  }
+  e->tma = 1;
+  e->qw = qw; e->qh = qh; e->qn = qn;
+  return B2G_OK;
 }
 
 }  // namespace b2g

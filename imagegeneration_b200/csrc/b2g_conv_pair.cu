@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
   }
   if (p.e.bias) {
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
-    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i];
+    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
   if (warp == 1) tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();

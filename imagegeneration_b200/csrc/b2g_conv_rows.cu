@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
   if (warp == 2 && lane == 0) tma_prefetch_desc(&p.bmap);
   if (p.e.bias) {
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
-    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i];
+    for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
   if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
   tc_fence_before();

@@ -55,6 +55,15 @@ class WgradArgs(C.Structure):
     ]
 
 
+class PackJob(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int), ("kh", C.c_int), ("kw", C.c_int), ("D2", C.c_int), ("D3", C.c_int),
+        ("n_is_d3", C.c_int), ("flip", C.c_int), ("ck_pad", C.c_int),
+        ("w", C.c_void_p), ("scale_scalar", C.c_void_p), ("scale_d2", C.c_void_p), ("scale_d3", C.c_void_p),
+        ("wpacked", C.c_void_p),
+    ]
+
+
 _lib = None
 
 
@@ -74,6 +83,8 @@ def load() -> C.CDLL:
     lib.b2g_conv_igemm.argtypes = [C.POINTER(ConvArgs), C.c_void_p]
     lib.b2g_pack_conv_weight.restype = C.c_int
     lib.b2g_pack_conv_weight.argtypes = [C.c_int] * 8 + [C.c_void_p] * 5 + [C.c_void_p]
+    lib.b2g_pack_conv_weight_multi.restype = C.c_int
+    lib.b2g_pack_conv_weight_multi.argtypes = [C.POINTER(PackJob), C.c_int, C.c_void_p]
     lib.b2g_pack_conv_weight_f32.restype = C.c_int
     lib.b2g_pack_conv_weight_f32.argtypes = [C.c_int] * 8 + [C.c_void_p] * 5 + [C.c_void_p]
     lib.b2g_conv_plan_query.restype = C.c_int
@@ -144,5 +155,6 @@ def check(rc: int, what: str, launches: int = 1) -> None:
 # Names every build of the library must export (tests/test_abi.py checks them against include/b200gan.h).
 def exported_symbols() -> list[str]:
     return ["b2g_version", "b2g_last_error", "b2g_conv_igemm", "b2g_pack_conv_weight", "b2g_pack_conv_weight_f32",
+            "b2g_pack_conv_weight_multi",
             "b2g_conv_plan_query",
             "b2g_pack_source_index", *_EXTRA_SIGNATURES]

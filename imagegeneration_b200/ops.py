@@ -76,6 +76,47 @@ def pack_conv_weight(kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = Fal
     return out
 
 
+class PackPlan:
+    """All bf16 weight packings of one model, run as ONE launch (b2g_pack_conv_weight_multi).
+
+    add() takes the arguments of pack_conv_weight, allocates the packed tensor and returns it; run() re-packs every
+    job from the current master weights.  The tensors handed to add() must stay alive and in place (arena views)."""
+
+    MAX_JOBS = 24
+
+    def __init__(self):
+        self._jobs = []
+        self._keep = []
+        self._arr = None
+
+    def add(self, kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = False,
+            scale_scalar: torch.Tensor | None = None, scale_d2: torch.Tensor | None = None,
+            scale_d3: torch.Tensor | None = None, ck_pad: int = 0) -> torch.Tensor:
+        _need_cuda(w, scale_scalar, scale_d2, scale_d3)
+        k, phases, taps = _KIND_GEOM[kind]
+        kh, kw, d2, d3 = w.shape
+        if w.dtype != torch.float32 or kh != k or kw != k or not w.is_contiguous():
+            raise B200GanError(f"PackPlan.add: expected contiguous fp32 [{k},{k},d2,d3], got {tuple(w.shape)} {w.dtype}")
+        if len(self._jobs) >= self.MAX_JOBS:
+            raise B200GanError(f"PackPlan: more than {self.MAX_JOBS} jobs")
+        cn, ck = (d3, d2) if n_is_d3 else (d2, d3)
+        out = torch.empty((phases, cn, taps * max(ck, ck_pad)), dtype=torch.bfloat16, device=w.device)
+        self._jobs.append(_lib.PackJob(kind=kind, kh=kh, kw=kw, D2=d2, D3=d3, n_is_d3=int(n_is_d3), flip=int(flip),
+                                       ck_pad=ck_pad, w=_ptr(w), scale_scalar=_ptr(scale_scalar),
+                                       scale_d2=_ptr(scale_d2), scale_d3=_ptr(scale_d3), wpacked=_ptr(out)))
+        self._keep.append((w, scale_scalar, scale_d2, scale_d3, out))
+        self._arr = None
+        return out
+
+    def run(self) -> None:
+        if not self._jobs:
+            return
+        if self._arr is None:
+            self._arr = (_lib.PackJob * len(self._jobs))(*self._jobs)
+        check(_lib.load().b2g_pack_conv_weight_multi(self._arr, len(self._jobs), _stream()),
+              "b2g_pack_conv_weight_multi")
+
+
 def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Tensor | None = None, *,
                bias: torch.Tensor | None = None, act: int = ACT_NONE, alpha: float = 0.0,
                dropout_thresh8: int = 0, dropout_seed: int = 0, yprev: torch.Tensor | None = None,

@@ -144,6 +144,7 @@ class Generator:
             elif name.endswith("gamma"):
                 v.fill_(1.0)
         self._inv_std = torch.full((1,), INV_STD, dtype=torch.float32, device=self.device)
+        self._pack_plan = None            # ops.PackPlan: all packings in one launch
         self._wp_f = [None] * 3           # packed fprop weights
         self._wp_d = [None] * 3           # packed dgrad weights
         self._wp4_f = None                # convT4 forward  (64 -> 3, flipped 3x3 taps), [1][3][576]
@@ -176,16 +177,18 @@ class Generator:
         return t
 
     def repack(self):
-        v = self.arena.variables
-        for i, k in enumerate((3, 6, 9)):
-            gamma = v[k + 1]   # folded BatchNorm scale gamma * inv_std goes into the packed bf16 weights
-            self._wp_f[i] = ops.pack_conv_weight(CONVT_K4S2, v[k], n_is_d3=False, scale_scalar=self._inv_std,
-                                                 scale_d2=gamma, out=self._wp_f[i])
-            self._wp_d[i] = ops.pack_conv_weight(CONV_K4S2, v[k], n_is_d3=True, scale_scalar=self._inv_std,
-                                                 scale_d2=gamma, out=self._wp_d[i])
-        self._wp4_f = ops.pack_conv_weight(CONV_K3S1, v[12], n_is_d3=False, flip=True, out=self._wp4_f)
-        self._wp4_d = ops.pack_conv_weight(CONV_K1S1, v[12].view(1, 1, 27, 64), n_is_d3=True, ck_pad=64,
-                                           out=self._wp4_d)
+        """One launch re-packs all eight packed weights (BatchNorm scale gamma * inv_std folded in)."""
+        if self._pack_plan is None:
+            v = self.arena.variables
+            plan = ops.PackPlan()
+            for i, k in enumerate((3, 6, 9)):
+                gamma = v[k + 1]
+                self._wp_f[i] = plan.add(CONVT_K4S2, v[k], n_is_d3=False, scale_scalar=self._inv_std, scale_d2=gamma)
+                self._wp_d[i] = plan.add(CONV_K4S2, v[k], n_is_d3=True, scale_scalar=self._inv_std, scale_d2=gamma)
+            self._wp4_f = plan.add(CONV_K3S1, v[12], n_is_d3=False, flip=True)
+            self._wp4_d = plan.add(CONV_K1S1, v[12].view(1, 1, 27, 64), n_is_d3=True, ck_pad=64)
+            self._pack_plan = plan
+        self._pack_plan.run()
         self._packed_dirty = False
 
     def forward(self, z):
@@ -281,6 +284,7 @@ class Discriminator:
         for name, v in zip(self.arena.names, self.arena.variables):
             if name.endswith("kernel"):
                 v.copy_(_glorot_uniform(tuple(v.shape), gen))
+        self._pack_plan = None
         self._wp_f = [None] * 7
         self._wp_d = [None] * 7
         self._packed_dirty = True
@@ -348,25 +352,25 @@ class Discriminator:
         return t
 
     def repack(self):
-        v = self.arena.variables
-        sc0 = self._inv_sigma(0)
-        self._wp_f[0] = ops.pack_conv_weight(CONV_K1S1, v[0].view(1, 1, 27, 64), n_is_d3=True, ck_pad=64,
-                                             scale_scalar=sc0, out=self._wp_f[0])           # im2col27 -> 64
-        self._wp_d[0] = ops.pack_conv_weight(CONV_K3S1, v[0], n_is_d3=False, flip=True, scale_scalar=sc0,
-                                             out=self._wp_d[0])                               # 64 -> 3
-        for i in range(1, 7):
-            _name, k, s, _ci, _co = D_CONVS[i]
-            sc = self._inv_sigma(i)
-            if s == 1:
-                self._wp_f[i] = ops.pack_conv_weight(CONV_K3S1, v[2 * i], n_is_d3=True, scale_scalar=sc,
-                                                     out=self._wp_f[i])
-                self._wp_d[i] = ops.pack_conv_weight(CONV_K3S1, v[2 * i], n_is_d3=False, flip=True, scale_scalar=sc,
-                                                     out=self._wp_d[i])
-            else:
-                self._wp_f[i] = ops.pack_conv_weight(CONV_K4S2, v[2 * i], n_is_d3=True, scale_scalar=sc,
-                                                     out=self._wp_f[i])
-                self._wp_d[i] = ops.pack_conv_weight(CONVT_K4S2, v[2 * i], n_is_d3=False, scale_scalar=sc,
-                                                     out=self._wp_d[i])
+        """One launch re-packs the forward and input-gradient packings of all seven conv layers (1/sigma folded in)."""
+        if self._pack_plan is None:
+            v = self.arena.variables
+            plan = ops.PackPlan()
+            sc0 = self._inv_sigma(0)
+            self._wp_f[0] = plan.add(CONV_K1S1, v[0].view(1, 1, 27, 64), n_is_d3=True, ck_pad=64,
+                                     scale_scalar=sc0)                                    # im2col27 -> 64
+            self._wp_d[0] = plan.add(CONV_K3S1, v[0], n_is_d3=False, flip=True, scale_scalar=sc0)   # 64 -> 3
+            for i in range(1, 7):
+                _name, k, s, _ci, _co = D_CONVS[i]
+                sc = self._inv_sigma(i)
+                if s == 1:
+                    self._wp_f[i] = plan.add(CONV_K3S1, v[2 * i], n_is_d3=True, scale_scalar=sc)
+                    self._wp_d[i] = plan.add(CONV_K3S1, v[2 * i], n_is_d3=False, flip=True, scale_scalar=sc)
+                else:
+                    self._wp_f[i] = plan.add(CONV_K4S2, v[2 * i], n_is_d3=True, scale_scalar=sc)
+                    self._wp_d[i] = plan.add(CONVT_K4S2, v[2 * i], n_is_d3=False, scale_scalar=sc)
+            self._pack_plan = plan
+        self._pack_plan.run()
         self._packed_dirty = False
 
     def forward(self, x, training=False, dropout_seeds=None, x27=None):

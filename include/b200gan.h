@@ -109,6 +109,19 @@ int b2g_pack_conv_weight_f32(int kind, int kh, int kw, int D2, int D3, int n_is_
                              const float* w, const float* scale_scalar, const float* scale_d2, const float* scale_d3,
                              void* wpacked, b2g_stream_t stream);
 
+/* Several bf16 packings in ONE launch (a train step re-packs every conv weight of a model after each optimizer
+ * update; see sndcgan/SNDCGAN.py:250,:258,:268 apply_gradients).  `jobs` is a HOST array of 1..24 entries whose
+ * fields mean what the arguments of b2g_pack_conv_weight mean. */
+typedef struct b2g_pack_job {
+  int kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad;
+  const float* w;
+  const float* scale_scalar;
+  const float* scale_d2;
+  const float* scale_d3;
+  void* wpacked;
+} b2g_pack_job;
+int b2g_pack_conv_weight_multi(const b2g_pack_job* jobs, int n_jobs, b2g_stream_t stream);
+
 /* fp32 [N,H,W,3] -> bf16 [N,H,W,64]: channel tap*3+c (tap = ky*3+kx) holds in[y+ky-1, x+kx-1, c] (zero outside),
  * channel 27 holds 1.0 (its wgrad row is the bias gradient), channels 28..63 are zero. */
 int b2g_im2col27(const float* in, void* out, int N, int H, int W, b2g_stream_t stream);

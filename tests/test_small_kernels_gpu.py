@@ -331,3 +331,33 @@ def test_edge_c3_fused_patch_kernel(n, h, w):
     dq = ops.conv_igemm(ops.CONV_K3S1_C3, dy.cuda(), wpd, yprev=a3.cuda().to(torch.bfloat16), dact=ops.ACT_RELU)
     torch.cuda.synchronize()
     assert _rel_l2(dq.float().cpu(), xin.grad * (a3 > 0).float()) < 6e-3
+
+
+def test_pack_plan_matches_single_packs():
+    """b2g_pack_conv_weight_multi (one launch, all layers) is bit-identical to the per-tensor packing."""
+    from imagegeneration_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    sc = torch.full((1,), 0.37, device="cuda")
+    jobs = [
+        (ops.CONV_K3S1, (3, 3, 64, 128), dict(n_is_d3=True, scale_scalar=sc)),
+        (ops.CONV_K3S1, (3, 3, 64, 128), dict(n_is_d3=False, flip=True)),
+        (ops.CONV_K4S2, (4, 4, 128, 64), dict(n_is_d3=True)),
+        (ops.CONVT_K4S2, (4, 4, 64, 128), dict(n_is_d3=False, scale_scalar=sc, scale_d2=torch.rand(64, generator=g).cuda())),
+        (ops.CONV_K1S1, (1, 1, 27, 64), dict(n_is_d3=True, ck_pad=64)),
+        (ops.CONV_K3S1, (3, 3, 3, 64), dict(n_is_d3=False, flip=True, scale_d3=torch.rand(64, generator=g).cuda())),
+    ]
+    plan = ops.PackPlan()
+    ws, outs = [], []
+    for kind, shape, kw in jobs:
+        w = (torch.rand(shape, generator=g) - 0.5).cuda()
+        ws.append(w)
+        outs.append(plan.add(kind, w, **kw))
+    plan.run()
+    torch.cuda.synchronize()
+    for (kind, _shape, kw), w, o in zip(jobs, ws, outs):
+        ref = ops.pack_conv_weight(kind, w, **kw)
+        assert o.shape == ref.shape and torch.equal(o, ref)
+    ws[0].mul_(2.0)                 # masters change in place; run() re-packs from them
+    plan.run()
+    kind, _shape, kw = jobs[0]
+    assert torch.equal(outs[0], ops.pack_conv_weight(kind, ws[0], **kw))

@@ -1,0 +1,56 @@
+"""CUDA-event timings of the memory-bound edge kernels at the bench shapes (run on the GPU box)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from imagegeneration_b200 import ops
+from imagegeneration_b200.sndcgan import SNDCGANEngine
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+
+def timeit(name, fn, bytes_moved=0, reps=10):
+    fn()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(reps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    us = tot / reps * 1e3
+    extra = f"  {bytes_moved / us / 1e3:7.1f} GB/s" if bytes_moved else ""
+    print(f"{name:44s} {us:8.1f} us{extra}")
+
+
+eng = SNDCGANEngine(B, dropout=0.5)
+D, G = eng.disc_model, eng.gen_model
+D.repack(); G.repack()
+timeit("D.repack (14 packings, one launch)", D.repack)
+timeit("G.repack (8 packings, one launch)", G.repack)
+
+x = torch.rand((B, 144, 256, 3), device="cuda") * 2 - 1
+y = torch.empty((B, 144, 256, 64), device="cuda", dtype=torch.bfloat16)
+bias = torch.zeros(64, device="cuda")
+px = B * 144 * 256
+timeit("conv_c3 fwd (bias, leaky, dropout)",
+       lambda: ops.conv_igemm(ops.CONV_K3S1_C3, x, D._wp_f[0], y, bias=bias, act=ops.ACT_LEAKY, alpha=0.1,
+                              dropout_thresh8=128, dropout_seed=7), px * (12 + 128))
+yprev = torch.rand((B, 144, 256, 64), device="cuda").to(torch.bfloat16)
+timeit("conv_c3 dgrad role (relu' from yprev)",
+       lambda: ops.conv_igemm(ops.CONV_K3S1_C3, x, G._wp4_d, y, yprev=yprev, dact=ops.ACT_RELU), px * (12 + 256))
+x27 = torch.empty((B, 144, 256, 64), device="cuda", dtype=torch.bfloat16)
+timeit("im2col27", lambda: ops.im2col27(x, x27), px * (12 + 128))
+g3 = torch.empty((B, 144, 256, 3), device="cuda")
+timeit("convT4 fwd 64->3 (tanh, fp32 out)",
+       lambda: ops.conv_igemm(ops.CONV_K3S1, yprev, G._wp4_f, g3, act=ops.ACT_TANH, out_f32=True), px * (128 + 12))
+dw = torch.zeros((27, 64), device="cuda")
+db = torch.zeros(64, device="cuda")
+timeit("edge wgrad (x27 x dy -> [27][64] + bias)",
+       lambda: ops.conv_wgrad(ops.CONV_K1S1, x27, yprev, dw, ca_valid=27, dbias=db), px * 256)
