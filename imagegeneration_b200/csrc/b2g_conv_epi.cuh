@@ -279,14 +279,16 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
 
 // Host: decides whether the TMA epilogue applies and builds its tensor maps (b2g_conv_epi_host.cu-free: inline).
 // `enabled` lets a kernel without shared-memory room opt out.
-inline int fill_epi_tma(const b2g_conv_args* a, const ConvPlan& pl, bool enabled, EpiParams* e, EpiTmaMaps* m) {
+// `row32`: the kernel's warps own 32 consecutive pixels of one row (row-slab kernel) whatever the plan's box says.
+inline int fill_epi_tma(const b2g_conv_args* a, const ConvPlan& pl, bool enabled, EpiParams* e, EpiTmaMaps* m,
+                        bool row32 = false) {
   static int env = []() { const char* s = getenv("B2G_EPI_TMA"); return s ? atoi(s) : 1; }();
   e->tma = 0;
   if (!enabled || !env || a->out_f32 || a->tf32 || a->Cout % 32) return B2G_OK;
-  const int qw = pl.bw < 32 ? pl.bw : 32;
-  const int qh = pl.bh < 32 / qw ? pl.bh : 32 / qw;
+  const int qw = row32 ? 32 : (pl.bw < 32 ? pl.bw : 32);
+  const int qh = row32 ? 1 : (pl.bh < 32 / qw ? pl.bh : 32 / qw);
   const int qn = 32 / (qw * qh);
-  if (qw * qh * qn != 32 || qn > pl.bn) return B2G_OK;
+  if (qw * qh * qn != 32 || (!row32 && qn > pl.bn)) return B2G_OK;
   const int os = pl.os;
   const size_t es = 2;
   for (int ph = 0; ph < pl.phases; ++ph) {

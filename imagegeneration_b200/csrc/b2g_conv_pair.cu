@@ -33,6 +33,7 @@ struct alignas(64) PairKernelParams {
   EpiParams e;
   int cin_chunks;   // Cin / 64
   int n_tiles;      // Cout / BLOCK_N
+  EpiTmaMaps em;    // TMA epilogue (used when e.tma)
   int brows;        // rows of the packed weight matrix per phase
   int m_pairs;      // plan.m_tiles / 2
   int total_pairs;  // phases * m_pairs * n_tiles
@@ -43,12 +44,17 @@ struct PairCfg {
   static constexpr int kABytes = 128 * 128;
   static constexpr int kBBytes = (BLOCK_N / 2) * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BLOCK_N == 256 ? 6 : 8;
+  // N <= 128 tiles: the TMA epilogue's per-warp boxes (b2g_conv_epi.cuh) take the room of one pipeline stage
+  static constexpr bool kEpiTma = BLOCK_N <= 128;
+  static constexpr int kStages = BLOCK_N == 256 ? 6 : (BLOCK_N == 128 ? 7 : 8);
   static constexpr int kAccBufs = BLOCK_N <= 64 ? 4 : 2;
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
   static constexpr int kEpiGroups = 4;
   static constexpr int kThreads = 64 + 128 * kEpiGroups;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;
+  static constexpr int kEpiWarps = 4 * kEpiGroups;
+  static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps) : 0;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 256 + 1024;
+  static_assert(kSmemBytes + 2048 <= 227 * 1024, "shared memory budget (incl. the static bias table)");
 };
 
 struct PairCoord {
@@ -76,7 +82,8 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
   __shared__ float sbias[512];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint8_t* epism = smem + Cfg::kStages * Cfg::kStageBytes;  // stage sizes are multiples of 1 KiB
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epism + Cfg::kEpiBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint64_t* tempty_bar = tfull_bar + Cfg::kAccBufs;
@@ -98,6 +105,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
       mbar_init(&tfull_bar[a], 1);                         // multicast tcgen05.commit
       mbar_init(&tempty_bar[a], 2 * 4 * kGroupsPerTile);   // epilogue warps of BOTH CTAs (leader's copy is used)
     }
+    if (Cfg::kEpiTma && p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps);
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
@@ -182,6 +190,10 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
     const int hl = (row / pl.bw) % pl.bh;
     const int nl = row / (pl.bw * pl.bh);
     const uint32_t tempty_leader = mapa_shared(smem_u32(&tempty_bar[0]), 0);
+    // origin of this warp's 32-pixel box inside a tile (TMA epilogue)
+    const int wl0 = (q * 32) % pl.bw, hl0 = ((q * 32) / pl.bw) % pl.bh, nl0 = (q * 32) / (pl.bw * pl.bh);
+    EpiWarpStage st = epi_tma_stage(epism, Cfg::kEpiWarps, warp - 2);
+    const bool use_tma = Cfg::kEpiTma && p.e.tma != 0;
     int it = 0;
     for (int pair = cluster_id; pair < p.total_pairs; pair += n_clusters, ++it) {
       const int as = it % Cfg::kAccBufs;
@@ -196,20 +208,25 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
       const int oy = gh * pl.os + pl.ph_y[tc.phase], ox = gw * pl.os + pl.ph_x[tc.phase];
       const size_t pix = (static_cast<size_t>(gn) * pl.Hout + oy) * pl.Wout + ox;
       const int col0 = tc.n_tile * BLOCK_N;
-      mbar_wait(&tfull_bar[as], (it / Cfg::kAccBufs) & 1);
+      const int bx = tc.tw * pl.bw + wl0, by = tc.th * pl.bh + hl0, bn = tc.tn * pl.bn + nl0;
+      if (use_tma) epi_tma_begin(p.e, &p.em.ymap[tc.phase], st, col0 + c_first * 32, bx, by, bn);
+      mbar_wait_parked(&tfull_bar[as], (it / Cfg::kAccBufs) & 1);
       tc_fence_after();
 #pragma unroll 1
       for (int c = c_first; c < kChunks; c += Cfg::kEpiGroups) {
+        if (use_tma && c != c_first) epi_tma_begin(p.e, &p.em.ymap[tc.phase], st, col0 + c * 32, bx, by, bn);
         uint32_t r[32];
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
-        conv_epilogue_chunk(p.e, sbias, r, pix, col0 + c * 32, valid);
+        if (use_tma) epi_tma_chunk(p.e, &p.em.omap[tc.phase], st, sbias, r, pix, col0 + c * 32, lane, bx, by, bn);
+        else conv_epilogue_chunk(p.e, sbias, r, pix, col0 + c * 32, valid);
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_leader + as * 8);
     }
+    if (use_tma) epi_tma_end();
   }
 
   tc_fence_before();
@@ -265,6 +282,10 @@ int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   memset(&kp, 0, sizeof(kp));
   kp.plan = pl;
   fill_epi_params(a, &kp.e);
+  {
+    int rc = fill_epi_tma(a, pl, block_n <= 128, &kp.e, &kp.em);
+    if (rc) return rc;
+  }
   kp.brows = a->Cout;
   kp.cin_chunks = a->Cin / 64;
   kp.n_tiles = a->Cout / block_n;

@@ -28,6 +28,7 @@ struct alignas(64) RowsKernelParams {
   EpiParams e;
   RowsGeom geom;
   RowsSched sched[2];
+  EpiTmaMaps em;     // TMA epilogue (used when e.tma)
   int n_tiles;       // Cout / BLOCK_N
   int brows;         // rows of the packed weight matrix per phase
   int total_tiles;   // PG * n_tiles * N * row_blocks * tiles_w
@@ -42,7 +43,13 @@ struct RowsCfg {
   static constexpr int kBBytes = BLOCK_N * 128;
   static constexpr int kBStages = SS::kStatic ? SS::kSB : (BLOCK_N == 128 ? 6 : 8);
   static constexpr int kBarBytes = 512;
-  static constexpr int kSmemBytes = kSlabs * kSlabBytes + kBStages * kBBytes + kBarBytes + 1024;
+  static constexpr int kMainBytes = kSlabs * kSlabBytes + kBStages * kBBytes;  // multiple of 1 KiB
+  static constexpr int kEpiWarps = 16;
+  // the TMA epilogue's per-warp boxes go behind the rings when they fit (b2g_conv_epi.cuh)
+  static constexpr bool kEpiTma =
+      BLOCK_N >= 64 && kMainBytes + epi_tma_smem_bytes(kEpiWarps) + kBarBytes + 1024 + 2048 <= 227 * 1024;
+  static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps) : 0;
+  static constexpr int kSmemBytes = kMainBytes + kEpiBytes + kBarBytes + 1024;
   static_assert(2 * (kSlabs + kBStages) * 8 + 4 * 8 + 8 <= kBarBytes, "barrier area");
   static_assert(kSmemBytes + 2048 <= 227 * 1024, "shared memory budget (incl. the static bias table)");
   static constexpr int kEpiGroups = 4;
@@ -140,7 +147,8 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* bsm = smem + Cfg::kSlabs * Cfg::kSlabBytes;
-  uint64_t* sfull = reinterpret_cast<uint64_t*>(bsm + Cfg::kBStages * Cfg::kBBytes);
+  uint8_t* epism = smem + Cfg::kMainBytes;
+  uint64_t* sfull = reinterpret_cast<uint64_t*>(epism + Cfg::kEpiBytes);
   uint64_t* sempty = sfull + Cfg::kSlabs;
   uint64_t* bfull = sempty + Cfg::kSlabs;
   uint64_t* bempty = bfull + Cfg::kBStages;
@@ -167,6 +175,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], 4 * Cfg::kEpiGroups);
     }
+    if (Cfg::kEpiTma && p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps);
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
@@ -318,11 +327,20 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     const int grp = (warp - 3) >> 2;
     const int row = q * 32 + lane;
     constexpr int kChunks = BLOCK_N / 32;
+    EpiWarpStage st = epi_tma_stage(epism, Cfg::kEpiWarps, warp - 3);
+    const bool use_tma = Cfg::kEpiTma && p.e.tma != 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int as = it & 1;
       const RowsTile t = decode_rows_tile(p, tile);
-      mbar_wait(&tfull[as], (it >> 1) & 1);
+      // TMA epilogue: the warp's box of item (acc, c) = 32 pixels from t.w0 + 32 q of grid row t.y0 + acc / P, in
+      // the output phase's sub-grid; the first item's saved-output load starts before the accumulator wait
+      if (use_tma && grp < n_acc * kChunks) {
+        const int acc = grp / kChunks;
+        epi_tma_begin(p.e, &p.em.ymap[t.pg * P + acc % P], st, t.n_tile * BLOCK_N + (grp % kChunks) * 32,
+                      t.w0 + q * 32, t.y0 + acc / P, t.n);
+      }
+      mbar_wait_parked(&tfull[as], (it >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
       for (int idx = grp; idx < n_acc * kChunks; idx += Cfg::kEpiGroups) {
@@ -332,17 +350,21 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
         const bool valid = gy < pl.Hg;
         const int oy = gy * pl.os + pl.ph_y[phase], ox = (t.w0 + row) * pl.os + pl.ph_x[phase];
         const size_t pix = (static_cast<size_t>(t.n) * pl.Hout + oy) * pl.Wout + ox;
+        const int cb = t.n_tile * BLOCK_N + c * 32;
+        if (use_tma && idx != grp) epi_tma_begin(p.e, &p.em.ymap[phase], st, cb, t.w0 + q * 32, gy, t.n);
         uint32_t v[32];
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * (n_acc * BLOCK_N) + acc * BLOCK_N + c * 32,
                       v);
         tmem_ld_wait();
-        conv_epilogue_chunk(p.e, sbias, v, pix, t.n_tile * BLOCK_N + c * 32, valid);
+        if (use_tma) epi_tma_chunk(p.e, &p.em.omap[phase], st, sbias, v, pix, cb, lane, t.w0 + q * 32, gy, t.n);
+        else conv_epilogue_chunk(p.e, sbias, v, pix, cb, valid);
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[as]);
     }
+    if (use_tma) epi_tma_end();
   }
 
   tc_fence_before();
@@ -371,7 +393,7 @@ static int launch_rows(const RowsKernelParams& kp, cudaStream_t stream) {
 static int rows_ring(int block_n) { return block_n == 128 ? RowsCfg<128>::kSlabs : RowsCfg<64>::kSlabs; }
 
 // compile-time schedules of the model's four wide roles: <kind, Cin/64, R, P, N tile, slab ring, weight-tile ring>
-using RowsConv3 = RowsStatic<B2G_CONV_K3S1, 2, 2, 1, 128, 4, 9>;    // D.conv3 fwd / dgrad (128 -> 128 @72x128)
+using RowsConv3 = RowsStatic<B2G_CONV_K3S1, 2, 2, 1, 128, 4, 6>;    // D.conv3 fwd / dgrad (128 -> 128 @72x128)
 using RowsConv2 = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 8>;    // D.conv2 fwd (64 -> 128, 144x256 -> 72x128)
 using RowsConvT3 = RowsStatic<B2G_CONVT_K4S2, 2, 2, 2, 64, 6, 8>;   // G.convT3 fwd / D.conv2 dgrad (128 -> 64)
 using RowsConvT4 = RowsStatic<B2G_CONV_K3S1, 1, 4, 1, 32, 6, 9>;    // G.convT4 fwd / D.conv1 dgrad (64 -> 3)
@@ -415,6 +437,14 @@ int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   if (!which && !build_rows_sched(pl, block_n, rows_ring(block_n), &kp.geom, kp.sched)) return B2G_OK;
   kp.plan = pl;
   fill_epi_params(a, &kp.e);
+  {
+    const bool room = which == 1   ? RowsCfg<128, RowsConv3>::kEpiTma
+                      : which == 2 ? RowsCfg<128, RowsConv2>::kEpiTma
+                      : which == 3 ? RowsCfg<64, RowsConvT3>::kEpiTma
+                                   : false;
+    int rc = fill_epi_tma(a, pl, room, &kp.e, &kp.em, /*row32=*/true);
+    if (rc) return rc;
+  }
   kp.brows = a->out_f32 ? a->cout_store : a->Cout;
   kp.n_tiles = a->Cout / block_n;
   kp.tiles_per_pg = kp.n_tiles * pl.N * kp.geom.row_blocks * pl.tiles_w;

@@ -54,3 +54,48 @@ dw = torch.zeros((27, 64), device="cuda")
 db = torch.zeros(64, device="cuda")
 timeit("edge wgrad (x27 x dy -> [27][64] + bias)",
        lambda: ops.conv_wgrad(ops.CONV_K1S1, x27, yprev, dw, ca_valid=27, dbias=db), px * 256)
+
+# --- narrow tensor-core layers (epilogue-bound candidates)
+def rnd(*shape):
+    return (torch.rand(shape, device="cuda") * 2 - 1).to(torch.bfloat16)
+
+
+def tf(name, fn, flops):
+    fn(); torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(10):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    us = tot / 10 * 1e3
+    print(f"{name:44s} {us:8.1f} us  {flops / us / 1e6:7.1f} TF/s")
+
+
+f32 = torch.float32
+x = rnd(B, 72, 128, 128); o = torch.empty((B, 144, 256, 64), device="cuda", dtype=torch.bfloat16)
+w = ops.pack_conv_weight(ops.CONVT_K4S2, torch.rand(4, 4, 64, 128, device="cuda") - 0.5, n_is_d3=False)
+bias = torch.zeros(64, device="cuda")
+fl = 2.0 * B * 144 * 256 * 64 * 128 * 4
+tf("convT3 fwd 128->64 (relu)", lambda: ops.conv_igemm(ops.CONVT_K4S2, x, w, o, bias=bias, act=ops.ACT_RELU), fl)
+tf("convT3 role dgrad (leaky' from yprev)", lambda: ops.conv_igemm(ops.CONVT_K4S2, x, w, o, yprev=yprev, dact=ops.ACT_LEAKY,
+                                                                    dact_alpha=0.1, dact_scale=2.0), fl)
+x3 = rnd(B, 72, 128, 128); o3 = torch.empty_like(x3); y3 = rnd(B, 72, 128, 128)
+w3 = ops.pack_conv_weight(ops.CONV_K3S1, torch.rand(3, 3, 128, 128, device="cuda") - 0.5, n_is_d3=True)
+b3 = torch.zeros(128, device="cuda")
+fl3 = 2.0 * B * 72 * 128 * 128 * 128 * 9
+tf("conv3 fwd 128->128 (leaky, dropout)", lambda: ops.conv_igemm(ops.CONV_K3S1, x3, w3, o3, bias=b3, act=ops.ACT_LEAKY, alpha=0.1,
+                                                                  dropout_thresh8=128, dropout_seed=3), fl3)
+tf("conv3 dgrad (leaky' from yprev)", lambda: ops.conv_igemm(ops.CONV_K3S1, x3, w3, o3, yprev=y3, dact=ops.ACT_LEAKY,
+                                                             dact_alpha=0.1, dact_scale=2.0), fl3)
+x2 = rnd(B, 36, 64, 256)
+w2 = ops.pack_conv_weight(ops.CONVT_K4S2, torch.rand(4, 4, 128, 256, device="cuda") - 0.5, n_is_d3=False)
+fl2 = 2.0 * B * 72 * 128 * 128 * 256 * 4
+tf("convT2 fwd 256->128 (relu)", lambda: ops.conv_igemm(ops.CONVT_K4S2, x2, w2, o3, bias=b3, act=ops.ACT_RELU), fl2)
+tf("convT2 role dgrad (leaky' from yprev)", lambda: ops.conv_igemm(ops.CONVT_K4S2, x2, w2, o3, yprev=y3, dact=ops.ACT_LEAKY,
+                                                                    dact_alpha=0.1, dact_scale=2.0), fl2)
+xc2 = rnd(B, 144, 256, 64)
+wc2 = ops.pack_conv_weight(ops.CONV_K4S2, torch.rand(4, 4, 64, 128, device="cuda") - 0.5, n_is_d3=True)
+flc2 = 2.0 * B * 72 * 128 * 128 * 64 * 16
+tf("conv2 fwd 64->128 s2 (leaky, dropout)", lambda: ops.conv_igemm(ops.CONV_K4S2, xc2, wc2, o3, bias=b3, act=ops.ACT_LEAKY, alpha=0.1,
+                                                                    dropout_thresh8=128, dropout_seed=3), flc2)
