@@ -1,119 +1,12 @@
 // b2g_dense.cu — the two dense layers of the SNDCGAN step and the loss.
-//   G stem  : Dense(128 -> 512*h*w, no bias) + inference BatchNorm + ReLU   (sndcgan/SNDCGAN.py:31-34)
-//             HBM-bound on the 151 MB fp32 weight; forward and backward read/write it exactly once per
-//             batch chunk of 32 samples.
+//   G stem  : Dense(128 -> 512*h*w, no bias) + inference BatchNorm + ReLU   (sndcgan/SNDCGAN.py:31-34):
+//             tensor-core kernels in b2g_dense_tc.cu
 //   D head  : Flatten + Dense(1) (:122-123), BinaryCrossentropy(from_logits) (:170,:246,:254,:262) or hinge,
 //             and the head's backward which also applies conv7's LeakyReLU/Dropout derivative.
 #include "b2g_host.h"
 #include "b2g_ptx.cuh"
 
 namespace b2g {
-
-constexpr int kDenseBC = 32;   // batch chunk held in registers
-constexpr int kDenseK = 128;   // z size (sndcgan/Trainer.py:8)
-
-// out[b][j] = relu(gscale[j] * sum_k z[b][k] W[k][j] + beta[j]),  gscale = gamma * inv_std
-__global__ void __launch_bounds__(128) dense_g_fwd_kernel(const float* __restrict__ z, const float* __restrict__ W,
-                                                          const float* __restrict__ gamma,
-                                                          const float* __restrict__ beta, float inv_std,
-                                                          __nv_bfloat16* __restrict__ out, int B, int F) {
-  __shared__ __align__(16) float zs[kDenseK][kDenseBC];
-  const int j = (blockIdx.x * 128 + threadIdx.x) * 2;
-  const bool live = j < F;
-  for (int b0 = 0; b0 < B; b0 += kDenseBC) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < kDenseK * kDenseBC; i += 128) {
-      const int k = i / kDenseBC, b = i % kDenseBC;
-      zs[k][b] = (b0 + b < B) ? z[(size_t)(b0 + b) * kDenseK + k] : 0.f;
-    }
-    __syncthreads();
-    if (!live) continue;
-    float acc0[kDenseBC], acc1[kDenseBC];
-#pragma unroll
-    for (int b = 0; b < kDenseBC; ++b) acc0[b] = acc1[b] = 0.f;
-#pragma unroll 4
-    for (int k = 0; k < kDenseK; ++k) {
-      const float2 w = __ldg(reinterpret_cast<const float2*>(W + (size_t)k * F + j));
-#pragma unroll
-      for (int b4 = 0; b4 < kDenseBC / 4; ++b4) {
-        const float4 zz = *reinterpret_cast<const float4*>(&zs[k][b4 * 4]);
-        acc0[b4 * 4 + 0] += zz.x * w.x; acc1[b4 * 4 + 0] += zz.x * w.y;
-        acc0[b4 * 4 + 1] += zz.y * w.x; acc1[b4 * 4 + 1] += zz.y * w.y;
-        acc0[b4 * 4 + 2] += zz.z * w.x; acc1[b4 * 4 + 2] += zz.z * w.y;
-        acc0[b4 * 4 + 3] += zz.w * w.x; acc1[b4 * 4 + 3] += zz.w * w.y;
-      }
-    }
-    const float g0 = gamma[j] * inv_std, g1 = gamma[j + 1] * inv_std;
-    const float be0 = beta[j], be1 = beta[j + 1];
-#pragma unroll
-    for (int b = 0; b < kDenseBC; ++b) {
-      if (b0 + b < B) {
-        const float y0 = fmaxf(acc0[b] * g0 + be0, 0.f), y1 = fmaxf(acc1[b] * g1 + be1, 0.f);
-        *reinterpret_cast<uint32_t*>(out + (size_t)(b0 + b) * F + j) = pack_bf16x2(y0, y1);
-      }
-    }
-  }
-}
-
-// Backward of the stem for one batch chunk [b0, b0+32): dq = dL/d(BN output before ReLU) with ReLU' applied.
-//   dbeta[j] (+)= sum_b dq[b][j];  G[k][j] = sum_b z[b][k] dq[b][j];  dW[k][j] (+)= gscale[j] * G[k][j];
-//   dgamma[j] (+)= inv_std * sum_k W[k][j] * G[k][j]      (x_hat never materialised)
-__global__ void __launch_bounds__(128) dense_g_bwd_kernel(const float* __restrict__ z, const float* __restrict__ W,
-                                                          const float* __restrict__ gamma, float inv_std,
-                                                          const __nv_bfloat16* __restrict__ dq,
-                                                          float* __restrict__ dW, float* __restrict__ dgamma,
-                                                          float* __restrict__ dbeta, int B, int F, int b0,
-                                                          int accumulate) {
-  __shared__ __align__(16) float zs[kDenseK][kDenseBC];
-  for (int i = threadIdx.x; i < kDenseK * kDenseBC; i += 128) {
-    const int k = i / kDenseBC, b = i % kDenseBC;
-    zs[k][b] = (b0 + b < B) ? z[(size_t)(b0 + b) * kDenseK + k] : 0.f;
-  }
-  __syncthreads();
-  const int j = (blockIdx.x * 128 + threadIdx.x) * 2;
-  if (j >= F) return;
-  float d0[kDenseBC], d1[kDenseBC];
-  float sb0 = 0.f, sb1 = 0.f;
-#pragma unroll
-  for (int b = 0; b < kDenseBC; ++b) {
-    uint32_t v = 0;
-    if (b0 + b < B) v = __ldg(reinterpret_cast<const uint32_t*>(dq + (size_t)(b0 + b) * F + j));
-    d0[b] = bf16_lo(v);
-    d1[b] = bf16_hi(v);
-    sb0 += d0[b];
-    sb1 += d1[b];
-  }
-  const float g0 = gamma[j] * inv_std, g1 = gamma[j + 1] * inv_std;
-  float sg0 = 0.f, sg1 = 0.f;
-#pragma unroll 2
-  for (int k = 0; k < kDenseK; ++k) {
-    float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-    for (int b4 = 0; b4 < kDenseBC / 4; ++b4) {
-      const float4 zz = *reinterpret_cast<const float4*>(&zs[k][b4 * 4]);
-      a0 += zz.x * d0[b4 * 4] + zz.y * d0[b4 * 4 + 1] + zz.z * d0[b4 * 4 + 2] + zz.w * d0[b4 * 4 + 3];
-      a1 += zz.x * d1[b4 * 4] + zz.y * d1[b4 * 4 + 1] + zz.z * d1[b4 * 4 + 2] + zz.w * d1[b4 * 4 + 3];
-    }
-    const float2 w = __ldg(reinterpret_cast<const float2*>(W + (size_t)k * F + j));
-    sg0 += w.x * a0;
-    sg1 += w.y * a1;
-    float2* dst = reinterpret_cast<float2*>(dW + (size_t)k * F + j);
-    float2 o = make_float2(a0 * g0, a1 * g1);
-    if (accumulate) {
-      const float2 old = *dst;
-      o.x += old.x;
-      o.y += old.y;
-    }
-    *dst = o;
-  }
-  if (accumulate) {
-    dgamma[j] += sg0 * inv_std; dgamma[j + 1] += sg1 * inv_std;
-    dbeta[j] += sb0; dbeta[j + 1] += sb1;
-  } else {
-    dgamma[j] = sg0 * inv_std; dgamma[j + 1] = sg1 * inv_std;
-    dbeta[j] = sb0; dbeta[j + 1] = sb1;
-  }
-}
 
 // ---------------------------------------------------------------------------------------------------------
 // D head: partial dot products  part[b][s] = sum_{j in slice s} x[b][j] * w[j]
@@ -242,30 +135,6 @@ __global__ void __launch_bounds__(256) dhead_bwd_kernel(const __nv_bfloat16* __r
 }  // namespace b2g
 
 using namespace b2g;
-
-extern "C" int b2g_dense_g_fwd(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
-                               void* out, int B, int F, b2g_stream_t stream_) {
-  if (!z || !W || !gamma || !beta || !out) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_fwd: null pointer");
-  if (F % 2) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_fwd: F must be even");
-  const int grid = (F / 2 + 127) / 128;
-  dense_g_fwd_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(z, W, gamma, beta, inv_std,
-                                                                            static_cast<__nv_bfloat16*>(out), B, F);
-  B2G_LAUNCH_CHECK();
-  return B2G_OK;
-}
-
-extern "C" int b2g_dense_g_bwd(const float* z, const float* W, const float* gamma, float inv_std, const void* dq,
-                               float* dW, float* dgamma, float* dbeta, int B, int F, b2g_stream_t stream_) {
-  if (!z || !W || !gamma || !dq || !dW || !dgamma || !dbeta) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_bwd: null pointer");
-  if (F % 2) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_bwd: F must be even");
-  const int grid = (F / 2 + 127) / 128;
-  for (int b0 = 0; b0 < B; b0 += kDenseBC) {
-    dense_g_bwd_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
-        z, W, gamma, inv_std, static_cast<const __nv_bfloat16*>(dq), dW, dgamma, dbeta, B, F, b0, b0 > 0);
-    B2G_LAUNCH_CHECK();
-  }
-  return B2G_OK;
-}
 
 extern "C" int b2g_dhead_fwd_loss(const void* x, const float* w, const float* wscale, const float* bias, int B,
                                   int F, int loss_kind, float label, float inv_batch, float* workspace,

@@ -101,6 +101,21 @@ class _QW(torch.autograd.Function):
         return g
 
 
+class _QTf32(torch.autograd.Function):
+    """what tcgen05 kind::tf32 reads of an fp32 operand: the low 13 mantissa bits are dropped (truncation);
+    straight-through in backward.  The CUDA path's generator stem (b2g_dense_tc.cu) multiplies z and the fp32
+    dense weight this way in forward; its backward is computed from the unrounded values."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x32 = x.to(torch.float32).contiguous()
+        return (x32.view(torch.int32) & ~0x1FFF).view(torch.float32).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
 def _qa(x, emu):
     return _QAct.apply(x) if emu else x
 
@@ -117,7 +132,7 @@ def generator_forward(gv: list[torch.Tensor], z: torch.Tensor, image_size=(144, 
     """SNDCGAN.py:28-61 with BatchNorm in INFERENCE mode (moving mean 0 / var 1): train_step calls
     self.gen_model(input_z) without training=True (:243) and create_samples passes training=False."""
     h, w = image_size[0] // 8, image_size[1] // 8
-    x = K.dense(z, gv[0])
+    x = K.dense(_QTf32.apply(z), _QTf32.apply(gv[0])) if emu else K.dense(z, gv[0])
     x = _qa(torch.relu(K.batchnorm_inference(x, gv[1], gv[2])), emu)
     x = x.reshape(-1, h, w, 512)                                        # :34 row-major NHWC
     if collect is not None:

@@ -99,3 +99,20 @@ wc2 = ops.pack_conv_weight(ops.CONV_K4S2, torch.rand(4, 4, 64, 128, device="cuda
 flc2 = 2.0 * B * 72 * 128 * 128 * 64 * 16
 tf("conv2 fwd 64->128 s2 (leaky, dropout)", lambda: ops.conv_igemm(ops.CONV_K4S2, xc2, wc2, o3, bias=b3, act=ops.ACT_LEAKY, alpha=0.1,
                                                                     dropout_thresh8=128, dropout_seed=3), flc2)
+
+# --- generator stem
+import math
+from imagegeneration_b200 import lib as L
+F = 512 * 18 * 32
+zz = torch.rand((B, 128), device="cuda") * 2 - 1
+Wd = (torch.rand((128, F), device="cuda") - 0.5) * 0.1
+gm = torch.ones(F, device="cuda"); bt = torch.zeros(F, device="cuda")
+od = torch.empty((B, F), device="cuda", dtype=torch.bfloat16)
+lib = L.load()
+_p = lambda t: t.data_ptr()
+_s = lambda: torch.cuda.current_stream().cuda_stream
+timeit("stem fwd (W 151 MB + out)", lambda: L.check(lib.b2g_dense_g_fwd(_p(zz), _p(Wd), _p(gm), _p(bt), 0.9995, _p(od), B, F, _s()), "f"),
+       F * 128 * 4 + B * F * 2)
+dWd = torch.empty_like(Wd); dg = torch.empty(F, device="cuda"); dbt = torch.empty(F, device="cuda")
+timeit("stem bwd (W + dW + dq)", lambda: L.check(lib.b2g_dense_g_bwd(_p(zz), _p(Wd), _p(gm), 0.9995, _p(od), _p(dWd), _p(dg), _p(dbt), B, F, _s()), "b"),
+       F * 128 * 8 + B * F * 2)
