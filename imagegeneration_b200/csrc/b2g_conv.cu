@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
   constexpr int kChunks = BLOCK_N / 32;
   constexpr int kGroupsPerTile = kChunks < kEpiGroups ? kChunks : kEpiGroups;  // groups that work on one tile
   __shared__ float sbias[512];
+  __shared__ float s_colsum[512];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
@@ -92,6 +93,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
     for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
+  epi_colsum_zero(p.e, s_colsum, pl.Cout);
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -190,7 +192,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
-        conv_epilogue_chunk(p.e, sbias, r, pix, col0 + c * 32, valid);
+        conv_epilogue_chunk(p.e, sbias, r, pix, col0 + c * 32, valid, s_colsum);
       }
       tc_fence_before();
       __syncwarp();
@@ -200,6 +202,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
 
   tc_fence_before();
   __syncthreads();
+  epi_colsum_flush(p.e, s_colsum, pl.Cout);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
@@ -250,6 +253,8 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
   if (a->Cout > 512) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cout=%d > 512", a->Cout);
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
+  if (a->colsum && (a->out_f32 || a->tf32 || a->bias || a->dact == B2G_ACT_NONE))
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: colsum needs a bf16 backward epilogue (dact, no bias)");
   if (a->dropout_thresh8 > 0 && a->act == B2G_ACT_TANH)  // the dropout scale is applied before the activation
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout needs a positively homogeneous activation (none/leaky/relu)");
 

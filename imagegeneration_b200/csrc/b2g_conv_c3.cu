@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
   constexpr int BLOCK_N = Cfg::kBlockN;
   constexpr int kChunks = BLOCK_N / 32;
   __shared__ float sbias[64];
+  __shared__ float s_colsum[64];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* bsm = smem + Cfg::kStages * Cfg::kABytes;
@@ -94,6 +95,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     fence_barrier_init();
   }
   epi_load_bias(p.e, sbias, BLOCK_N);
+  epi_colsum_zero(p.e, s_colsum, BLOCK_N);
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -220,8 +222,8 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       __syncwarp();
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
       tmem_ld_wait();
-      if (use_tma) epi_tma_chunk(p.e, &p.em.omap[0], st, sbias, r, pix, c * 32, lane, bx, by, bn);
-      else conv_epilogue_chunk(p.e, sbias, r, pix, c * 32, valid);
+      if (use_tma) epi_tma_chunk(p.e, &p.em.omap[0], st, sbias, r, pix, c * 32, lane, bx, by, bn, s_colsum);
+      else conv_epilogue_chunk(p.e, sbias, r, pix, c * 32, valid, s_colsum);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[as]);
@@ -231,6 +233,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
 
   tc_fence_before();
   __syncthreads();
+  epi_colsum_flush(p.e, s_colsum, BLOCK_N);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
@@ -244,6 +247,8 @@ int launch_conv_c3(const b2g_conv_args* a, void* stream_) {
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255)
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
+  if (a->colsum && (a->bias || a->dact == B2G_ACT_NONE))
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: colsum needs a bf16 backward epilogue (dact, no bias)");
   if (a->dropout_thresh8 > 0 && a->act == B2G_ACT_TANH)
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout needs a positively homogeneous activation (none/leaky/relu)");
   C3KernelParams kp;

@@ -33,6 +33,8 @@ struct EpiParams {
   int cs;       // channel stride of the output tensor (== Cout unless out_f32)
   int Cout;
   int f32_io;   // tf32 path: out / yprev are full-width fp32 [pixels][Cout]
+  float* colsum;  // optional fp32 [Cout]: += per-channel sums of the stored (bf16-rounded) outputs over all pixels
+                  // = bias / BatchNorm-beta gradient of the layer whose output gradient this kernel produces
   int tma;      // 1: bf16 output (and yprev) move through per-warp shared-memory boxes and TMA (EpiTmaMaps)
   int qw, qh, qn;  // the 32 pixels one epilogue warp owns, as a box of the tile (qw * qh * qn == 32)
 };
@@ -50,7 +52,8 @@ constexpr int kEpiStageBytes = 2048;  // one warp's [32 pixels][32 channels] bf1
 // both are only called for bf16 tensors and valid pixels.
 template <class YLoad, class OStore>
 __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
-                                                   size_t pix, int cb, bool valid, YLoad yload, OStore ostore) {
+                                                   size_t pix, int cb, bool valid, YLoad yload, OStore ostore,
+                                                   float* s_colsum = nullptr, bool colsum_here = false) {
   const size_t off = pix * p.Cout + cb;  // element offset of this thread's 32 outputs
   float v[32];
 #pragma unroll
@@ -145,13 +148,37 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
       o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
       o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
       ostore(g, o);
+      if (colsum_here) {  // keep the ROUNDED values for the column sums below
+        v[g * 8 + 0] = bf16_lo(o.x); v[g * 8 + 1] = bf16_hi(o.x); v[g * 8 + 2] = bf16_lo(o.y); v[g * 8 + 3] = bf16_hi(o.y);
+        v[g * 8 + 4] = bf16_lo(o.z); v[g * 8 + 5] = bf16_hi(o.z); v[g * 8 + 6] = bf16_lo(o.w); v[g * 8 + 7] = bf16_hi(o.w);
+      }
     }
+  }
+  if (colsum_here) {
+    // column sums over the warp's 32 pixels by a transposing butterfly: after the step with offset `off` every
+    // lane holds half as many partial sums; lane l ends with the sum of channel cb + l (31 shuffles in total)
+    if (!valid) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = 0.f;
+    }
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      const bool up = (lane & off) != 0;
+#pragma unroll
+      for (int i = 0; i < off; ++i) {
+        const float mine = up ? v[i + off] : v[i];
+        const float theirs = up ? v[i] : v[i + off];
+        v[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, off);
+      }
+    }
+    atomicAdd(&s_colsum[cb + lane], v[0]);
   }
 }
 
 // r: 32 accumulator columns [cb, cb+32) of output pixel `pix` (flat N*H*W index); `valid` = pixel inside the tensor.
 __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
-                                                    size_t pix, int cb, bool valid) {
+                                                    size_t pix, int cb, bool valid, float* s_colsum = nullptr) {
   if (p.out_f32) {  // narrow fp32 output (3 real channels): tanh / tanh' epilogues of the generator's last layer
     if (valid && cb < p.cs) {
       float* of = reinterpret_cast<float*>(p.out) + pix * p.cs + cb;
@@ -175,7 +202,19 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
   conv_epilogue_math(
       p, sbias, r, pix, cb, valid,
       [&](int g) { return __ldg(reinterpret_cast<const uint4*>(p.yprev + pix * p.Cout + cb) + g); },
-      [&](int g, const uint4& o) { reinterpret_cast<uint4*>(p.out + pix * p.Cout + cb)[g] = o; });
+      [&](int g, const uint4& o) { reinterpret_cast<uint4*>(p.out + pix * p.Cout + cb)[g] = o; }, s_colsum,
+      p.colsum != nullptr);
+}
+
+// Block-wide helpers of the fused column sums: per-CTA partial sums live in a shared table (zeroed before the
+// block sync of the prologue, flushed with one atomic per channel after the final block sync).
+__device__ __forceinline__ void epi_colsum_zero(const EpiParams& p, float* s_colsum, int n) {
+  if (p.colsum)
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s_colsum[i] = 0.f;
+}
+__device__ __forceinline__ void epi_colsum_flush(const EpiParams& p, const float* s_colsum, int n) {
+  if (p.colsum)
+    for (int i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(p.colsum + i, s_colsum[i]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -224,7 +263,7 @@ __device__ __forceinline__ void epi_tma_begin(const EpiParams& p, const CUtensor
 // Whole warp: epilogue math of one chunk (lane = pixel) through the box, then the TMA store.
 __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensorMap* omap, EpiWarpStage& st,
                                               const float* sbias, const uint32_t (&r)[32], size_t pix, int cb, int lane,
-                                              int bx, int by, int bn) {
+                                              int bx, int by, int bn, float* s_colsum = nullptr) {
   uint8_t* row = st.buf + lane * 64;
   const uint32_t sw = (lane >> 1) & 3;  // 64-byte swizzle: 16-byte group g of row i lives at g ^ ((i >> 1) & 3)
   if (p.dact != B2G_ACT_NONE) {
@@ -239,6 +278,19 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
   __syncwarp();
   if (elect_one_sync()) tma_store_4d(omap, st.buf, cb, bx, by, bn);
   __syncwarp();
+  if (p.colsum) {
+    // column sums straight from the box: lane l reads channel cb + l of the 32 pixel rows (the 32 lanes of one
+    // read cover one 64-byte row: conflict free).  Rows of pixels outside the tensor hold exact zeros (zero-filled
+    // operands, no bias in a backward epilogue).
+    float sum = 0.f;
+    const uint32_t cg = lane >> 3, ce = (lane & 7) * 2;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const uint16_t h = *reinterpret_cast<const uint16_t*>(st.buf + i * 64 + ((cg ^ ((i >> 1) & 3)) << 4) + ce);
+      sum += __uint_as_float(static_cast<uint32_t>(h) << 16);
+    }
+    atomicAdd(&s_colsum[cb + lane], sum);
+  }
 }
 
 // Whole warp, before the kernel's final block-wide sync: the last store must have read the box.
@@ -274,6 +326,7 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->cs = a->out_f32 ? a->cout_store : a->Cout;
   e->Cout = a->Cout;
   e->f32_io = a->tf32;
+  e->colsum = a->colsum;
   e->tma = 0;
 }
 

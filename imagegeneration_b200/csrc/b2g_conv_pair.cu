@@ -54,7 +54,7 @@ struct PairCfg {
   static constexpr int kEpiWarps = 4 * kEpiGroups;
   static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps) : 0;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 256 + 1024;
-  static_assert(kSmemBytes + 2048 <= 227 * 1024, "shared memory budget (incl. the static bias table)");
+  static_assert(kSmemBytes + 4096 <= 227 * 1024, "shared memory budget (incl. the static bias / column-sum tables)");
 };
 
 struct PairCoord {
@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
   constexpr int kChunks = BLOCK_N / 32;
   constexpr int kGroupsPerTile = kChunks < Cfg::kEpiGroups ? kChunks : Cfg::kEpiGroups;
   __shared__ float sbias[512];
+  __shared__ float s_colsum[512];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* epism = smem + Cfg::kStages * Cfg::kStageBytes;  // stage sizes are multiples of 1 KiB
@@ -116,6 +117,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
     for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
+  epi_colsum_zero(p.e, s_colsum, pl.Cout);
   if (warp == 1) tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -219,8 +221,8 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
-        if (use_tma) epi_tma_chunk(p.e, &p.em.omap[tc.phase], st, sbias, r, pix, col0 + c * 32, lane, bx, by, bn);
-        else conv_epilogue_chunk(p.e, sbias, r, pix, col0 + c * 32, valid);
+        if (use_tma) epi_tma_chunk(p.e, &p.em.omap[tc.phase], st, sbias, r, pix, col0 + c * 32, lane, bx, by, bn, s_colsum);
+        else conv_epilogue_chunk(p.e, sbias, r, pix, col0 + c * 32, valid, s_colsum);
       }
       tc_fence_before();
       __syncwarp();
@@ -231,6 +233,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
 
   tc_fence_before();
   __syncthreads();
+  epi_colsum_flush(p.e, s_colsum, pl.Cout);
   cluster_sync_all();  // no CTA frees TMEM / exits while its peer may still signal or read it
   if (warp == 1) {
     tc_fence_after();

@@ -47,11 +47,11 @@ struct RowsCfg {
   static constexpr int kEpiWarps = 16;
   // the TMA epilogue's per-warp boxes go behind the rings when they fit (b2g_conv_epi.cuh)
   static constexpr bool kEpiTma =
-      BLOCK_N >= 64 && kMainBytes + epi_tma_smem_bytes(kEpiWarps) + kBarBytes + 1024 + 2048 <= 227 * 1024;
+      BLOCK_N >= 64 && kMainBytes + epi_tma_smem_bytes(kEpiWarps) + kBarBytes + 1024 + 4096 <= 227 * 1024;
   static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps) : 0;
   static constexpr int kSmemBytes = kMainBytes + kEpiBytes + kBarBytes + 1024;
   static_assert(2 * (kSlabs + kBStages) * 8 + 4 * 8 + 8 <= kBarBytes, "barrier area");
-  static_assert(kSmemBytes + 2048 <= 227 * 1024, "shared memory budget (incl. the static bias table)");
+  static_assert(kSmemBytes + 4096 <= 227 * 1024, "shared memory budget (incl. the static bias / column-sum tables)");
   static constexpr int kEpiGroups = 4;
   static constexpr int kThreads = 96 + 128 * kEpiGroups;
 };
@@ -144,6 +144,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     conv_rows_kernel(const __grid_constant__ RowsKernelParams p) {
   using Cfg = RowsCfg<BLOCK_N, SS>;
   __shared__ float sbias[512];
+  __shared__ float s_colsum[512];
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* bsm = smem + Cfg::kSlabs * Cfg::kSlabBytes;
@@ -186,6 +187,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
     for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
+  epi_colsum_zero(p.e, s_colsum, pl.Cout);
   if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
   tc_fence_before();
   __syncthreads();
@@ -357,8 +359,8 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * (n_acc * BLOCK_N) + acc * BLOCK_N + c * 32,
                       v);
         tmem_ld_wait();
-        if (use_tma) epi_tma_chunk(p.e, &p.em.omap[phase], st, sbias, v, pix, cb, lane, t.w0 + q * 32, gy, t.n);
-        else conv_epilogue_chunk(p.e, sbias, v, pix, cb, valid);
+        if (use_tma) epi_tma_chunk(p.e, &p.em.omap[phase], st, sbias, v, pix, cb, lane, t.w0 + q * 32, gy, t.n, s_colsum);
+        else conv_epilogue_chunk(p.e, sbias, v, pix, cb, valid, s_colsum);
       }
       tc_fence_before();
       __syncwarp();
@@ -369,6 +371,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
 
   tc_fence_before();
   __syncthreads();
+  epi_colsum_flush(p.e, s_colsum, pl.Cout);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, tmem_cols);

@@ -38,6 +38,7 @@ class ConvArgs(C.Structure):
         ("dact_alpha", C.c_float), ("dact_scale", C.c_float), ("dact_zero", C.c_float),
         ("out_f32", C.c_int), ("cout_store", C.c_int),
         ("tf32", C.c_int),
+        ("colsum", C.c_void_p),
     ]
 
 

@@ -121,11 +121,13 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                bias: torch.Tensor | None = None, act: int = ACT_NONE, alpha: float = 0.0,
                dropout_thresh8: int = 0, dropout_seed: int = 0, yprev: torch.Tensor | None = None,
                dact: int = ACT_NONE, dact_alpha: float = 0.0, dact_scale: float = 1.0,
-               dact_zero: float = 0.0, out_f32: bool = False, tf32: bool = False) -> torch.Tensor:
+               dact_zero: float = 0.0, out_f32: bool = False, tf32: bool = False,
+               colsum: torch.Tensor | None = None) -> torch.Tensor:
     """Tensor-core implicit-GEMM conv / transposed conv with fused epilogue (see include/b200gan.h).
 
-    out_f32=True: narrow fp32 output — wpacked has `cout_store` (<= 8) rows and out is fp32 [N,Ho,Wo,cout_store]."""
-    _need_cuda(x, wpacked, out, bias, yprev)
+    out_f32=True: narrow fp32 output — wpacked has `cout_store` (<= 8) rows and out is fp32 [N,Ho,Wo,cout_store].
+    colsum: fp32 [Cout], += per-channel sums of the stored outputs (bias / beta gradient fused into a backward call)."""
+    _need_cuda(x, wpacked, out, bias, yprev, colsum)
     n, h, w, cin = x.shape
     k, phases, taps = _KIND_GEOM[kind]
     if kind == CONV_K3S1_C3:
@@ -153,6 +155,9 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
         raise B200GanError("conv_igemm: yprev must match the output")
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout):
         raise B200GanError("conv_igemm: bias must be fp32 [Cout]")
+    if colsum is not None and (colsum.dtype != torch.float32 or colsum.numel() != cout or out_f32 or tf32
+                               or bias is not None or dact == ACT_NONE):
+        raise B200GanError("conv_igemm: colsum needs fp32 [Cout], bf16 output, no bias and a backward (dact) epilogue")
     cout_store = 0
     if out_f32:
         cout_store, cout = cout, 32
@@ -161,7 +166,7 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                  dropout_thresh8=dropout_thresh8, dropout_seed=dropout_seed & 0xFFFFFFFFFFFFFFFF,
                  yprev=None if yprev is None else yprev.data_ptr(), dact=dact, dact_alpha=dact_alpha,
                  dact_scale=dact_scale, dact_zero=dact_zero, out_f32=int(out_f32), cout_store=cout_store,
-                 tf32=int(tf32))
+                 tf32=int(tf32), colsum=None if colsum is None else colsum.data_ptr())
     ev = _prof_begin()
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
     cin_alg = 27 if kind in (CONV_K1S1, CONV_K3S1_C3) else cin   # edge layers: 27 real taps*channels

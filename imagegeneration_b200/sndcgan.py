@@ -236,20 +236,22 @@ class Generator:
         # (ReLU' of a3 in the epilogue)
         x27 = ops.im2col27(d_pre_tanh, self._buf("dy27", (B, H, W, 64), torch.bfloat16))
         ops.conv_wgrad(CONV_K1S1, x27, a3, g[12], ca_valid=27)
+        # every input-gradient call also leaves the per-channel sums of what it stored = the beta gradient of the
+        # BatchNorm in front of it (fused into the epilogue: no separate pass over dq)
         dq = self._buf("dq3", tuple(a3.shape), torch.bfloat16)
-        ops.conv_igemm(CONV_K3S1_C3, d_pre_tanh, self._wp4_d, dq, yprev=a3, dact=ACT_RELU)
+        ops.conv_igemm(CONV_K3S1_C3, d_pre_tanh, self._wp4_d, dq, yprev=a3, dact=ACT_RELU, colsum=g[9 + 2])
         acts_in = [a0, a1, a2]
         for i in (2, 1, 0):
             k = (3, 6, 9)[i]
             x_in = acts_in[i]
             cout, cin = v[k].shape[2], v[k].shape[3]
-            # beta gradient, raw weight gradient (w.r.t. the folded weight), then gamma gradient + rescale
-            check(lib.b2g_colsum_bf16(_p(dq), _p(g[k + 2]), dq.numel() // cout, cout, _stream()), "b2g_colsum_bf16")
+            # raw weight gradient (w.r.t. the folded weight), then gamma gradient + rescale
             ops.conv_wgrad(CONV_K4S2, dq, x_in, g[k])
             check(lib.b2g_bn_fold_finalize(_p(v[k]), _p(g[k]), _p(v[k + 1]), INV_STD, _p(g[k + 1]), 16, cout, cin,
                                            _stream()), "b2g_bn_fold_finalize")
             dprev = self._buf(f"dq{i}", tuple(x_in.shape), torch.bfloat16)
-            ops.conv_igemm(CONV_K4S2, dq, self._wp_d[i], dprev, yprev=x_in, dact=ACT_RELU)
+            ops.conv_igemm(CONV_K4S2, dq, self._wp_d[i], dprev, yprev=x_in, dact=ACT_RELU,
+                           colsum=g[(3, 6, 9)[i - 1] + 2] if i > 0 else None)
             dq = dprev
         check(lib.b2g_dense_g_bwd(_p(self._z), _p(v[0]), _p(v[1]), INV_STD, _p(dq), _p(g[0]), _p(g[1]), _p(g[2]),
                                   B, self.F, _stream()), "b2g_dense_g_bwd", (B + 31) // 32)
@@ -446,12 +448,16 @@ class Discriminator:
             _name, k, s, _ci, cout = D_CONVS[i]
             x_in = acts[i - 1]
             if need_wgrad:
-                check(lib.b2g_colsum_bf16(_p(dpre), _p(g[2 * i + 1]), dpre.numel() // cout, cout, _stream()),
-                      "b2g_colsum_bf16")
+                if i == 6:  # conv7's output gradient comes from the head kernel; the others carry fused sums
+                    check(lib.b2g_colsum_bf16(_p(dpre), _p(g[2 * i + 1]), dpre.numel() // cout, cout, _stream()),
+                          "b2g_colsum_bf16")
                 ops.conv_wgrad(CONV_K3S1 if s == 1 else CONV_K4S2, x_in, dpre, g[2 * i])
             dprev = self._buf(f"dpre{i}", tuple(x_in.shape), torch.bfloat16)
+            # the input-gradient call also sums what it stores per channel = bias gradient of the layer below
+            # (conv1's comes out of its weight-gradient GEMM through the ones channel of the im2col operand)
             ops.conv_igemm(CONV_K3S1 if s == 1 else CONVT_K4S2, dpre, self._wp_d[i], dprev, yprev=x_in,
-                           dact=ACT_LEAKY, dact_alpha=LEAKY_ALPHA, dact_scale=dscale, dact_zero=dzero)
+                           dact=ACT_LEAKY, dact_alpha=LEAKY_ALPHA, dact_scale=dscale, dact_zero=dzero,
+                           colsum=g[2 * (i - 1) + 1] if (need_wgrad and i >= 2) else None)
             dpre = dprev
         H, W = self.input_size[0], self.input_size[1]
         if need_wgrad:

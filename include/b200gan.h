@@ -85,6 +85,10 @@ typedef struct b2g_conv_args {
   /* tf32 = 1: the fp32 / tf32 path of north_star: `in`, `out`, `yprev` are fp32 NHWC (Cin % 32 == 0), wpacked is the
      fp32 packing produced by b2g_pack_conv_weight_f32, the MMAs are tcgen05 kind::tf32 (fp32 accumulate). */
   int tf32;
+  /* optional fp32 [Cout] (bf16 outputs, no bias, dact != NONE — a backward epilogue): += the per-channel sums of
+     the stored outputs over all pixels, i.e. the bias / BatchNorm-beta gradient of the layer whose output
+     gradient this call produces (replaces a separate reduction pass over `out`). */
+  float* colsum;
 } b2g_conv_args;
 
 int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
