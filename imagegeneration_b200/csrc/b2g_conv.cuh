@@ -189,6 +189,8 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvPlan& pl, int n_tiles
 
 // CTA-pair (cta_group::2) kernel (b2g_conv_pair.cu); *handled tells the caller whether the role was taken
 int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream, bool* handled);
+// weight gradient with the shifted operand read once per pixel row (b2g_wgrad_slab.cu)
+int launch_wgrad_slab(const b2g_wgrad_args* a, void* stream, bool* handled);
 // 3-channel 3x3 conv with the im2col patch built in shared memory (b2g_conv_c3.cu)
 int launch_conv_c3(const b2g_conv_args* a, void* stream);
 

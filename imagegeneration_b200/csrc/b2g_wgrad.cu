@@ -519,6 +519,11 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   // Measured on B200 (profiles/r1_wgrad_variants.md): grouping taps wins when the other kernel's N tile would be
   // narrow (Cb == 128: 64->128 and 128->128 layers); for Cb >= 256 the per-tap kernel with vector reds is faster.
   const bool use_taps = taps_ok && (force_taps < 0 ? a->Cb == 128 : force_taps != 0);
+  if (use_taps) {  // same layers, shifted operand read once per pixel row when the grid is >= 64 pixels wide
+    bool handled = false;
+    int rc = launch_wgrad_slab(a, stream_, &handled);
+    if (rc || handled) return rc;
+  }
   if (use_taps) {
     // tap-grouped kernel (M = unshifted operand, N = taps x shifted channels)
     WgradTapsParams tp;

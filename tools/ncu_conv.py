@@ -51,5 +51,8 @@ for _ in range(reps):
     ops.conv_wgrad(ops.CONV_K3S1, x3, rnd(B, 72, 128, 128), dw3)
     dw5 = torch.zeros(3, 3, 256, 256, device=dev)
     ops.conv_wgrad(ops.CONV_K3S1, rnd(B, 36, 64, 256), rnd(B, 36, 64, 256), dw5)
+    # 7. wgrad conv2 (64 -> 128, stride 2): tap-grouped kernel, 16 taps
+    dw2 = torch.zeros(4, 4, 64, 128, device=dev)
+    ops.conv_wgrad(ops.CONV_K4S2, rnd(B, 144, 256, 64), rnd(B, 72, 128, 128), dw2)
 torch.cuda.synchronize()
 print("ok")
