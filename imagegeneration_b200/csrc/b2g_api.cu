@@ -61,13 +61,15 @@ __global__ void pack_conv_weight_kernel(int kind, int kh, int kw, int D2, int D3
   }
 }
 
-// All packings of one model in ONE launch (the train step re-packs every conv weight after each optimizer update):
-// the jobs travel as kernel parameters, block b works on job j with first_block[j] <= b < first_block[j + 1].
+// All packings of one model in ONE launch (the train step re-packs every conv weight after each optimizer update).
+// The jobs travel as kernel parameters; block b works on tile (b - first_block[j]) of job j.  A tile is 32 output
+// rows n x 64 packed columns c of one (phase, tap): the fp32 source is read along whichever of n / c is contiguous in
+// the Keras layout (coalesced), transposed through shared memory and written as 128-byte bf16 rows.
 constexpr int kMaxPackJobs = 24;
-constexpr int kPackElemsPerBlock = 2048;
+constexpr int kPackTileN = 32, kPackTileC = 64;
 struct PackJobDev {
-  int kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, taps, first_block;
-  long total;
+  int kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, taps, phases, first_block;
+  int Cn, Ckr, Ck, n_blocks, c_blocks;
   const float *w, *scale_scalar, *scale_d2, *scale_d3;
   __nv_bfloat16* out;
 };
@@ -77,24 +79,76 @@ struct alignas(16) PackMultiParams {
 };
 
 __global__ void __launch_bounds__(256) pack_conv_weight_multi_kernel(const __grid_constant__ PackMultiParams p) {
+  __shared__ float tile[kPackTileN][kPackTileC + 1];
   int j = 0;
   while (j + 1 < p.n_jobs && (int)blockIdx.x >= p.job[j + 1].first_block) ++j;
   const PackJobDev& q = p.job[j];
-  const float s0 = q.scale_scalar ? *q.scale_scalar : 1.f;
-  const long base = (long)(blockIdx.x - q.first_block) * kPackElemsPerBlock;
-#pragma unroll 1
-  for (int e = threadIdx.x; e < kPackElemsPerBlock; e += 256) {
-    const long i = base + e;
-    if (i >= q.total) break;
-    int d2, d3;
-    const long src = pack_source_index(q.kind, q.kh, q.kw, q.D2, q.D3, q.n_is_d3, q.flip, q.ck_pad, q.taps, i, &d2, &d3);
-    float v = 0.f;
-    if (src >= 0) {
-      v = q.w[src] * s0;
-      if (q.scale_d2) v *= q.scale_d2[d2];
-      if (q.scale_d3) v *= q.scale_d3[d3];
+  int t = blockIdx.x - q.first_block;
+  const int cb = t % q.c_blocks; t /= q.c_blocks;
+  const int nb = t % q.n_blocks; t /= q.n_blocks;
+  const int tap = t % q.taps;
+  const int ph = t / q.taps;
+  const int n0 = nb * kPackTileN, c0 = cb * kPackTileC;
+  int ky, kx;
+  if (q.kind == B2G_CONVT_K4S2) {
+    int d;
+    convt_tap(ph >> 1, tap >> 1, &ky, &d);
+    convt_tap(ph & 1, tap & 1, &kx, &d);
+  } else {
+    ky = tap / q.kw;
+    kx = tap % q.kw;
+    if (q.flip) {
+      ky = q.kh - 1 - ky;
+      kx = q.kw - 1 - kx;
     }
-    q.out[i] = __float2bfloat16_rn(v);
+  }
+  const float* src = q.w + ((size_t)ky * q.kw + kx) * q.D2 * q.D3;  // [D2][D3] plane of this tap
+  const float s0 = q.scale_scalar ? *q.scale_scalar : 1.f;
+  const int tid = threadIdx.x;
+  if (q.n_is_d3) {  // n = d3 is the contiguous source index: a warp reads 32 consecutive n of one c
+    const int nx = tid & 31, cy = tid >> 5;
+    const int n = n0 + nx;
+    const float sn = (q.scale_d3 && n < q.Cn) ? q.scale_d3[n] : 1.f;
+#pragma unroll
+    for (int r = 0; r < kPackTileC / 8; ++r) {
+      const int cl = cy + 8 * r, c = c0 + cl;
+      float v = 0.f;
+      if (n < q.Cn && c < q.Ckr) {
+        v = src[(size_t)c * q.D3 + n] * s0;  // same multiplication order as the single-tensor kernel
+        if (q.scale_d2) v *= q.scale_d2[c];
+        v *= sn;
+      }
+      tile[nx][cl] = v;
+    }
+  } else {  // c = d3 is contiguous: 64 consecutive c of one n
+    const int cx = tid & 63, ny = tid >> 6;
+    const int c = c0 + cx;
+    const float sc = (q.scale_d3 && c < q.Ckr) ? q.scale_d3[c] : 1.f;
+#pragma unroll
+    for (int r = 0; r < kPackTileN / 4; ++r) {
+      const int nl = ny + 4 * r, n = n0 + nl;
+      float v = 0.f;
+      if (n < q.Cn && c < q.Ckr) {
+        v = src[(size_t)n * q.D3 + c] * s0;
+        if (q.scale_d2) v *= q.scale_d2[n];
+        v *= sc;
+      }
+      tile[nl][cx] = v;
+    }
+  }
+  __syncthreads();
+  // out[ph][n][tap * Ck + c]: 8 threads write the 64 columns of one row (16 bytes each)
+  const int nl = tid >> 3, c8 = (tid & 7) * 8;
+  const int n = n0 + nl;
+  if (n < q.Cn && c0 + c8 < q.Ck) {
+    const float* tr = &tile[nl][c8];
+    uint4 o;
+    o.x = pack_bf16x2(tr[0], tr[1]);
+    o.y = pack_bf16x2(tr[2], tr[3]);
+    o.z = pack_bf16x2(tr[4], tr[5]);
+    o.w = pack_bf16x2(tr[6], tr[7]);
+    __nv_bfloat16* dst = q.out + ((size_t)ph * q.Cn + n) * ((size_t)q.taps * q.Ck) + (size_t)tap * q.Ck + c0 + c8;
+    *reinterpret_cast<uint4*>(dst) = o;
   }
 }
 
@@ -181,14 +235,17 @@ extern "C" int b2g_pack_conv_weight_multi(const b2g_pack_job* jobs, int n_jobs, 
     if (rc) return rc;
     const int ckr = s.n_is_d3 ? s.D2 : s.D3, cn = s.n_is_d3 ? s.D3 : s.D2;
     const int ck = s.ck_pad > ckr ? s.ck_pad : ckr;
+    if (ck % 8) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_pack_conv_weight_multi: job %d packs %d columns per tap (not a multiple of 8)", j, ck);
     PackJobDev& d = p.job[j];
     d.kind = s.kind; d.kh = s.kh; d.kw = s.kw; d.D2 = s.D2; d.D3 = s.D3;
-    d.n_is_d3 = s.n_is_d3; d.flip = s.flip; d.ck_pad = s.ck_pad; d.taps = taps;
-    d.total = (long)phases * taps * cn * ck;
+    d.n_is_d3 = s.n_is_d3; d.flip = s.flip; d.ck_pad = s.ck_pad; d.taps = taps; d.phases = phases;
+    d.Cn = cn; d.Ckr = ckr; d.Ck = ck;
+    d.n_blocks = (cn + kPackTileN - 1) / kPackTileN;
+    d.c_blocks = (ck + kPackTileC - 1) / kPackTileC;
     d.first_block = blocks;
     d.w = s.w; d.scale_scalar = s.scale_scalar; d.scale_d2 = s.scale_d2; d.scale_d3 = s.scale_d3;
     d.out = static_cast<__nv_bfloat16*>(s.wpacked);
-    blocks += (int)((d.total + kPackElemsPerBlock - 1) / kPackElemsPerBlock);
+    blocks += phases * taps * d.n_blocks * d.c_blocks;
   }
   p.n_jobs = n_jobs;
   pack_conv_weight_multi_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(p);
