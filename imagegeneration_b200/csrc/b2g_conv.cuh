@@ -191,6 +191,8 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvPlan& pl, int n_tiles
 int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream, bool* handled);
 // weight gradient with the shifted operand read once per pixel row (b2g_wgrad_slab.cu)
 int launch_wgrad_slab(const b2g_wgrad_args* a, void* stream, bool* handled);
+// weight + bias gradient of the 3-channel edge layers, im2col operand built in shared memory (b2g_wgrad_c3.cu)
+int launch_wgrad_c3(const b2g_wgrad_args* a, void* stream);
 // 3-channel 3x3 conv with the im2col patch built in shared memory (b2g_conv_c3.cu)
 int launch_conv_c3(const b2g_conv_args* a, void* stream);
 

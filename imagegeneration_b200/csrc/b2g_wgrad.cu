@@ -504,6 +504,7 @@ using namespace b2g;
 extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!a || !a->shifted || !a->unshifted || !a->dw) return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: null pointer");
+  if (a->kind == B2G_CONV_K3S1_C3) return launch_wgrad_c3(a, stream_);  // 3-channel edge layers (b2g_wgrad_c3.cu)
   if (a->kind != B2G_CONV_K3S1 && a->kind != B2G_CONV_K4S2 && a->kind != B2G_CONV_K1S1)
     return fail(B2G_E_INVALID_ARG, "b2g_conv_wgrad: kind must be K3S1, K4S2 or K1S1 (tap plan of the shifted operand)");
   if (a->Ca % 64 || a->Cb % 64 || a->Ca <= 0 || a->Cb <= 0)

@@ -182,9 +182,23 @@ def conv_wgrad(kind: int, shifted: torch.Tensor, unshifted: torch.Tensor, dw: to
 
     dw is fp32 [k,k,Ca,Cb] and is accumulated into (zero it first for a fresh gradient).  tf32=True takes fp32
     operands (kind::tf32 products, the per-layer 1e-3 parity path); the training step uses bf16 operands."""
-    _need_cuda(shifted, unshifted, dw)
+    _need_cuda(shifted, unshifted, dw, dbias)
     n, hs, ws, ca = shifted.shape
     cb = unshifted.shape[3]
+    if kind == CONV_K3S1_C3:
+        # 3-channel edge layers: fp32 [N,H,W,3] x bf16 [N,H,W,64] -> dw [27][64] (+ dbias [64]); the im2col operand
+        # of the K1S1 route is built inside the kernel
+        if (shifted.dtype != torch.float32 or ca != 3 or unshifted.dtype != torch.bfloat16 or cb != 64
+                or tuple(unshifted.shape[:3]) != (n, hs, ws) or dw.dtype != torch.float32 or dw.numel() != 27 * 64
+                or tf32 or ca_valid not in (0, 27)):
+            raise B200GanError("conv_wgrad(K3S1_C3): expected fp32 [N,H,W,3], bf16 [N,H,W,64] and fp32 dw [27][64]")
+        a = WgradArgs(kind=kind, N=n, Hs=hs, Ws=ws, Ca=3, Cb=64, shifted=shifted.data_ptr(),
+                      unshifted=unshifted.data_ptr(), dw=dw.data_ptr(), ca_valid=27,
+                      dbias=None if dbias is None else dbias.data_ptr(), tf32=0)
+        ev = _prof_begin()
+        check(_lib.load().b2g_conv_wgrad(C.byref(a), _stream()), "b2g_conv_wgrad")
+        _prof_end(ev, "conv_wgrad", 2.0 * n * hs * ws * 27 * 64, f"kind{kind} {n}x{hs}x{ws} Ca3 Cb64")
+        return dw
     k = {CONV_K3S1: 3, CONV_K4S2: 4, CONV_K1S1: 1}[kind]
     hg, wg = (hs // 2, ws // 2) if kind == CONV_K4S2 else (hs, ws)
     if tuple(unshifted.shape) != (n, hg, wg, cb):

@@ -234,8 +234,7 @@ class Generator:
         self.zero_grads()
         # convT4 (64 -> 3, k3 s1) on tensor cores through the 27-channel im2col of dY: wgrad + input gradient
         # (ReLU' of a3 in the epilogue)
-        x27 = ops.im2col27(d_pre_tanh, self._buf("dy27", (B, H, W, 64), torch.bfloat16))
-        ops.conv_wgrad(CONV_K1S1, x27, a3, g[12], ca_valid=27)
+        ops.conv_wgrad(CONV_K3S1_C3, d_pre_tanh, a3, g[12])
         # every input-gradient call also leaves the per-channel sums of what it stored = the beta gradient of the
         # BatchNorm in front of it (fused into the epilogue: no separate pass over dq)
         dq = self._buf("dq3", tuple(a3.shape), torch.bfloat16)
@@ -461,10 +460,10 @@ class Discriminator:
             dpre = dprev
         H, W = self.input_size[0], self.input_size[1]
         if need_wgrad:
-            x27 = self._x27
-            if x27 is None:
-                x27 = ops.im2col27(self._x_in, self._buf("x27", (B, H, W, 64), torch.bfloat16))
-            ops.conv_wgrad(CONV_K1S1, x27, dpre, g[0], ca_valid=27, dbias=g[1])
+            if self._x27 is not None:   # caller supplied the im2col operand (b2g_im2col27): K1S1 GEMM route
+                ops.conv_wgrad(CONV_K1S1, self._x27, dpre, g[0], ca_valid=27, dbias=g[1])
+            else:                       # patch built inside the kernel from the fp32 input
+                ops.conv_wgrad(CONV_K3S1_C3, self._x_in, dpre, g[0], dbias=g[1])
             if self.spectral_norm:
                 for i in range(8):
                     check(lib.b2g_sn_grad_finalize(_p(v[2 * i]), _p(g[2 * i]), _p(self.sn_u[i]), _p(self.sn_vraw[i]),

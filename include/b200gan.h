@@ -137,6 +137,9 @@ int b2g_im2col27(const float* in, void* out, int N, int H, int W, b2g_stream_t s
  *     Conv2D k4 s2  [4,4,Cin,Cout]:  kind=K4S2, shifted = layer input x   (Ca=Cin),  unshifted = dY (Cb=Cout)
  *     Conv2DTranspose k4 s2 [4,4,Cout,Cin]: kind=K4S2, shifted = dY (Ca=Cout), unshifted = layer input (Cb=Cin)
  *     3-channel edge layers [3,3,3,64]:     kind=K1S1, shifted = im2col27(3-channel tensor), unshifted = 64-ch tensor
+ *       or, without the im2col27 tensor:    kind=K3S1_C3, shifted = the fp32 [N,Hs,Ws,3] tensor itself (Ca=3),
+ *       unshifted = bf16 [N,Hs,Ws,64] (Cb=64), dw = [27][64] (row tap*3+c), dbias = [64] or NULL — the patch is
+ *       built in shared memory inside the kernel
  *   Hs, Ws = spatial size of the shifted operand; the unshifted one is (Hs,Ws) for K3S1, (Hs/2,Ws/2) for K4S2.
  *   Replaces Conv2DBackpropFilter behind tape.gradient (sndcgan/SNDCGAN.py:248,:256,:266). */
 typedef struct b2g_wgrad_args {

@@ -97,6 +97,27 @@ def test_edge_wgrad_tensor_core(n, h, w):
     assert _rel_l2(db, bb.grad) < 2e-3
 
 
+@pytest.mark.parametrize("n,h,w", EDGE)
+def test_edge_wgrad_fused_patch_kernel(n, h, w):
+    """Same gradients with the patch built inside the kernel (kind K3S1_C3): no im2col27 tensor; bit-compatible
+    accumulation semantics (dw / dbias are added to)."""
+    from imagegeneration_b200 import ops
+    x = _rand((n, h, w, 3), 9)
+    dy = _bf(_rand((n, h, w, 64), 10))
+    wt = torch.zeros((3, 3, 3, 64), requires_grad=True)
+    bb = torch.zeros((64,), requires_grad=True)
+    K.conv2d_same(_bf(x), wt, bb, 1).backward(dy)
+    dw = torch.zeros((3, 3, 3, 64), device="cuda")
+    db = torch.zeros((64,), device="cuda")
+    ops.conv_wgrad(ops.CONV_K3S1_C3, x.cuda(), dy.cuda().to(torch.bfloat16), dw, dbias=db)
+    torch.cuda.synchronize()
+    assert _rel_l2(dw, wt.grad) < 2e-3
+    assert _rel_l2(db, bb.grad) < 2e-3
+    ops.conv_wgrad(ops.CONV_K3S1_C3, x.cuda(), dy.cuda().to(torch.bfloat16), dw)      # accumulates, bias optional
+    torch.cuda.synchronize()
+    assert _rel_l2(dw, 2 * wt.grad) < 2e-3 and _rel_l2(db, bb.grad) < 2e-3
+
+
 @pytest.mark.parametrize("n,h,w", EDGE[:2])
 def test_edge_cuda_core_variants(n, h, w):
     """The direct (CUDA-core) edge kernels kept in the ABI agree with the oracle too."""

@@ -116,3 +116,6 @@ timeit("stem fwd (W 151 MB + out)", lambda: L.check(lib.b2g_dense_g_fwd(_p(zz), 
 dWd = torch.empty_like(Wd); dg = torch.empty(F, device="cuda"); dbt = torch.empty(F, device="cuda")
 timeit("stem bwd (W + dW + dq)", lambda: L.check(lib.b2g_dense_g_bwd(_p(zz), _p(Wd), _p(gm), 0.9995, _p(od), _p(dWd), _p(dg), _p(dbt), B, F, _s()), "b"),
        F * 128 * 8 + B * F * 2)
+x_img = torch.rand((B, 144, 256, 3), device="cuda") * 2 - 1
+timeit("edge wgrad fused (fp32 x, dy -> [27][64] + bias)",
+       lambda: ops.conv_wgrad(ops.CONV_K3S1_C3, x_img, yprev, dw, dbias=db), px * (12 + 128))
