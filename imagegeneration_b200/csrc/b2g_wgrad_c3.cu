@@ -7,9 +7,11 @@
 //                 3-channel tensor ((bw+8)*3 floats x (bh+2) rows x bn images, zero fill outside the image)
 //   warp 1      : MMA issuer — 4 MMAs (K = 16 pixels each, M = 128 with the upper 64 rows a constant zero box,
 //                 N = 64), MN-major operands: a pixel is one 128-byte line of either tile
-//   warps 2..3  : patch builders, one pixel per thread: 27 LDS.32 from the halo box -> one 128-byte line
-//                 [27 taps*channels, 1.0, zeros] at its SW128-swizzled place (= a row of the im2col27 tensor)
-//   warps 4..7  : epilogue after the CTA's last k-step: rows 0..26 -> dW (fp32 reds), row 27 -> dbias
+//   warps 2..5  : patch builders, two groups of 64 threads taking alternate k-steps (one k-step is a serial chain
+//                 wait -> 27 LDS -> pack -> 8 STS -> proxy fence -> arrive; two chains in flight hide it), one pixel
+//                 per thread: 27 LDS.32 from the halo box -> one 128-byte line [27 taps*channels, 1.0, zeros] at
+//                 its SW128-swizzled place (= a row of the im2col27 tensor)
+//   warps 6..9  : epilogue after the CTA's last k-step: rows 0..26 -> dW (fp32 reds), row 27 -> dbias
 //
 // HBM traffic per pixel: 12 B + 128 B, against 12 + 128 (im2col27) + 128 + 128 (K1S1 weight-gradient GEMM) for the
 // two-kernel route.  Replaces Conv2DBackpropFilter / BiasAddGrad of D.conv1 (sndcgan/SNDCGAN.py:73-78 under
@@ -29,27 +31,32 @@ struct alignas(64) WgradC3Params {
   ConvPlan plan;     // K1S1 geometry, 64-pixel boxes
   int in_box_bytes;
   int ptiles;
+  int dbg_skip;
   float* dw;         // [27][64]
   float* dbias;      // [64] or null
 };
 
 struct WgradC3Cfg {
   static constexpr int kTile = 64 * 128;      // one [64 px][64 ch] bf16 tile
-  static constexpr int kStageBytes = 3 * kTile;  // built tile, constant zero tile (M rows 64..127), U tile
-  static constexpr int kStages = 4;
-  static constexpr int kInStages = 6;
-  static constexpr int kInStageBytes = 8192;
-  static constexpr int kThreads = 64 + 64 + 128;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kInStages * kInStageBytes + 256 + 1024;
+  static constexpr int kStages = 4;           // built tiles; ONE constant zero tile (M rows 64..127) follows them
+  static constexpr int kUStages = 12;         // U tiles: 96 KB in flight per SM (the kernel is an HBM stream over U)
+  static constexpr int kInStages = 16;        // halo boxes: small, slow-to-arrive TMA boxes (8-byte elements) -> deep ring
+  static constexpr int kInStageBytes = 4096;  // 64-pixel row tile: 3 x 72 x 12 = 2592 bytes
+  static constexpr int kBuilderGroups = 2;
+  static constexpr int kThreads = 64 + 64 * kBuilderGroups + 128;
+  static constexpr int kSmemBytes = (kStages + 1 + kUStages) * kTile + kInStages * kInStageBytes + 512 + 1024;
 };
 
 __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const __grid_constant__ WgradC3Params p) {
   using Cfg = WgradC3Cfg;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* insm = smem + Cfg::kStages * Cfg::kStageBytes;
+  uint8_t* zsm = smem + Cfg::kStages * Cfg::kTile;  // the zero tile
+  uint8_t* usm = zsm + Cfg::kTile;
+  uint8_t* insm = usm + Cfg::kUStages * Cfg::kTile;
   uint64_t* ufull = reinterpret_cast<uint64_t*>(insm + Cfg::kInStages * Cfg::kInStageBytes);
-  uint64_t* sfull = ufull + Cfg::kStages;
+  uint64_t* uempty = ufull + Cfg::kUStages;
+  uint64_t* sfull = uempty + Cfg::kUStages;
   uint64_t* empty = sfull + Cfg::kStages;
   uint64_t* in_full = empty + Cfg::kStages;
   uint64_t* in_empty = in_full + Cfg::kInStages;
@@ -65,9 +72,12 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::kStages; ++s) {
-      mbar_init(&ufull[s], 1);
       mbar_init(&sfull[s], 2);
       mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < Cfg::kUStages; ++s) {
+      mbar_init(&ufull[s], 1);
+      mbar_init(&uempty[s], 1);
     }
     for (int s = 0; s < Cfg::kInStages; ++s) {
       mbar_init(&in_full[s], 1);
@@ -76,11 +86,9 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
     mbar_init(tfull, 1);
     fence_barrier_init();
   }
-  // the zero tile of every stage (M rows 64..127 of the shifted operand), written once
-  for (int i = threadIdx.x; i < Cfg::kStages * (Cfg::kTile / 16); i += Cfg::kThreads) {
-    const int s = i / (Cfg::kTile / 16), o = i % (Cfg::kTile / 16);
-    *reinterpret_cast<uint4*>(smem + s * Cfg::kStageBytes + Cfg::kTile + o * 16) = make_uint4(0, 0, 0, 0);
-  }
+  // the zero tile (M rows 64..127 of the shifted operand), written once
+  for (int i = threadIdx.x; i < Cfg::kTile / 16; i += Cfg::kThreads)
+    *reinterpret_cast<uint4*>(zsm + i * 16) = make_uint4(0, 0, 0, 0);
   fence_proxy_async_smem();
   if (warp == 1) tmem_alloc(tmem_slot, 64);
   tc_fence_before();
@@ -95,26 +103,27 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
       tma_prefetch_desc(&p.umap);
       tma_prefetch_desc(&p.imap);
     }
-    int stage = 0, istage = 0;
-    uint32_t phase = 0, iphase = 0;
+    int ustage = 0, istage = 0;
+    uint32_t uphase = 0, iphase = 0;
     for (int pt = p_begin; pt < p_end; ++pt) {
       const int tw = pt % pl.tiles_w;
       const int r2 = pt / pl.tiles_w;
       const int th = r2 % pl.tiles_h, tn = r2 / pl.tiles_h;
       const int w0 = tw * pl.bw, h0 = th * pl.bh, n0 = tn * pl.bn;
       mbar_wait(&in_empty[istage], iphase ^ 1);
-      if (leader) {
+      if (leader && p.dbg_skip) mbar_arrive(&in_full[istage]);
+      if (leader && !p.dbg_skip) {
         mbar_expect_tx(&in_full[istage], p.in_box_bytes);
         tma_load_3d(insm + istage * Cfg::kInStageBytes, &p.imap, &in_full[istage], (w0 - 4) * 3 / 2, h0 - 1, n0);
       }
       __syncwarp();
-      mbar_wait(&empty[stage], phase ^ 1);
+      mbar_wait(&uempty[ustage], uphase ^ 1);
       if (leader) {
-        mbar_expect_tx(&ufull[stage], Cfg::kTile);
-        tma_load_4d(smem + stage * Cfg::kStageBytes + 2 * Cfg::kTile, &p.umap, &ufull[stage], 0, w0, h0, n0);
+        mbar_expect_tx(&ufull[ustage], Cfg::kTile);
+        tma_load_4d(usm + ustage * Cfg::kTile, &p.umap, &ufull[ustage], 0, w0, h0, n0);
       }
       __syncwarp();
-      if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      if (++ustage == Cfg::kUStages) { ustage = 0; uphase ^= 1; }
       if (++istage == Cfg::kInStages) { istage = 0; iphase ^= 1; }
     }
   } else if (warp == 1) {
@@ -122,35 +131,38 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
     const uint32_t leader = elect_one_sync();
     constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 128, 64);
     const uint32_t smem_base = smem_u32(smem);
-    int stage = 0;
-    uint32_t phase = 0;
+    int stage = 0, ustage = 0;
+    uint32_t phase = 0, uphase = 0;
     for (int pt = p_begin; pt < p_end; ++pt) {
-      mbar_wait(&ufull[stage], phase);
+      mbar_wait(&ufull[ustage], uphase);
       mbar_wait(&sfull[stage], phase);
       tc_fence_after();
-      const uint32_t s_addr = smem_base + stage * Cfg::kStageBytes;
-      const uint64_t sdesc = umma_smem_desc(s_addr, Cfg::kTile, 1024);  // atoms: built tile, zero tile
-      const uint64_t udesc = umma_smem_desc(s_addr + 2 * Cfg::kTile, Cfg::kTile, 1024);
+      // atoms of the M side: built tile of this stage, then the zero tile behind the ring
+      const uint64_t sdesc = umma_smem_desc(smem_base + stage * Cfg::kTile, (Cfg::kStages - stage) * Cfg::kTile, 1024);
+      const uint64_t udesc = umma_smem_desc(smem_u32(usm) + ustage * Cfg::kTile, Cfg::kTile, 1024);
       if (leader) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16(tmem_base, sdesc + 128 * k, udesc + 128 * k, idesc, (pt > p_begin) || k != 0);
         umma_commit(&empty[stage]);
+        umma_commit(&uempty[ustage]);
       }
       __syncwarp();
       if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      if (++ustage == Cfg::kUStages) { ustage = 0; uphase ^= 1; }
     }
     if (leader) umma_commit(tfull);
     __syncwarp();
-  } else if (warp < 4) {
+  } else if (warp < 2 + 2 * Cfg::kBuilderGroups) {
     // ------------------------------------------------ patch builders: thread m owns pixel (k) line m of the tile
-    const int m = threadIdx.x - 64;
+    const int grp = (warp - 2) >> 1;
+    const int m = (threadIdx.x - 64) & 63;
     const int wl = m % pl.bw, hl = (m / pl.bw) % pl.bh, nl = m / (pl.bw * pl.bh);
     const uint32_t row_off = m * 128, sw = m & 7;
     const int pitch = (pl.bw + 8) * 3;
     const int win_off = ((nl * (pl.bh + 2) + hl) * (pl.bw + 8) + wl + 3) * 3;
-    int stage = 0, istage = 0;
-    uint32_t phase = 0, iphase = 0;
-    for (int pt = p_begin; pt < p_end; ++pt) {
+    for (int i = grp; i < p_end - p_begin; i += Cfg::kBuilderGroups) {
+      const int stage = i % Cfg::kStages, istage = i % Cfg::kInStages;
+      const uint32_t phase = (i / Cfg::kStages) & 1, iphase = (i / Cfg::kInStages) & 1;
       float v[32];
       mbar_wait_parked(&in_full[istage], iphase);
       const float* src = reinterpret_cast<const float*>(insm + istage * Cfg::kInStageBytes) + win_off;
@@ -162,7 +174,7 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
 #pragma unroll
       for (int k = 28; k < 32; ++k) v[k] = 0.f;
       mbar_wait_parked(&empty[stage], phase ^ 1);
-      uint8_t* dst = smem + stage * Cfg::kStageBytes + row_off;
+      uint8_t* dst = smem + stage * Cfg::kTile + row_off;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         uint4 o = make_uint4(0, 0, 0, 0);
@@ -180,8 +192,6 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
         mbar_arrive(&in_empty[istage]);
         mbar_arrive(&sfull[stage]);
       }
-      if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-      if (++istage == Cfg::kInStages) { istage = 0; iphase ^= 1; }
     }
   } else {
     // ------------------------------------------------ epilogue: accumulator rows = im2col channel a, columns = b
@@ -246,6 +256,7 @@ int launch_wgrad_c3(const b2g_wgrad_args* a, void* stream_) {
     if (rc) return rc;
   }
   kp.ptiles = pl.m_tiles;
+  kp.dbg_skip = getenv("B2G_DBG_SKIP_HALO") ? 1 : 0;
   kp.dw = a->dw;
   kp.dbias = a->dbias;
   static bool attr_set = false;
