@@ -3,15 +3,18 @@
 //
 //   dW[tap*3 + c][b] = sum_px in[px shifted by tap][c] * U[px][b]      dbias[b] = sum_px U[px][b]
 //
-//   warp 0      : TMA producer — per 64-pixel k-step one [64 px][64 ch] bf16 box of U and one fp32 halo box of the
-//                 3-channel tensor ((bw+8)*3 floats x (bh+2) rows x bn images, zero fill outside the image)
+//   warp 0      : TMA producer of U — per 64-pixel k-step one [64 px][64 ch] bf16 box (12-deep ring)
+//   warp 2      : TMA producer of the fp32 halo boxes of the 3-channel tensor ((bw+8)*3 floats x (bh+2) rows x bn
+//                 images, zero fill outside the image).  Two producer warps with division-free tile iterators: a
+//                 k-step moves only 10.6 KB, so the per-iteration cost of ONE issuing warp (measured ~800 clk
+//                 with the decode's integer divisions) was the bound of the whole kernel
 //   warp 1      : MMA issuer — 4 MMAs (K = 16 pixels each, M = 128 with the upper 64 rows a constant zero box,
 //                 N = 64), MN-major operands: a pixel is one 128-byte line of either tile
-//   warps 2..5  : patch builders, two groups of 64 threads taking alternate k-steps (one k-step is a serial chain
+//   warps 3..6  : patch builders, two groups of 64 threads taking alternate k-steps (one k-step is a serial chain
 //                 wait -> 27 LDS -> pack -> 8 STS -> proxy fence -> arrive; two chains in flight hide it), one pixel
 //                 per thread: 27 LDS.32 from the halo box -> one 128-byte line [27 taps*channels, 1.0, zeros] at
 //                 its SW128-swizzled place (= a row of the im2col27 tensor)
-//   warps 6..9  : epilogue after the CTA's last k-step: rows 0..26 -> dW (fp32 reds), row 27 -> dbias
+//   warps 7..10 : epilogue after the CTA's last k-step: rows 0..26 -> dW (fp32 reds), row 27 -> dbias
 //
 // HBM traffic per pixel: 12 B + 128 B, against 12 + 128 (im2col27) + 128 + 128 (K1S1 weight-gradient GEMM) for the
 // two-kernel route.  Replaces Conv2DBackpropFilter / BiasAddGrad of D.conv1 (sndcgan/SNDCGAN.py:73-78 under
@@ -27,11 +30,10 @@ namespace b2g {
 
 struct alignas(64) WgradC3Params {
   CUtensorMap umap;  // U bf16 [N,H,W,64], box {64 ch, bw, bh, bn}
-  CUtensorMap imap;  // fp32 [N,H,W,3] as 8-byte elements: dims {W*3/2, H, N}, box {(bw+8)*3/2, bh+2, bn}
+  CUtensorMap imap;  // fp32 [N,H,W,3] as rows of floats: dims {W*3, H, N}, box {(bw+8)*3, bh+2, bn}
   ConvPlan plan;     // K1S1 geometry, 64-pixel boxes
   int in_box_bytes;
   int ptiles;
-  int dbg_skip;
   float* dw;         // [27][64]
   float* dbias;      // [64] or null
 };
@@ -43,7 +45,7 @@ struct WgradC3Cfg {
   static constexpr int kInStages = 16;        // halo boxes: small, slow-to-arrive TMA boxes (8-byte elements) -> deep ring
   static constexpr int kInStageBytes = 4096;  // 64-pixel row tile: 3 x 72 x 12 = 2592 bytes
   static constexpr int kBuilderGroups = 2;
-  static constexpr int kThreads = 64 + 64 * kBuilderGroups + 128;
+  static constexpr int kThreads = 96 + 64 * kBuilderGroups + 128;
   static constexpr int kSmemBytes = (kStages + 1 + kUStages) * kTile + kInStages * kInStageBytes + 512 + 1024;
 };
 
@@ -96,35 +98,38 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
-    // ------------------------------------------------ TMA producer
+  if (warp == 0 || warp == 2) {
+    // ------------------------------------------------ TMA producers: warp 0 = U tiles, warp 2 = fp32 halo boxes
     const uint32_t leader = elect_one_sync();
-    if (leader) {
-      tma_prefetch_desc(&p.umap);
-      tma_prefetch_desc(&p.imap);
-    }
-    int ustage = 0, istage = 0;
-    uint32_t uphase = 0, iphase = 0;
+    const bool is_u = warp == 0;
+    if (leader) tma_prefetch_desc(is_u ? &p.umap : &p.imap);
+    // division-free iterator over this CTA's consecutive tiles
+    int tw = p_begin % pl.tiles_w;
+    int r2 = p_begin / pl.tiles_w;
+    int th = r2 % pl.tiles_h, tn = r2 / pl.tiles_h;
+    const int n_stages = is_u ? Cfg::kUStages : Cfg::kInStages;
+    uint64_t* fullb = is_u ? ufull : in_full;
+    uint64_t* emptyb = is_u ? uempty : in_empty;
+    int stage = 0;
+    uint32_t phase = 0;
     for (int pt = p_begin; pt < p_end; ++pt) {
-      const int tw = pt % pl.tiles_w;
-      const int r2 = pt / pl.tiles_w;
-      const int th = r2 % pl.tiles_h, tn = r2 / pl.tiles_h;
       const int w0 = tw * pl.bw, h0 = th * pl.bh, n0 = tn * pl.bn;
-      mbar_wait(&in_empty[istage], iphase ^ 1);
-      if (leader && p.dbg_skip) mbar_arrive(&in_full[istage]);
-      if (leader && !p.dbg_skip) {
-        mbar_expect_tx(&in_full[istage], p.in_box_bytes);
-        tma_load_3d(insm + istage * Cfg::kInStageBytes, &p.imap, &in_full[istage], (w0 - 4) * 3 / 2, h0 - 1, n0);
-      }
-      __syncwarp();
-      mbar_wait(&uempty[ustage], uphase ^ 1);
+      mbar_wait(&emptyb[stage], phase ^ 1);
       if (leader) {
-        mbar_expect_tx(&ufull[ustage], Cfg::kTile);
-        tma_load_4d(usm + ustage * Cfg::kTile, &p.umap, &ufull[ustage], 0, w0, h0, n0);
+        if (is_u) {
+          mbar_expect_tx(&fullb[stage], Cfg::kTile);
+          tma_load_4d(usm + stage * Cfg::kTile, &p.umap, &fullb[stage], 0, w0, h0, n0);
+        } else {
+          mbar_expect_tx(&fullb[stage], p.in_box_bytes);
+          tma_load_3d(insm + stage * Cfg::kInStageBytes, &p.imap, &fullb[stage], (w0 - 4) * 3, h0 - 1, n0);
+        }
       }
       __syncwarp();
-      if (++ustage == Cfg::kUStages) { ustage = 0; uphase ^= 1; }
-      if (++istage == Cfg::kInStages) { istage = 0; iphase ^= 1; }
+      if (++stage == n_stages) { stage = 0; phase ^= 1; }
+      if (++tw == pl.tiles_w) {
+        tw = 0;
+        if (++th == pl.tiles_h) { th = 0; ++tn; }
+      }
     }
   } else if (warp == 1) {
     // ------------------------------------------------ MMA issuer
@@ -152,10 +157,10 @@ __global__ void __launch_bounds__(WgradC3Cfg::kThreads, 1) wgrad_c3_kernel(const
     }
     if (leader) umma_commit(tfull);
     __syncwarp();
-  } else if (warp < 2 + 2 * Cfg::kBuilderGroups) {
+  } else if (warp < 3 + 2 * Cfg::kBuilderGroups) {
     // ------------------------------------------------ patch builders: thread m owns pixel (k) line m of the tile
-    const int grp = (warp - 2) >> 1;
-    const int m = (threadIdx.x - 64) & 63;
+    const int grp = (warp - 3) >> 1;
+    const int m = (threadIdx.x - 96) & 63;
     const int wl = m % pl.bw, hl = (m / pl.bw) % pl.bh, nl = m / (pl.bw * pl.bh);
     const uint32_t row_off = m * 128, sw = m & 7;
     const int pitch = (pl.bw + 8) * 3;
@@ -242,10 +247,11 @@ int launch_wgrad_c3(const b2g_wgrad_args* a, void* stream_) {
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad(K3S1_C3): cannot stage N=%d H=%d W=%d (box %d bytes)", a->N,
                 a->Hs, a->Ws, kp.in_box_bytes);
   {
-    const uint64_t dims[3] = {(uint64_t)a->Ws * 3 / 2, (uint64_t)a->Hs, (uint64_t)a->N};
+    // rows of (bw + 8) * 3 <= 216 floats: the box fits the 256-element limit as plain fp32
+    const uint64_t dims[3] = {(uint64_t)a->Ws * 3, (uint64_t)a->Hs, (uint64_t)a->N};
     const uint64_t str[2] = {(uint64_t)a->Ws * 12, (uint64_t)a->Hs * a->Ws * 12};
-    const uint32_t ibox[3] = {(uint32_t)(pl.bw + 8) * 3 / 2, (uint32_t)pl.bh + 2, (uint32_t)pl.bn};
-    int rc = make_tmap(&kp.imap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, a->shifted, dims, str, ibox, CU_TENSOR_MAP_SWIZZLE_NONE);
+    const uint32_t ibox[3] = {(uint32_t)(pl.bw + 8) * 3, (uint32_t)pl.bh + 2, (uint32_t)pl.bn};
+    int rc = make_tmap(&kp.imap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, a->shifted, dims, str, ibox, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
   }
   {
@@ -256,7 +262,6 @@ int launch_wgrad_c3(const b2g_wgrad_args* a, void* stream_) {
     if (rc) return rc;
   }
   kp.ptiles = pl.m_tiles;
-  kp.dbg_skip = getenv("B2G_DBG_SKIP_HALO") ? 1 : 0;
   kp.dw = a->dw;
   kp.dbias = a->dbias;
   static bool attr_set = false;
