@@ -309,6 +309,17 @@ def run_b200(args):
         roof[name] = {"bound": "tensor", "achieved": fl / sec / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
                       "frac": fl / sec / 1e12 / peak_tf, "traffic": None, "launches_per_step": cnt,
                       "ms_per_step": sec * 1e3, "peak_kind": f"{peak_kind} sustained bf16"}
+    # DRAM bytes per launch of the same kernel families from one ncu capture of one step (profiles/, committed with
+    # the command that produced it); None when the file is absent
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_conv_traffic.json")) as f:
+            traffic = json.load(f)
+        for name, v in roof.items():
+            if name in traffic:
+                v["traffic"] = traffic[name]["dram_bytes_per_launch"]
+                v["traffic_source"] = "profiles/r1_conv_traffic.json (ncu dram__bytes_read+write per launch, one step)"
+    except (OSError, ValueError, KeyError):
+        pass
     tc_ms = sum(v["ms_per_step"] for v in roof.values())
     hbm_roof = _hbm_kernel_rooflines(eng, peaks, peak_kind) if rank == 0 else None
 
