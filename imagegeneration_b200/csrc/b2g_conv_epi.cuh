@@ -27,6 +27,7 @@ struct EpiParams {
                     // the bias FFMA; the kernels' shared bias tables hold bias * pre_scale (epi_load_bias)
   int leaky_max;    // 0 <= alpha <= 1: LeakyReLU(v) = max(v, alpha * v)
   uint32_t seed_lo, seed_hi;
+  const unsigned long long* seed_dev;  // non-null: the seed lives in device memory (graph replay), see epi_resolve
   int dact;
   float dact_alpha, dact_scale, dact_zero;
   int out_f32;  // narrow fp32 output: `cs` real channels, out/yprev are float [pixels][cs]
@@ -299,6 +300,18 @@ __device__ __forceinline__ void epi_tma_end() {
   __syncwarp();
 }
 
+// Epilogue warps work on a private copy of the parameters whose dropout seed has been read from device memory when
+// the call asked for it (b2g_conv_args.dropout_seed_dev).
+__device__ __forceinline__ EpiParams epi_resolve(const EpiParams& p) {
+  EpiParams e = p;
+  if (p.seed_dev) {
+    const unsigned long long s = *p.seed_dev;
+    e.seed_lo = static_cast<uint32_t>(s & 0xFFFFFFFFull);
+    e.seed_hi = static_cast<uint32_t>(s >> 32);
+  }
+  return e;
+}
+
 // Block-wide: shared bias table = bias[0..n) * pre_scale (see EpiParams::pre_scale); call before the block sync.
 __device__ __forceinline__ void epi_load_bias(const EpiParams& p, float* sbias, int n) {
   if (p.bias)
@@ -318,6 +331,7 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->leaky_max = (a->alpha >= 0.f && a->alpha <= 1.f) ? 1 : 0;
   e->seed_lo = (uint32_t)(a->dropout_seed & 0xFFFFFFFFull);
   e->seed_hi = (uint32_t)(a->dropout_seed >> 32);
+  e->seed_dev = a->dropout_seed_dev;
   e->dact = a->dact;
   e->dact_alpha = a->dact_alpha;
   e->dact_scale = a->dact_scale;

@@ -16,7 +16,9 @@ namespace b2g {
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) adam_kernel(float4* __restrict__ w, const float4* __restrict__ g,
                                                    float4* __restrict__ m, float4* __restrict__ v, long n4,
-                                                   float lr_t, float b1, float b2, float eps, float gscale) {
+                                                   float lr_t_val, const float* __restrict__ lr_t_dev, float b1,
+                                                   float b2, float eps, float gscale) {
+  const float lr_t = lr_t_dev ? *lr_t_dev : lr_t_val;
   const float c1 = 1.f - b1, c2 = 1.f - b2;
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
     float4 gw = g[i], mw = m[i], vw = v[i], ww = w[i];
@@ -237,8 +239,30 @@ __global__ void zero_scalar_kernel(float* p) { *p = 0.f; }
 
 using namespace b2g;
 
-extern "C" int b2g_adam(float* w, const float* g, float* m, float* v, long n, float lr_t, float beta1, float beta2,
-                        float eps, float gscale, b2g_stream_t stream_) {
+__global__ void step_prologue_kernel(long long* step_ctr, unsigned long long seed_base, unsigned long long* seeds,
+                                     float* lr3, float lr_g, float lr_d, float b1, float b2) {
+  const long long s = *step_ctr;
+  const int i = threadIdx.x;
+  if (i < 21) {
+    const int pass = i / 7, layer = i % 7;
+    unsigned long long x = seed_base ^ (unsigned long long)((3 * s + pass) * 8 + layer);
+    x += 0x9E3779B97F4A7C15ull;  // splitmix64
+    unsigned long long z = x;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    seeds[i] = z ^ (z >> 31);
+  } else if (i < 24) {
+    const int k = i - 21;  // 0: generator, 1 / 2: first / second discriminator update of the step
+    const double t = k == 0 ? (double)(s + 1) : (double)(2 * s + k);
+    const double lr = k == 0 ? lr_g : lr_d;
+    lr3[k] = (float)(lr * sqrt(1.0 - pow((double)b2, t)) / (1.0 - pow((double)b1, t)));
+  }
+  __syncthreads();
+  if (i == 0) *step_ctr = s + 1;
+}
+
+static int adam_any(float* w, const float* g, float* m, float* v, long n, float lr_t, const float* lr_t_dev,
+                    float beta1, float beta2, float eps, float gscale, b2g_stream_t stream_) {
   if (!w || !g || !m || !v) return fail(B2G_E_INVALID_ARG, "b2g_adam: null pointer");
   if (n % 4) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_adam: arena length must be a multiple of 4 (pad it)");
   const long n4 = n / 4;
@@ -247,7 +271,25 @@ extern "C" int b2g_adam(float* w, const float* g, float* m, float* v, long n, fl
   if (blocks > cap) blocks = cap;
   adam_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
       reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(m),
-      reinterpret_cast<float4*>(v), n4, lr_t, beta1, beta2, eps, gscale);
+      reinterpret_cast<float4*>(v), n4, lr_t, lr_t_dev, beta1, beta2, eps, gscale);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+extern "C" int b2g_adam(float* w, const float* g, float* m, float* v, long n, float lr_t, float beta1, float beta2,
+                        float eps, float gscale, b2g_stream_t stream) {
+  return adam_any(w, g, m, v, n, lr_t, nullptr, beta1, beta2, eps, gscale, stream);
+}
+extern "C" int b2g_adam_dev(float* w, const float* g, float* m, float* v, long n, const float* lr_t_dev, float beta1,
+                            float beta2, float eps, float gscale, b2g_stream_t stream) {
+  if (!lr_t_dev) return fail(B2G_E_INVALID_ARG, "b2g_adam_dev: null lr_t pointer");
+  return adam_any(w, g, m, v, n, 0.f, lr_t_dev, beta1, beta2, eps, gscale, stream);
+}
+extern "C" int b2g_step_prologue(long long* step_ctr, unsigned long long seed_base, unsigned long long* seeds21,
+                                 float* lr3, float lr_g, float lr_d, float beta1, float beta2, b2g_stream_t stream_) {
+  if (!step_ctr || !seeds21 || !lr3) return fail(B2G_E_INVALID_ARG, "b2g_step_prologue: null pointer");
+  step_prologue_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream_)>>>(step_ctr, seed_base, seeds21, lr3, lr_g, lr_d,
+                                                                         beta1, beta2);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }

@@ -39,6 +39,7 @@ class ConvArgs(C.Structure):
         ("out_f32", C.c_int), ("cout_store", C.c_int),
         ("tf32", C.c_int),
         ("colsum", C.c_void_p),
+        ("dropout_seed_dev", C.c_void_p),
     ]
 
 
@@ -128,6 +129,10 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_dhead_bwd": [_P, _P, _P, _P, _I, _I, _F, _F, _F, _P, _P, _P, _P],
     # w, g, m, v, n, lr_t, b1, b2, eps, gscale, stream
     "b2g_adam": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _P],
+    # w, g, m, v, n, lr_t_dev, b1, b2, eps, gscale, stream
+    "b2g_adam_dev": [_P, _P, _P, _P, _L, _P, _F, _F, _F, _F, _P],
+    # step_ctr, seed_base, seeds21, lr3, lr_g, lr_d, b1, b2, stream
+    "b2g_step_prologue": [_P, C.c_ulonglong, _P, _P, _F, _F, _F, _F, _P],
     # x, out, P, C, stream
     "b2g_colsum_bf16": [_P, _P, _L, _I, _P],
     # W, G, gamma, inv_std, dgamma, taps, Co, Ci, stream

@@ -126,7 +126,8 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
     """Tensor-core implicit-GEMM conv / transposed conv with fused epilogue (see include/b200gan.h).
 
     out_f32=True: narrow fp32 output — wpacked has `cout_store` (<= 8) rows and out is fp32 [N,Ho,Wo,cout_store].
-    colsum: fp32 [Cout], += per-channel sums of the stored outputs (bias / beta gradient fused into a backward call)."""
+    colsum: fp32 [Cout], += per-channel sums of the stored outputs (bias / beta gradient fused into a backward call).
+    dropout_seed: an int, or a 1-element int64 CUDA tensor the kernel reads the seed from (CUDA-graph replay)."""
     _need_cuda(x, wpacked, out, bias, yprev, colsum)
     n, h, w, cin = x.shape
     k, phases, taps = _KIND_GEOM[kind]
@@ -161,12 +162,17 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
     cout_store = 0
     if out_f32:
         cout_store, cout = cout, 32
+    seed_dev = None
+    if isinstance(dropout_seed, torch.Tensor):
+        if dropout_seed.dtype != torch.int64 or dropout_seed.numel() != 1 or not dropout_seed.is_cuda:
+            raise B200GanError("conv_igemm: a device dropout seed must be a 1-element int64 CUDA tensor")
+        seed_dev, dropout_seed = dropout_seed.data_ptr(), 0
     a = ConvArgs(kind=kind, N=n, Hin=h, Win=w, Cin=cin, Cout=cout, inp=x.data_ptr(), wpacked=wpacked.data_ptr(),
                  out=out.data_ptr(), bias=None if bias is None else bias.data_ptr(), act=act, alpha=alpha,
                  dropout_thresh8=dropout_thresh8, dropout_seed=dropout_seed & 0xFFFFFFFFFFFFFFFF,
                  yprev=None if yprev is None else yprev.data_ptr(), dact=dact, dact_alpha=dact_alpha,
                  dact_scale=dact_scale, dact_zero=dact_zero, out_f32=int(out_f32), cout_store=cout_store,
-                 tf32=int(tf32), colsum=None if colsum is None else colsum.data_ptr())
+                 tf32=int(tf32), colsum=None if colsum is None else colsum.data_ptr(), dropout_seed_dev=seed_dev)
     ev = _prof_begin()
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
     cin_alg = 27 if kind in (CONV_K1S1, CONV_K3S1_C3) else cin   # edge layers: 27 real taps*channels

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import torch
 
@@ -109,7 +110,14 @@ class Adam:
         self.beta_1, self.beta_2, self.epsilon = beta_1, beta_2, epsilon
         self.iterations = 0
 
-    def apply_arena(self, arena: ParamArena, gscale: float = 1.0) -> None:
+    def apply_arena(self, arena: ParamArena, gscale: float = 1.0, lr_t_dev: torch.Tensor | None = None) -> None:
+        """lr_t_dev (1-element fp32 CUDA tensor written by b2g_step_prologue): the bias-corrected rate is read on
+        the device, so the launch can sit in a replayed CUDA graph; `iterations` is then advanced by the caller."""
+        if lr_t_dev is not None:
+            check(_lib.load().b2g_adam_dev(_p(arena.w), _p(arena.g), _p(arena.m), _p(arena.v), arena.numel,
+                                           _p(lr_t_dev), self.beta_1, self.beta_2, self.epsilon, gscale, _stream()),
+                  "b2g_adam_dev")
+            return
         self.iterations += 1
         t = self.iterations
         lr_t = self.learning_rate * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
@@ -499,7 +507,7 @@ class SNDCGANEngine:
 
     def __init__(self, batch_size, dropout=0.5, learning_rate_disc=2e-4, learning_rate_gen=2e-4,
                  image_size=(144, 256, 3), z_size=Z_SIZE, device="cuda", seed=62, spectral_norm=False, loss="bce",
-                 process_group=None):
+                 process_group=None, cuda_graph=None):
         if z_size != Z_SIZE:
             raise B200GanError("z_size must be 128 (sndcgan/Trainer.py:8)")
         if loss not in ("bce", "hinge"):
@@ -530,9 +538,21 @@ class SNDCGANEngine:
             self.gen_model._packed_dirty = True
             self.disc_model._packed_dirty = True
         self.gpu_launches = 0
+        # Single-GPU steps with engine-chosen dropout seeds are replayed as ONE CUDA graph after two eager steps
+        # (the per-step scalars — dropout seeds, Adam's bias-corrected rates — then come from device memory, written
+        # by b2g_step_prologue).  cuda_graph=False or B2G_CUDA_GRAPH=0 keeps every step eager.
+        if cuda_graph is None:
+            cuda_graph = os.environ.get("B2G_CUDA_GRAPH", "1") != "0"
+        self.cuda_graph = bool(cuda_graph)
+        self._graph = None
+        self._graph_failed = None
+        self._eager_steps = 0
+
+    def _seed_base(self) -> int:
+        return (self.seed * 0x1000003 + self.rank * 0x10001 + 1) & _MASK64
 
     def _dropout_seeds(self, pass_idx: int):
-        base = (self.seed * 0x1000003 + self.rank * 0x10001 + 1) & _MASK64
+        base = self._seed_base()
         return [_splitmix64(base ^ ((self.step_count * 3 + pass_idx) * 8 + layer)) for layer in range(7)]
 
     def _allreduce(self, flat, async_op=False):
@@ -546,11 +566,83 @@ class SNDCGANEngine:
 
         Returns (g_loss, d_loss, d_loss_real, d_loss_fake, d_logits_real, d_logits_fake) as CUDA tensors.
         dropout_seeds: optional (seeds_a, seeds_b, seeds_c), 7 ints each, for reproducible masks."""
+        if self._graph_usable(input_real, input_z, dropout_seeds):
+            if self._graph is None:
+                self._capture_graph()
+            if self._graph is not None:
+                return self._train_step_graph(input_real, input_z)
+        sa, sb, sc = dropout_seeds if dropout_seeds is not None else [self._dropout_seeds(i) for i in range(3)]
+        out = self._step_body(input_real, input_z, sa, sb, sc, None)
+        self.step_count += 1
+        self._eager_steps += 1
+        return out
+
+    # -- CUDA-graph replay of the whole step ------------------------------------------------------------------
+    def _graph_usable(self, input_real, input_z, dropout_seeds) -> bool:
+        return (self.cuda_graph and self._graph_failed is None and self.world == 1 and dropout_seeds is None
+                and _lib.profile_sink is None and self._eager_steps >= 2
+                and input_real.shape[0] == self.batch_size and input_z.shape[0] == self.batch_size
+                and input_real.dtype == torch.float32 and input_z.dtype == torch.float32
+                and self.d_optimizer.iterations == 2 * self.step_count
+                and self.g_optimizer.iterations == self.step_count
+                and not torch.cuda.is_current_stream_capturing())
+
+    def _capture_graph(self) -> None:
+        lib, dev, B = _lib.load(), self.device, self.batch_size
+        try:
+            self._gs_ctr = torch.full((1,), self.step_count, dtype=torch.int64, device=dev)
+            self._gs_ctr_host = self.step_count
+            self._gs_seeds = torch.zeros(21, dtype=torch.int64, device=dev)
+            self._gs_lr = torch.zeros(3, dtype=torch.float32, device=dev)
+            self._g_real = torch.empty((B, *self.image_size), dtype=torch.float32, device=dev)
+            self._g_z = torch.empty((B, self.z_size), dtype=torch.float32, device=dev)
+            seeds = [[self._gs_seeds[p * 7 + i:p * 7 + i + 1] for i in range(7)] for p in range(3)]
+            lrs = [self._gs_lr[k:k + 1] for k in range(3)]
+            g_opt, d_opt = self.g_optimizer, self.d_optimizer
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream())
+            l0 = _lib.launch_count
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(graph, stream=side):
+                    check(lib.b2g_step_prologue(_p(self._gs_ctr), C.c_ulonglong(self._seed_base()),
+                                                _p(self._gs_seeds), _p(self._gs_lr), g_opt.learning_rate,
+                                                d_opt.learning_rate, d_opt.beta_1, d_opt.beta_2, _stream()),
+                          "b2g_step_prologue")
+                    outs = self._step_body(self._g_real, self._g_z, seeds[0], seeds[1], seeds[2], lrs)
+            torch.cuda.current_stream().wait_stream(side)
+            self._graph, self._graph_outs = graph, outs
+            self._graph_launches = _lib.launch_count - l0
+            _lib.launch_count = l0          # nothing ran during capture; replays add the count
+        except Exception as exc:            # capture unsupported here: stay eager (same results, more launches)
+            self._graph = None
+            self._graph_failed = repr(exc)
+
+    def _train_step_graph(self, input_real, input_z):
+        if self._gs_ctr_host != self.step_count:     # eager steps ran in between: re-align the device step index
+            self._gs_ctr.fill_(self.step_count)
+        if input_real.data_ptr() != self._g_real.data_ptr():
+            self._g_real.copy_(input_real)
+        if input_z.data_ptr() != self._g_z.data_ptr():
+            self._g_z.copy_(input_z)
+        self._graph.replay()
+        _lib.launch_count += self._graph_launches
+        self.step_count += 1
+        self._gs_ctr_host = self.step_count
+        self.g_optimizer.iterations += 1
+        self.d_optimizer.iterations += 2
+        self.gen_model._packed_dirty = True
+        self.disc_model._packed_dirty = True
+        return tuple(o.clone() for o in self._graph_outs)   # the graph's own buffers are rewritten by the next replay
+
+    def _step_body(self, input_real, input_z, sa, sb, sc, lr_dev):
+        """The launches of one step.  sa/sb/sc: 7 dropout seeds per discriminator pass (ints, or 1-element device
+        tensors under graph capture); lr_dev: None, or the three device-resident Adam rates (G, D first, D second)."""
         G, D = self.gen_model, self.disc_model
         B = input_real.shape[0]
         inv_b = 1.0 / B
         gs = 1.0 / self.world
-        sa, sb, sc = dropout_seeds if dropout_seeds is not None else [self._dropout_seeds(i) for i in range(3)]
+        lr_g, lr_d1, lr_d2 = lr_dev if lr_dev is not None else (None, None, None)
         g_kind = LOSS_BCE if self.loss == "bce" else LOSS_HINGE_G
         d_kind = LOSS_BCE if self.loss == "bce" else LOSS_HINGE_D
 
@@ -570,7 +662,7 @@ class SNDCGANEngine:
         d_logits_real = d_logits_real.clone()
         D.backward(need_wgrad=True, need_input_grad=False)                          # :256
         self._allreduce(D.arena.g)
-        self.d_optimizer.apply_arena(D.arena, gs)                                   # :257
+        self.d_optimizer.apply_arena(D.arena, gs, lr_d1)                            # :257
         D._packed_dirty = True
 
         # (3) discriminator step on the stale fake batch (:259-267)
@@ -578,16 +670,15 @@ class SNDCGANEngine:
         d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)                # :261-262
         D.backward(need_wgrad=True, need_input_grad=False)                          # :266
         self._allreduce(D.arena.g)
-        self.d_optimizer.apply_arena(D.arena, gs)                                   # :267
+        self.d_optimizer.apply_arena(D.arena, gs, lr_d2)                            # :267
         D._packed_dirty = True
 
         if g_work is not None:
             g_work.wait()
-        self.g_optimizer.apply_arena(G.arena, gs)                                   # :249 (deferred)
+        self.g_optimizer.apply_arena(G.arena, gs, lr_g)                             # :249 (deferred)
         G._packed_dirty = True
 
         d_loss = d_loss_fake + d_loss_real                                          # :264
-        self.step_count += 1
         return (g_loss, d_loss, d_loss_real, d_loss_fake, d_logits_real, d_logits_fake)
 
 

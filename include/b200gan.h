@@ -89,6 +89,9 @@ typedef struct b2g_conv_args {
      the stored outputs over all pixels, i.e. the bias / BatchNorm-beta gradient of the layer whose output
      gradient this call produces (replaces a separate reduction pass over `out`). */
   float* colsum;
+  /* optional device pointer to the 64-bit dropout seed (overrides dropout_seed when non-NULL): lets a captured CUDA
+     graph of a whole training step be replayed with fresh masks — b2g_step_prologue writes the seeds of a step. */
+  const unsigned long long* dropout_seed_dev;
 } b2g_conv_args;
 
 int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
@@ -210,6 +213,16 @@ int b2g_dhead_bwd(const void* x, const float* w, const float* wscale, const floa
  * sn_grad_finalize: G <- G/sigma - (<G,W>/sigma^2) v u^T in place (gradient through W/sigma). */
 int b2g_adam(float* w, const float* g, float* m, float* v, long n, float lr_t, float beta1, float beta2, float eps,
              float gscale, b2g_stream_t stream);
+/* Adam with lr_t read from device memory (one float) — the graph-replay form of b2g_adam. */
+int b2g_adam_dev(float* w, const float* g, float* m, float* v, long n, const float* lr_t_dev, float beta1,
+                 float beta2, float eps, float gscale, b2g_stream_t stream);
+/* First node of a captured training step (sndcgan/SNDCGAN.py:241-269 replayed as one CUDA graph): reads the step
+ * index s = *step_ctr, writes the 21 dropout seeds of the step (3 discriminator passes x 7 layers:
+ * splitmix64(seed_base ^ ((3 s + pass) * 8 + layer))) and the three bias-corrected Adam rates
+ * lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t) for t = s + 1 (generator) and t = 2 s + 1, 2 s + 2 (discriminator), then
+ * stores s + 1. */
+int b2g_step_prologue(long long* step_ctr, unsigned long long seed_base, unsigned long long* seeds21, float* lr3,
+                      float lr_g, float lr_d, float beta1, float beta2, b2g_stream_t stream);
 int b2g_colsum_bf16(const void* x, float* out, long P, int C, b2g_stream_t stream);
 int b2g_bn_fold_finalize(const float* W, float* G, const float* gamma, float inv_std, float* dgamma, int taps, int Co,
                          int Ci, b2g_stream_t stream);

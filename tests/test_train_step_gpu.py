@@ -144,3 +144,39 @@ def test_train_step_matches_oracle(image_size, batch, dropout):
         for name, a, b in zip(model.arena.names, model.trainable_variables, ref_vars):
             d = (a.cpu() - b).abs().mean()
             assert float(d) < 0.5 * lr, f"{name}: mean |dw| {float(d)}"
+
+
+@pytest.mark.parametrize("image_size,batch", [((16, 32, 3), 4), ((144, 256, 3), 2)])
+def test_cuda_graph_replay_matches_eager(image_size, batch):
+    """After two eager steps the engine replays the step as one CUDA graph (dropout seeds and Adam rates read from
+    device memory, b2g_step_prologue).  Same seeds, same schedule: losses and weights must track the eager engine
+    (fp32 atomics in the weight gradients make runs differ in the last bits, hence tolerances, not equality)."""
+    from imagegeneration_b200 import lib as L
+    from imagegeneration_b200.sndcgan import SNDCGANEngine
+    eager = SNDCGANEngine(batch, dropout=0.5, image_size=image_size, seed=62, cuda_graph=False)
+    graph = SNDCGANEngine(batch, dropout=0.5, image_size=image_size, seed=62, cuda_graph=True)
+    for step in range(6):
+        real, z = _inputs(image_size, batch, step)
+        real, z = real.cuda(), z.cuda()
+        a = eager.train_step(real, z)
+        l0 = L.launch_count
+        b = graph.train_step(real, z)
+        launched = L.launch_count - l0
+        torch.cuda.synchronize()
+        assert launched > 50                      # replays are accounted for in the launch counter
+        for name, x, y in zip(("g_loss", "d_loss", "d_loss_real", "d_loss_fake"), a[:4], b[:4]):
+            assert abs(float(y) - float(x)) < 5e-3 * max(1.0, abs(float(x))), f"step {step} {name}: {float(y)} vs {float(x)}"
+        assert float((a[4] - b[4]).abs().max()) < 5e-3 * (1 + float(a[4].abs().max()))
+    assert graph._graph is not None, graph._graph_failed
+    assert eager._graph is None
+    assert graph.step_count == 6 and graph.d_optimizer.iterations == 12 and graph.g_optimizer.iterations == 6
+    for name, wa, wb in zip(eager.disc_model.arena.names, eager.disc_model.trainable_variables,
+                            graph.disc_model.trainable_variables):
+        assert float((wa - wb).abs().mean()) < 0.5 * 2e-4, name
+    # an explicit-seed (eager) step in between keeps the device step index aligned
+    real, z = _inputs(image_size, batch, 7)
+    seeds = tuple([900 + 10 * p + i for i in range(7)] for p in range(3))
+    graph.train_step(real.cuda(), z.cuda(), dropout_seeds=seeds)
+    out = graph.train_step(real.cuda(), z.cuda())
+    torch.cuda.synchronize()
+    assert graph.step_count == 8 and all(torch.isfinite(o).all() for o in out)
