@@ -579,7 +579,8 @@ class SNDCGANEngine:
 
     # -- CUDA-graph replay of the whole step ------------------------------------------------------------------
     def _graph_usable(self, input_real, input_z, dropout_seeds) -> bool:
-        return (self.cuda_graph and self._graph_failed is None and self.world == 1 and dropout_seeds is None
+        return (self.cuda_graph and self._graph_failed is None and dropout_seeds is None
+                and (self.world == 1 or os.environ.get("B2G_CUDA_GRAPH_DP", "0") == "1")
                 and _lib.profile_sink is None and self._eager_steps >= 2
                 and input_real.shape[0] == self.batch_size and input_z.shape[0] == self.batch_size
                 and input_real.dtype == torch.float32 and input_z.dtype == torch.float32
