@@ -259,6 +259,11 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   if (a->dropout_thresh8 > 0 && a->act == B2G_ACT_TANH)  // the dropout scale is applied before the activation
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout needs a positively homogeneous activation (none/leaky/relu)");
 
+  if (a->out_f32 && !tf32) {  // 64 -> 3 channels on 128/256-pixel rows: per-pixel GEMM + gather
+    bool handled = false;
+    const int rc = launch_conv_o3(a, stream_, &handled);
+    if (rc != B2G_OK || handled) return rc;
+  }
   ConvKernelParams kp;
   memset(&kp, 0, sizeof(kp));
   if (!build_conv_plan(a->kind, a->N, a->Hin, a->Win, a->Cin, a->Cout, 128, &kp.plan))

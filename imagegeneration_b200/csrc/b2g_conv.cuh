@@ -195,5 +195,7 @@ int launch_wgrad_slab(const b2g_wgrad_args* a, void* stream, bool* handled);
 int launch_wgrad_c3(const b2g_wgrad_args* a, void* stream);
 // 3-channel 3x3 conv with the im2col patch built in shared memory (b2g_conv_c3.cu)
 int launch_conv_c3(const b2g_conv_args* a, void* stream);
+// 64 -> 3 channel 3x3 conv as one 64 -> 27 GEMM per pixel + a gather over a ring of rows (b2g_conv_o3.cu)
+int launch_conv_o3(const b2g_conv_args* a, void* stream, bool* handled);
 
 }  // namespace b2g
