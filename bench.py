@@ -199,7 +199,7 @@ def _hbm_kernel_rooflines(eng, peaks, peak_kind):
         byt = 4.0 * sum(k * c for k, c in zip(D._sn_K, D._sn_C))
         out["spectral_norm_multi"] = {"bound": "hbm", "achieved": byt / sec / 1e9, "peak": peak, "unit": "GB/s",
                                       "frac": byt / sec / 1e9 / peak, "bytes_per_launch": byt, "us": sec * 1e6,
-                                      "note": "8 matrices, 24.6 MB in 2 launches: latency-bound at this size",
+                                      "note": "8 matrices, 24.6 MB in one launch (3.8 us at the copy peak): launch-latency-bound at this size",
                                       "peak_kind": f"{peak_kind} copy bandwidth"}
         del sn
     except Exception as e:  # the option is not on the reference path; never fail the bench line for it

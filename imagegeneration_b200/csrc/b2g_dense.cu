@@ -39,7 +39,8 @@ __global__ void __launch_bounds__(256) dhead_partial_kernel(const __nv_bfloat16*
 }
 
 // logits[b] = wscale * sum_s part[b][s] + bias;  loss and dL/dlogit.  One block.
-//   loss_kind 0: BCE-with-logits against `label`;  1: D hinge (label 1: relu(1-x), 0: relu(1+x));  2: G hinge (-x)
+//   loss_kind 0: BCE-with-logits against `label`;  1: D hinge (label 1: relu(1-x), 0: relu(1+x));  2: G hinge (-x);
+//   3: Wasserstein label*x
 //   loss_out[0] = inv_batch * sum_b loss_b ;  dlogit[b] = inv_batch * dloss_b/dx ; loss_out[1] = inv_batch*sum sigmoid
 __global__ void dhead_loss_kernel(const float* __restrict__ part, int S, const float* __restrict__ wscale,
                                   const float* __restrict__ bias, int B, int loss_kind, float label, float inv_batch,
@@ -61,9 +62,12 @@ __global__ void dhead_loss_kernel(const float* __restrict__ part, int S, const f
     } else if (loss_kind == 1) {
       if (label > 0.5f) { l = fmaxf(1.f - x, 0.f); d = x < 1.f ? -1.f : 0.f; }
       else              { l = fmaxf(1.f + x, 0.f); d = x > -1.f ? 1.f : 0.f; }
-    } else {
+    } else if (loss_kind == 2) {
       l = -x;
       d = -1.f;
+    } else {  // 3: Wasserstein, mean(y_true * y_pred) with y_true = label (wasserstein_gan/WGAN.py:48-49)
+      l = label * x;
+      d = label;
     }
     dlogit[b] = d * inv_batch;
     lsum += l;

@@ -31,6 +31,7 @@ struct alignas(64) StemFwdParams {
   const float* gamma;
   const float* beta;
   float inv_std;
+  float alpha;  // LeakyReLU slope of the output activation (0 = ReLU)
   __nv_bfloat16* out;
   int B, F, b0, tiles;
 };
@@ -140,7 +141,10 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_fwd_kernel(const __grid_
         for (int c = 0; c < 32; ++c) {
           const int b = p.b0 + h * 32 + c;
           if (b < p.B)  // 32 consecutive features per warp: one 64-byte line per sample
-            p.out[(size_t)b * p.F + j] = __float2bfloat16_rn(fmaxf(fmaf(__uint_as_float(r[c]), g, be), 0.f));
+          {
+            const float y = fmaf(__uint_as_float(r[c]), g, be);
+            p.out[(size_t)b * p.F + j] = __float2bfloat16_rn(fmaxf(y, y * p.alpha));  // alpha in [0, 1)
+          }
         }
       }
       tc_fence_before();
@@ -341,8 +345,9 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_bwd_kernel(const __grid_
 
 using namespace b2g;
 
-extern "C" int b2g_dense_g_fwd(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
-                               void* out, int B, int F, b2g_stream_t stream_) {
+static int dense_g_fwd_any(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
+                           float alpha, void* out, int B, int F, b2g_stream_t stream_) {
+  if (alpha < 0.f || alpha >= 1.f) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_fwd: alpha must be in [0, 1)");
   if (!z || !W || !gamma || !beta || !out) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_fwd: null pointer");
   if (F % 128 || F <= 0 || B <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_fwd: F=%d must be a multiple of 128", F);
   static bool attr_set = false;
@@ -366,7 +371,7 @@ extern "C" int b2g_dense_g_fwd(const float* z, const float* W, const float* gamm
     int rc = make_tmap(&p.zmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, z, dims, str, box);
     if (rc) return rc;
   }
-  p.gamma = gamma; p.beta = beta; p.inv_std = inv_std;
+  p.gamma = gamma; p.beta = beta; p.inv_std = inv_std; p.alpha = alpha;
   p.out = static_cast<__nv_bfloat16*>(out);
   p.B = B; p.F = F; p.tiles = F / 128;
   const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
@@ -376,6 +381,15 @@ extern "C" int b2g_dense_g_fwd(const float* z, const float* W, const float* gamm
     B2G_LAUNCH_CHECK();
   }
   return B2G_OK;
+}
+
+extern "C" int b2g_dense_g_fwd(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
+                               void* out, int B, int F, b2g_stream_t stream) {
+  return dense_g_fwd_any(z, W, gamma, beta, inv_std, 0.f, out, B, F, stream);
+}
+extern "C" int b2g_dense_g_fwd_leaky(const float* z, const float* W, const float* gamma, const float* beta,
+                                     float inv_std, float alpha, void* out, int B, int F, b2g_stream_t stream) {
+  return dense_g_fwd_any(z, W, gamma, beta, inv_std, alpha, out, B, F, stream);
 }
 
 extern "C" int b2g_dense_g_bwd(const float* z, const float* W, const float* gamma, float inv_std, const void* dq,

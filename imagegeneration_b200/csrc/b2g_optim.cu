@@ -92,91 +92,173 @@ __global__ void __launch_bounds__(256) bn_fold_finalize_kernel(const float* __re
 
 // ---------------------------------------------------------------------------------------------------------
 // Spectral normalisation, multi-tensor.  Layer l: W_l [K_l][C_l] row-major (Keras reshape(W, (-1, Cout))).
-// Pass 1 (one launch, all layers): v_raw = W u ; vsq += |v_raw|^2 ; t_raw += W^T v_raw  — W read ONCE.
-// Pass 2 (one launch, one block per layer): nv = |v_raw| ; t = t_raw/nv ; sigma = |t| ; u <- t/sigma.
-// (v = v_raw/nv and W^T v = t, so sigma = v^T W u_new = |t|.)
+// ONE launch for all layers; every weight matrix is read exactly once:
+//   v_raw = W u ; vsq += |v_raw|^2 ; t_raw += W^T v_raw   (row blocks, byte-balanced across the layers)
+//   the last block of a layer to finish (ticket in scal[4]) finalises it:
+//   nv = |v_raw| ; t = t_raw/nv ; sigma = |t| ; u <- t/sigma.   (v = v_raw/nv and W^T v = t, so sigma = v^T W u_new = |t|.)
+// Rows are read as float4 per lane (C in {128,256,512}: 4 KiB per warp iteration, the next 4 KiB prefetched), partial
+// W^T v sums go registers -> per-warp shared slabs -> one red per column per block.
 // ---------------------------------------------------------------------------------------------------------
 struct SnLayer {
   const float* W;
-  float* u;       // [C]   persistent, updated by pass 2
+  float* u;       // [C]   persistent, updated by the finalising block
   float* v_raw;   // [K]
-  float* t_raw;   // [C]   scratch, zero on entry, re-zeroed by pass 2
-  float* scal;    // [4]   {vsq scratch (zero on entry), sigma, 1/sigma, nv}
+  float* t_raw;   // [C]   scratch, zero on entry, re-zeroed on exit
+  float* scal;    // [8]   {vsq scratch (zero on entry), sigma, 1/sigma, nv, ticket (uint, zero on entry), -, -, -}
   int K, C;
 };
 constexpr int kSnMaxLayers = 8;
+constexpr int kSnThreads = 256;
 struct SnParams {
   SnLayer layer[kSnMaxLayers];
+  int blk_start[kSnMaxLayers + 1];  // first block of each layer; blk_start[n_layers] = grid size
   int n_layers;
-  int blocks_per_layer;
 };
 
-__global__ void __launch_bounds__(256) sn_power_kernel(const __grid_constant__ SnParams p) {
-  const SnLayer& L = p.layer[blockIdx.y];
-  const int K = L.K, C = L.C;
-  __shared__ float tsh[512];
-  __shared__ float vsq_sh;
-  for (int i = threadIdx.x; i < 512; i += 256) tsh[i] = 0.f;
-  if (threadIdx.x == 0) vsq_sh = 0.f;
-  __syncthreads();
+template <int NV, int R>
+__device__ __forceinline__ void sn_load_rows(const float4* __restrict__ W4, int k0, int K, int lane, float4 (&w)[R][NV]) {
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int j = 0; j < NV; ++j)
+      w[r][j] = (k0 + r < K) ? __ldg(W4 + (size_t)(k0 + r) * (NV * 32) + j * 32 + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// R rows of C = NV*128 columns per warp iteration, the next iteration's rows in flight while this one is reduced.
+// Partial W^T v sums: registers -> this warp's slab of shared memory (no shared atomics: fp32 atomicAdd on shared
+// memory is a compare-and-swap loop).
+template <int NV, int R>
+__device__ __forceinline__ void sn_rows_vec(const SnLayer& L, int lb, int nb, float* slab, float& vsq) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float vsq = 0.f;
-  if (C >= 32) {
-    const int per = C / 32;  // columns per lane (C in {64,128,256,512} -> 2..16)
-    float ureg[16], tacc[16];
+  constexpr int kWarps = kSnThreads / 32;
+  const float4* __restrict__ W4 = reinterpret_cast<const float4*>(L.W);
+  float4 u4[NV], tacc[NV];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      ureg[i] = (i < per) ? L.u[lane + 32 * i] : 0.f;
-      tacc[i] = 0.f;
+  for (int j = 0; j < NV; ++j) {
+    u4[j] = __ldg(reinterpret_cast<const float4*>(L.u) + j * 32 + lane);
+    tacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const int K = L.K;
+  const int stride = nb * kWarps * R;
+  int k0 = (lb * kWarps + warp) * R;
+  float4 wn[R][NV];
+  if (k0 < K) sn_load_rows<NV, R>(W4, k0, K, lane, wn);
+  while (k0 < K) {
+    float4 w[R][NV];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int j = 0; j < NV; ++j) w[r][j] = wn[r][j];
+    const int k1 = k0 + stride;
+    if (k1 < K) sn_load_rows<NV, R>(W4, k1, K, lane, wn);
+    float dot[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      float d = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j)
+        d += w[r][j].x * u4[j].x + w[r][j].y * u4[j].y + w[r][j].z * u4[j].z + w[r][j].w * u4[j].w;
+      dot[r] = d;
     }
-    for (int k = blockIdx.x * 8 + warp; k < K; k += gridDim.x * 8) {
-      float wreg[16];
-      float dot = 0.f;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        wreg[i] = (i < per) ? __ldg(L.W + (size_t)k * C + lane + 32 * i) : 0.f;
-        dot += wreg[i] * ureg[i];
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int r = 0; r < R; ++r) dot[r] += __shfl_xor_sync(0xffffffffu, dot[r], o);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (lane == 0 && k0 + r < K) {
+        L.v_raw[k0 + r] = dot[r];
+        vsq += dot[r] * dot[r];
       }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-      if (lane == 0) L.v_raw[k] = dot;
-      vsq += (lane == 0) ? dot * dot : 0.f;
+      for (int j = 0; j < NV; ++j) {
+        tacc[j].x += w[r][j].x * dot[r];
+        tacc[j].y += w[r][j].y * dot[r];
+        tacc[j].z += w[r][j].z * dot[r];
+        tacc[j].w += w[r][j].w * dot[r];
+      }
+    }
+    k0 = k1;
+  }
 #pragma unroll
-      for (int i = 0; i < 16; ++i) tacc[i] += wreg[i] * dot;
+  for (int j = 0; j < NV; ++j) reinterpret_cast<float4*>(slab + warp * 512)[j * 32 + lane] = tacc[j];
+}
+
+// Generic columns (C a multiple of 32, <= 512): one row per warp iteration, scalar loads (the 27 x 64 layer).
+__device__ __forceinline__ void sn_rows_scalar(const SnLayer& L, int lb, int nb, float* slab, float& vsq) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kWarps = kSnThreads / 32;
+  const int K = L.K, C = L.C;
+  const int per = C / 32;
+  float ureg[16], tacc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    ureg[i] = (i < per) ? L.u[lane + 32 * i] : 0.f;
+    tacc[i] = 0.f;
+  }
+  for (int k = lb * kWarps + warp; k < K; k += nb * kWarps) {
+    float wreg[16];
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      wreg[i] = (i < per) ? __ldg(L.W + (size_t)k * C + lane + 32 * i) : 0.f;
+      dot += wreg[i] * ureg[i];
     }
 #pragma unroll
-    for (int i = 0; i < 16; ++i)
-      if (i < per) atomicAdd(&tsh[lane + 32 * i], tacc[i]);
-  } else {  // C == 1 (Dense head): thread per row
-    const float u0 = L.u[0];
-    float t = 0.f;
-    for (int k = blockIdx.x * 256 + threadIdx.x; k < K; k += gridDim.x * 256) {
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if (lane == 0) {
+      L.v_raw[k] = dot;
+      vsq += dot * dot;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tacc[i] += wreg[i] * dot;
+  }
+#pragma unroll
+  for (int i = 0; i < 16; ++i)
+    if (i < per) slab[warp * 512 + lane + 32 * i] = tacc[i];
+}
+
+// C == 1 (Dense head, K x 1): v_raw = W u0, thread per 4 rows when K % 4 == 0.
+__device__ __forceinline__ void sn_rows_c1(const SnLayer& L, int lb, int nb, float* slab, float& vsq) {
+  const float u0 = L.u[0];
+  const int K = L.K;
+  float t = 0.f;
+  if ((K & 3) == 0) {
+    const float4* __restrict__ W4 = reinterpret_cast<const float4*>(L.W);
+    float4* V4 = reinterpret_cast<float4*>(L.v_raw);
+    const int n4 = K / 4, stride = nb * kSnThreads;
+    for (int k = lb * kSnThreads + threadIdx.x; k < n4; k += 4 * stride) {
+      float4 wv[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        wv[q] = (k + q * stride < n4) ? __ldg(W4 + k + q * stride) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 d = make_float4(wv[q].x * u0, wv[q].y * u0, wv[q].z * u0, wv[q].w * u0);
+        if (k + q * stride < n4) V4[k + q * stride] = d;
+        vsq += d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w;
+        t += wv[q].x * d.x + wv[q].y * d.y + wv[q].z * d.z + wv[q].w * d.w;
+      }
+    }
+  } else {
+    for (int k = lb * kSnThreads + threadIdx.x; k < K; k += nb * kSnThreads) {
       const float wv = __ldg(L.W + k);
       const float d = wv * u0;
       L.v_raw[k] = d;
       vsq += d * d;
       t += wv * d;
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if (lane == 0) atomicAdd(&tsh[0], t);
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) vsq += __shfl_xor_sync(0xffffffffu, vsq, o);
-  if (lane == 0) atomicAdd(&vsq_sh, vsq);
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += 256) atomicAdd(L.t_raw + i, tsh[i]);
-  if (threadIdx.x == 0) atomicAdd(L.scal, vsq_sh);
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if ((threadIdx.x & 31) == 0) slab[(threadIdx.x >> 5) * 512] = t;
 }
 
-__global__ void __launch_bounds__(256) sn_finalize_kernel(const __grid_constant__ SnParams p) {
-  const SnLayer& L = p.layer[blockIdx.x];
-  __shared__ float red[8];
-  __shared__ float sig_sh;
-  const float nv = sqrtf(L.scal[0]) + 1e-12f;
+__device__ __forceinline__ void sn_finalize_layer(const SnLayer& L, float* red, float* sig_sh) {
+  const float nv = sqrtf(__ldcg(L.scal)) + 1e-12f;
   float acc = 0.f;
-  for (int i = threadIdx.x; i < L.C; i += 256) {
-    const float t = L.t_raw[i] / nv;
+  for (int i = threadIdx.x; i < L.C; i += kSnThreads) {
+    const float t = __ldcg(L.t_raw + i) / nv;
     acc += t * t;
   }
 #pragma unroll
@@ -185,22 +267,69 @@ __global__ void __launch_bounds__(256) sn_finalize_kernel(const __grid_constant_
   __syncthreads();
   if (threadIdx.x == 0) {
     float t = 0.f;
-    for (int i = 0; i < 8; ++i) t += red[i];
-    sig_sh = sqrtf(t);
+    for (int i = 0; i < kSnThreads / 32; ++i) t += red[i];
+    *sig_sh = sqrtf(t);
   }
   __syncthreads();
-  const float sigma = sig_sh;
-  for (int i = threadIdx.x; i < L.C; i += 256) {
-    L.u[i] = L.t_raw[i] / nv / (sigma + 1e-12f);
+  const float sigma = *sig_sh;
+  for (int i = threadIdx.x; i < L.C; i += kSnThreads) {
+    L.u[i] = __ldcg(L.t_raw + i) / nv / (sigma + 1e-12f);
     L.t_raw[i] = 0.f;
   }
-  __syncthreads();
   if (threadIdx.x == 0) {
     L.scal[0] = 0.f;
     L.scal[1] = sigma;
     L.scal[2] = 1.f / sigma;
     L.scal[3] = nv;
+    *reinterpret_cast<unsigned*>(L.scal + 4) = 0u;
   }
+}
+
+__global__ void __launch_bounds__(kSnThreads, 2) sn_power_kernel(const __grid_constant__ SnParams p) {
+  int li = 0;
+  while (li + 1 < p.n_layers && (int)blockIdx.x >= p.blk_start[li + 1]) ++li;
+  const SnLayer& L = p.layer[li];
+  const int lb = blockIdx.x - p.blk_start[li], nb = p.blk_start[li + 1] - p.blk_start[li];
+  const int C = L.C;
+  constexpr int kWarps = kSnThreads / 32;
+  __shared__ __align__(16) float slab[kWarps * 512];  // per-warp partial W^T v
+  __shared__ float red[kWarps];
+  __shared__ float sig_sh;
+  __shared__ int last_sh;
+  for (int i = threadIdx.x; i < kWarps * 512; i += kSnThreads) slab[i] = 0.f;
+  __syncthreads();
+  float vsq = 0.f;
+  if (C == 512) sn_rows_vec<4, 2>(L, lb, nb, slab, vsq);
+  else if (C == 256) sn_rows_vec<2, 4>(L, lb, nb, slab, vsq);
+  else if (C == 128) sn_rows_vec<1, 8>(L, lb, nb, slab, vsq);
+  else if (C >= 32) sn_rows_scalar(L, lb, nb, slab, vsq);
+  else sn_rows_c1(L, lb, nb, slab, vsq);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) vsq += __shfl_xor_sync(0xffffffffu, vsq, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = vsq;
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += kSnThreads) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) t += slab[w * 512 + i];
+    atomicAdd(L.t_raw + i, t);
+  }
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < kWarps; ++w) t += red[w];
+    atomicAdd(L.scal, t);
+  }
+  // last block of this layer finalises it
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(L.scal + 4), 1u);
+    last_sh = (ticket == (unsigned)(nb - 1));
+  }
+  __syncthreads();
+  if (!last_sh) return;
+  __threadfence();
+  sn_finalize_layer(L, red, &sig_sh);
 }
 
 // Gradient through W_sn = W / sigma with sigma = v^T W u (u, v constants):
@@ -330,11 +459,25 @@ extern "C" int b2g_spectral_norm_multi(int n_layers, const float* const* W, floa
     p.layer[i] = SnLayer{W[i], u[i], v_raw[i], t_raw[i], scal[i], K[i], C[i]};
   }
   p.n_layers = n_layers;
-  p.blocks_per_layer = (num_sms() * 4 + n_layers - 1) / n_layers;
+  // blocks per layer in proportion to the bytes of W (at least one), two 256-thread blocks per SM in total
+  double total = 0.0;
+  for (int i = 0; i < n_layers; ++i) total += (double)K[i] * C[i];
+  const int budget = num_sms() * 2;
+  int start = 0;
+  for (int i = 0; i < n_layers; ++i) {
+    p.blk_start[i] = start;
+    const double share = (double)K[i] * C[i] / total * budget;
+    int nb = (int)(share + 0.5);
+    // no more blocks than 4 KiB row groups per warp can use
+    const long units = ((long)K[i] * C[i] + 1023) / 1024;
+    const long max_nb = (units + (kSnThreads / 32) - 1) / (kSnThreads / 32);
+    if (nb > max_nb) nb = (int)max_nb;
+    if (nb < 1) nb = 1;
+    start += nb;
+  }
+  p.blk_start[n_layers] = start;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  sn_power_kernel<<<dim3(p.blocks_per_layer, n_layers), 256, 0, stream>>>(p);
-  B2G_LAUNCH_CHECK();
-  sn_finalize_kernel<<<n_layers, 256, 0, stream>>>(p);
+  sn_power_kernel<<<start, kSnThreads, 0, stream>>>(p);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }

@@ -141,6 +141,20 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_spectral_norm_multi": [_I, _P, _P, _P, _P, _P, _P, _P, _P],
     # W, G, u, v_raw, scal, dot_scratch, K, C, stream
     "b2g_sn_grad_finalize": [_P, _P, _P, _P, _P, _P, _I, _I, _P],
+    # z, W, gamma, beta, inv_std, alpha, out, B, F, stream
+    "b2g_dense_g_fwd_leaky": [_P, _P, _P, _P, _F, _F, _P, _I, _I, _P],
+    # x, sums, P, C, stream
+    "b2g_bn_stats": [_P, _P, _L, _I, _P],
+    # sums, P, C, eps, momentum, stat, moving_mean, moving_var, stream
+    "b2g_bn_finalize": [_P, _L, _I, _F, _F, _P, _P, _P, _P],
+    # moving_mean, moving_var, C, eps, stat, stream
+    "b2g_bn_inference_stat": [_P, _P, _I, _F, _P, _P],
+    # x, stat, gamma, beta, alpha, y, P, C, stream
+    "b2g_bn_apply_act": [_P, _P, _P, _P, _F, _P, _L, _I, _P],
+    # g, x, stat, gamma, red, dx, dgamma, dbeta, P, C, stream
+    "b2g_bn_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _L, _I, _P],
+    # w, g, rms, n, lr, rho, eps, gscale, clip_n, clip, stream
+    "b2g_rmsprop": [_P, _P, _P, _L, _F, _F, _F, _F, _L, _F, _P],
     # kind, N, Hin, Win, Cin, block_n, phase_group, out, out_len   (host-only)
     "b2g_conv_rows_plan_query": [_I, _I, _I, _I, _I, _I, _I, C.POINTER(C.c_int), _I],
 }

@@ -316,7 +316,7 @@ class Discriminator:
             self.sn_u.append((u / u.norm()).to(torch.float32).to(self.device))
             self.sn_vraw.append(torch.zeros(k, dtype=torch.float32, device=self.device))
             self.sn_traw.append(torch.zeros(cout, dtype=torch.float32, device=self.device))
-            self.sn_scal.append(torch.zeros(4, dtype=torch.float32, device=self.device))
+            self.sn_scal.append(torch.zeros(8, dtype=torch.float32, device=self.device))
             Ks.append(k)
             Cs.append(cout)
         arr = lambda ts: (C.c_void_p * 8)(*[t.data_ptr() for t in ts])

@@ -188,10 +188,41 @@ int b2g_dense_g_fwd(const float* z, const float* W, const float* gamma, const fl
                     int B, int F, b2g_stream_t stream);
 int b2g_dense_g_bwd(const float* z, const float* W, const float* gamma, float inv_std, const void* dq, float* dW,
                     float* dgamma, float* dbeta, int B, int F, b2g_stream_t stream);
+/* Same forward with LeakyReLU(alpha) instead of ReLU, 0 <= alpha < 1 (WGAN generator stem, Dense + LeakyReLU(0.2),
+ * wasserstein_gan/WGAN.py:113-114: pass gamma = 1, beta = 0, inv_std = 1). */
+int b2g_dense_g_fwd_leaky(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
+                          float alpha, void* out, int B, int F, b2g_stream_t stream);
+
+/* ---- WGAN path: training-mode BatchNormalization + RMSprop with weight clipping --------
+ * Activations are bf16 NHWC viewed as [P][C] (P = B*H*W; C a power of two in 8..2048).  Replaces the
+ * FusedBatchNormV3(is_training=True) / FusedBatchNormGradV3 ops behind the BatchNormalization layers of
+ * wasserstein_gan/WGAN.py:62-92 (critic) and :118-128 (generator) under train_on_batch (:298,:303,:317).
+ * bn_stats:    sums[c] = sum_p x[p][c], sums[C+c] = sum_p x[p][c]^2 (zeroed inside).
+ * bn_finalize: stat[c] = mean, stat[C+c] = 1/sqrt(biased var + eps); when moving_mean/var are given they move with
+ *              `momentum` (Keras 0.99), the variance Bessel-corrected (P/(P-1)) as on Keras' fused path.
+ * bn_inference_stat: stat from the moving statistics (generator.predict, WGAN.py:224).
+ * bn_apply_act: y = leaky_alpha(gamma (x - mean) invstd + beta), bf16 [P][C].
+ * bn_bwd:      g = dL/d(BN output) (activation derivative already applied), x = the BN input of the forward:
+ *              dx = gamma invstd (g - mean(g) - xhat mean(g xhat)); dgamma[c] = sum g xhat, dbeta[c] = sum g
+ *              (either may be NULL); red = fp32 [2C] scratch.  Two launches.
+ * rmsprop:     Keras RMSprop (rho, momentum 0, not centred): rms = rho rms + (1-rho) g^2; w -= lr g/(sqrt(rms)+eps)
+ *              (WGAN.py:99,:150); g is multiplied by gscale first; the first clip_n elements of the arena are
+ *              clamped to [-clip, clip] afterwards (ClipConstraint, WGAN.py:33-44 — store the clipped kernels first). */
+int b2g_bn_stats(const void* x, float* sums, long P, int C, b2g_stream_t stream);
+int b2g_bn_finalize(const float* sums, long P, int C, float eps, float momentum, float* stat, float* moving_mean,
+                    float* moving_var, b2g_stream_t stream);
+int b2g_bn_inference_stat(const float* moving_mean, const float* moving_var, int C, float eps, float* stat,
+                          b2g_stream_t stream);
+int b2g_bn_apply_act(const void* x, const float* stat, const float* gamma, const float* beta, float alpha, void* y,
+                     long P, int C, b2g_stream_t stream);
+int b2g_bn_bwd(const void* g, const void* x, const float* stat, const float* gamma, float* red, void* dx,
+               float* dgamma, float* dbeta, long P, int C, b2g_stream_t stream);
+int b2g_rmsprop(float* w, const float* g, float* rms, long n, float lr, float rho, float eps, float gscale,
+                long clip_n, float clip, b2g_stream_t stream);
 
 /* ---- discriminator head: Flatten + Dense(1) (SNDCGAN.py:122-123) fused with the loss (:170) ------------
  * fwd_loss: logits[b] = wscale * <x[b,:], w> + bias; loss_kind 0 = BCE-with-logits vs `label`,
- *           1 = D hinge, 2 = G hinge; loss_out[0] = inv_batch*sum loss, loss_out[1] = inv_batch*sum sigmoid(x);
+ *           1 = D hinge, 2 = G hinge, 3 = Wasserstein label*x (wasserstein_gan/WGAN.py:48-49); loss_out[0] = inv_batch*sum loss, loss_out[1] = inv_batch*sum sigmoid(x);
  *           dlogit[b] = inv_batch * dloss/dlogit.  workspace: >= 64*B floats.
  * bwd:      dx bf16 [B,F] = dlogit[b]*wscale*w[j]*act'(x[b,j]) (LeakyReLU/Dropout derivative of conv7 from its
  *           saved output x); dw[j] += sum_b dlogit[b]*x[b,j]; db += sum_b dlogit[b]  (dw/db may be NULL). */
@@ -208,8 +239,10 @@ int b2g_dhead_bwd(const void* x, const float* w, const float* wscale, const floa
  * colsum_bf16: out[c] += sum_p x[p][c] (BiasAddGrad / BatchNorm-beta gradient).
  * bn_fold_finalize: Conv2DTranspose kernel W[taps][Co][Ci] whose forward used W*gamma[co]*inv_std:
  *       dgamma[co] = inv_std*sum W*G, then G *= gamma[co]*inv_std in place.
- * spectral_norm_multi: one power iteration for up to 8 matrices W_l [K_l][C_l] reading each W once;
- *       scal_l = {scratch, sigma, 1/sigma, |W u|}; t_raw_l / scal_l[0] must be zero on first use.
+ * spectral_norm_multi: one power iteration for up to 8 matrices W_l [K_l][C_l] in ONE launch reading each W once
+ *       (row blocks balanced by bytes; the last block of a layer finalises sigma and u);
+ *       scal_l = float[8] {scratch, sigma, 1/sigma, |W u|, ticket (uint), -, -, -}; t_raw_l and scal_l must be
+ *       zero on first use (the kernel re-zeroes its scratch).
  * sn_grad_finalize: G <- G/sigma - (<G,W>/sigma^2) v u^T in place (gradient through W/sigma). */
 int b2g_adam(float* w, const float* g, float* m, float* v, long n, float lr_t, float beta1, float beta2, float eps,
              float gscale, b2g_stream_t stream);

@@ -284,7 +284,7 @@ def test_spectral_norm_power_iteration_and_grad():
     uc = [u.clone().cuda() for u in us]
     vr = [torch.zeros(s[0], device="cuda") for s in shapes]
     tr = [torch.zeros(s[1], device="cuda") for s in shapes]
-    sc = [torch.zeros(4, device="cuda") for s in shapes]
+    sc = [torch.zeros(8, device="cuda") for s in shapes]
     arr = lambda ts: (C.c_void_p * 8)(*[t.data_ptr() for t in ts])
     Ks = (C.c_int * 8)(*[s[0] for s in shapes])
     Cs = (C.c_int * 8)(*[s[1] for s in shapes])
