@@ -4,7 +4,7 @@
 // All activation tensors are bf16 NHWC viewed as [P][C] (P = B*H*W pixels, C channels innermost, C % 8 == 0 and
 // 256 % (C/8) == 0 so that a thread of a 256-thread block owns the same 8 channels on every grid-stride step and
 // keeps their per-channel constants in registers).  Every kernel is a pure HBM stream (16-byte loads/stores):
-//   bn_stats      : sums[c] = sum x, sums[C+c] = sum x^2                               reads  2 B/elt
+//   bn_stats      : sums[q][c] = sum x, sums[q][C+c] = sum x^2 (8 partial copies q)          reads  2 B/elt
 //   bn_finalize   : mean, 1/sqrt(var_biased+eps); moving stats (momentum, Bessel-corrected variance)
 //   bn_apply_act  : y = leaky(gamma (x-mean) invstd + beta)                            reads 2, writes 2 B/elt
 //   bn_bwd_reduce : red[c] = sum g, red[C+c] = sum g (x-mean)                          reads  4 B/elt
@@ -27,6 +27,8 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return make_uint4(pack2(f[0], f[1]), pack2(f[2], f[3]), pack2(f[4], f[5]), pack2(f[6], f[7]));
 }
 
+constexpr int kBnCopies = 8;  // the reduction outputs are [kBnCopies][2C]; their consumers add the copies
+
 // two per-channel sums per element stream; MODE 0: (x, x^2) ; MODE 1: (g, g*(x-mean))
 template <int MODE>
 __global__ void __launch_bounds__(256) bn_reduce_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
@@ -41,32 +43,59 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const uint4* __restrict_
 #pragma unroll
   for (int k = 0; k < 8; ++k) mean[k] = MODE == 1 ? stat[cg * 8 + k] : 0.f;
   float s0[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, s1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < n8; i += (long)gridDim.x * 256) {
-    float fa[8];
-    unpack8(__ldg(a + i), fa);
-    if (MODE == 0) {
+  const long stride = (long)gridDim.x * 256;
+  constexpr int U = 4;  // independent 16-byte loads in flight per thread
+  for (long i0 = (long)blockIdx.x * 256 + threadIdx.x; i0 < n8; i0 += U * stride) {
+    uint4 va[U], vb[U];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        s0[k] += fa[k];
-        s1[k] = fmaf(fa[k], fa[k], s1[k]);
-      }
-    } else {
-      float fb[8];
-      unpack8(__ldg(b + i), fb);
+    for (int q = 0; q < U; ++q) {
+      const long i = i0 + q * stride;
+      va[q] = i < n8 ? __ldg(a + i) : make_uint4(0u, 0u, 0u, 0u);
+      if (MODE == 1) vb[q] = i < n8 ? __ldg(b + i) : make_uint4(0u, 0u, 0u, 0u);
+    }
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        s0[k] += fa[k];
-        s1[k] = fmaf(fa[k], fb[k] - mean[k], s1[k]);
+    for (int q = 0; q < U; ++q) {
+      float fa[8];
+      unpack8(va[q], fa);   // out-of-range slots are zeros: they add nothing to either sum
+      if (MODE == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          s0[k] += fa[k];
+          s1[k] = fmaf(fa[k], fa[k], s1[k]);
+        }
+      } else {
+        float fb[8];
+        unpack8(vb[q], fb);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          s0[k] += fa[k];
+          s1[k] = fmaf(fa[k], fb[k] - mean[k], s1[k]);
+        }
       }
     }
   }
+  // lanes of a warp that own the same channel group (C < 256) are summed by shuffles first; the block's totals then go
+  // to one of kBnCopies copies of the output (same-address reds serialise in L2: spread them)
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    atomicAdd(&sacc[cg * 8 + k], s0[k]);
-    atomicAdd(&sacc[C + cg * 8 + k], s1[k]);
+  for (int off = 16; off > 0; off >>= 1) {
+    if (off >= groups) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s0[k] += __shfl_xor_sync(0xffffffffu, s0[k], off);
+        s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], off);
+      }
+    }
+  }
+  if ((threadIdx.x & 31) < groups) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      atomicAdd(&sacc[cg * 8 + k], s0[k]);
+      atomicAdd(&sacc[C + cg * 8 + k], s1[k]);
+    }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += 256) atomicAdd(out + i, sacc[i]);
+  float* dst = out + (size_t)(blockIdx.x % kBnCopies) * 2 * C;
+  for (int i = threadIdx.x; i < 2 * C; i += 256) atomicAdd(dst + i, sacc[i]);
 }
 
 __global__ void bn_finalize_kernel(const float* __restrict__ sums, float inv_p, float bessel, int C, float eps,
@@ -74,8 +103,14 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sums, float inv_p, 
                                    float* __restrict__ moving_var) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  const float mean = sums[c] * inv_p;
-  const float var = fmaxf(sums[C + c] * inv_p - mean * mean, 0.f);
+  float sx = 0.f, sxx = 0.f;
+#pragma unroll
+  for (int q = 0; q < kBnCopies; ++q) {
+    sx += sums[q * 2 * C + c];
+    sxx += sums[q * 2 * C + C + c];
+  }
+  const float mean = sx * inv_p;
+  const float var = fmaxf(sxx * inv_p - mean * mean, 0.f);
   stat[c] = mean;
   stat[C + c] = rsqrtf(var + eps);
   if (moving_mean) {
@@ -104,15 +139,28 @@ __global__ void __launch_bounds__(256) bn_apply_act_kernel(const uint4* __restri
     sc[k] = gamma[c] * stat[C + c];
     sh[k] = beta[c] - stat[c] * sc[k];
   }
-  for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < n8; i += (long)gridDim.x * 256) {
-    float f[8];
-    unpack8(__ldg(x + i), f);
+  const long stride = (long)gridDim.x * 256;
+  constexpr int U = 4;
+  for (long i0 = (long)blockIdx.x * 256 + threadIdx.x; i0 < n8; i0 += U * stride) {
+    uint4 v[U];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float v = fmaf(f[k], sc[k], sh[k]);
-      f[k] = fmaxf(v, v * alpha);
+    for (int q = 0; q < U; ++q) {
+      const long i = i0 + q * stride;
+      if (i < n8) v[q] = __ldg(x + i);
     }
-    y[i] = pack8(f);
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const long i = i0 + q * stride;
+      if (i >= n8) break;
+      float f[8];
+      unpack8(v[q], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float t = fmaf(f[k], sc[k], sh[k]);
+        f[k] = fmaxf(t, t * alpha);
+      }
+      y[i] = pack8(f);
+    }
   }
 }
 
@@ -128,7 +176,13 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const uint4* __restri
   for (int k = 0; k < 8; ++k) {
     const int c = cg * 8 + k;
     const float mean = stat[c], invstd = stat[C + c];
-    const float sg = red[c], sgx = red[C + c] * invstd;  // sum g, sum g*xhat
+    float sg = 0.f, sgx = 0.f;  // sum g, sum g*xhat
+#pragma unroll
+    for (int q = 0; q < kBnCopies; ++q) {
+      sg += red[q * 2 * C + c];
+      sgx += red[q * 2 * C + C + c];
+    }
+    sgx *= invstd;
     a[k] = gamma[c] * invstd;
     c1[k] = -a[k] * sgx * inv_p * invstd;
     c0[k] = -a[k] * sg * inv_p - c1[k] * mean;
@@ -174,9 +228,9 @@ static int check_pc(const char* fn, long P, int C) {
     return fail(B2G_E_UNSUPPORTED_SHAPE, "%s: P=%ld C=%d unsupported (C in 8,16,...,2048, powers of two)", fn, P, C);
   return B2G_OK;
 }
-static int stream_grid(long n8) {
+static int stream_grid(long n8, int per_sm = 8) {
   long blocks = (n8 + 255) / 256;
-  const long cap = (long)num_sms() * 8;
+  const long cap = (long)num_sms() * per_sm;
   if (blocks > cap) blocks = cap;
   return (int)(blocks < 1 ? 1 : blocks);
 }
@@ -189,9 +243,9 @@ extern "C" int b2g_bn_stats(const void* x, float* sums, long P, int C, b2g_strea
   if (!x || !sums) return fail(B2G_E_INVALID_ARG, "b2g_bn_stats: null pointer");
   if (int rc = check_pc("b2g_bn_stats", P, C)) return rc;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  B2G_CUDA_CHECK(cudaMemsetAsync(sums, 0, 2 * C * sizeof(float), stream));
+  B2G_CUDA_CHECK(cudaMemsetAsync(sums, 0, kBnCopies * 2 * C * sizeof(float), stream));
   const long n8 = P * (C / 8);
-  bn_reduce_kernel<0><<<stream_grid(n8), 256, 2 * C * sizeof(float), stream>>>(
+  bn_reduce_kernel<0><<<stream_grid(n8, 4), 256, 2 * C * sizeof(float), stream>>>(
       static_cast<const uint4*>(x), nullptr, nullptr, sums, n8, C);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
@@ -234,9 +288,9 @@ extern "C" int b2g_bn_bwd(const void* g, const void* x, const float* stat, const
   if (!g || !x || !stat || !gamma || !red || !dx) return fail(B2G_E_INVALID_ARG, "b2g_bn_bwd: null pointer");
   if (int rc = check_pc("b2g_bn_bwd", P, C)) return rc;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  B2G_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * C * sizeof(float), stream));
+  B2G_CUDA_CHECK(cudaMemsetAsync(red, 0, kBnCopies * 2 * C * sizeof(float), stream));
   const long n8 = P * (C / 8);
-  bn_reduce_kernel<1><<<stream_grid(n8), 256, 2 * C * sizeof(float), stream>>>(
+  bn_reduce_kernel<1><<<stream_grid(n8, 4), 256, 2 * C * sizeof(float), stream>>>(
       static_cast<const uint4*>(g), static_cast<const uint4*>(x), stat, red, n8, C);
   B2G_LAUNCH_CHECK();
   bn_bwd_apply_kernel<<<stream_grid(n8), 256, 0, stream>>>(static_cast<const uint4*>(g), static_cast<const uint4*>(x),

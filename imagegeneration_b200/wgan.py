@@ -62,7 +62,7 @@ class _BatchNormSet:
         self.stat = [torch.zeros(2 * c, dtype=torch.float32, device=device) for c in channels]
         self.moving_mean = [torch.zeros(c, dtype=torch.float32, device=device) for c in channels]
         self.moving_var = [torch.ones(c, dtype=torch.float32, device=device) for c in channels]
-        self.scratch = torch.zeros(2 * max(channels), dtype=torch.float32, device=device)
+        self.scratch = torch.zeros(16 * max(channels), dtype=torch.float32, device=device)   # [8][2C] partial sums
 
     def forward(self, i, raw, gamma, beta, alpha, out, training):
         lib = _lib.load()
@@ -229,7 +229,9 @@ class Critic:
             # dcur = dL/d(BN output of layer i) -> dL/d(raw conv output), in place; gamma / beta gradients
             self.bn.backward(i, dcur, raws[i], v[16 + 2 * i], dcur, g[16 + 2 * i], g[17 + 2 * i])
             if need_wgrad:
-                check(lib.b2g_colsum_bf16(_p(dcur), _p(g[7 + i]), dcur.numel() // co, co, _stream()), "b2g_colsum_bf16")
+                # conv bias gradient = sum over pixels of dL/d(raw) = 0 identically under BatchNorm (the mean is
+                # subtracted).  The reference's autodiff value is fp32 rounding noise (~1e-9, far below RMSprop's
+                # epsilon 1e-7, so its biases stay put); g[7 + i] keeps the exact zero written by arena.g.zero_().
                 if i == 0:
                     ops.conv_wgrad(CONV_K3S1_C3, self._x_in, dcur, g[0])
                 else:

@@ -197,14 +197,15 @@ int b2g_dense_g_fwd_leaky(const float* z, const float* W, const float* gamma, co
  * Activations are bf16 NHWC viewed as [P][C] (P = B*H*W; C a power of two in 8..2048).  Replaces the
  * FusedBatchNormV3(is_training=True) / FusedBatchNormGradV3 ops behind the BatchNormalization layers of
  * wasserstein_gan/WGAN.py:62-92 (critic) and :118-128 (generator) under train_on_batch (:298,:303,:317).
- * bn_stats:    sums[c] = sum_p x[p][c], sums[C+c] = sum_p x[p][c]^2 (zeroed inside).
+ * bn_stats:    sums = fp32 [8][2C] partial sums (zeroed inside; 8 copies spread the same-address reds):
+ *              sum_q sums[q][c] = sum_p x[p][c], sum_q sums[q][C+c] = sum_p x[p][c]^2.
  * bn_finalize: stat[c] = mean, stat[C+c] = 1/sqrt(biased var + eps); when moving_mean/var are given they move with
  *              `momentum` (Keras 0.99), the variance Bessel-corrected (P/(P-1)) as on Keras' fused path.
  * bn_inference_stat: stat from the moving statistics (generator.predict, WGAN.py:224).
  * bn_apply_act: y = leaky_alpha(gamma (x - mean) invstd + beta), bf16 [P][C].
  * bn_bwd:      g = dL/d(BN output) (activation derivative already applied), x = the BN input of the forward:
  *              dx = gamma invstd (g - mean(g) - xhat mean(g xhat)); dgamma[c] = sum g xhat, dbeta[c] = sum g
- *              (either may be NULL); red = fp32 [2C] scratch.  Two launches.
+ *              (either may be NULL); red = fp32 [8][2C] scratch.  Two launches.
  * rmsprop:     Keras RMSprop (rho, momentum 0, not centred): rms = rho rms + (1-rho) g^2; w -= lr g/(sqrt(rms)+eps)
  *              (WGAN.py:99,:150); g is multiplied by gscale first; the first clip_n elements of the arena are
  *              clamped to [-clip, clip] afterwards (ClipConstraint, WGAN.py:33-44 — store the clipped kernels first). */
