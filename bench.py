@@ -222,8 +222,21 @@ def run_b200(args):
     torch.cuda.set_device(local_rank)
     pg = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        pg = dist.group.WORLD
+        # NCCL prints its version banner on STDOUT when the first communicator comes up; the contract is ONE JSON line
+        # on stdout, so stdout points at stderr until the communicator exists
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            pg = dist.group.WORLD
+            warm = torch.zeros(1, device="cuda")
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     B = args.batch
     eng = SNDCGANEngine(B, dropout=0.5, image_size=IMAGE_SIZE, seed=62, spectral_norm=args.spectral_norm,
                         loss=args.loss, process_group=pg)
@@ -365,7 +378,17 @@ def main():
     ap.add_argument("--loss", default="bce", choices=["bce", "hinge"])
     ap.add_argument("--spectral-norm", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="sndcgan", choices=["sndcgan", "wgan"],
+                    help="sndcgan (default): the BASELINE metric; wgan: BASELINE configs[3] on one GPU (SURVEY 8(f) N1), "
+                         "a step = one WGAN.train iteration (5 critic iterations + 1 generator update)")
     args = ap.parse_args()
+    if args.workload == "wgan":
+        if args.impl != "b200" or args.gpus != 1:
+            raise SystemExit("--workload wgan measures our arm on one GPU (tools/wgan_bench.py)")
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import wgan_bench
+        print(json.dumps(wgan_bench.run(max(1, args.steps // 4), max(1, args.warmup), args.batch)), flush=True)
+        return
     if args.impl == "reference":
         run_reference(args)
     else:

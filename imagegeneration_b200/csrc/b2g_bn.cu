@@ -44,14 +44,33 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const uint4* __restrict_
   for (int k = 0; k < 8; ++k) mean[k] = MODE == 1 ? stat[cg * 8 + k] : 0.f;
   float s0[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, s1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const long stride = (long)gridDim.x * 256;
-  constexpr int U = 4;  // independent 16-byte loads in flight per thread
-  for (long i0 = (long)blockIdx.x * 256 + threadIdx.x; i0 < n8; i0 += U * stride) {
+  constexpr int U = 4;  // 16-byte loads per stream per iteration; the NEXT iteration's loads are issued before this
+                        // iteration's values are consumed (a plain unrolled loop is re-serialised into load -> use pairs)
+  long i0 = (long)blockIdx.x * 256 + threadIdx.x;
+  uint4 na[U], nb[U];
+#pragma unroll
+  for (int q = 0; q < U; ++q) {
+    const long i = i0 + q * stride;
+    const long ic = i < n8 ? i : n8 - 1;   // clamped: unconditional loads; slots past the end are zeroed below
+    na[q] = __ldg(a + ic);
+    if (MODE == 1) nb[q] = __ldg(b + ic);
+  }
+  while (i0 < n8) {
     uint4 va[U], vb[U];
 #pragma unroll
     for (int q = 0; q < U; ++q) {
-      const long i = i0 + q * stride;
-      va[q] = i < n8 ? __ldg(a + i) : make_uint4(0u, 0u, 0u, 0u);
-      if (MODE == 1) vb[q] = i < n8 ? __ldg(b + i) : make_uint4(0u, 0u, 0u, 0u);
+      va[q] = (i0 + q * stride < n8) ? na[q] : make_uint4(0u, 0u, 0u, 0u);
+      if (MODE == 1) vb[q] = nb[q];
+    }
+    const long i1 = i0 + U * stride;
+    if (i1 < n8) {
+#pragma unroll
+      for (int q = 0; q < U; ++q) {
+        const long i = i1 + q * stride;
+        const long ic = i < n8 ? i : n8 - 1;
+        na[q] = __ldg(a + ic);
+        if (MODE == 1) nb[q] = __ldg(b + ic);
+      }
     }
 #pragma unroll
     for (int q = 0; q < U; ++q) {
@@ -73,6 +92,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const uint4* __restrict_
         }
       }
     }
+    i0 = i1;
   }
   // lanes of a warp that own the same channel group (C < 256) are summed by shuffles first; the block's totals then go
   // to one of kBnCopies copies of the output (same-address reds serialise in L2: spread them)
@@ -146,7 +166,7 @@ __global__ void __launch_bounds__(256) bn_apply_act_kernel(const uint4* __restri
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       const long i = i0 + q * stride;
-      if (i < n8) v[q] = __ldg(x + i);
+      v[q] = __ldg(x + (i < n8 ? i : n8 - 1));   // clamped: unconditional, issued back to back
     }
 #pragma unroll
     for (int q = 0; q < U; ++q) {
@@ -191,13 +211,28 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const uint4* __restri
       if (dbeta) dbeta[c] = sg;
     }
   }
-  for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < n8; i += (long)gridDim.x * 256) {
-    float fg[8], fx[8];
-    unpack8(__ldg(g + i), fg);
-    unpack8(__ldg(x + i), fx);
+  const long stride = (long)gridDim.x * 256;
+  constexpr int U = 2;
+  for (long i0 = (long)blockIdx.x * 256 + threadIdx.x; i0 < n8; i0 += U * stride) {
+    uint4 vg[U], vx[U];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) fg[k] = fmaf(a[k], fg[k], fmaf(c1[k], fx[k], c0[k]));
-    dx[i] = pack8(fg);
+    for (int q = 0; q < U; ++q) {
+      const long i = i0 + q * stride;
+      const long ic = i < n8 ? i : n8 - 1;
+      vg[q] = __ldg(g + ic);
+      vx[q] = __ldg(x + ic);
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const long i = i0 + q * stride;
+      if (i >= n8) break;
+      float fg[8], fx[8];
+      unpack8(vg[q], fg);
+      unpack8(vx[q], fx);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) fg[k] = fmaf(a[k], fg[k], fmaf(c1[k], fx[k], c0[k]));
+      dx[i] = pack8(fg);
+    }
   }
 }
 
@@ -290,7 +325,7 @@ extern "C" int b2g_bn_bwd(const void* g, const void* x, const float* stat, const
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   B2G_CUDA_CHECK(cudaMemsetAsync(red, 0, kBnCopies * 2 * C * sizeof(float), stream));
   const long n8 = P * (C / 8);
-  bn_reduce_kernel<1><<<stream_grid(n8, 4), 256, 2 * C * sizeof(float), stream>>>(
+  bn_reduce_kernel<1><<<stream_grid(n8, 2), 256, 2 * C * sizeof(float), stream>>>(
       static_cast<const uint4*>(g), static_cast<const uint4*>(x), stat, red, n8, C);
   B2G_LAUNCH_CHECK();
   bn_bwd_apply_kernel<<<stream_grid(n8), 256, 0, stream>>>(static_cast<const uint4*>(g), static_cast<const uint4*>(x),
@@ -313,6 +348,54 @@ extern "C" int b2g_rmsprop(float* w, const float* g, float* rms, long n, float l
   rmsprop_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
       reinterpret_cast<float4*>(w), reinterpret_cast<const float4*>(g), reinterpret_cast<float4*>(rms), n4, lr, rho, eps,
       gscale, clip_n / 4, clip);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// AveragePooling2D(pool_size=(8, 8)) (stride 8, 'valid') over a bf16 NHWC activation -> fp32 [N][H/8][W/8][C]:
+// the feature extractor of the reference's FID-like score (sndcgan/generator_evaluation.py:134-138), SURVEY 8(f) N3.
+// One thread per (output pixel, 8-channel group): 64 16-byte loads, fp32 accumulation.
+// ---------------------------------------------------------------------------------------------------------
+namespace b2g {
+__global__ void __launch_bounds__(256) avgpool8_kernel(const uint4* __restrict__ x, float4* __restrict__ out, int N,
+                                                       int H, int W, int C) {
+  const int groups = C / 8, ph = H / 8, pw = W / 8;
+  const long total = (long)N * ph * pw * groups;
+  for (long t = blockIdx.x * 256L + threadIdx.x; t < total; t += gridDim.x * 256L) {
+    const int cg = (int)(t % groups);
+    long r = t / groups;
+    const int ox = (int)(r % pw);
+    r /= pw;
+    const int oy = (int)(r % ph);
+    const int n = (int)(r / ph);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int dy = 0; dy < 8; ++dy) {
+      const uint4* row = x + (((long)n * H + oy * 8 + dy) * W + ox * 8) * groups + cg;
+#pragma unroll
+      for (int dx = 0; dx < 8; ++dx) {
+        float f[8];
+        unpack8(__ldg(row + (long)dx * groups), f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      }
+    }
+    const float s = 1.f / 64.f;
+    out[t * 2] = make_float4(acc[0] * s, acc[1] * s, acc[2] * s, acc[3] * s);
+    out[t * 2 + 1] = make_float4(acc[4] * s, acc[5] * s, acc[6] * s, acc[7] * s);
+  }
+}
+}  // namespace b2g
+
+extern "C" int b2g_avgpool8_bf16(const void* x, float* out, int N, int H, int W, int C, b2g_stream_t stream_) {
+  if (!x || !out) return fail(B2G_E_INVALID_ARG, "b2g_avgpool8_bf16: null pointer");
+  if (N <= 0 || H < 8 || W < 8 || C < 8 || C % 8)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_avgpool8_bf16: N=%d H=%d W=%d C=%d (H, W >= 8; C %% 8 == 0)", N, H, W, C);
+  const long total = (long)N * (H / 8) * (W / 8) * (C / 8);
+  long blocks = (total + 255) / 256;
+  if (blocks > num_sms() * 8L) blocks = num_sms() * 8L;
+  avgpool8_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const uint4*>(x), reinterpret_cast<float4*>(out), N, H, W, C);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }

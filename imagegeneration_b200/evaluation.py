@@ -1,0 +1,53 @@
+"""FID-like score of the reference (sndcgan/generator_evaluation.py), SURVEY.md section 8(f) row N3.
+
+  calculate_fid(disc_model, images_fake, images_real)     generator_evaluation.py:36-55
+  feature extractor = discriminator minus Flatten/Dense + AveragePooling2D(8, 8) + Flatten   :134-138
+
+The discriminator forward runs on the tcgen05 conv kernels (inference: no dropout), the pooling on b2g_avgpool8_bf16.
+The Fréchet distance itself is small dense linear algebra on [B, 4096] features: means / traces by torch reductions,
+and tr sqrtm(cov_fake cov_real) as the nuclear norm of the B x B matrix Xc Yc^T / sqrt((n-1)(m-1)) (exactly the trace
+of the principal square root, without forming or square-rooting the singular 4096 x 4096 product the reference hands to
+scipy.linalg.sqrtm) — torch.linalg on the device, library code off the training hot path."""
+from __future__ import annotations
+
+import torch
+
+from . import lib as _lib
+from .lib import B200GanError, check
+from .sndcgan import Discriminator, _p, _stream
+
+
+def discriminator_features(disc_model: Discriminator, images: torch.Tensor) -> torch.Tensor:
+    """disc_model.predict(images) of the popped + pooled model: fp32 [B, (H/64)*(W/64)*512] (4096 at 144x256)."""
+    if not isinstance(disc_model, Discriminator):
+        raise B200GanError("discriminator_features needs an imagegeneration_b200 Discriminator")
+    disc_model.forward(images.to(torch.float32), training=False)
+    c7 = disc_model._acts[6]
+    n, h, w, c = c7.shape
+    if h < 8 or w < 8:
+        raise B200GanError("AveragePooling2D(8, 8) needs a conv7 activation of at least 8 x 8 (images >= 64 x 64)")
+    out = torch.empty((n, h // 8, w // 8, c), dtype=torch.float32, device=c7.device)
+    check(_lib.load().b2g_avgpool8_bf16(_p(c7), _p(out), n, h, w, c, _stream()), "b2g_avgpool8_bf16")
+    return out.reshape(n, -1)
+
+
+def fid_from_features(predict_fake: torch.Tensor, predict_real: torch.Tensor) -> float:
+    """generator_evaluation.py:41-55 on device tensors (fp64 accumulation)."""
+    f, r = predict_fake.double(), predict_real.double()
+    n, m = f.shape[0], r.shape[0]
+    if n < 2 or m < 2:
+        raise B200GanError("calculate_fid needs at least two images per set (np.cov)")
+    mu_f, mu_r = f.mean(0), r.mean(0)
+    xc, yc = f - mu_f, r - mu_r
+    ssdiff = ((mu_f - mu_r) ** 2).sum()
+    tr_f = (xc * xc).sum() / (n - 1)          # trace of np.cov(predict_fake, rowvar=False)
+    tr_r = (yc * yc).sum() / (m - 1)
+    cross = xc @ yc.t() / ((n - 1) * (m - 1)) ** 0.5
+    tr_covmean = torch.linalg.svdvals(cross).sum()
+    return float(ssdiff + tr_f + tr_r - 2.0 * tr_covmean)
+
+
+def calculate_fid(disc_model: Discriminator, images_fake: torch.Tensor, images_real: torch.Tensor) -> float:
+    """sndcgan/generator_evaluation.py:36."""
+    return fid_from_features(discriminator_features(disc_model, images_fake).clone(),
+                             discriminator_features(disc_model, images_real))

@@ -221,6 +221,11 @@ int b2g_bn_bwd(const void* g, const void* x, const float* stat, const float* gam
 int b2g_rmsprop(float* w, const float* g, float* rms, long n, float lr, float rho, float eps, float gscale,
                 long clip_n, float clip, b2g_stream_t stream);
 
+/* ---- evaluation path: AveragePooling2D(8, 8) of the discriminator's conv7 activation ----
+ * x bf16 [N,H,W,C] -> out fp32 [N,H/8,W/8,C] (stride 8, 'valid': trailing rows / columns are dropped) — the layer the
+ * reference appends to the popped discriminator for its FID-like score (sndcgan/generator_evaluation.py:134-138). */
+int b2g_avgpool8_bf16(const void* x, float* out, int N, int H, int W, int C, b2g_stream_t stream);
+
 /* ---- discriminator head: Flatten + Dense(1) (SNDCGAN.py:122-123) fused with the loss (:170) ------------
  * fwd_loss: logits[b] = wscale * <x[b,:], w> + bias; loss_kind 0 = BCE-with-logits vs `label`,
  *           1 = D hinge, 2 = G hinge, 3 = Wasserstein label*x (wasserstein_gan/WGAN.py:48-49); loss_out[0] = inv_batch*sum loss, loss_out[1] = inv_batch*sum sigmoid(x);

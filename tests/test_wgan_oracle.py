@@ -84,3 +84,21 @@ def test_train_on_batch_trainable_sets():
 def test_wasserstein_loss():
     y = torch.tensor([[1.0], [3.0]])
     assert float(W.wasserstein_loss(-1.0, y)) == -2.0
+
+
+def test_fid_oracle_lowrank_identity_and_pooling():
+    """tr sqrtm(cov_f cov_r) == nuclear norm of Xc Yc^T / sqrt((n-1)(m-1)) (what the CUDA path evaluates), checked
+    against the reference's scipy.linalg.sqrtm arithmetic; AveragePooling2D(8, 8) 'valid' drops trailing rows."""
+    import numpy as np
+    from oracle import evaluation_oracle as E
+    rng = np.random.default_rng(0)
+    a, b = rng.normal(size=(40, 24)), rng.normal(size=(50, 24)) * 1.3 + 0.2
+    fid = E.calculate_fid_from_features(a, b)
+    alt = (np.sum((a.mean(0) - b.mean(0)) ** 2) + np.trace(np.cov(a, rowvar=False)) + np.trace(np.cov(b, rowvar=False))
+           - 2 * E.trace_sqrt_product_lowrank(a, b))
+    assert abs(fid - alt) < 1e-8 * abs(fid)
+    assert abs(E.calculate_fid_from_features(a, a)) < 1e-6
+    x = torch.arange(2 * 18 * 32 * 3, dtype=torch.float64).reshape(2, 18, 32, 3)
+    p = E.avg_pool_8x8(x)
+    assert tuple(p.shape) == (2, 2, 4, 3)
+    assert torch.allclose(p[0, 1, 2], x[0, 8:16, 16:24].mean(dim=(0, 1)))
