@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const uint4* __restrict_
 
 __global__ void bn_finalize_kernel(const float* __restrict__ sums, float inv_p, float bessel, int C, float eps,
                                    float momentum, float* __restrict__ stat, float* __restrict__ moving_mean,
-                                   float* __restrict__ moving_var) {
+                                   float* __restrict__ moving_var, const float* __restrict__ bias) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float sx = 0.f, sxx = 0.f;
@@ -134,16 +134,18 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sums, float inv_p, 
   stat[c] = mean;
   stat[C + c] = rsqrtf(var + eps);
   if (moving_mean) {
-    moving_mean[c] = moving_mean[c] * momentum + mean * (1.f - momentum);
+    // `bias`: the statistics were taken of the conv output WITHOUT its bias (BatchNorm cancels it); the layer's
+    // true batch mean, which the moving mean tracks, includes it
+    moving_mean[c] = moving_mean[c] * momentum + (mean + (bias ? bias[c] : 0.f)) * (1.f - momentum);
     moving_var[c] = moving_var[c] * momentum + var * bessel * (1.f - momentum);
   }
 }
 
 __global__ void bn_inference_stat_kernel(const float* __restrict__ moving_mean, const float* __restrict__ moving_var,
-                                         int C, float eps, float* __restrict__ stat) {
+                                         int C, float eps, float* __restrict__ stat, const float* __restrict__ bias) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  stat[c] = moving_mean[c];
+  stat[c] = moving_mean[c] - (bias ? bias[c] : 0.f);
   stat[C + c] = rsqrtf(moving_var[c] + eps);
 }
 
@@ -287,21 +289,21 @@ extern "C" int b2g_bn_stats(const void* x, float* sums, long P, int C, b2g_strea
 }
 
 extern "C" int b2g_bn_finalize(const float* sums, long P, int C, float eps, float momentum, float* stat,
-                               float* moving_mean, float* moving_var, b2g_stream_t stream_) {
+                               float* moving_mean, float* moving_var, const float* bias, b2g_stream_t stream_) {
   if (!sums || !stat || (!moving_mean) != (!moving_var)) return fail(B2G_E_INVALID_ARG, "b2g_bn_finalize: null pointer");
   if (P <= 0 || C <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_bn_finalize: P=%ld C=%d", P, C);
   const float bessel = P > 1 ? (float)((double)P / (double)(P - 1)) : 1.f;
   bn_finalize_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream_)>>>(
-      sums, (float)(1.0 / (double)P), bessel, C, eps, momentum, stat, moving_mean, moving_var);
+      sums, (float)(1.0 / (double)P), bessel, C, eps, momentum, stat, moving_mean, moving_var, bias);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
 
 extern "C" int b2g_bn_inference_stat(const float* moving_mean, const float* moving_var, int C, float eps, float* stat,
-                                     b2g_stream_t stream_) {
+                                     const float* bias, b2g_stream_t stream_) {
   if (!moving_mean || !moving_var || !stat || C <= 0) return fail(B2G_E_INVALID_ARG, "b2g_bn_inference_stat: bad argument");
   bn_inference_stat_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream_)>>>(moving_mean, moving_var, C,
-                                                                                            eps, stat);
+                                                                                            eps, stat, bias);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }

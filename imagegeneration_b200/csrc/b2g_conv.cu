@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
     for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
-  epi_colsum_zero(p.e, s_colsum, pl.Cout);
+  epi_colsum_zero(p.e, s_colsum, pl.Cout, sbias);
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
 
   tc_fence_before();
   __syncthreads();
-  epi_colsum_flush(p.e, s_colsum, pl.Cout);
+  epi_colsum_flush(p.e, s_colsum, pl.Cout, sbias);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
@@ -254,8 +254,10 @@ extern "C" int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream_) {
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
   if (a->Cout > 512) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm: Cout=%d > 512", a->Cout);
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
-  if (a->colsum && (a->out_f32 || a->tf32 || a->bias || a->dact == B2G_ACT_NONE))
+  if (a->colsum && (a->out_f32 || a->tf32 || a->bias || (a->dact == B2G_ACT_NONE && !a->colsumsq)))
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: colsum needs a bf16 backward epilogue (dact, no bias)");
+  if (a->colsumsq && (!a->colsum || a->dropout_thresh8))
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: colsumsq needs colsum, no bias and no dropout (BatchNorm statistics)");
   if (a->dropout_thresh8 > 0 && a->act == B2G_ACT_TANH)  // the dropout scale is applied before the activation
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout needs a positively homogeneous activation (none/leaky/relu)");
 

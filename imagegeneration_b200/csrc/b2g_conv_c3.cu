@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     fence_barrier_init();
   }
   epi_load_bias(p.e, sbias, BLOCK_N);
-  epi_colsum_zero(p.e, s_colsum, BLOCK_N);
+  epi_colsum_zero(p.e, s_colsum, BLOCK_N, sbias);
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
 
   tc_fence_before();
   __syncthreads();
-  epi_colsum_flush(p.e, s_colsum, BLOCK_N);
+  epi_colsum_flush(p.e, s_colsum, BLOCK_N, sbias);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
@@ -248,8 +248,10 @@ int launch_conv_c3(const b2g_conv_args* a, void* stream_) {
   if (a->dact != B2G_ACT_NONE && !a->yprev) return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dact without yprev");
   if (a->dropout_thresh8 < 0 || a->dropout_thresh8 > 255)
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout_thresh8 out of range");
-  if (a->colsum && (a->bias || a->dact == B2G_ACT_NONE))
+  if (a->colsum && (a->bias || (a->dact == B2G_ACT_NONE && !a->colsumsq)))
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: colsum needs a bf16 backward epilogue (dact, no bias)");
+  if (a->colsumsq && (!a->colsum || a->dropout_thresh8))
+    return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: colsumsq needs colsum, no bias and no dropout (BatchNorm statistics)");
   if (a->dropout_thresh8 > 0 && a->act == B2G_ACT_TANH)
     return fail(B2G_E_INVALID_ARG, "b2g_conv_igemm: dropout needs a positively homogeneous activation (none/leaky/relu)");
   C3KernelParams kp;

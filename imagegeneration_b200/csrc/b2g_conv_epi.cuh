@@ -36,6 +36,9 @@ struct EpiParams {
   int f32_io;   // tf32 path: out / yprev are full-width fp32 [pixels][Cout]
   float* colsum;  // optional fp32 [Cout]: += per-channel sums of the stored (bf16-rounded) outputs over all pixels
                   // = bias / BatchNorm-beta gradient of the layer whose output gradient this kernel produces
+  float* colsumsq;  // optional fp32 [Cout] (with colsum, bias == NULL): += per-channel sums of SQUARES of the stored
+                    // outputs — with colsum the batch statistics of a training-mode BatchNorm behind this conv
+                    // (WGAN path).  The per-CTA partials live in the kernels' bias table, unused without a bias.
   int tma;      // 1: bf16 output (and yprev) move through per-warp shared-memory boxes and TMA (EpiTmaMaps)
   int qw, qh, qn;  // the 32 pixels one epilogue warp owns, as a box of the tile (qw * qh * qn == 32)
 };
@@ -54,7 +57,8 @@ constexpr int kEpiStageBytes = 2048;  // one warp's [32 pixels][32 channels] bf1
 template <class YLoad, class OStore>
 __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
                                                    size_t pix, int cb, bool valid, YLoad yload, OStore ostore,
-                                                   float* s_colsum = nullptr, bool colsum_here = false) {
+                                                   float* s_colsum = nullptr, bool colsum_here = false,
+                                                   float* s_colsq = nullptr) {
   const size_t off = pix * p.Cout + cb;  // element offset of this thread's 32 outputs
   float v[32];
 #pragma unroll
@@ -163,6 +167,22 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
       for (int j = 0; j < 32; ++j) v[j] = 0.f;
     }
     const int lane = threadIdx.x & 31;
+    if (s_colsq) {  // sums of squares first (the butterfly below consumes v)
+      float q[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) q[j] = v[j] * v[j];
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+          const float mine = up ? q[i + off] : q[i];
+          const float theirs = up ? q[i] : q[i + off];
+          q[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, off);
+        }
+      }
+      atomicAdd(&s_colsq[cb + lane], q[0]);
+    }
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) {
       const bool up = (lane & off) != 0;
@@ -204,18 +224,23 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
       p, sbias, r, pix, cb, valid,
       [&](int g) { return __ldg(reinterpret_cast<const uint4*>(p.yprev + pix * p.Cout + cb) + g); },
       [&](int g, const uint4& o) { reinterpret_cast<uint4*>(p.out + pix * p.Cout + cb)[g] = o; }, s_colsum,
-      p.colsum != nullptr);
+      p.colsum != nullptr, p.colsumsq ? const_cast<float*>(sbias) : nullptr);
 }
 
 // Block-wide helpers of the fused column sums: per-CTA partial sums live in a shared table (zeroed before the
 // block sync of the prologue, flushed with one atomic per channel after the final block sync).
-__device__ __forceinline__ void epi_colsum_zero(const EpiParams& p, float* s_colsum, int n) {
+__device__ __forceinline__ void epi_colsum_zero(const EpiParams& p, float* s_colsum, int n, float* sbias = nullptr) {
   if (p.colsum)
     for (int i = threadIdx.x; i < n; i += blockDim.x) s_colsum[i] = 0.f;
+  if (p.colsumsq && sbias)  // sums of squares use the bias table (no bias in that mode)
+    for (int i = threadIdx.x; i < n; i += blockDim.x) sbias[i] = 0.f;
 }
-__device__ __forceinline__ void epi_colsum_flush(const EpiParams& p, const float* s_colsum, int n) {
+__device__ __forceinline__ void epi_colsum_flush(const EpiParams& p, const float* s_colsum, int n,
+                                                 const float* sbias = nullptr) {
   if (p.colsum)
     for (int i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(p.colsum + i, s_colsum[i]);
+  if (p.colsumsq && sbias)
+    for (int i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(p.colsumsq + i, sbias[i]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -283,14 +308,17 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
     // column sums straight from the box: lane l reads channel cb + l of the 32 pixel rows (the 32 lanes of one
     // read cover one 64-byte row: conflict free).  Rows of pixels outside the tensor hold exact zeros (zero-filled
     // operands, no bias in a backward epilogue).
-    float sum = 0.f;
+    float sum = 0.f, sq = 0.f;
     const uint32_t cg = lane >> 3, ce = (lane & 7) * 2;
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
       const uint16_t h = *reinterpret_cast<const uint16_t*>(st.buf + i * 64 + ((cg ^ ((i >> 1) & 3)) << 4) + ce);
-      sum += __uint_as_float(static_cast<uint32_t>(h) << 16);
+      const float f = __uint_as_float(static_cast<uint32_t>(h) << 16);
+      sum += f;
+      sq = fmaf(f, f, sq);
     }
     atomicAdd(&s_colsum[cb + lane], sum);
+    if (p.colsumsq) atomicAdd(&const_cast<float*>(sbias)[cb + lane], sq);
   }
 }
 
@@ -341,6 +369,7 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->Cout = a->Cout;
   e->f32_io = a->tf32;
   e->colsum = a->colsum;
+  e->colsumsq = a->colsumsq;
   e->tma = 0;
 }
 

@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
     for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
-  epi_colsum_zero(p.e, s_colsum, pl.Cout);
+  epi_colsum_zero(p.e, s_colsum, pl.Cout, sbias);
   if (warp == 1) tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
 
   tc_fence_before();
   __syncthreads();
-  epi_colsum_flush(p.e, s_colsum, pl.Cout);
+  epi_colsum_flush(p.e, s_colsum, pl.Cout, sbias);
   cluster_sync_all();  // no CTA frees TMEM / exits while its peer may still signal or read it
   if (warp == 1) {
     tc_fence_after();

@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     const int nb = p.e.out_f32 ? p.e.cs : pl.Cout;
     for (int i = threadIdx.x; i < nb && i < 512; i += blockDim.x) sbias[i] = p.e.bias[i] * p.e.pre_scale;
   }
-  epi_colsum_zero(p.e, s_colsum, pl.Cout);
+  epi_colsum_zero(p.e, s_colsum, pl.Cout, sbias);
   if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
   tc_fence_before();
   __syncthreads();
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
 
   tc_fence_before();
   __syncthreads();
-  epi_colsum_flush(p.e, s_colsum, pl.Cout);
+  epi_colsum_flush(p.e, s_colsum, pl.Cout, sbias);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, tmem_cols);

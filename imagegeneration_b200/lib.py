@@ -40,6 +40,7 @@ class ConvArgs(C.Structure):
         ("tf32", C.c_int),
         ("colsum", C.c_void_p),
         ("dropout_seed_dev", C.c_void_p),
+        ("colsumsq", C.c_void_p),
     ]
 
 
@@ -145,10 +146,10 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_dense_g_fwd_leaky": [_P, _P, _P, _P, _F, _F, _P, _I, _I, _P],
     # x, sums, P, C, stream
     "b2g_bn_stats": [_P, _P, _L, _I, _P],
-    # sums, P, C, eps, momentum, stat, moving_mean, moving_var, stream
-    "b2g_bn_finalize": [_P, _L, _I, _F, _F, _P, _P, _P, _P],
-    # moving_mean, moving_var, C, eps, stat, stream
-    "b2g_bn_inference_stat": [_P, _P, _I, _F, _P, _P],
+    # sums, P, C, eps, momentum, stat, moving_mean, moving_var, bias, stream
+    "b2g_bn_finalize": [_P, _L, _I, _F, _F, _P, _P, _P, _P, _P],
+    # moving_mean, moving_var, C, eps, stat, bias, stream
+    "b2g_bn_inference_stat": [_P, _P, _I, _F, _P, _P, _P],
     # x, stat, gamma, beta, alpha, y, P, C, stream
     "b2g_bn_apply_act": [_P, _P, _P, _P, _F, _P, _L, _I, _P],
     # g, x, stat, gamma, red, dx, dgamma, dbeta, P, C, stream

@@ -122,13 +122,15 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                dropout_thresh8: int = 0, dropout_seed: int = 0, yprev: torch.Tensor | None = None,
                dact: int = ACT_NONE, dact_alpha: float = 0.0, dact_scale: float = 1.0,
                dact_zero: float = 0.0, out_f32: bool = False, tf32: bool = False,
-               colsum: torch.Tensor | None = None) -> torch.Tensor:
+               colsum: torch.Tensor | None = None, colsumsq: torch.Tensor | None = None) -> torch.Tensor:
     """Tensor-core implicit-GEMM conv / transposed conv with fused epilogue (see include/b200gan.h).
 
     out_f32=True: narrow fp32 output — wpacked has `cout_store` (<= 8) rows and out is fp32 [N,Ho,Wo,cout_store].
     colsum: fp32 [Cout], += per-channel sums of the stored outputs (bias / beta gradient fused into a backward call).
+    colsumsq: fp32 [Cout], with colsum on a call without bias / dropout (forward allowed): += sums of squares — the batch
+    statistics of a training-mode BatchNorm behind the conv (WGAN path).
     dropout_seed: an int, or a 1-element int64 CUDA tensor the kernel reads the seed from (CUDA-graph replay)."""
-    _need_cuda(x, wpacked, out, bias, yprev, colsum)
+    _need_cuda(x, wpacked, out, bias, yprev, colsum, colsumsq)
     n, h, w, cin = x.shape
     k, phases, taps = _KIND_GEOM[kind]
     if kind == CONV_K3S1_C3:
@@ -157,8 +159,11 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
     if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout):
         raise B200GanError("conv_igemm: bias must be fp32 [Cout]")
     if colsum is not None and (colsum.dtype != torch.float32 or colsum.numel() != cout or out_f32 or tf32
-                               or bias is not None or dact == ACT_NONE):
+                               or bias is not None or (dact == ACT_NONE and colsumsq is None)):
         raise B200GanError("conv_igemm: colsum needs fp32 [Cout], bf16 output, no bias and a backward (dact) epilogue")
+    if colsumsq is not None and (colsum is None or colsumsq.dtype != torch.float32 or colsumsq.numel() != cout
+                                 or dropout_thresh8):
+        raise B200GanError("conv_igemm: colsumsq needs colsum, fp32 [Cout] and no dropout")
     cout_store = 0
     if out_f32:
         cout_store, cout = cout, 32
@@ -172,7 +177,8 @@ def conv_igemm(kind: int, x: torch.Tensor, wpacked: torch.Tensor, out: torch.Ten
                  dropout_thresh8=dropout_thresh8, dropout_seed=dropout_seed & 0xFFFFFFFFFFFFFFFF,
                  yprev=None if yprev is None else yprev.data_ptr(), dact=dact, dact_alpha=dact_alpha,
                  dact_scale=dact_scale, dact_zero=dact_zero, out_f32=int(out_f32), cout_store=cout_store,
-                 tf32=int(tf32), colsum=None if colsum is None else colsum.data_ptr(), dropout_seed_dev=seed_dev)
+                 tf32=int(tf32), colsum=None if colsum is None else colsum.data_ptr(), dropout_seed_dev=seed_dev,
+                 colsumsq=None if colsumsq is None else colsumsq.data_ptr())
     ev = _prof_begin()
     check(_lib.load().b2g_conv_igemm(C.byref(a), _stream()), "b2g_conv_igemm")
     cin_alg = 27 if kind in (CONV_K1S1, CONV_K3S1_C3) else cin   # edge layers: 27 real taps*channels

@@ -64,17 +64,28 @@ class _BatchNormSet:
         self.moving_var = [torch.ones(c, dtype=torch.float32, device=device) for c in channels]
         self.scratch = torch.zeros(16 * max(channels), dtype=torch.float32, device=device)   # [8][2C] partial sums
 
-    def forward(self, i, raw, gamma, beta, alpha, out, training):
+    def stat_targets(self, i):
+        """(colsum, colsumsq) views for the conv in front of BatchNorm i: copy 0 of the [8][2C] partial sums, zeroed
+        here — the conv epilogue accumulates the batch statistics while it stores its output."""
+        c = self.channels[i]
+        self.scratch[:16 * c].zero_()
+        return self.scratch[:c], self.scratch[c:2 * c]
+
+    def forward(self, i, raw, gamma, beta, alpha, out, training, bias=None, fused_stats=False):
+        """bias: the conv ran without its bias (cancelled by the mean subtraction); the moving mean still tracks it.
+        fused_stats: the sums are already in scratch (stat_targets + conv epilogue) — no reduction pass over raw."""
         lib = _lib.load()
         c = self.channels[i]
         p = raw.numel() // c
         if training:
-            check(lib.b2g_bn_stats(_p(raw), _p(self.scratch), p, c, _stream()), "b2g_bn_stats")
+            if not fused_stats:
+                check(lib.b2g_bn_stats(_p(raw), _p(self.scratch), p, c, _stream()), "b2g_bn_stats")
             check(lib.b2g_bn_finalize(_p(self.scratch), p, c, BN_EPS, BN_MOMENTUM, _p(self.stat[i]),
-                                      _p(self.moving_mean[i]), _p(self.moving_var[i]), _stream()), "b2g_bn_finalize")
+                                      _p(self.moving_mean[i]), _p(self.moving_var[i]), _p(bias), _stream()),
+                  "b2g_bn_finalize")
         else:
             check(lib.b2g_bn_inference_stat(_p(self.moving_mean[i]), _p(self.moving_var[i]), c, BN_EPS,
-                                            _p(self.stat[i]), _stream()), "b2g_bn_inference_stat")
+                                            _p(self.stat[i]), _p(bias), _stream()), "b2g_bn_inference_stat")
         check(lib.b2g_bn_apply_act(_p(raw), _p(self.stat[i]), _p(gamma), _p(beta), alpha, _p(out), p, c, _stream()),
               "b2g_bn_apply_act")
         return out
@@ -184,9 +195,17 @@ class Critic:
             oh, ow = cur.shape[1] // s, cur.shape[2] // s
             raw = self._buf(f"raw{i + 1}", (B, oh, ow, co), torch.bfloat16)
             kind = CONV_K3S1_C3 if i == 0 else (CONV_K3S1 if s == 1 else CONV_K4S2)
-            ops.conv_igemm(kind, cur, self._wp_f[i], raw, bias=v[7 + i], act=ACT_NONE)
+            # the conv bias is NOT added: BatchNorm subtracts the channel mean, so normalised outputs and every
+            # gradient are identical without it (only the moving mean sees it: bn_finalize adds it back).  That
+            # leaves a bias-free epilogue, which in training mode also accumulates sum x / sum x^2 per channel.
+            if training:
+                cs, cq = self.bn.stat_targets(i)
+                ops.conv_igemm(kind, cur, self._wp_f[i], raw, act=ACT_NONE, colsum=cs, colsumsq=cq)
+            else:
+                ops.conv_igemm(kind, cur, self._wp_f[i], raw, act=ACT_NONE)
             y = self._buf(f"c{i + 1}", (B, oh, ow, co), torch.bfloat16)
-            self.bn.forward(i, raw, v[16 + 2 * i], v[17 + 2 * i], alpha, y, training)
+            self.bn.forward(i, raw, v[16 + 2 * i], v[17 + 2 * i], alpha, y, training, bias=v[7 + i],
+                            fused_stats=training)
             raws.append(raw)
             acts.append(y)
             cur = y
@@ -346,9 +365,13 @@ class WGenerator:
             cout = v[k].shape[2]
             shape = (B, x.shape[1] * 2, x.shape[2] * 2, cout)
             raw = self._buf(f"graw{i + 1}", shape, torch.bfloat16)
-            ops.conv_igemm(CONVT_K4S2, x, self._wp_f[i], raw, act=ACT_NONE)
+            if training:
+                cs, cq = self.bn.stat_targets(i)
+                ops.conv_igemm(CONVT_K4S2, x, self._wp_f[i], raw, act=ACT_NONE, colsum=cs, colsumsq=cq)
+            else:
+                ops.conv_igemm(CONVT_K4S2, x, self._wp_f[i], raw, act=ACT_NONE)
             y = self._buf(f"a{i + 1}", shape, torch.bfloat16)
-            self.bn.forward(i, raw, v[k + 1], v[k + 2], GEN_ALPHA, y, training)
+            self.bn.forward(i, raw, v[k + 1], v[k + 2], GEN_ALPHA, y, training, fused_stats=training)
             raws.append(raw)
             acts.append(y)
             x = y

@@ -92,6 +92,11 @@ typedef struct b2g_conv_args {
   /* optional device pointer to the 64-bit dropout seed (overrides dropout_seed when non-NULL): lets a captured CUDA
      graph of a whole training step be replayed with fresh masks — b2g_step_prologue writes the seeds of a step. */
   const unsigned long long* dropout_seed_dev;
+  /* optional fp32 [Cout], only together with colsum (then also allowed on a FORWARD call: dact == NONE, no bias, no
+     dropout): += the per-channel sums of squares of the stored outputs.  colsum + colsumsq are the batch statistics of
+     a training-mode BatchNormalization behind this conv (wasserstein_gan/WGAN.py:60-92,116-128) — no separate
+     reduction pass over the activation (feed them to b2g_bn_finalize as copy 0 of its [8][2C] sums). */
+  float* colsumsq;
 } b2g_conv_args;
 
 int b2g_conv_igemm(const b2g_conv_args* a, b2g_stream_t stream);
@@ -201,7 +206,9 @@ int b2g_dense_g_fwd_leaky(const float* z, const float* W, const float* gamma, co
  *              sum_q sums[q][c] = sum_p x[p][c], sum_q sums[q][C+c] = sum_p x[p][c]^2.
  * bn_finalize: stat[c] = mean, stat[C+c] = 1/sqrt(biased var + eps); when moving_mean/var are given they move with
  *              `momentum` (Keras 0.99), the variance Bessel-corrected (P/(P-1)) as on Keras' fused path.
- * bn_inference_stat: stat from the moving statistics (generator.predict, WGAN.py:224).
+ *              `bias` (or NULL): the conv in front ran WITHOUT its bias (BatchNorm cancels it exactly) and its fused
+ *              colsum / colsumsq epilogue produced `sums`; the moving mean then tracks mean + bias.
+ * bn_inference_stat: stat from the moving statistics (generator.predict, WGAN.py:224); `bias` as above (subtracted).
  * bn_apply_act: y = leaky_alpha(gamma (x - mean) invstd + beta), bf16 [P][C].
  * bn_bwd:      g = dL/d(BN output) (activation derivative already applied), x = the BN input of the forward:
  *              dx = gamma invstd (g - mean(g) - xhat mean(g xhat)); dgamma[c] = sum g xhat, dbeta[c] = sum g
@@ -211,9 +218,9 @@ int b2g_dense_g_fwd_leaky(const float* z, const float* W, const float* gamma, co
  *              clamped to [-clip, clip] afterwards (ClipConstraint, WGAN.py:33-44 — store the clipped kernels first). */
 int b2g_bn_stats(const void* x, float* sums, long P, int C, b2g_stream_t stream);
 int b2g_bn_finalize(const float* sums, long P, int C, float eps, float momentum, float* stat, float* moving_mean,
-                    float* moving_var, b2g_stream_t stream);
+                    float* moving_var, const float* bias, b2g_stream_t stream);
 int b2g_bn_inference_stat(const float* moving_mean, const float* moving_var, int C, float eps, float* stat,
-                          b2g_stream_t stream);
+                          const float* bias, b2g_stream_t stream);
 int b2g_bn_apply_act(const void* x, const float* stat, const float* gamma, const float* beta, float alpha, void* y,
                      long P, int C, b2g_stream_t stream);
 int b2g_bn_bwd(const void* g, const void* x, const float* stat, const float* gamma, float* red, void* dx,

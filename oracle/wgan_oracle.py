@@ -92,7 +92,10 @@ def critic_forward(cv, moving, x, training: bool, emu=False, collect=None):
     a = x
     for i, (_k, s, _ci, _co, alpha) in enumerate(CRITIC_CONVS):
         w, b, g, be = cv[4 * i:4 * i + 4]
-        raw = _qa(K.conv2d_same(a if i else _qa(a, emu), _qw(w, emu), b, s), emu)
+        if emu:   # the CUDA path stores the conv output WITHOUT the bias in bf16 (BatchNorm cancels the bias exactly;
+            raw = _qa(K.conv2d_same(a if i else _qa(a, emu), _qw(w, emu), None, s), emu) + b   # only the moving mean sees it)
+        else:
+            raw = K.conv2d_same(a, w, b, s)
         a = _qa(K.leaky_relu(batchnorm(raw, g, be, moving[i], training), alpha), emu)
         if collect is not None:
             collect[f"raw{i + 1}"], collect[f"c{i + 1}"] = raw, a

@@ -60,7 +60,7 @@ def test_batchnorm_training_forward_backward(P, Cn):
     mm, mv = torch.zeros(Cn, device="cuda"), torch.ones(Cn, device="cuda")
     gc, bc = gamma.cuda(), beta.cuda()
     L.check(lib.b2g_bn_stats(_p(xc), _p(sums), P, Cn, _s()), "stats")
-    L.check(lib.b2g_bn_finalize(_p(sums), P, Cn, 1e-3, 0.99, _p(stat), _p(mm), _p(mv), _s()), "fin")
+    L.check(lib.b2g_bn_finalize(_p(sums), P, Cn, 1e-3, 0.99, _p(stat), _p(mm), _p(mv), None, _s()), "fin")
     L.check(lib.b2g_bn_apply_act(_p(xc), _p(stat), _p(gc), _p(bc), alpha, _p(yc), P, Cn, _s()), "apply")
     torch.cuda.synchronize()
     mean_ref = x.double().mean(0)
@@ -83,11 +83,48 @@ def test_batchnorm_training_forward_backward(P, Cn):
     torch.cuda.synchronize()
     assert _rel_l2(dyc.float(), dxc.float()) < 2e-3
     # inference statistics
-    L.check(lib.b2g_bn_inference_stat(_p(mm), _p(mv), Cn, 1e-3, _p(stat), _s()), "inf")
+    L.check(lib.b2g_bn_inference_stat(_p(mm), _p(mv), Cn, 1e-3, _p(stat), None, _s()), "inf")
     L.check(lib.b2g_bn_apply_act(_p(xc), _p(stat), _p(gc), _p(bc), alpha, _p(yc), P, Cn, _s()), "apply")
     torch.cuda.synchronize()
     yi = K.leaky_relu(W.batchnorm(x.double(), gamma.double(), beta.double(), moving, False), alpha)
     assert _rel_l2(yc.float(), yi) < 6e-3
+
+
+@pytest.mark.parametrize("kind,shape,cout", [("k3s1", (2, 16, 32, 64), 128), ("k4s2", (2, 16, 32, 64), 128),
+                                             ("convt", (2, 8, 16, 128), 64), ("k3s1", (1, 8, 128, 64), 64),
+                                             ("convt", (1, 4, 64, 128), 64), ("k3s1", (2, 8, 16, 256), 256),
+                                             ("k4s2", (2, 8, 128, 64), 128), ("c3", (2, 16, 32, 3), 64),
+                                             ("c3", (1, 8, 256, 3), 64)])
+def test_conv_forward_accumulates_batch_statistics(kind, shape, cout):
+    """colsum + colsumsq on a forward call (no bias): the per-channel sum and sum of squares of the STORED bf16
+    outputs, from every conv kernel family (per-tap, CTA pair, row slab, 3-channel edge), TMA and direct epilogues."""
+    from imagegeneration_b200 import ops
+    g = torch.Generator().manual_seed(sum(shape) + cout)
+    n, h, w, cin = shape
+    if kind == "c3":
+        x = (torch.rand(shape, generator=g) * 2 - 1).cuda()
+        wt = (torch.randn((3, 3, 3, cout), generator=g) * 0.2).cuda()
+        wp = ops.pack_conv_weight(ops.CONV_K1S1, wt.view(1, 1, 27, cout), n_is_d3=True, ck_pad=64)
+        k = ops.CONV_K3S1_C3
+    else:
+        x = (torch.rand(shape, generator=g) * 2 - 1).to(torch.bfloat16).cuda()
+        if kind == "convt":
+            wt = (torch.randn((4, 4, cout, cin), generator=g) * 0.05).cuda()
+            wp, k = ops.pack_conv_weight(ops.CONVT_K4S2, wt, n_is_d3=False), ops.CONVT_K4S2
+        elif kind == "k4s2":
+            wt = (torch.randn((4, 4, cin, cout), generator=g) * 0.05).cuda()
+            wp, k = ops.pack_conv_weight(ops.CONV_K4S2, wt, n_is_d3=True), ops.CONV_K4S2
+        else:
+            wt = (torch.randn((3, 3, cin, cout), generator=g) * 0.05).cuda()
+            wp, k = ops.pack_conv_weight(ops.CONV_K3S1, wt, n_is_d3=True), ops.CONV_K3S1
+    ref = ops.conv_igemm(k, x, wp, act=ops.ACT_NONE)
+    cs, cq = torch.zeros(cout, device="cuda"), torch.zeros(cout, device="cuda")
+    out = ops.conv_igemm(k, x, wp, act=ops.ACT_NONE, colsum=cs, colsumsq=cq)
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref)
+    o = out.double().reshape(-1, cout)
+    assert _rel_l2(cs, o.sum(0)) < 1e-4 or float((cs.double().cpu() - o.sum(0).cpu()).abs().max()) < 1e-3
+    assert _rel_l2(cq, (o * o).sum(0)) < 1e-5
 
 
 def test_batchnorm_rejects_bad_shapes():
@@ -171,7 +208,9 @@ def test_critic_train_on_batch_matches_oracle():
     assert abs(float(le) - float(lo)) < 2e-2 * scale, (float(le), float(lo))
     C_ = eng.critic_model
     for i in range(7):
-        assert _rel_l2(C_._raws[i].float(), col[f"raw{i + 1}"]) < 2e-2, f"raw{i + 1}"
+        # the engine's raw conv output leaves the bias out (BatchNorm cancels it; bn_finalize adds it to the moving mean)
+        raw_with_bias = C_._raws[i].float() + C_.arena.variables[7 + i]
+        assert _rel_l2(raw_with_bias, col[f"raw{i + 1}"]) < 2e-2, f"raw{i + 1}"
         assert _rel_l2(C_._acts[i].float(), col[f"c{i + 1}"]) < 2e-2, f"c{i + 1}"
         assert _rel_l2(C_.bn.moving_var[i], orc.c_moving[i][1]) < 1e-3
         assert float((C_.bn.moving_mean[i].cpu() - orc.c_moving[i][0]).abs().max()) < 1e-3

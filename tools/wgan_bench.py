@@ -106,7 +106,7 @@ def run(steps=5, warmup=2, batch=64, n_critic=5):
 
     sec = timed(lambda: L.check(lib.b2g_bn_stats(_p(x), _p(sums), P, Cn, s), "stats"))
     hb["bn_stats"] = entry(sec, 2.0 * n, "critic conv1 output, 64 x 144 x 256 x 64 bf16: one read")
-    L.check(lib.b2g_bn_finalize(_p(sums), P, Cn, 1e-3, 0.99, _p(stat), _p(mm), _p(mv), s), "fin")
+    L.check(lib.b2g_bn_finalize(_p(sums), P, Cn, 1e-3, 0.99, _p(stat), _p(mm), _p(mv), None, s), "fin")
     sec = timed(lambda: L.check(lib.b2g_bn_apply_act(_p(x), _p(stat), _p(gamma), _p(beta), 0.2, _p(y), P, Cn, s), "apply"))
     hb["bn_apply_act"] = entry(sec, 4.0 * n, "read + write")
     sec = timed(lambda: L.check(lib.b2g_bn_bwd(_p(dy), _p(x), _p(stat), _p(gamma), _p(red), _p(dx), None, None, P, Cn, s), "bwd", 2))
