@@ -387,7 +387,8 @@ def main():
             raise SystemExit("--workload wgan measures our arm on one GPU (tools/wgan_bench.py)")
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import wgan_bench
-        print(json.dumps(wgan_bench.run(max(1, args.steps // 4), max(1, args.warmup), args.batch)), flush=True)
+        print(json.dumps(wgan_bench.run(max(1, args.steps // 4), max(1, args.warmup), args.batch,
+                                        with_cpu_baseline=not args.no_cpu_baseline)), flush=True)
         return
     if args.impl == "reference":
         run_reference(args)

@@ -34,7 +34,34 @@ def _p(t):
     return C.c_void_p(t.data_ptr())
 
 
-def run(steps=5, warmup=2, batch=64, n_critic=5):
+def cpu_baseline(batch=4):
+    """The oracle's restatement of the same loop on the host cores (kind "port": TensorFlow cannot run here): one
+    critic update on real images, one predict + critic update on fakes, one generator update at `batch` images, scaled
+    to an iteration (5 x the critic pair + 1 generator update).  Images/s = real images per second, as in our arm."""
+    import time
+
+    import torch
+    from oracle import wgan_oracle as W
+    cores = torch.get_num_threads()
+    orc = W.OracleWGAN(IMAGE_SIZE, seed=62)
+    g = torch.Generator().manual_seed(3)
+    real = torch.rand((batch, *IMAGE_SIZE), generator=g) * 2 - 1
+    z = torch.randn((batch, 128), generator=g)
+    t0 = time.perf_counter()
+    orc.train_critic_on_batch(real, -1.0)
+    orc.train_critic_on_batch(orc.predict(z), 1.0)
+    t_pair = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    orc.train_gan_on_batch(z)
+    t_gan = time.perf_counter() - t0
+    t_iter = 5 * t_pair + t_gan
+    return {"value": 5 * batch / t_iter, "unit": "images/s", "cores": cores, "kind": "port",
+            "sample": f"oracle (PyTorch-CPU restatement of wasserstein_gan/WGAN.py:296-318, fp32) at batch {batch}: one "
+                      f"critic real+fake pair {t_pair:.2f} s, one generator update {t_gan:.2f} s, scaled to 5 pairs + 1 "
+                      f"update; {cores} threads"}
+
+
+def run(steps=5, warmup=2, batch=64, n_critic=5, with_cpu_baseline=False):
     import torch
     from imagegeneration_b200 import lib as L
     from imagegeneration_b200.wgan import WGANEngine
@@ -117,6 +144,8 @@ def run(steps=5, warmup=2, batch=64, n_critic=5):
     hb["rmsprop_critic_arena"] = entry(sec, 20.0 * a_.numel, "20 B/param (read w, g, rms; write w, rms); 6.2 M params: "
                                        "latency-bound at 123 MB")
     line["roofline_hbm"] = hb
+    if with_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline()
     return line
 
 
@@ -125,5 +154,6 @@ if __name__ == "__main__":
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--cpu-baseline", action="store_true")
     args = ap.parse_args()
-    print(json.dumps(run(args.steps, args.warmup, args.batch)), flush=True)
+    print(json.dumps(run(args.steps, args.warmup, args.batch, with_cpu_baseline=args.cpu_baseline)), flush=True)
