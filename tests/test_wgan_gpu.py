@@ -349,6 +349,26 @@ def test_wgan_class_trains_over_a_dataset():
     assert all(torch.isfinite(torch.tensor(v)).all() for v in hist.values())
 
 
+def test_ragged_last_batch_and_empty_batch():
+    """image_dataset_from_directory does not drop the remainder: the last real batch of an epoch can be smaller than
+    bach_size while generate_fake_samples still draws bach_size fakes (WGAN.py:298-303).  An empty batch is an error."""
+    from imagegeneration_b200.lib import B200GanError
+    from imagegeneration_b200.wgan import WGAN
+    g = torch.Generator().manual_seed(8)
+    data = [torch.rand((b, *IMAGE), generator=g) * 2 - 1 for b in (BATCH, BATCH, BATCH, 3, 1)]
+    wg = WGAN(data, IMAGE, BATCH, 5)
+    hist = wg.train(1)
+    assert len(hist["g_hist"]) == 1 and wg.critic_optimizer.iterations == 10
+    assert all(torch.isfinite(torch.tensor(v)).all() for v in hist.values())
+    # same ragged batch through the oracle: the batch-of-3 critic step still matches
+    eng, orc = _make_pair(emu=True)
+    x3 = data[3]
+    le, lo = eng.train_critic_on_batch(x3.cuda(), -1.0), orc.train_critic_on_batch(x3, -1.0)
+    assert abs(float(le) - float(lo)) < 2e-2 * (float(eng.critic_model.logits.abs().mean()) + 1e-3)
+    with pytest.raises(B200GanError):
+        eng.train_critic_on_batch(torch.zeros((0, *IMAGE), device="cuda"), -1.0)
+
+
 def test_cpu_tensors_are_rejected():
     from imagegeneration_b200.lib import B200GanError
     from imagegeneration_b200.wgan import WGANEngine
