@@ -435,9 +435,15 @@ class Discriminator:
                                              _stream()), "b2g_dhead_fwd_loss", 2)
         return self._loss[0], self.logits
 
-    def backward(self, need_wgrad: bool, need_input_grad: bool, g_out=None):
+    # first variable of the gradient range that is complete once conv6's weight gradient has been issued
+    # (dense, conv7, conv6: 19 of the 24.6 MB) — data-parallel runs start reducing it while conv5..conv1 still run
+    EARLY_GRAD_FIRST_VAR = 10
+
+    def backward(self, need_wgrad: bool, need_input_grad: bool, g_out=None, on_tail_grads_ready=None):
         """Backward from the dlogit of the last head_loss.  need_wgrad fills arena.g (zeroed first);
-        need_input_grad returns dL/d(pre-tanh generator output) fp32 [B,H,W,3] (uses tanh'(g_out))."""
+        need_input_grad returns dL/d(pre-tanh generator output) fp32 [B,H,W,3] (uses tanh'(g_out)).
+        on_tail_grads_ready: called once the gradients of variables EARLY_GRAD_FIRST_VAR.. are final (never with
+        spectral norm, whose finalisation rewrites every kernel gradient at the end)."""
         lib = _lib.load()
         v, g = self.arena.variables, self.arena.grads
         acts = self._acts
@@ -459,6 +465,8 @@ class Discriminator:
                     check(lib.b2g_colsum_bf16(_p(dpre), _p(g[2 * i + 1]), dpre.numel() // cout, cout, _stream()),
                           "b2g_colsum_bf16")
                 ops.conv_wgrad(CONV_K3S1 if s == 1 else CONV_K4S2, x_in, dpre, g[2 * i])
+                if i == 5 and on_tail_grads_ready is not None and not self.spectral_norm:
+                    on_tail_grads_ready()
             dprev = self._buf(f"dpre{i}", tuple(x_in.shape), torch.bfloat16)
             # the input-gradient call also sums what it stores per channel = bias gradient of the layer below
             # (conv1's comes out of its weight-gradient GEMM through the ones channel of the im2col operand)
@@ -561,6 +569,28 @@ class SNDCGANEngine:
         from .dp import allreduce_sum_
         return allreduce_sum_(flat, self.pg, async_op)
 
+    def _d_backward_allreduce(self, D):
+        """Discriminator backward with its gradient all-reduce (data parallel): the tail of the arena (conv6, conv7,
+        Dense: 19 of 24.6 MB) is reduced asynchronously as soon as it is final, behind the conv5..conv1 backward
+        kernels; only the 5.5 MB head is reduced after the last kernel."""
+        if self.world == 1:
+            D.backward(need_wgrad=True, need_input_grad=False)
+            return
+        split = D.arena.offsets[D.EARLY_GRAD_FIRST_VAR]
+        pending = []
+        early = ((not D.spectral_norm) and not torch.cuda.is_current_stream_capturing()
+                 and os.environ.get("B2G_DP_EARLY_ALLREDUCE", "1") != "0")
+        D.backward(need_wgrad=True, need_input_grad=False,
+                   on_tail_grads_ready=(lambda: pending.append(self._allreduce(D.arena.g[split:], async_op=True)))
+                   if early else None)
+        if pending:
+            self._allreduce(D.arena.g[:split])
+            for w in pending:
+                if w is not None:
+                    w.wait()
+        else:
+            self._allreduce(D.arena.g)
+
     def train_step(self, input_real, input_z, dropout_seeds=None):
         """One G update + two D updates, in the reference's order (SNDCGAN.py:241-269).
 
@@ -661,16 +691,14 @@ class SNDCGANEngine:
         D.forward(input_real, training=True, dropout_seeds=sb)                      # :252
         d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b)                # :253-254
         d_logits_real = d_logits_real.clone()
-        D.backward(need_wgrad=True, need_input_grad=False)                          # :256
-        self._allreduce(D.arena.g)
+        self._d_backward_allreduce(D)                                               # :256
         self.d_optimizer.apply_arena(D.arena, gs, lr_d1)                            # :257
         D._packed_dirty = True
 
         # (3) discriminator step on the stale fake batch (:259-267)
         D.forward(g_output, training=True, dropout_seeds=sc)                        # :260
         d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)                # :261-262
-        D.backward(need_wgrad=True, need_input_grad=False)                          # :266
-        self._allreduce(D.arena.g)
+        self._d_backward_allreduce(D)                                               # :266
         self.d_optimizer.apply_arena(D.arena, gs, lr_d2)                            # :267
         D._packed_dirty = True
 
