@@ -24,7 +24,15 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
+static int g_sm_limit = 0;  // b2g_set_sm_limit: 0 = all SMs
+
 int num_sms() {
+  const int hw = hw_num_sms();
+  const int lim = g_sm_limit;
+  return (lim > 0 && lim < hw) ? lim : hw;
+}
+
+int hw_num_sms() {
   static int n = []() {
     int dev = 0, v = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 148;
@@ -157,6 +165,15 @@ __global__ void __launch_bounds__(256) pack_conv_weight_multi_kernel(const __gri
 using namespace b2g;
 
 extern "C" int b2g_version(void) { return 100; }
+
+extern "C" int b2g_set_sm_limit(int n) {
+  if (n < 0) return fail(B2G_E_INVALID_ARG, "b2g_set_sm_limit: n must be >= 0 (0 = all SMs)");
+  const int prev = b2g::g_sm_limit;
+  b2g::g_sm_limit = (n > 0 && n < 8) ? 8 : n;
+  (void)prev;
+  return B2G_OK;
+}
+extern "C" int b2g_num_sms(void) { return b2g::num_sms(); }
 extern "C" const char* b2g_last_error(void) { return error_buffer(); }
 
 // phases / taps of a packing kind; rejects kernel sizes and flips the kind does not define

@@ -63,6 +63,7 @@ inline int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int rank, const voi
   return B2G_OK;
 }
 
-int num_sms();  // cached SM count of the current device (b2g_api.cu)
+int num_sms();     // SMs the launchers may fill: the device's count, or the b2g_set_sm_limit budget (b2g_api.cu)
+int hw_num_sms();  // cached SM count of the current device
 
 }  // namespace b2g

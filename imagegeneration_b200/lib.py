@@ -156,6 +156,9 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_bn_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _L, _I, _P],
     # w, g, rms, n, lr, rho, eps, gscale, clip_n, clip, stream
     "b2g_rmsprop": [_P, _P, _P, _L, _F, _F, _F, _F, _L, _F, _P],
+    # n
+    "b2g_set_sm_limit": [_I],
+    "b2g_num_sms": [],
     # x, out, N, H, W, C, stream
     "b2g_avgpool8_bf16": [_P, _P, _I, _I, _I, _I, _P],
     # kind, N, Hin, Win, Cin, block_n, phase_group, out, out_len   (host-only)

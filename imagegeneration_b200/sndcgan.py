@@ -688,10 +688,24 @@ class SNDCGANEngine:
         # result is identical and its gradient all-reduce overlaps both discriminator steps.
 
         # (2) discriminator step on the real batch (:251-257)
-        D.forward(input_real, training=True, dropout_seeds=sb)                      # :252
-        d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b)                # :253-254
-        d_logits_real = d_logits_real.clone()
-        self._d_backward_allreduce(D)                                               # :256
+        # While the generator's 164 MB all-reduce is in flight its NCCL kernel holds some SMs; a persistent grid of
+        # one CTA per SM would wait for them (two waves).  B2G_DP_SM_RESERVE=n leaves n SMs free for the first
+        # discriminator forward (and backward with B2G_DP_SM_RESERVE_BWD=1) after the all-reduce is launched.
+        reserve = int(os.environ.get("B2G_DP_SM_RESERVE", "0")) if g_work is not None else 0
+        reserve_bwd = reserve and os.environ.get("B2G_DP_SM_RESERVE_BWD", "0") == "1"
+        lib = _lib.load()
+        if reserve:
+            check(lib.b2g_set_sm_limit(max(8, lib.b2g_num_sms() - reserve)), "b2g_set_sm_limit", 0)
+        try:
+            D.forward(input_real, training=True, dropout_seeds=sb)                  # :252
+            d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b)            # :253-254
+            d_logits_real = d_logits_real.clone()
+            if reserve and not reserve_bwd:
+                check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
+            self._d_backward_allreduce(D)                                           # :256
+        finally:
+            if reserve:
+                check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
         self.d_optimizer.apply_arena(D.arena, gs, lr_d1)                            # :257
         D._packed_dirty = True
 

@@ -30,6 +30,12 @@ enum {
 };
 
 int b2g_version(void);
+/* SM budget of the persistent kernels (process-wide, set from the one host thread that launches): every launcher sizes
+ * its grid for min(device SMs, n) SMs; n = 0 restores the whole device.  Data-parallel runs leave a few SMs to the
+ * NCCL all-reduce kernel that overlaps the discriminator steps — a persistent grid of one CTA per SM otherwise waits
+ * for the SMs the collective holds and runs as two waves.  b2g_num_sms returns the current budget. */
+int b2g_set_sm_limit(int n);
+int b2g_num_sms(void);
 const char* b2g_last_error(void); /* thread-local, valid until the next failing call on this thread */
 
 /* ---- implicit-GEMM convolutions on tcgen05 tensor cores (TMA-fed, TMEM accumulators) -------------------
