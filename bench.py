@@ -207,6 +207,20 @@ def _hbm_kernel_rooflines(eng, peaks, peak_kind):
     return out
 
 
+def _teardown(eng, dist):
+    """Drops the captured step graph (it references NCCL kernels), then tears the process group down.  A watchdog ends
+    the process if the teardown does not return: the measurement is complete and printed by then."""
+    import threading
+    sys.stdout.flush()
+    t = threading.Timer(30.0, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    eng.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    t.cancel()
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -222,6 +236,8 @@ def run_b200(args):
     torch.cuda.set_device(local_rank)
     pg = None
     if world > 1:
+        # data-parallel steps are replayed as one CUDA graph too (all-reduces captured); _teardown releases it
+        os.environ.setdefault("B2G_CUDA_GRAPH_DP", "1")
         # NCCL prints its version banner on STDOUT when the first communicator comes up; the contract is ONE JSON line
         # on stdout, so stdout points at stderr until the communicator exists
         sys.stdout.flush()
@@ -338,7 +354,7 @@ def run_b200(args):
 
     if rank != 0:
         if world > 1:
-            dist.destroy_process_group()
+            _teardown(eng, dist)
         return
     line = {
         "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
@@ -365,7 +381,7 @@ def run_b200(args):
         line["cpu_baseline"] = cpu_baseline()
     print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        _teardown(eng, dist)
 
 
 def main():

@@ -556,6 +556,15 @@ class SNDCGANEngine:
         self._graph_failed = None
         self._eager_steps = 0
 
+    def close(self) -> None:
+        """Drops the captured CUDA graph (it references the NCCL kernels of a data-parallel step) and waits for the
+        device: call before torch.distributed.destroy_process_group()."""
+        self._graph = None
+        self._graph_outs = None
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
+
     def _seed_base(self) -> int:
         return (self.seed * 0x1000003 + self.rank * 0x10001 + 1) & _MASK64
 
