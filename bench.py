@@ -124,6 +124,11 @@ def run_reference(args):
     if rank != 0:
         return
     import torch
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the reference arm uses every host core it may run on
+    try:
+        torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+    except (AttributeError, OSError):
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
     cores = torch.get_num_threads()
     probe = _oracle_step_factory(1)
     t0 = time.perf_counter()
