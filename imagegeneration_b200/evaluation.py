@@ -51,3 +51,21 @@ def calculate_fid(disc_model: Discriminator, images_fake: torch.Tensor, images_r
     """sndcgan/generator_evaluation.py:36."""
     return fid_from_features(discriminator_features(disc_model, images_fake).clone(),
                              discriminator_features(disc_model, images_real))
+
+
+def evaluate_fid(disc_model: Discriminator, gen_model, generator_weights: dict, img_real_used, random_z_used):
+    """The evaluation loop of sndcgan/generator_evaluation.py:156-175 without its .h5 / pickle bookkeeping: for every
+    saved generator (epoch -> list of weights in trainable_variables order, e.g. from the trainer's checkpoints) and
+    every real batch i, images_fake = create_samples(gen_model, random_z_used[i], B) (range [0, 1], as the reference
+    feeds them) and fid = calculate_fid(disc_model, images_fake, images_real).  Returns (epochs, [fids per epoch])."""
+    from .sndcgan import create_samples
+    epochs, epoch_fids = [], []
+    for epoch in sorted(generator_weights):
+        gen_model.set_weights(generator_weights[epoch])
+        fids = []
+        for images_real, z in zip(img_real_used, random_z_used):
+            images_fake = create_samples(gen_model, z, images_real.shape[0])
+            fids.append(calculate_fid(disc_model, images_fake, images_real))
+        epochs.append(epoch)
+        epoch_fids.append(fids)
+    return epochs, epoch_fids

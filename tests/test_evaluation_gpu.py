@@ -59,3 +59,27 @@ def test_calculate_fid_end_to_end():
     got = calculate_fid(D, fake.cuda(), real.cuda())
     ref = E.calculate_fid(dv, fake, real)
     assert abs(got - ref) < 5e-2 * abs(ref), (got, ref)
+
+
+def test_evaluate_fid_loop_over_saved_generators():
+    """generator_evaluation.py:156-175: one FID per (saved generator, real batch); identical generators give identical
+    scores, a perturbed generator a different one; every score matches the oracle on the same fakes."""
+    from imagegeneration_b200.evaluation import evaluate_fid
+    from imagegeneration_b200.sndcgan import create_samples, make_dcgan_discriminator, make_dcgan_generator
+    from oracle import sndcgan_oracle as O
+    image = (64, 128, 3)
+    D = make_dcgan_discriminator(0.5, image, seed=7)
+    G = make_dcgan_generator(image, seed=8)
+    w0 = [v.detach().clone() for v in G.trainable_variables]
+    w1 = [v * 1.5 if v.dim() > 1 else v.clone() for v in w0]
+    g = torch.Generator().manual_seed(2)
+    reals = [(torch.rand((4, *image), generator=g) * 2 - 1).cuda() for _ in range(2)]
+    zs = [(torch.rand((4, 128), generator=g) * 2 - 1).cuda() for _ in range(2)]
+    epochs, fids = evaluate_fid(D, G, {5: w0, 10: w1, 15: w0}, reals, zs)
+    assert epochs == [5, 10, 15] and [len(f) for f in fids] == [2, 2, 2]
+    assert all(abs(a - b) < 1e-6 * abs(a) + 1e-9 for a, b in zip(fids[0], fids[2]))
+    assert any(abs(a - b) > 1e-3 * abs(a) for a, b in zip(fids[0], fids[1]))
+    dv = [v.detach().cpu() for v in D.trainable_variables]
+    fake0 = O.create_samples([v.cpu() for v in w0], zs[0].cpu(), 4, image)
+    ref = E.calculate_fid(dv, fake0, reals[0].cpu())
+    assert abs(fids[0][0] - ref) < 5e-2 * abs(ref), (fids[0][0], ref)
