@@ -259,6 +259,7 @@ int launch_conv_c3(const b2g_conv_args* a, void* stream_) {
   if (!build_conv_plan(a->kind, a->N, a->Hin, a->Win, 64, a->Cout, 128, &kp.plan))
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm(K3S1_C3): cannot tile N=%d H=%d W=%d", a->N, a->Hin, a->Win);
   fill_epi_params(a, &kp.e);
+  kp.e.cs_copies = 1;  // this kernel's column-sum tables hold one [64] copy
   {
     int rc = fill_epi_tma(a, kp.plan, true, &kp.e, &kp.em);
     if (rc) return rc;

@@ -39,6 +39,9 @@ struct EpiParams {
   float* colsumsq;  // optional fp32 [Cout] (with colsum, bias == NULL): += per-channel sums of SQUARES of the stored
                     // outputs — with colsum the batch statistics of a training-mode BatchNorm behind this conv
                     // (WGAN path).  The per-CTA partials live in the kernels' bias table, unused without a bias.
+  int cs_copies;  // the per-CTA column-sum tables hold this many copies of [Cout] (512 / Cout in the 512-float tables):
+                  // warp w adds into copy w % cs_copies — fp32 shared-memory atomicAdd is a compare-and-swap loop,
+                  // and with Cout = 64 eight epilogue warps would otherwise fight over the same 32 words per chunk
   int tma;      // 1: bf16 output (and yprev) move through per-warp shared-memory boxes and TMA (EpiTmaMaps)
   int qw, qh, qn;  // the 32 pixels one epilogue warp owns, as a box of the tile (qw * qh * qn == 32)
 };
@@ -167,6 +170,7 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
       for (int j = 0; j < 32; ++j) v[j] = 0.f;
     }
     const int lane = threadIdx.x & 31;
+    const int cs_off = (static_cast<int>(threadIdx.x >> 5) % p.cs_copies) * p.Cout;
     if (s_colsq) {  // sums of squares first (the butterfly below consumes v)
       float q[32];
 #pragma unroll
@@ -181,7 +185,7 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
           q[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, off);
         }
       }
-      atomicAdd(&s_colsq[cb + lane], q[0]);
+      atomicAdd(&s_colsq[cs_off + cb + lane], q[0]);
     }
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) {
@@ -193,7 +197,7 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
         v[i] = mine + __shfl_xor_sync(0xffffffffu, theirs, off);
       }
     }
-    atomicAdd(&s_colsum[cb + lane], v[0]);
+    atomicAdd(&s_colsum[cs_off + cb + lane], v[0]);
   }
 }
 
@@ -230,17 +234,26 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
 // Block-wide helpers of the fused column sums: per-CTA partial sums live in a shared table (zeroed before the
 // block sync of the prologue, flushed with one atomic per channel after the final block sync).
 __device__ __forceinline__ void epi_colsum_zero(const EpiParams& p, float* s_colsum, int n, float* sbias = nullptr) {
+  const int m = n * p.cs_copies;
   if (p.colsum)
-    for (int i = threadIdx.x; i < n; i += blockDim.x) s_colsum[i] = 0.f;
+    for (int i = threadIdx.x; i < m; i += blockDim.x) s_colsum[i] = 0.f;
   if (p.colsumsq && sbias)  // sums of squares use the bias table (no bias in that mode)
-    for (int i = threadIdx.x; i < n; i += blockDim.x) sbias[i] = 0.f;
+    for (int i = threadIdx.x; i < m; i += blockDim.x) sbias[i] = 0.f;
 }
 __device__ __forceinline__ void epi_colsum_flush(const EpiParams& p, const float* s_colsum, int n,
                                                  const float* sbias = nullptr) {
   if (p.colsum)
-    for (int i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(p.colsum + i, s_colsum[i]);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      float t = 0.f;
+      for (int c = 0; c < p.cs_copies; ++c) t += s_colsum[c * n + i];
+      atomicAdd(p.colsum + i, t);
+    }
   if (p.colsumsq && sbias)
-    for (int i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(p.colsumsq + i, sbias[i]);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      float t = 0.f;
+      for (int c = 0; c < p.cs_copies; ++c) t += sbias[c * n + i];
+      atomicAdd(p.colsumsq + i, t);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -317,8 +330,9 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
       sum += f;
       sq = fmaf(f, f, sq);
     }
-    atomicAdd(&s_colsum[cb + lane], sum);
-    if (p.colsumsq) atomicAdd(&const_cast<float*>(sbias)[cb + lane], sq);
+    const int cs_off = (static_cast<int>(threadIdx.x >> 5) % p.cs_copies) * p.Cout;
+    atomicAdd(&s_colsum[cs_off + cb + lane], sum);
+    if (p.colsumsq) atomicAdd(&const_cast<float*>(sbias)[cs_off + cb + lane], sq);
   }
 }
 
@@ -370,6 +384,7 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->f32_io = a->tf32;
   e->colsum = a->colsum;
   e->colsumsq = a->colsumsq;
+  e->cs_copies = (a->Cout > 0 && a->Cout <= 512) ? (512 / a->Cout > 0 ? 512 / a->Cout : 1) : 1;  // 512-float tables
   e->tma = 0;
 }
 
