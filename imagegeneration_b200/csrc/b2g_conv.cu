@@ -161,7 +161,8 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
     }
   } else {
     // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
-    const EpiParams e = epi_resolve(p.e);  // dropout seed possibly read from device memory
+    const EpiParams& e = p.e;                 // stays in the constant bank
+    const EpiSeed sd = epi_resolve_seed(p.e);  // dropout seed possibly read from device memory
     const int q = warp & 3;
     const int grp = (warp - 2) >> 2;
     const int row = q * 32 + lane;
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(conv_threads<BLOCK_N>(), 1)
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
-        conv_epilogue_chunk(e, sbias, r, pix, col0 + c * 32, valid, s_colsum);
+        conv_epilogue_chunk(e, sbias, r, pix, col0 + c * 32, valid, s_colsum, sd);
       }
       tc_fence_before();
       __syncwarp();

@@ -197,7 +197,8 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     }
   } else {
     // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
-    const EpiParams e = epi_resolve(p.e);  // dropout seed possibly read from device memory
+    const EpiParams& e = p.e;                 // stays in the constant bank
+    const EpiSeed sd = epi_resolve_seed(p.e);  // dropout seed possibly read from device memory
     const int q = warp & 3;
     const int grp = (warp - 2 - Cfg::kBuilderWarps) >> 2;
     const int row = q * 32 + lane;
@@ -223,8 +224,8 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       __syncwarp();
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
       tmem_ld_wait();
-      if (use_tma) epi_tma_chunk(e, &p.em.omap[0], st, sbias, r, pix, c * 32, lane, bx, by, bn, s_colsum);
-      else conv_epilogue_chunk(e, sbias, r, pix, c * 32, valid, s_colsum);
+      if (use_tma) epi_tma_chunk(e, &p.em.omap[0], st, sbias, r, pix, c * 32, lane, bx, by, bn, s_colsum, sd);
+      else conv_epilogue_chunk(e, sbias, r, pix, c * 32, valid, s_colsum, sd);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[as]);

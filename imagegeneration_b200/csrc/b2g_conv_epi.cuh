@@ -46,6 +46,13 @@ struct EpiParams {
   int qw, qh, qn;  // the 32 pixels one epilogue warp owns, as a box of the tile (qw * qh * qn == 32)
 };
 
+// The dropout seed of a call, resolved once per epilogue warp (it may live in device memory for graph replay).  Kept
+// OUT of EpiParams on purpose: copying the whole parameter block into a per-thread struct to patch two words moved
+// every epilogue constant from the constant bank into registers and cost the backward (dact) epilogues 15-25 %.
+struct EpiSeed {
+  uint32_t lo, hi;
+};
+
 // Tensor maps of the TMA epilogue: bf16 NHWC output / saved forward output, one map per output phase (transposed
 // conv: phase (py, px) is the stride-2 sub-grid starting at (py, px)); box {32 channels, qw, qh, qn}, 64-byte swizzle.
 struct alignas(64) EpiTmaMaps {
@@ -61,7 +68,7 @@ template <class YLoad, class OStore>
 __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
                                                    size_t pix, int cb, bool valid, YLoad yload, OStore ostore,
                                                    float* s_colsum = nullptr, bool colsum_here = false,
-                                                   float* s_colsq = nullptr) {
+                                                   float* s_colsq = nullptr, EpiSeed sd = EpiSeed{0u, 0u}) {
   const size_t off = pix * p.Cout + cb;  // element offset of this thread's 32 outputs
   float v[32];
 #pragma unroll
@@ -96,7 +103,7 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
     const uint32_t t24 = static_cast<uint32_t>(p.drop_thresh8) << 24;
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
-      const uint32_t bits = b2g_dropout_bits(g0 + g, p.seed_lo, p.seed_hi);
+      const uint32_t bits = b2g_dropout_bits(g0 + g, sd.lo, sd.hi);
       v[g * 4 + 0] = (bits << 24) >= t24 ? v[g * 4 + 0] : 0.f;
       v[g * 4 + 1] = (bits << 16) >= t24 ? v[g * 4 + 1] : 0.f;
       v[g * 4 + 2] = (bits << 8) >= t24 ? v[g * 4 + 2] : 0.f;
@@ -203,7 +210,8 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
 
 // r: 32 accumulator columns [cb, cb+32) of output pixel `pix` (flat N*H*W index); `valid` = pixel inside the tensor.
 __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
-                                                    size_t pix, int cb, bool valid, float* s_colsum = nullptr) {
+                                                    size_t pix, int cb, bool valid, float* s_colsum = nullptr,
+                                                    EpiSeed sd = EpiSeed{0u, 0u}) {
   if (p.out_f32) {  // narrow fp32 output (3 real channels): tanh / tanh' epilogues of the generator's last layer
     if (valid && cb < p.cs) {
       float* of = reinterpret_cast<float*>(p.out) + pix * p.cs + cb;
@@ -228,7 +236,7 @@ __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const fl
       p, sbias, r, pix, cb, valid,
       [&](int g) { return __ldg(reinterpret_cast<const uint4*>(p.yprev + pix * p.Cout + cb) + g); },
       [&](int g, const uint4& o) { reinterpret_cast<uint4*>(p.out + pix * p.Cout + cb)[g] = o; }, s_colsum,
-      p.colsum != nullptr, p.colsumsq ? const_cast<float*>(sbias) : nullptr);
+      p.colsum != nullptr, p.colsumsq ? const_cast<float*>(sbias) : nullptr, sd);
 }
 
 // Block-wide helpers of the fused column sums: per-CTA partial sums live in a shared table (zeroed before the
@@ -302,7 +310,8 @@ __device__ __forceinline__ void epi_tma_begin(const EpiParams& p, const CUtensor
 // Whole warp: epilogue math of one chunk (lane = pixel) through the box, then the TMA store.
 __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensorMap* omap, EpiWarpStage& st,
                                               const float* sbias, const uint32_t (&r)[32], size_t pix, int cb, int lane,
-                                              int bx, int by, int bn, float* s_colsum = nullptr) {
+                                              int bx, int by, int bn, float* s_colsum = nullptr,
+                                              EpiSeed sd = EpiSeed{0u, 0u}) {
   uint8_t* row = st.buf + lane * 64;
   const uint32_t sw = (lane >> 1) & 3;  // 64-byte swizzle: 16-byte group g of row i lives at g ^ ((i >> 1) & 3)
   if (p.dact != B2G_ACT_NONE) {
@@ -312,7 +321,8 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
   conv_epilogue_math(
       p, sbias, r, pix, cb, true,
       [&](int g) { return *reinterpret_cast<const uint4*>(row + ((g ^ sw) << 4)); },
-      [&](int g, const uint4& o) { *reinterpret_cast<uint4*>(row + ((g ^ sw) << 4)) = o; });
+      [&](int g, const uint4& o) { *reinterpret_cast<uint4*>(row + ((g ^ sw) << 4)) = o; }, nullptr, false, nullptr,
+      sd);
   fence_proxy_async_smem();
   __syncwarp();
   if (elect_one_sync()) tma_store_4d(omap, st.buf, cb, bx, by, bn);
@@ -342,16 +352,16 @@ __device__ __forceinline__ void epi_tma_end() {
   __syncwarp();
 }
 
-// Epilogue warps work on a private copy of the parameters whose dropout seed has been read from device memory when
-// the call asked for it (b2g_conv_args.dropout_seed_dev).
-__device__ __forceinline__ EpiParams epi_resolve(const EpiParams& p) {
-  EpiParams e = p;
+// The dropout seed of this call: from the arguments, or read from device memory when the call asked for it
+// (b2g_conv_args.dropout_seed_dev: graph replay).
+__device__ __forceinline__ EpiSeed epi_resolve_seed(const EpiParams& p) {
+  EpiSeed sd{p.seed_lo, p.seed_hi};
   if (p.seed_dev) {
     const unsigned long long s = *p.seed_dev;
-    e.seed_lo = static_cast<uint32_t>(s & 0xFFFFFFFFull);
-    e.seed_hi = static_cast<uint32_t>(s >> 32);
+    sd.lo = static_cast<uint32_t>(s & 0xFFFFFFFFull);
+    sd.hi = static_cast<uint32_t>(s >> 32);
   }
-  return e;
+  return sd;
 }
 
 // Block-wide: shared bias table = bias[0..n) * pre_scale (see EpiParams::pre_scale); call before the block sync.

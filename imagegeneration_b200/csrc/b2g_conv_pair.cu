@@ -185,7 +185,8 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
     }
   } else {
     // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
-    const EpiParams e = epi_resolve(p.e);  // dropout seed possibly read from device memory
+    const EpiParams& e = p.e;                 // stays in the constant bank
+    const EpiSeed sd = epi_resolve_seed(p.e);  // dropout seed possibly read from device memory
     const int q = warp & 3;
     const int grp = (warp - 2) >> 2;
     const int row = q * 32 + lane;
@@ -222,8 +223,8 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         tmem_ld_wait();
-        if (use_tma) epi_tma_chunk(e, &p.em.omap[tc.phase], st, sbias, r, pix, col0 + c * 32, lane, bx, by, bn, s_colsum);
-        else conv_epilogue_chunk(e, sbias, r, pix, col0 + c * 32, valid, s_colsum);
+        if (use_tma) epi_tma_chunk(e, &p.em.omap[tc.phase], st, sbias, r, pix, col0 + c * 32, lane, bx, by, bn, s_colsum, sd);
+        else conv_epilogue_chunk(e, sbias, r, pix, col0 + c * 32, valid, s_colsum, sd);
       }
       tc_fence_before();
       __syncwarp();

@@ -325,7 +325,8 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     }
   } else {
     // ------------------------------------------------ epilogue (warp w owns TMEM lanes 32*(w%4)..+31)
-    const EpiParams e = epi_resolve(p.e);  // dropout seed possibly read from device memory
+    const EpiParams& e = p.e;                 // stays in the constant bank
+    const EpiSeed sd = epi_resolve_seed(p.e);  // dropout seed possibly read from device memory
     const int q = warp & 3;
     const int grp = (warp - 3) >> 2;
     const int row = q * 32 + lane;
@@ -360,8 +361,8 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * (n_acc * BLOCK_N) + acc * BLOCK_N + c * 32,
                       v);
         tmem_ld_wait();
-        if (use_tma) epi_tma_chunk(e, &p.em.omap[phase], st, sbias, v, pix, cb, lane, t.w0 + q * 32, gy, t.n, s_colsum);
-        else conv_epilogue_chunk(e, sbias, v, pix, cb, valid, s_colsum);
+        if (use_tma) epi_tma_chunk(e, &p.em.omap[phase], st, sbias, v, pix, cb, lane, t.w0 + q * 32, gy, t.n, s_colsum, sd);
+        else conv_epilogue_chunk(e, sbias, v, pix, cb, valid, s_colsum, sd);
       }
       tc_fence_before();
       __syncwarp();
