@@ -56,8 +56,8 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
   using Cfg = C3Cfg;
   constexpr int BLOCK_N = Cfg::kBlockN;
   constexpr int kChunks = BLOCK_N / 32;
-  __shared__ float sbias[64];
-  __shared__ float s_colsum[64];
+  __shared__ float sbias[512];     // bias table, or 8 copies of the [64] sums of squares (EpiParams::cs_copies)
+  __shared__ float s_colsum[512];  // 8 copies of the [64] column sums: one per pair of epilogue warps
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* bsm = smem + Cfg::kStages * Cfg::kABytes;
@@ -260,7 +260,6 @@ int launch_conv_c3(const b2g_conv_args* a, void* stream_) {
   if (!build_conv_plan(a->kind, a->N, a->Hin, a->Win, 64, a->Cout, 128, &kp.plan))
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_igemm(K3S1_C3): cannot tile N=%d H=%d W=%d", a->N, a->Hin, a->Win);
   fill_epi_params(a, &kp.e);
-  kp.e.cs_copies = 1;  // this kernel's column-sum tables hold one [64] copy
   {
     int rc = fill_epi_tma(a, kp.plan, true, &kp.e, &kp.em);
     if (rc) return rc;
