@@ -344,6 +344,17 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
         epi_tma_begin(p.e, &p.em.ymap[t.pg * P + acc % P], st, t.n_tile * BLOCK_N + (grp % kChunks) * 32,
                       t.w0 + q * 32, t.y0 + acc / P, t.n);
       }
+      // backward epilogues: the saved-output boxes of the warp's remaining items of this tile go to L2 now, while the
+      // MMAs of the tile still run — a warp has ONE box, so each item's load is issued only after the previous store
+      // has drained and its DRAM latency was the critical path of the epilogue (ncu source page)
+      if (use_tma && p.e.dact != B2G_ACT_NONE) {
+        for (int idx = grp + Cfg::kEpiGroups; idx < n_acc * kChunks; idx += Cfg::kEpiGroups) {
+          const int acc = idx / kChunks, c = idx % kChunks;
+          if (elect_one_sync())
+            tma_prefetch_4d(&p.em.ymap[t.pg * P + acc % P], t.n_tile * BLOCK_N + c * 32, t.w0 + q * 32, t.y0 + acc / P, t.n);
+        }
+        __syncwarp();
+      }
       mbar_wait_parked(&tfull[as], (it >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1

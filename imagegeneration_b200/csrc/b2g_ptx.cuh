@@ -135,6 +135,14 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* m, uin
       : "memory");
 }
 
+// TMA prefetch of one box into L2 (no shared memory, no barrier): hides the DRAM latency of a later tma_load_4d of
+// the same box.
+__device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap* m, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
+               ::"l"(m), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
 // TMA tiled store (shared -> global) as a bulk async-group of the issuing thread; elements outside the tensor are
 // clipped.  The same thread must wait (tma_store_wait_read) before the shared-memory box is written again or the
 // CTA exits.
