@@ -98,61 +98,69 @@ def _oracle_step_factory(batch):
     return step
 
 
-def cpu_baseline(target_seconds=20.0):
-    """Oracle train_step on the host cores: one step at batch 16 fp32 (BASELINE config[0]) unless a 1-image probe
-    says that would take much longer than `target_seconds`, in which case a smaller batch is used."""
+REF_BATCH = 16   # BASELINE configs[0]: the reference's own CPU-runnable case; never shrunk
+
+
+def _host_threads():
     import torch
-    cores = torch.get_num_threads()
-    probe = _oracle_step_factory(1)
-    t0 = time.perf_counter()
-    probe()
-    t1 = time.perf_counter() - t0
-    batch = 16
-    while batch > 1 and t1 * batch > 2.0 * target_seconds:
-        batch //= 2
-    step = _oracle_step_factory(batch)
-    t0 = time.perf_counter()
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm uses every host core it may run on
+    try:
+        torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+    except (AttributeError, OSError):
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+    return torch.get_num_threads()
+
+
+def _timed_oracle_steps(steps, warmup, budget_s):
+    """The oracle's train_step at batch 16 fp32 on the host cores.  The first step is always untimed (oneDNN primitive
+    creation, first-touch page faults); if `steps` would overrun `budget_s`, the STEP COUNT is reduced, never the
+    batch.  Returns (images/s, timed steps, seconds, threads, untimed steps)."""
+    cores = _host_threads()
+    step = _oracle_step_factory(REF_BATCH)
+    t_begin = time.perf_counter()
     step()
+    t1 = None
+    for _ in range(max(1, warmup - 1)):
+        t0 = time.perf_counter()
+        step()
+        t1 = time.perf_counter() - t0
+    untimed = 1 + max(1, warmup - 1)
+    left = budget_s - (time.perf_counter() - t_begin)
+    n = max(1, min(steps, int(left / t1)))
+    t0 = time.perf_counter()
+    for _ in range(n):
+        step()
     dt = time.perf_counter() - t0
-    return {"value": batch / dt, "unit": "images/s", "cores": cores, "kind": "port",
-            "sample": f"1 oracle train_step (PyTorch-CPU restatement of SNDCGAN.py:241-269, fp32, dropout 0.5) at "
-                      f"batch {batch}, {dt:.2f} s, {cores} threads; TensorFlow itself is not installable here"}
+    return REF_BATCH * n / dt, n, dt, cores, untimed
+
+
+def _cpu_sample_text(n, dt, cores, untimed):
+    return (f"{n} oracle train_step(s) (PyTorch-CPU restatement of SNDCGAN.py:241-269, fp32, dropout 0.5) at batch "
+            f"{REF_BATCH} (BASELINE configs[0]) after {untimed} untimed warm-up step(s), {dt:.2f} s, {cores} host threads; "
+            "TensorFlow itself is not installable here")
+
+
+def cpu_baseline(budget_s=25.0):
+    """`cpu_baseline` leg of our arm's line: the same function and the same fixed batch as `--impl reference`."""
+    value, n, dt, cores, untimed = _timed_oracle_steps(3, 2, budget_s)
+    return {"value": value, "unit": "images/s", "cores": cores, "kind": "port",
+            "sample": _cpu_sample_text(n, dt, cores, untimed), "batch_per_step": REF_BATCH, "steps": n}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
-    # torchrun exports OMP_NUM_THREADS=1 to its workers; the reference arm uses every host core it may run on
-    try:
-        torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
-    except (AttributeError, OSError):
-        torch.set_num_threads(max(1, os.cpu_count() or 1))
-    cores = torch.get_num_threads()
-    probe = _oracle_step_factory(1)
-    t0 = time.perf_counter()
-    probe()
-    t1 = time.perf_counter() - t0
-    total = args.steps + args.warmup
-    batch = int(os.environ.get("B2G_REF_MAX_BATCH", "16"))
-    while batch > 1 and t1 * batch * total > 150.0:
-        batch //= 2
-    step = _oracle_step_factory(batch)
-    for _ in range(args.warmup):
-        step()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    dt = time.perf_counter() - t0
-    value = batch * args.steps / dt
-    sample = (f"{args.steps} oracle train_steps at batch {batch} per step (bounded sample of the batch-64 workload), "
-              f"{cores} host threads")
+    value, n, dt, cores, untimed = _timed_oracle_steps(args.steps, args.warmup, float(os.environ.get("B2G_REF_BUDGET_S", "240")))
+    sample = _cpu_sample_text(n, dt, cores, untimed)
+    if n != args.steps:
+        sample += f" (asked for {args.steps} steps; the count, not the batch, was cut to stay inside the time budget)"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "steps": n, "warmup": untimed, "ms_per_step": dt / n * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "SNDCGAN one G+D train_step at 256x144, fp32, CPU (PyTorch restatement of the "
-                                   "reference; TensorFlow unavailable)", "batch_per_step": batch},
+                                   "reference; TensorFlow unavailable)", "batch_per_step": REF_BATCH,
+                       "steps_requested": args.steps},
             "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -166,7 +174,8 @@ def _hbm_kernel_rooflines(eng, peaks, peak_kind):
     """Achieved HBM GB/s of the memory-bound parameter kernels, each timed alone with CUDA events on torch's current
     stream (the stream they are launched on), L2 flushed between repetitions by a 512 MB fill.
       adam (G arena): 28 B per parameter (read w, g, m, v; write w, m, v)            SURVEY.md section 8(d)
-      spectral_norm_multi (all 8 D matrices, one power iteration): 4 B per weight (W read once)"""
+      spectral norm: the stand-alone power iteration (4 B per weight, W read once) on the 8 D matrices and on a
+      294 912 x 128 matrix, and the fused optimizer pass that carries it inside a training step"""
     import torch
     from imagegeneration_b200.sndcgan import SNDCGANEngine
     peak = float(peaks.get("hbm_gbs", 6650.0))
@@ -174,9 +183,12 @@ def _hbm_kernel_rooflines(eng, peaks, peak_kind):
     out = {}
 
     def timed(fn, reps=5):
+        # L2 is flushed by READING 512 MB: after a write flush the 126 MB of dirty lines drain into the first ~20 us
+        # of the timed kernel, which is most of a 30 us launch (measured in round 1 on the BatchNorm kernels)
         ts = []
+        flush.fill_(1.0)
         for _ in range(reps):
-            flush.fill_(1.0)
+            flush.sum()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             fn()
@@ -198,18 +210,92 @@ def _hbm_kernel_rooflines(eng, peaks, peak_kind):
                                    "frac": byt / sec / 1e9 / peak, "bytes_per_launch": byt, "us": sec * 1e6,
                                    "peak_kind": f"{peak_kind} copy bandwidth"}
     try:
+        import ctypes as C
+        from imagegeneration_b200 import lib as _L
+        lib_ = _L.load()
         sn = SNDCGANEngine(4, dropout=0.0, image_size=IMAGE_SIZE, seed=62, spectral_norm=True)
         D = sn.disc_model
+        n_w = float(sum(k * c for k, c in zip(D._sn_K, D._sn_C)))
+        # (a) stand-alone power iteration over the 8 discriminator matrices: only runs at init / set_weights / restore
         sec = timed(D.sn_power_iteration)
-        byt = 4.0 * sum(k * c for k, c in zip(D._sn_K, D._sn_C))
+        byt = 4.0 * n_w
         out["spectral_norm_multi"] = {"bound": "hbm", "achieved": byt / sec / 1e9, "peak": peak, "unit": "GB/s",
                                       "frac": byt / sec / 1e9 / peak, "bytes_per_launch": byt, "us": sec * 1e6,
-                                      "note": "8 matrices, 24.6 MB in one launch (3.8 us at the copy peak): launch-latency-bound at this size",
+                                      "note": "stand-alone iteration, 8 matrices = 24.6 MB (3.8 us at the copy peak): "
+                                              "latency-bound at this size and OFF the training step since round 2 — "
+                                              "training updates carry their power iteration inside b2g_adam_sn",
                                       "peak_kind": f"{peak_kind} copy bandwidth"}
+        # (b) what spectral norm costs inside a step now: the fused optimizer pass against plain Adam on the same arena
+        A = D.arena
+        sec_plain = timed(lambda: sn.d_optimizer.apply_arena(A, 0.0))
+        D.sn_power_iteration()
+
+        def fused():
+            sn.d_optimizer.apply_model(D, 0.0)
+        sec_fused = timed(fused)
+        out["adam_sn_discriminator_arena"] = {
+            "bound": "hbm", "achieved": 28.0 * A.numel / sec_fused / 1e9, "peak": peak, "unit": "GB/s",
+            "frac": 28.0 * A.numel / sec_fused / 1e9 / peak, "bytes_per_launch": 28.0 * A.numel,
+            "us": sec_fused * 1e6, "us_plain_adam": sec_plain * 1e6, "extra_us_for_spectral_norm": (sec_fused - sec_plain) * 1e6,
+            "extra_bytes": 4.0 * n_w + 8.0 * sum(D._sn_K),
+            "note": "b2g_sn_dot_multi (<G,W>: +4 B/weight for W; G is re-read by Adam) + b2g_adam_sn (Adam + gradient "
+                    "through W/sigma + next power iteration in one pass); two updates per step",
+            "peak_kind": f"{peak_kind} copy bandwidth"}
         del sn
+        # (c) SURVEY 7.3's large-matrix case: one power iteration on a 294 912 x 128 fp32 matrix (151 MB, the
+        # generator's Dense kernel shape), W read exactly once
+        K_, C_ = 294912, 128
+        Wl = torch.randn(K_, C_, device="cuda") * 0.02
+        ul = torch.nn.functional.normalize(torch.randn(C_, device="cuda"), dim=0)
+        vr, tr, sc = torch.zeros(K_, device="cuda"), torch.zeros(C_, device="cuda"), torch.zeros(8, device="cuda")
+        arr = lambda t: (C.c_void_p * 1)(t.data_ptr())
+        Ks, Cs = (C.c_int * 1)(K_), (C.c_int * 1)(C_)
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+        def big():
+            rc = lib_.b2g_spectral_norm_multi(1, arr(Wl), arr(ul), arr(vr), arr(tr), arr(sc), Ks, Cs, st)
+            if rc:
+                raise RuntimeError("b2g_spectral_norm_multi failed")
+        sec = timed(big)
+        byt = 4.0 * K_ * C_
+        out["spectral_norm_large_matrix"] = {"bound": "hbm", "achieved": byt / sec / 1e9, "peak": peak, "unit": "GB/s",
+                                             "frac": byt / sec / 1e9 / peak, "bytes_per_launch": byt, "us": sec * 1e6,
+                                             "shape": [K_, C_], "peak_kind": f"{peak_kind} copy bandwidth"}
     except Exception as e:  # the option is not on the reference path; never fail the bench line for it
         out["spectral_norm_multi"] = {"error": str(e)[:200]}
     return out
+
+
+def _parity_check(out, batch, world, args):
+    """The first warm-up step of THIS process against the committed oracle outputs for the same seeds
+    (tests/golden/bench_step0.json, made by tests/golden/make_bench_golden.py from oracle/sndcgan_oracle.py): the timed
+    configuration is parity-checked in the run that times it.  North-star tolerance: 2e-2 relative on the losses, 2e-2
+    of the logit scale on the logits.  With several ranks only the quantities computed before the first (all-reduced)
+    discriminator update are comparable with the single-process oracle: g_loss, d_loss_real, d_logits_real."""
+    path = os.path.join(ROOT, "tests", "golden", "bench_step0.json")
+    key = f"batch{batch}"
+    if (args.loss != "bce" or args.spectral_norm or args.dtype != "bf16" or not os.path.exists(path)):
+        return {"checked": False, "why": "no committed oracle values for this configuration"}
+    with open(path) as f:
+        gold = json.load(f)
+    if key not in gold:
+        return {"checked": False, "why": f"no committed oracle values for batch {batch}"}
+    gold = gold[key]
+    import torch
+    losses = [float(x) for x in out[:4]]
+    idx = (0, 1, 2, 3) if world == 1 else (0, 2)
+    rel = max(abs(losses[i] - gold["losses"][i]) / (abs(gold["losses"][i]) + 1e-12) for i in idx)
+    pairs = [(out[4], gold["d_logits_real"])] + ([(out[5], gold["d_logits_fake"])] if world == 1 else [])
+    lerr = 0.0
+    for a, b in pairs:
+        b = torch.tensor(b, dtype=torch.float32)
+        lerr = max(lerr, float((a.float().cpu().flatten() - b).abs().max()) / (1.0 + float(b.abs().max())))
+    res = {"checked": True, "against": "tests/golden/bench_step0.json (CPU oracle, fp32)", "step": 0,
+           "losses": losses, "oracle_losses": gold["losses"], "max_rel_loss_err": rel, "max_logit_err": lerr,
+           "tolerance": 2e-2, "ok": bool(rel < 2e-2 and lerr < 2e-2)}
+    if not res["ok"] and not args.no_parity_check:
+        raise SystemExit(f"bench.py: the timed configuration FAILED its parity check against the oracle: {res}")
+    return res
 
 
 def _teardown(eng, dist):
@@ -259,8 +345,15 @@ def run_b200(args):
             os.dup2(saved_stdout, 1)
             os.close(saved_stdout)
     B = args.batch
+    scaling = "weak"
+    if args.global_batch:
+        # BASELINE configs[2]: a FIXED global batch (512) split over the ranks = strong scaling
+        if args.global_batch % world:
+            raise SystemExit(f"--global-batch {args.global_batch} is not divisible by {world} ranks")
+        B = args.global_batch // world
+        scaling = "strong"
     eng = SNDCGANEngine(B, dropout=0.5, image_size=IMAGE_SIZE, seed=62, spectral_norm=args.spectral_norm,
-                        loss=args.loss, process_group=pg)
+                        loss=args.loss, process_group=pg, **({"dtype": args.dtype} if args.dtype != "bf16" else {}))
     g = torch.Generator().manual_seed(1234 + rank)
     real_host = [(torch.rand((B, *IMAGE_SIZE), generator=g) * 2 - 1).pin_memory() for _ in range(2)]
     z_host = [(torch.rand((B, 128), generator=g) * 2 - 1).pin_memory() for _ in range(2)]
@@ -280,8 +373,11 @@ def run_b200(args):
         return float(t.item())
 
     # ---- device-resident timing: `value`
+    parity = None
     for i in range(args.warmup):
-        eng.train_step(real_dev[i & 1], z_dev[i & 1])
+        o = eng.train_step(real_dev[i & 1], z_dev[i & 1])
+        if i == 0 and rank == 0:
+            parity = _parity_check(o, B, world, args)
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     l0 = lib.launch_count
@@ -363,8 +459,8 @@ def run_b200(args):
         return
     line = {
         "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling,
+        "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": "SNDCGAN one G+D train_step at 256x144 (1 G + 2 D Adam updates, 3 D forwards), "
                                "bf16 activations / fp32 accumulate + master weights, dropout 0.5",
                    "batch_per_gpu": B, "global_batch": B * world, "parallelism": f"dp{world}",
@@ -381,6 +477,7 @@ def run_b200(args):
                        "frac_of_peak_whole_step": FLOP_PER_IMAGE * B / (ms_per_step * 1e-3) / 1e12 / peak_tf,
                        "tensor_core_kernels_ms": tc_ms, "other_ms": ms_per_step - tc_ms},
         "losses_last_step": losses,
+        "parity_check": parity,
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline()
@@ -399,6 +496,12 @@ def main():
     ap.add_argument("--loss", default="bce", choices=["bce", "hinge"])
     ap.add_argument("--spectral-norm", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true",
+                    help="report a failed step-0 parity check in the JSON line instead of aborting")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="fixed GLOBAL batch split over the ranks (strong scaling; BASELINE configs[2] uses 512)")
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "tf32"],
+                    help="bf16 (BASELINE configs[1]) or the fp32-storage / kind::tf32 parity path")
     ap.add_argument("--workload", default="sndcgan", choices=["sndcgan", "wgan"],
                     help="sndcgan (default): the BASELINE metric; wgan: BASELINE configs[3] on one GPU (SURVEY 8(f) N1), "
                          "a step = one WGAN.train iteration (5 critic iterations + 1 generator update)")

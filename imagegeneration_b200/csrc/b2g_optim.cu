@@ -364,6 +364,349 @@ __global__ void __launch_bounds__(256) sn_grad_apply_kernel(float* __restrict__ 
 }
 __global__ void zero_scalar_kernel(float* p) { *p = 0.f; }
 
+// ---------------------------------------------------------------------------------------------------------
+// Adam FUSED with spectral normalisation: ONE pass over the discriminator arena per apply_gradients replaces the
+// stand-alone power iteration (24.6 MB read again, 3 x per step), the 8 x 3 gradient-finalisation launches and the
+// plain Adam launch.  For every spectrally-normalised matrix W_l inside the arena a warp owns whole rows and
+//   (1) turns the raw weight gradient G = dL/d(W/sigma) into dL/dW = G/sigma - (<G,W>/sigma^2) v u^T   (u, v_raw, sigma
+//       of the power iteration the forward pass used; <G,W> comes from sn_dot_multi_kernel),
+//   (2) applies Keras Adam to the row (registers),
+//   (3) runs the NEXT power iteration on the updated row while it is still in registers:
+//       v_raw[k] = w'_k . u,  t_raw += w'_k * v_raw[k]   (Miyato et al. Alg. 1: one iteration per weight update),
+// and the last block of a layer (ticket) finalises sigma and u exactly like sn_power_kernel.  Biases and alignment
+// padding between the matrices are updated element-wise by one trailing block.  Extra HBM traffic over plain Adam:
+// the K floats of v_raw per layer.
+// ---------------------------------------------------------------------------------------------------------
+struct AdamSnLayer {
+  long off;  // element offset of W_l in the arena
+  int K, C;
+  float *u, *v_raw, *t_raw, *scal, *dot;
+};
+struct AdamSnRest {
+  long off;
+  int n;
+};
+struct AdamSnParams {
+  AdamSnLayer layer[kSnMaxLayers];
+  AdamSnRest rest[kSnMaxLayers + 1];
+  int blk_start[kSnMaxLayers + 1];
+  int n_layers, n_rest;
+  float *w, *m, *v;
+  const float* g;
+  float lr_t_val;
+  const float* lr_t_dev;
+  float b1, b2, eps, gscale;
+};
+
+__device__ __forceinline__ SnLayer L_as_sn(const AdamSnLayer& L) {
+  return SnLayer{nullptr, L.u, L.v_raw, L.t_raw, L.scal, L.K, L.C};
+}
+
+struct AdamCoef {
+  float lr_t, c1, c2, eps;
+};
+__device__ __forceinline__ void adam_elt(const AdamCoef& a, float gg, float& w, float& m, float& v) {
+  m += (gg - m) * a.c1;
+  v += (gg * gg - v) * a.c2;
+  w -= a.lr_t * m / (sqrtf(v) + a.eps);
+}
+
+template <int NV, int R>
+__device__ __forceinline__ void adam_sn_rows_vec(const AdamSnParams& p, const AdamSnLayer& L, const AdamCoef& a, int lb,
+                                                 int nb, float* slab, float& vsq) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kWarps = kSnThreads / 32;
+  float4* W4 = reinterpret_cast<float4*>(p.w + L.off);
+  float4* M4 = reinterpret_cast<float4*>(p.m + L.off);
+  float4* V4 = reinterpret_cast<float4*>(p.v + L.off);
+  const float4* G4 = reinterpret_cast<const float4*>(p.g + L.off);
+  float4 u4[NV], tacc[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    u4[j] = __ldcg(reinterpret_cast<const float4*>(L.u) + j * 32 + lane);
+    tacc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const float inv = __ldcg(L.scal + 2), nv = __ldcg(L.scal + 3);
+  const float coef = nv > 0.f ? __ldcg(L.dot) * inv * inv / nv : 0.f;
+  const float gs = p.gscale;
+  const int K = L.K;
+  for (int k0 = (lb * kWarps + warp) * R; k0 < K; k0 += nb * kWarps * R) {
+    float4 w[R][NV], g[R][NV], m[R][NV], v[R][NV];
+    float vold[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const bool ok = k0 + r < K;
+      vold[r] = ok ? __ldcg(L.v_raw + k0 + r) : 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        const size_t i = (size_t)(k0 + r) * (NV * 32) + j * 32 + lane;
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        w[r][j] = ok ? W4[i] : z;
+        g[r][j] = ok ? __ldcs(G4 + i) : z;
+        m[r][j] = ok ? M4[i] : z;
+        v[r][j] = ok ? V4[i] : z;
+      }
+    }
+    float dot[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float cv = coef * vold[r];
+      float d = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        float* wp = &w[r][j].x; float* mp = &m[r][j].x; float* vp = &v[r][j].x;
+        const float* gp = &g[r][j].x; const float* up = &u4[j].x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          adam_elt(a, gs * (gp[e] * inv - cv * up[e]), wp[e], mp[e], vp[e]);
+          d += wp[e] * up[e];
+        }
+      }
+      dot[r] = d;
+      if (k0 + r < K) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+          const size_t i = (size_t)(k0 + r) * (NV * 32) + j * 32 + lane;
+          W4[i] = w[r][j]; M4[i] = m[r][j]; V4[i] = v[r][j];
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int r = 0; r < R; ++r) dot[r] += __shfl_xor_sync(0xffffffffu, dot[r], o);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (lane == 0 && k0 + r < K) {
+        L.v_raw[k0 + r] = dot[r];
+        vsq += dot[r] * dot[r];
+      }
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        tacc[j].x += w[r][j].x * dot[r];
+        tacc[j].y += w[r][j].y * dot[r];
+        tacc[j].z += w[r][j].z * dot[r];
+        tacc[j].w += w[r][j].w * dot[r];
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NV; ++j) reinterpret_cast<float4*>(slab + warp * 512)[j * 32 + lane] = tacc[j];
+}
+
+// any C that is a multiple of 32 (<= 512): one row per warp iteration, scalar accesses (the 27 x 64 layer)
+__device__ __forceinline__ void adam_sn_rows_scalar(const AdamSnParams& p, const AdamSnLayer& L, const AdamCoef& a,
+                                                    int lb, int nb, float* slab, float& vsq) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kWarps = kSnThreads / 32;
+  const int K = L.K, C = L.C, per = C / 32;
+  const float inv = __ldcg(L.scal + 2), nv = __ldcg(L.scal + 3);
+  const float coef = nv > 0.f ? __ldcg(L.dot) * inv * inv / nv : 0.f;
+  float ureg[16], tacc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    ureg[i] = (i < per) ? __ldcg(L.u + lane + 32 * i) : 0.f;
+    tacc[i] = 0.f;
+  }
+  for (int k = lb * kWarps + warp; k < K; k += nb * kWarps) {
+    const float cv = coef * __ldcg(L.v_raw + k);
+    float wreg[16];
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      wreg[i] = 0.f;
+      if (i < per) {
+        const size_t idx = L.off + (size_t)k * C + lane + 32 * i;
+        float w = p.w[idx], m = p.m[idx], v = p.v[idx];
+        adam_elt(a, p.gscale * (p.g[idx] * inv - cv * ureg[i]), w, m, v);
+        p.w[idx] = w; p.m[idx] = m; p.v[idx] = v;
+        wreg[i] = w;
+        dot += w * ureg[i];
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if (lane == 0) {
+      L.v_raw[k] = dot;
+      vsq += dot * dot;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tacc[i] += wreg[i] * dot;
+  }
+#pragma unroll
+  for (int i = 0; i < 16; ++i)
+    if (i < per) slab[warp * 512 + lane + 32 * i] = tacc[i];
+}
+
+// C == 1 (Dense head, K x 1): a thread owns rows (float4 = 4 rows when K % 4 == 0); v_raw = w' u0, t = sum w' v_raw
+__device__ __forceinline__ void adam_sn_rows_c1(const AdamSnParams& p, const AdamSnLayer& L, const AdamCoef& a, int lb,
+                                                int nb, float* slab, float& vsq) {
+  const float u0 = __ldcg(L.u);
+  const float inv = __ldcg(L.scal + 2), nv = __ldcg(L.scal + 3);
+  const float coef = nv > 0.f ? __ldcg(L.dot) * inv * inv / nv : 0.f;
+  const float cu = coef * u0, gs = p.gscale;
+  const int K = L.K;
+  float t = 0.f;
+  if ((K & 3) == 0) {
+    float4* W4 = reinterpret_cast<float4*>(p.w + L.off);
+    float4* M4 = reinterpret_cast<float4*>(p.m + L.off);
+    float4* V4 = reinterpret_cast<float4*>(p.v + L.off);
+    const float4* G4 = reinterpret_cast<const float4*>(p.g + L.off);
+    float4* R4 = reinterpret_cast<float4*>(L.v_raw);
+    const int n4 = K / 4, stride = nb * kSnThreads;
+    for (int k = lb * kSnThreads + threadIdx.x; k < n4; k += 2 * stride) {
+      float4 w[2], g[2], m[2], v[2], vo[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int i = k + q * stride;
+        const bool ok = i < n4;
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        w[q] = ok ? W4[i] : z; g[q] = ok ? __ldcs(G4 + i) : z; m[q] = ok ? M4[i] : z; v[q] = ok ? V4[i] : z;
+        vo[q] = ok ? __ldcg(R4 + i) : z;
+      }
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int i = k + q * stride;
+        float* wp = &w[q].x; float* mp = &m[q].x; float* vp = &v[q].x;
+        const float* gp = &g[q].x; const float* op = &vo[q].x;
+        float4 d4;
+        float* dp = &d4.x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          adam_elt(a, gs * (gp[e] * inv - cu * op[e]), wp[e], mp[e], vp[e]);
+          dp[e] = wp[e] * u0;
+        }
+        if (i < n4) {
+          W4[i] = w[q]; M4[i] = m[q]; V4[i] = v[q]; R4[i] = d4;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            vsq += dp[e] * dp[e];
+            t += wp[e] * dp[e];
+          }
+        }
+      }
+    }
+  } else {
+    for (int k = lb * kSnThreads + threadIdx.x; k < K; k += nb * kSnThreads) {
+      const size_t idx = L.off + k;
+      float w = p.w[idx], m = p.m[idx], v = p.v[idx];
+      adam_elt(a, gs * (p.g[idx] * inv - cu * L.v_raw[k]), w, m, v);
+      p.w[idx] = w; p.m[idx] = m; p.v[idx] = v;
+      const float d = w * u0;
+      L.v_raw[k] = d;
+      vsq += d * d;
+      t += w * d;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if ((threadIdx.x & 31) == 0) slab[(threadIdx.x >> 5) * 512] = t;
+}
+
+__global__ void __launch_bounds__(kSnThreads, 2) adam_sn_kernel(const __grid_constant__ AdamSnParams p) {
+  AdamCoef a;
+  a.lr_t = p.lr_t_dev ? *p.lr_t_dev : p.lr_t_val;
+  a.c1 = 1.f - p.b1; a.c2 = 1.f - p.b2; a.eps = p.eps;
+  if ((int)blockIdx.x >= p.blk_start[p.n_layers]) {  // trailing block: biases + padding, plain Adam
+    for (int s = 0; s < p.n_rest; ++s) {
+      const long off = p.rest[s].off;
+      for (int i = threadIdx.x; i < p.rest[s].n; i += kSnThreads) {
+        float w = p.w[off + i], m = p.m[off + i], v = p.v[off + i];
+        adam_elt(a, p.g[off + i] * p.gscale, w, m, v);
+        p.w[off + i] = w; p.m[off + i] = m; p.v[off + i] = v;
+      }
+    }
+    return;
+  }
+  int li = 0;
+  while (li + 1 < p.n_layers && (int)blockIdx.x >= p.blk_start[li + 1]) ++li;
+  const AdamSnLayer& L = p.layer[li];
+  const int lb = blockIdx.x - p.blk_start[li], nb = p.blk_start[li + 1] - p.blk_start[li];
+  const int C = L.C;
+  constexpr int kWarps = kSnThreads / 32;
+  __shared__ __align__(16) float slab[kWarps * 512];
+  __shared__ float red[kWarps];
+  __shared__ float sig_sh;
+  __shared__ int last_sh;
+  for (int i = threadIdx.x; i < kWarps * 512; i += kSnThreads) slab[i] = 0.f;
+  __syncthreads();
+  float vsq = 0.f;
+  if (C == 512) adam_sn_rows_vec<4, 1>(p, L, a, lb, nb, slab, vsq);
+  else if (C == 256) adam_sn_rows_vec<2, 2>(p, L, a, lb, nb, slab, vsq);
+  else if (C == 128) adam_sn_rows_vec<1, 4>(p, L, a, lb, nb, slab, vsq);
+  else if (C >= 32) adam_sn_rows_scalar(p, L, a, lb, nb, slab, vsq);
+  else adam_sn_rows_c1(p, L, a, lb, nb, slab, vsq);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) vsq += __shfl_xor_sync(0xffffffffu, vsq, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = vsq;
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += kSnThreads) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) t += slab[w * 512 + i];
+    atomicAdd(L.t_raw + i, t);
+  }
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < kWarps; ++w) t += red[w];
+    atomicAdd(L.scal, t);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(L.scal + 4), 1u);
+    last_sh = (ticket == (unsigned)(nb - 1));
+  }
+  __syncthreads();
+  if (!last_sh) return;
+  __threadfence();
+  sn_finalize_layer(L_as_sn(L), red, &sig_sh);
+  if (threadIdx.x == 0) *L.dot = 0.f;  // consumed: the next sn_dot_multi accumulates from zero
+}
+
+// dot[l] += <G_l, W_l> for every spectrally-normalised matrix, one launch (blocks balanced by bytes)
+struct SnDotParams {
+  const float* W[kSnMaxLayers];
+  const float* G[kSnMaxLayers];
+  float* dot[kSnMaxLayers];
+  long n[kSnMaxLayers];
+  int blk_start[kSnMaxLayers + 1];
+  int n_layers;
+};
+__global__ void __launch_bounds__(256) sn_dot_multi_kernel(const __grid_constant__ SnDotParams p) {
+  int li = 0;
+  while (li + 1 < p.n_layers && (int)blockIdx.x >= p.blk_start[li + 1]) ++li;
+  const int lb = blockIdx.x - p.blk_start[li], nb = p.blk_start[li + 1] - p.blk_start[li];
+  const float* __restrict__ W = p.W[li];
+  const float* __restrict__ G = p.G[li];
+  const long n = p.n[li];
+  float acc = 0.f;
+  if ((n & 3) == 0) {
+    const float4* W4 = reinterpret_cast<const float4*>(W);
+    const float4* G4 = reinterpret_cast<const float4*>(G);
+    const long n4 = n / 4, stride = (long)nb * 256;
+    for (long i = lb * 256L + threadIdx.x; i < n4; i += 2 * stride) {
+      const float4 a0 = __ldg(W4 + i), b0 = __ldg(G4 + i);
+      const bool ok = i + stride < n4;
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 a1 = ok ? __ldg(W4 + i + stride) : z, b1 = ok ? __ldg(G4 + i + stride) : z;
+      acc += a0.x * b0.x + a0.y * b0.y + a0.z * b0.z + a0.w * b0.w + a1.x * b1.x + a1.y * b1.y + a1.z * b1.z + a1.w * b1.w;
+    }
+  } else {
+    for (long i = lb * 256L + threadIdx.x; i < n; i += (long)nb * 256) acc += W[i] * G[i];
+  }
+  __shared__ float red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    atomicAdd(p.dot[li], t);
+  }
+}
+
 }  // namespace b2g
 
 using namespace b2g;
@@ -493,6 +836,83 @@ extern "C" int b2g_sn_grad_finalize(const float* W, float* G, const float* u, co
   sn_grad_dot_kernel<<<(int)blocks, 256, 0, stream>>>(W, G, n, dot_scratch);
   B2G_LAUNCH_CHECK();
   sn_grad_apply_kernel<<<(int)blocks, 256, 0, stream>>>(G, u, v_raw, scal, dot_scratch, K, C);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+// ---- Adam fused with spectral normalisation (see adam_sn_kernel) ----------------------------------------------------
+extern "C" int b2g_sn_dot_multi(const float* w, const float* g, int n_layers, const long* off, const int* K,
+                                const int* C, float* dots, b2g_stream_t stream_) {
+  if (!w || !g || !off || !K || !C || !dots) return fail(B2G_E_INVALID_ARG, "b2g_sn_dot_multi: null pointer");
+  if (n_layers < 1 || n_layers > kSnMaxLayers) return fail(B2G_E_INVALID_ARG, "b2g_sn_dot_multi: 1..8 layers");
+  SnDotParams p;
+  memset(&p, 0, sizeof(p));
+  double total = 0.0;
+  for (int i = 0; i < n_layers; ++i) total += (double)K[i] * C[i];
+  const int budget = num_sms() * 4;
+  int start = 0;
+  for (int i = 0; i < n_layers; ++i) {
+    if (off[i] % 4) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_sn_dot_multi: matrix offsets must be multiples of 4");
+    p.W[i] = w + off[i];
+    p.G[i] = g + off[i];
+    p.dot[i] = dots + i;
+    p.n[i] = (long)K[i] * C[i];
+    p.blk_start[i] = start;
+    int nb = (int)((double)p.n[i] / total * budget + 0.5);
+    const long max_nb = (p.n[i] + 2047) / 2048;  // at least two float4 per thread
+    if (nb > max_nb) nb = (int)max_nb;
+    if (nb < 1) nb = 1;
+    start += nb;
+  }
+  p.blk_start[n_layers] = start;
+  p.n_layers = n_layers;
+  sn_dot_multi_kernel<<<start, 256, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
+extern "C" int b2g_adam_sn(float* w, const float* g, float* m, float* v, long n, int n_layers, const long* off,
+                           const int* K, const int* C, float* const* u, float* const* v_raw, float* const* t_raw,
+                           float* const* scal, float* dots, float lr_t, const float* lr_t_dev, float beta1, float beta2,
+                           float eps, float gscale, b2g_stream_t stream_) {
+  if (!w || !g || !m || !v || !off || !K || !C || !u || !v_raw || !t_raw || !scal || !dots)
+    return fail(B2G_E_INVALID_ARG, "b2g_adam_sn: null pointer");
+  if (n_layers < 1 || n_layers > kSnMaxLayers) return fail(B2G_E_INVALID_ARG, "b2g_adam_sn: 1..8 layers");
+  AdamSnParams p;
+  memset(&p, 0, sizeof(p));
+  p.w = w; p.g = g; p.m = m; p.v = v;
+  p.lr_t_val = lr_t; p.lr_t_dev = lr_t_dev; p.b1 = beta1; p.b2 = beta2; p.eps = eps; p.gscale = gscale;
+  double total = 0.0;
+  long pos = 0;
+  int n_rest = 0;
+  for (int i = 0; i < n_layers; ++i) {
+    const long len = (long)K[i] * C[i];
+    if (off[i] % 4 || off[i] < pos || off[i] + len > n)
+      return fail(B2G_E_INVALID_ARG, "b2g_adam_sn: matrices must be 4-aligned, ascending and inside the arena");
+    if (!(C[i] == 1 || (C[i] % 32 == 0 && C[i] <= 512)))
+      return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_adam_sn: C=%d unsupported", C[i]);
+    if (!u[i] || !v_raw[i] || !t_raw[i] || !scal[i]) return fail(B2G_E_INVALID_ARG, "b2g_adam_sn: null layer pointer");
+    if (off[i] > pos) p.rest[n_rest++] = AdamSnRest{pos, (int)(off[i] - pos)};
+    pos = off[i] + len;
+    p.layer[i] = AdamSnLayer{off[i], K[i], C[i], u[i], v_raw[i], t_raw[i], scal[i], dots + i};
+    total += (double)len * (C[i] == 1 ? 4.0 : 1.0);
+  }
+  if (pos < n) p.rest[n_rest++] = AdamSnRest{pos, (int)(n - pos)};
+  p.n_rest = n_rest;
+  p.n_layers = n_layers;
+  const int budget = num_sms() * 2;
+  int start = 0;
+  for (int i = 0; i < n_layers; ++i) {
+    p.blk_start[i] = start;
+    const double wgt = (double)K[i] * C[i] * (C[i] == 1 ? 4.0 : 1.0);
+    int nb = (int)(wgt / total * budget + 0.5);
+    const long units = C[i] == 1 ? ((long)K[i] + 1023) / 1024 : ((long)K[i] * C[i] + 4095) / 4096;  // work per block
+    if (nb > units) nb = (int)units;
+    if (nb < 1) nb = 1;
+    start += nb;
+  }
+  p.blk_start[n_layers] = start;
+  adam_sn_kernel<<<start + 1, kSnThreads, 0, static_cast<cudaStream_t>(stream_)>>>(p);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }

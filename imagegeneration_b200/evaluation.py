@@ -53,11 +53,11 @@ def calculate_fid(disc_model: Discriminator, images_fake: torch.Tensor, images_r
                              discriminator_features(disc_model, images_real))
 
 
-def evaluate_fid(disc_model: Discriminator, gen_model, generator_weights: dict, img_real_used, random_z_used):
-    """The evaluation loop of sndcgan/generator_evaluation.py:156-175 without its .h5 / pickle bookkeeping: for every
-    saved generator (epoch -> list of weights in trainable_variables order, e.g. from the trainer's checkpoints) and
-    every real batch i, images_fake = create_samples(gen_model, random_z_used[i], B) (range [0, 1], as the reference
-    feeds them) and fid = calculate_fid(disc_model, images_fake, images_real).  Returns (epochs, [fids per epoch])."""
+def evaluate_fid_models(disc_model: Discriminator, gen_model, generator_weights: dict, img_real_used, random_z_used):
+    """The inner loop of sndcgan/generator_evaluation.py:156-175 on in-memory models: for every generator (epoch -> list of
+    weights in trainable_variables order) and every real batch i, images_fake = create_samples(gen_model,
+    random_z_used[i], B) (range [0, 1], as the reference feeds them) and fid = calculate_fid(disc_model, images_fake,
+    images_real).  Returns (epochs, [fids per epoch])."""
     from .sndcgan import create_samples
     epochs, epoch_fids = [], []
     for epoch in sorted(generator_weights):
@@ -69,3 +69,85 @@ def evaluate_fid(disc_model: Discriminator, gen_model, generator_weights: dict, 
         epochs.append(epoch)
         epoch_fids.append(fids)
     return epochs, epoch_fids
+
+
+MAX_BATCHES = 50          # generator_evaluation.py:27 (max_batches)
+
+
+def _saved_epochs(model_dir, prefix):
+    import glob
+    import os
+    files = glob.glob(os.path.join(model_dir, prefix + "*.pt"))
+    return sorted(int(os.path.basename(f)[len(prefix):-3]) for f in files)
+
+
+def init_fid_evaluation(dir_path, dataset, batch_size, output, step_size, start_epoch, disc_epoch,
+                        image_size=(144, 256, 3), z_size=128):
+    """generator_evaluation.py:58-102: which saved generators to score, and the fixed real batches / latent batches."""
+    import os
+    import pickle
+    from .trainer import get_dataset
+    epochs_used = [e for e in _saved_epochs(os.path.join(dir_path, "models", "generator"), "gen_model-")
+                   if e >= start_epoch][::step_size]
+    train_ds = get_dataset(dataset, batch_size, image_size)
+    batches_used = min(MAX_BATCHES, len(train_ds))
+    img_real_used, random_z_used = [], []
+    for i, (images_real, _) in enumerate(train_ds):
+        img_real_used.append(images_real.cpu())
+        random_z_used.append(torch.rand((images_real.shape[0], z_size)) * 2.0 - 1.0)
+        if i == batches_used - 1:
+            break
+    init = {"epochs_used": epochs_used, "img_real_used": img_real_used, "random_z_used": random_z_used,
+            "batches_used": batches_used, "disc_epoch": disc_epoch}
+    with open(os.path.join(output, "fid_tmp_init.pickle"), "wb") as f:
+        pickle.dump(init, f)
+    return init
+
+
+def evaluate_fid(dir_path, dataset, batch_size, output, step_size, start_epoch, disc_epoch, continue_,
+                 image_size=(144, 256, 3), z_size=128):
+    """sndcgan/generator_evaluation.py:107-199, same signature: scores every saved generator
+    `<dir_path>/models/generator/gen_model-<epoch>.pt` (written by SNDCGAN.train at each checkpoint) with the FID-like
+    distance on the features of `<dir_path>/models/discriminator/disc_model-<disc_epoch>.pt`, resumable through the same
+    pickles (fid_tmp_init / fid_tmp_results / fid_results under <output>/evaluation).  The matplotlib box / line plots
+    (:202-245) are not drawn (no matplotlib, no display).  Returns (epochs_used, epoch_fids)."""
+    import os
+    import pickle
+    import shutil
+    from .sndcgan import create_samples
+    from .trainer import load_model
+    output = os.path.join(output, "evaluation")
+    if not continue_ and os.path.exists(output):
+        shutil.rmtree(output)
+    os.makedirs(output, exist_ok=True)
+    if not continue_:
+        init = init_fid_evaluation(dir_path, dataset, batch_size, output, step_size, start_epoch, disc_epoch,
+                                   image_size, z_size)
+    else:
+        with open(os.path.join(output, "fid_tmp_init.pickle"), "rb") as f:
+            init = pickle.load(f)
+    epochs_used, disc_epoch = init["epochs_used"], init["disc_epoch"]
+    disc_model = load_model(os.path.join(dir_path, "models", "discriminator", f"disc_model-{disc_epoch}.pt"))
+    dev = disc_model.device
+    tmp_results = os.path.join(output, "fid_tmp_results.pickle")
+    epochs_finished, epoch_fids = [], []
+    if continue_ and os.path.exists(tmp_results):
+        with open(tmp_results, "rb") as f:
+            d = pickle.load(f)
+        epochs_finished, epoch_fids = d["epochs_finished"], d["epoch_fids"]
+    for epoch in [e for e in epochs_used if e not in epochs_finished]:
+        print("\n## Start FID calculation of epoch", epoch)
+        gen_model = load_model(os.path.join(dir_path, "models", "generator", f"gen_model-{epoch}.pt"))
+        fids = []
+        for i, images_real in enumerate(init["img_real_used"]):
+            print(f"\r### Calculate FID of Batch {i + 1}/{init['batches_used']}", end="", flush=True)
+            images_fake = create_samples(gen_model, init["random_z_used"][i].to(dev), images_real.shape[0])
+            fids.append(calculate_fid(disc_model, images_fake, images_real.to(dev)))
+        epochs_finished.append(epoch)
+        epoch_fids.append(fids)
+        with open(tmp_results, "wb") as f:
+            pickle.dump({"epochs_finished": epochs_finished, "epoch_fids": epoch_fids}, f)
+    print("\n\n## Calculation finished.")
+    with open(os.path.join(output, "fid_results.pickle"), "wb") as f:
+        pickle.dump({"epochs": epochs_used, "fids": epoch_fids}, f)
+    return epochs_used, epoch_fids

@@ -142,6 +142,18 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_spectral_norm_multi": [_I, _P, _P, _P, _P, _P, _P, _P, _P],
     # W, G, u, v_raw, scal, dot_scratch, K, C, stream
     "b2g_sn_grad_finalize": [_P, _P, _P, _P, _P, _P, _I, _I, _P],
+    # w, g, n_layers, off*, K*, C*, dots, stream
+    "b2g_sn_dot_multi": [_P, _P, _I, _P, _P, _P, _P, _P],
+    # w, g, m, v, n, n_layers, off*, K*, C*, u**, v_raw**, t_raw**, scal**, dots, lr_t, lr_t_dev, b1, b2, eps, gscale, stream
+    "b2g_adam_sn": [_P, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _F, _P, _F, _F, _F, _F, _P],
+    # g, y, out, n, f32, kind, alpha, scale, zero, stream
+    "b2g_dact": [_P, _P, _P, _L, _I, _I, _F, _F, _F, _P],
+    # logits, labels, B, loss_out, dlogit, stream
+    "b2g_bce_logits": [_P, _P, _I, _P, _P, _P],
+    # images_u8, idx, out, B, per_image, stream
+    "b2g_gather_u8_to_f32": [_P, _P, _P, _I, _L, _P],
+    # x, out, P, C, stream
+    "b2g_colsum_f32": [_P, _P, _L, _I, _P],
     # z, W, gamma, beta, inv_std, alpha, out, B, F, stream
     "b2g_dense_g_fwd_leaky": [_P, _P, _P, _P, _F, _F, _P, _I, _I, _P],
     # x, sums, P, C, stream

@@ -39,6 +39,14 @@ def _splitmix64(x: int) -> int:
     return z ^ (z >> 31)
 
 
+def step_dropout_seeds(seed: int, rank: int, step: int, pass_idx: int) -> list[int]:
+    """The 7 per-layer dropout seeds the engine uses for discriminator pass `pass_idx` (0: generator step, 1: real,
+    2: stale fake) of training step `step` — a pure function of (engine seed, rank, step), restated on the device by
+    b2g_step_prologue, so tests and bench.py can regenerate the masks (oracle/dropout_hash.py) without a GPU."""
+    base = (seed * 0x1000003 + rank * 0x10001 + 1) & _MASK64
+    return [_splitmix64(base ^ ((step * 3 + pass_idx) * 8 + layer)) for layer in range(7)]
+
+
 def rate_to_thresh8(rate: float) -> int:
     return max(0, min(255, int(round(rate * 256.0))))
 
@@ -119,10 +127,35 @@ class Adam:
                   "b2g_adam_dev")
             return
         self.iterations += 1
-        t = self.iterations
-        lr_t = self.learning_rate * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
-        check(_lib.load().b2g_adam(_p(arena.w), _p(arena.g), _p(arena.m), _p(arena.v), arena.numel, lr_t,
+        check(_lib.load().b2g_adam(_p(arena.w), _p(arena.g), _p(arena.m), _p(arena.v), arena.numel, self._lr_t(),
                                    self.beta_1, self.beta_2, self.epsilon, gscale, _stream()), "b2g_adam")
+
+    def _lr_t(self) -> float:
+        t = self.iterations
+        return self.learning_rate * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
+
+    def apply_model(self, model, gscale: float = 1.0, lr_t_dev: torch.Tensor | None = None) -> None:
+        """apply_gradients for a whole model.  A spectrally-normalised discriminator takes the fused path: one dot
+        launch (<G,W> per matrix) + ONE pass over the arena that maps the raw gradients through d(W/sigma)/dW, applies
+        Adam and runs the next power iteration on the updated rows (b2g_adam_sn) — no stand-alone spectral-norm pass."""
+        if not getattr(model, "spectral_norm", False) or model._sn_grads_final:
+            self.apply_arena(model.arena, gscale, lr_t_dev)
+            if getattr(model, "spectral_norm", False):
+                model._sn_stale = True          # weights moved: the next forward runs a stand-alone power iteration
+            model._packed_dirty = True
+            return
+        lib, a, sn = _lib.load(), model.arena, model._sn_args
+        check(lib.b2g_sn_dot_multi(_p(a.w), _p(a.g), 8, model._sn_off, sn[5], sn[6], _p(model._sn_dots), _stream()),
+              "b2g_sn_dot_multi")
+        lr_t = 0.0
+        if lr_t_dev is None:
+            self.iterations += 1
+            lr_t = self._lr_t()
+        check(lib.b2g_adam_sn(_p(a.w), _p(a.g), _p(a.m), _p(a.v), a.numel, 8, model._sn_off, sn[5], sn[6], sn[1], sn[2],
+                              sn[3], sn[4], _p(model._sn_dots), lr_t, _p(lr_t_dev), self.beta_1, self.beta_2,
+                              self.epsilon, gscale, _stream()), "b2g_adam_sn")
+        model._sn_stale = False                 # sigma / u now belong to the updated weights
+        model._packed_dirty = True
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -160,6 +193,7 @@ class Generator:
         self._packed_dirty = True
         self._bufs = {}
         self._z = None
+        self._params = None
 
     # -- Keras-like surface
     @property
@@ -171,9 +205,20 @@ class Generator:
             v.copy_(t.to(self.device, torch.float32))
         self._packed_dirty = True
 
+    def parameters(self):
+        """The trainable variables as autograd LEAVES (views of the weight arena, requires_grad=True).  Once a caller
+        has asked for them, `model(z)` under torch.enable_grad() builds an autograd graph out of the b200gan custom ops
+        (torch_ops.py) and `.backward()` fills their `.grad` — any loss can be put on top."""
+        if self._params is None:
+            self._params = [v.requires_grad_(True) for v in self.arena.variables]
+        return self._params
+
     def __call__(self, z, training=False):
         # BatchNorm runs in inference mode whatever `training` says: the moving statistics stay at (0, 1) in the
         # reference because its train_step never passes training=True to the generator (SNDCGAN.py:243).
+        if self._params is not None and torch.is_grad_enabled():
+            from .torch_ops import generator_graph
+            return generator_graph(self, z)
         return self.forward(z)
 
     # -- engine
@@ -298,7 +343,10 @@ class Discriminator:
         self._wp_d = [None] * 7
         self._packed_dirty = True
         self._bufs = {}
+        self._params = None
         self.spectral_norm = bool(spectral_norm)
+        self._sn_stale = False
+        self._sn_grads_final = False
         if self.spectral_norm:
             self._init_sn(seed + 1)
 
@@ -324,12 +372,32 @@ class Discriminator:
                          arr(self.sn_scal), (C.c_int * 8)(*Ks), (C.c_int * 8)(*Cs))
         self._sn_K, self._sn_C = Ks, Cs
         self._sn_dot = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self._sn_dots = torch.zeros(8, dtype=torch.float32, device=self.device)      # <G,W> per matrix (fused path)
+        self._sn_off = (C.c_long * 8)(*[self.arena.offsets[2 * i] for i in range(8)])
+        # sigma is undefined until a power iteration has seen the current weights: the first forward (training or
+        # not) runs a stand-alone one; afterwards every optimizer update carries the next iteration (b2g_adam_sn)
+        self._sn_stale = True
 
     def sn_power_iteration(self):
+        """Stand-alone power iteration (one launch, all 8 matrices): used when the weights were set from outside
+        (initialisation, set_weights, checkpoint restore).  Training updates get theirs inside b2g_adam_sn."""
         a = self._sn_args
         check(_lib.load().b2g_spectral_norm_multi(8, a[0], a[1], a[2], a[3], a[4], a[5], a[6], _stream()),
               "b2g_spectral_norm_multi", 2)
+        self._sn_stale = False
         self._packed_dirty = True
+
+    def finalize_sn_grads(self):
+        """Maps the raw kernel gradients of the last backward (dL/d(W/sigma)) to dL/dW in place — only for callers
+        that want to READ the gradients; train_step leaves them raw because b2g_adam_sn applies the same map."""
+        if not self.spectral_norm or self._sn_grads_final:
+            return
+        lib, v, g = _lib.load(), self.arena.variables, self.arena.grads
+        for i in range(8):
+            check(lib.b2g_sn_grad_finalize(_p(v[2 * i]), _p(g[2 * i]), _p(self.sn_u[i]), _p(self.sn_vraw[i]),
+                                           _p(self.sn_scal[i]), _p(self._sn_dot), self._sn_K[i], self._sn_C[i],
+                                           _stream()), "b2g_sn_grad_finalize", 3)
+        self._sn_grads_final = True
 
     def _inv_sigma(self, i):
         return self.sn_scal[i][2:3] if self.spectral_norm else None
@@ -343,12 +411,25 @@ class Discriminator:
         for v, t in zip(self.arena.variables, tensors):
             v.copy_(t.to(self.device, torch.float32))
         self._packed_dirty = True
+        self._sn_stale = self.spectral_norm
+
+    def parameters(self):
+        """See Generator.parameters: autograd leaves over the weight arena; enables the torch.library graph path."""
+        if self._params is None:
+            self._params = [v.requires_grad_(True) for v in self.arena.variables]
+        return self._params
 
     def __call__(self, x, training=False, dropout_seeds=None):
-        """Keras-style call: returns the logits [B,1] (SNDCGAN.py:244,252,260)."""
+        """Keras-style call: returns the logits [B,1] (SNDCGAN.py:244,252,260).  When autograd is recording (the
+        input requires grad, or parameters() has been handed out) the call builds a differentiable graph of b200gan
+        custom ops instead of using the engine's buffers."""
         if training and dropout_seeds is None and self.thresh8:
             self._call_count = getattr(self, "_call_count", 0) + 1
             dropout_seeds = [_splitmix64(0xD15C0000 + self._call_count * 8 + i) for i in range(7)]
+        if torch.is_grad_enabled() and (self._params is not None or x.requires_grad):
+            from .torch_ops import discriminator_graph
+            self.parameters()
+            return discriminator_graph(self, x, training, dropout_seeds)
         self.forward(x, training=training, dropout_seeds=dropout_seeds)
         _loss, logits = self.head_loss(0, 1.0, 1.0 / x.shape[0])
         return logits.clone()
@@ -390,7 +471,7 @@ class Discriminator:
         if x.dtype != torch.float32 or not x.is_cuda or tuple(x.shape[1:]) != self.input_size:
             raise B200GanError(f"discriminator input must be a CUDA fp32 tensor [B,{self.input_size}]")
         x = x.contiguous()
-        if self.spectral_norm and training:
+        if self.spectral_norm and self._sn_stale:
             self.sn_power_iteration()
         if self._packed_dirty:
             self.repack()
@@ -452,6 +533,7 @@ class Discriminator:
         dzero = 0.0 if self._train_fwd else LEAKY_ALPHA
         if need_wgrad:
             self.arena.g.zero_()
+            self._sn_grads_final = False
         c7 = acts[6]
         dpre = self._buf("dpre7", tuple(c7.shape), torch.bfloat16)
         check(lib.b2g_dhead_bwd(_p(c7), _p(v[14]), _p(self._inv_sigma(7)), _p(self._dlogit), B, self.F, LEAKY_ALPHA,
@@ -480,11 +562,8 @@ class Discriminator:
                 ops.conv_wgrad(CONV_K1S1, self._x27, dpre, g[0], ca_valid=27, dbias=g[1])
             else:                       # patch built inside the kernel from the fp32 input
                 ops.conv_wgrad(CONV_K3S1_C3, self._x_in, dpre, g[0], dbias=g[1])
-            if self.spectral_norm:
-                for i in range(8):
-                    check(lib.b2g_sn_grad_finalize(_p(v[2 * i]), _p(g[2 * i]), _p(self.sn_u[i]), _p(self.sn_vraw[i]),
-                                                   _p(self.sn_scal[i]), _p(self._sn_dot), self._sn_K[i],
-                                                   self._sn_C[i], _stream()), "b2g_sn_grad_finalize", 3)
+            # with spectral norm the kernel gradients stay RAW (dL/d(W/sigma)): the optimizer's fused pass maps them
+            # through d(W/sigma)/dW (Adam.apply_model); finalize_sn_grads() does it in place for callers that read them
         d_in = None
         if need_input_grad:
             d_in = self._buf("d_in", (B, H, W, 3), torch.float32)
@@ -531,6 +610,8 @@ class SNDCGANEngine:
         self.disc_model = make_dcgan_discriminator(dropout, input_size=image_size, device=device, seed=seed + 1,
                                                    spectral_norm=spectral_norm)                          # :167
         self.d_optimizer = Adam(learning_rate=learning_rate_disc)                                        # :168
+        from .torch_ops import BinaryCrossentropy
+        self.loss_fn = BinaryCrossentropy(from_logits=True)                                              # :170
         self.seed = seed
         self.step_count = 0
         self.pg = process_group
@@ -569,8 +650,7 @@ class SNDCGANEngine:
         return (self.seed * 0x1000003 + self.rank * 0x10001 + 1) & _MASK64
 
     def _dropout_seeds(self, pass_idx: int):
-        base = self._seed_base()
-        return [_splitmix64(base ^ ((self.step_count * 3 + pass_idx) * 8 + layer)) for layer in range(7)]
+        return step_dropout_seeds(self.seed, self.rank, self.step_count, pass_idx)
 
     def _allreduce(self, flat, async_op=False):
         if self.world == 1:
@@ -679,8 +759,10 @@ class SNDCGANEngine:
         """The launches of one step.  sa/sb/sc: 7 dropout seeds per discriminator pass (ints, or 1-element device
         tensors under graph capture); lr_dev: None, or the three device-resident Adam rates (G, D first, D second)."""
         G, D = self.gen_model, self.disc_model
-        B = input_real.shape[0]
-        inv_b = 1.0 / B
+        # the reference draws batch_size latent vectors even for a ragged last real batch (SNDCGAN.py:283): the two
+        # batches may differ in size, each loss is a mean over its own
+        inv_b = 1.0 / input_z.shape[0]
+        inv_b_real = 1.0 / input_real.shape[0]
         gs = 1.0 / self.world
         lr_g, lr_d1, lr_d2 = lr_dev if lr_dev is not None else (None, None, None)
         g_kind = LOSS_BCE if self.loss == "bce" else LOSS_HINGE_G
@@ -707,7 +789,7 @@ class SNDCGANEngine:
             check(lib.b2g_set_sm_limit(max(8, lib.b2g_num_sms() - reserve)), "b2g_set_sm_limit", 0)
         try:
             D.forward(input_real, training=True, dropout_seeds=sb)                  # :252
-            d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b)            # :253-254
+            d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b_real)       # :253-254
             d_logits_real = d_logits_real.clone()
             if reserve and not reserve_bwd:
                 check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
@@ -715,15 +797,14 @@ class SNDCGANEngine:
         finally:
             if reserve:
                 check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
-        self.d_optimizer.apply_arena(D.arena, gs, lr_d1)                            # :257
-        D._packed_dirty = True
+        self.d_optimizer.apply_model(D, gs, lr_d1)                                  # :257
 
         # (3) discriminator step on the stale fake batch (:259-267)
         D.forward(g_output, training=True, dropout_seeds=sc)                        # :260
         d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)                # :261-262
         self._d_backward_allreduce(D)                                               # :266
-        self.d_optimizer.apply_arena(D.arena, gs, lr_d2)                            # :267
-        D._packed_dirty = True
+        d_logits_fake = d_logits_fake.clone()       # D.logits is a reused buffer: the caller gets its own tensor
+        self.d_optimizer.apply_model(D, gs, lr_d2)                                  # :267
 
         if g_work is not None:
             g_work.wait()

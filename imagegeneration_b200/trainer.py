@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import argparse
 import glob
+import math
 import os
 import pickle
 import shutil
@@ -28,69 +29,151 @@ z_size = 128
 # ----------------------------------------------------------------------------------------------------------
 # dataset  (SNDCGAN.py:131-145)
 # ----------------------------------------------------------------------------------------------------------
-class ImageFolderDataset:
-    """`image_dataset_from_directory(seed=123, crop_to_aspect_ratio=True)` + `Rescaling(1/127.5, offset=-1)` +
-    cache/shuffle: decodes every image once (centre crop to the target aspect ratio, bilinear resize), keeps the
-    uint8 cache in memory and yields shuffled fp32 NHWC batches in [-1, 1] with dummy labels."""
+def _decode_folder(root, size):
+    """image_dataset_from_directory(image_size=..., crop_to_aspect_ratio=True): every file is decoded ONCE (PIL), the
+    largest centred window with the target aspect ratio is cropped and resized with half-pixel BILINEAR interpolation
+    WITHOUT antialiasing (what Keras' smart_resize / tf.image.resize do; PIL's BILINEAR would antialias when shrinking).
+    Returns uint8 [N, H, W, 3] — the resized floats are rounded to 8 bits for the cache (<= 0.5/255 per pixel)."""
+    from PIL import Image
+    exts = ("*.jpg", "*.jpeg", "*.png", "*.bmp")
+    files = sorted(f for e in exts for f in glob.glob(os.path.join(root, "**", e), recursive=True))
+    if not files:
+        raise FileNotFoundError(f"no images under {root!r} (use --data synthetic for generated data)")
+    h, w = size[:2]
+    imgs = torch.empty((len(files), h, w, 3), dtype=torch.uint8)
+    for i, f in enumerate(files):
+        im = Image.open(f).convert("RGB")
+        iw, ih = im.size
+        if iw * h > ih * w:      # too wide: crop width
+            cw = int(ih * w / h)
+            x0 = (iw - cw) // 2
+            im = im.crop((x0, 0, x0 + cw, ih))
+        else:
+            ch = int(iw * h / w)
+            y0 = (ih - ch) // 2
+            im = im.crop((0, y0, iw, y0 + ch))
+        t = torch.from_numpy(np.asarray(im).copy()).permute(2, 0, 1)[None].float()
+        t = torch.nn.functional.interpolate(t, size=(h, w), mode="bilinear", align_corners=False, antialias=False)
+        imgs[i] = t[0].permute(1, 2, 0).round().clamp(0, 255).to(torch.uint8)
+    return imgs
 
-    def __init__(self, root, batch_size, size, seed=123):
-        from PIL import Image
-        exts = ("*.jpg", "*.jpeg", "*.png", "*.bmp")
-        files = sorted(f for e in exts for f in glob.glob(os.path.join(root, "**", e), recursive=True))
-        if not files:
-            raise FileNotFoundError(f"no images under {root!r} (use --synthetic for generated data)")
-        h, w = size[:2]
-        imgs = np.empty((len(files), h, w, 3), dtype=np.uint8)
-        for i, f in enumerate(files):
-            im = Image.open(f).convert("RGB")
-            iw, ih = im.size
-            if iw * h > ih * w:      # too wide: crop width
-                cw = int(ih * w / h)
-                x0 = (iw - cw) // 2
-                im = im.crop((x0, 0, x0 + cw, ih))
-            else:
-                ch = int(iw * h / w)
-                y0 = (ih - ch) // 2
-                im = im.crop((0, y0, iw, y0 + ch))
-            imgs[i] = np.asarray(im.resize((w, h), Image.BILINEAR))
-        self.images = torch.from_numpy(imgs)
+
+class DeviceImageDataset:
+    """get_dataset's `Rescaling(1/127.5, offset=-1)` + `.cache().shuffle(10000).prefetch()` (SNDCGAN.py:141-143) with the
+    cache RESIDENT IN HBM as uint8 (the reference's 7 244 usable images at 144x256x3 are 0.8 GB): an epoch is a device-side
+    permutation of indices, a batch is one b2g_gather_u8_to_f32 launch (gather + /127.5 - 1 into a fresh fp32 NHWC
+    tensor).  No host work, no H2D copy per step.  Like tf.data (drop_remainder=False) the last batch may be ragged.
+    Yields (images fp32 CUDA [b,H,W,3] in [-1,1], labels int64 zeros [b])."""
+
+    def __init__(self, images_u8: torch.Tensor, batch_size: int, device="cuda", seed=123):
+        if images_u8.dtype != torch.uint8 or images_u8.dim() != 4 or images_u8.shape[3] != 3:
+            raise ValueError("DeviceImageDataset needs uint8 [N,H,W,3] images")
+        self.device = torch.device(device)
+        self.images = images_u8.contiguous().to(self.device)
         self.batch_size = batch_size
-        self.gen = torch.Generator().manual_seed(seed)
+        self.image_size = tuple(self.images.shape[1:])
+        self.per_image = int(self.images[0].numel())
+        if self.per_image % 16:
+            raise ValueError("image bytes (H*W*3) must be a multiple of 16")
+        self.gen = torch.Generator(device=self.device).manual_seed(seed)
 
     def __len__(self):
-        return (len(self.images) + self.batch_size - 1) // self.batch_size
+        return (self.images.shape[0] + self.batch_size - 1) // self.batch_size
 
     def __iter__(self):
-        perm = torch.randperm(len(self.images), generator=self.gen)
-        for i in range(0, len(perm), self.batch_size):
-            idx = perm[i:i + self.batch_size]
-            x = self.images[idx].to(torch.float32) * (1.0 / 127.5) - 1.0
-            yield x.pin_memory() if torch.cuda.is_available() else x, torch.zeros(len(idx), dtype=torch.int64)
+        from . import lib as _lib
+        n = self.images.shape[0]
+        perm = torch.randperm(n, generator=self.gen, device=self.device)
+        for i in range(0, n, self.batch_size):
+            idx = perm[i:i + self.batch_size].contiguous()
+            b = idx.numel()
+            out = torch.empty((b, *self.image_size), dtype=torch.float32, device=self.device)
+            _lib.check(_lib.load().b2g_gather_u8_to_f32(
+                self.images.data_ptr(), idx.data_ptr(), out.data_ptr(), b, self.per_image,
+                torch.cuda.current_stream().cuda_stream), "b2g_gather_u8_to_f32")
+            yield out, torch.zeros(b, dtype=torch.int64, device=self.device)
 
 
-class SyntheticDataset:
-    """U(-1,1) images of the reference's training shape (Open Images is not available offline); 7 244 images per
-    epoch by default = the reference's usable set (dataset_creator/results_open_images/stats.json)."""
-
-    def __init__(self, batch_size, size, n_images=7244, seed=123):
-        self.batch_size, self.size, self.n = batch_size, size, n_images
-        self.gen = torch.Generator().manual_seed(seed)
-
-    def __len__(self):
-        return self.n // self.batch_size
-
-    def __iter__(self):
-        for _ in range(len(self)):
-            x = torch.rand((self.batch_size, *self.size), generator=self.gen) * 2 - 1
-            yield x.pin_memory() if torch.cuda.is_available() else x, torch.zeros(self.batch_size, dtype=torch.int64)
-
-
-def get_dataset(dataset, batch_size, image_size):
-    """SNDCGAN.py:131: directory of images -> iterable of (fp32 NHWC in [-1,1], labels); "synthetic" -> generated."""
+def get_dataset(dataset, batch_size, image_size, device="cuda"):
+    """SNDCGAN.py:131: directory of images -> iterable of (fp32 NHWC in [-1,1], labels).  "synthetic[:N]" -> N (default
+    7 244 = the reference's usable set, dataset_creator/results_open_images/stats.json) generated uint8 images, because
+    Open Images is not available offline.  Either way the cache lives on the device (DeviceImageDataset)."""
     if dataset == "synthetic" or str(dataset).startswith("synthetic:"):
         n = int(str(dataset).split(":")[1]) if ":" in str(dataset) else 7244
-        return SyntheticDataset(batch_size, tuple(image_size), n)
-    return ImageFolderDataset(dataset, batch_size, tuple(image_size))
+        g = torch.Generator().manual_seed(123)
+        imgs = torch.randint(0, 256, (n, *tuple(image_size)), generator=g, dtype=torch.uint8)
+    else:
+        imgs = _decode_folder(dataset, tuple(image_size))
+    return DeviceImageDataset(imgs, batch_size, device=device)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# persistence  (SNDCGAN.py:181-199, :317-331)
+# ----------------------------------------------------------------------------------------------------------
+def save_model(model, path):
+    """`model.save(path, include_optimizer=False)` (SNDCGAN.py:327-331): architecture arguments + the trainable variables
+    in Keras order and Keras layouts, as one torch file (h5py / TensorFlow are not available: no .h5 byte compatibility)."""
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    from .sndcgan import Generator
+    state = {"kind": "generator" if isinstance(model, Generator) else "discriminator",
+             "image_size": tuple(model.output_size if isinstance(model, Generator) else model.input_size),
+             "names": list(model.arena.names), "weights": [v.detach().cpu().clone() for v in model.trainable_variables]}
+    if state["kind"] == "discriminator":
+        state["dropout_rate"] = model.dropout_rate
+        state["spectral_norm"] = model.spectral_norm
+        if model.spectral_norm:
+            if model._sn_stale:
+                model.sn_power_iteration()
+            state["sn_u"] = [u.cpu() for u in model.sn_u]
+    torch.save(state, path)
+
+
+def load_model(path, device="cuda"):
+    """tf.keras.models.load_model(path) for files written by save_model (generator_output.py:67, generator_evaluation.py:
+    134,160): returns a ready Generator / Discriminator."""
+    from .sndcgan import make_dcgan_discriminator, make_dcgan_generator
+    st = torch.load(path, map_location="cpu")
+    if st["kind"] == "generator":
+        model = make_dcgan_generator(st["image_size"], device=device)
+    else:
+        model = make_dcgan_discriminator(st["dropout_rate"], st["image_size"], device=device,
+                                         spectral_norm=st.get("spectral_norm", False))
+        if st.get("sn_u"):
+            for u, s in zip(model.sn_u, st["sn_u"]):
+                u.copy_(s)
+    model.set_weights(st["weights"])
+    return model
+
+
+class CheckpointManager:
+    """tf.train.CheckpointManager(ckpt, directory, max_to_keep=2) as the reference uses it (SNDCGAN.py:181-199,318):
+    `latest_checkpoint`, `checkpoints`, `save(checkpoint_number=epoch)`; plus `restore(path)` (Checkpoint.restore).
+    Files are torch.save archives `ckpt-<n>.pt` holding both models, both optimizers' slots and counters."""
+
+    def __init__(self, owner, directory, max_to_keep=2):
+        self.owner, self.directory, self.max_to_keep = owner, directory, max_to_keep
+        os.makedirs(directory, exist_ok=True)
+
+    @property
+    def checkpoints(self):
+        files = glob.glob(os.path.join(self.directory, "ckpt-*.pt"))
+        return sorted(files, key=lambda f: int(os.path.basename(f).split("-")[-1].split(".")[0]))
+
+    @property
+    def latest_checkpoint(self):
+        c = self.checkpoints
+        return c[-1] if c else None
+
+    def save(self, checkpoint_number):
+        path = os.path.join(self.directory, f"ckpt-{checkpoint_number}.pt")
+        self.owner._save_state(path, checkpoint_number)
+        if self.max_to_keep:
+            for old in self.checkpoints[:-self.max_to_keep]:
+                os.remove(old)
+        return path
+
+    def restore(self, path):
+        self.owner._restore(path)
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -115,36 +198,31 @@ class SNDCGAN(SNDCGANEngine):
         else:
             self.losses = {"epoch": [], "avg_g_loss": [], "avg_d_loss": [], "d_real": [], "d_fake": []}
         self.checkpoint_path = os.path.join(dir_path, "checkpoints")
-        os.makedirs(self.checkpoint_path, exist_ok=True)
-        latest = self._latest_checkpoint()
+        self.ckpt_manager = CheckpointManager(self, self.checkpoint_path, max_to_keep=2)      # :187-188
+        latest = self.ckpt_manager.latest_checkpoint
         if continue_ and latest:                                 # :192-196
             self.start_epoch = int(os.path.basename(latest).split("-")[-1].split(".")[0]) + 1
-            self._restore(latest)
+            self.ckpt_manager.restore(latest)
             print("Latest checkpoint restored!!")
         else:
             self.start_epoch = 0
             print("No checkpoints were restored!!")
         print("\nInitialized SNDCGAN successfully!\n")
 
-    # -- checkpoints: CheckpointManager(max_to_keep=2) semantics with torch.save files ckpt-<epoch>.pt
-    def _checkpoints(self):
-        files = glob.glob(os.path.join(self.checkpoint_path, "ckpt-*.pt"))
-        return sorted(files, key=lambda f: int(os.path.basename(f).split("-")[-1].split(".")[0]))
-
-    def _latest_checkpoint(self):
-        c = self._checkpoints()
-        return c[-1] if c else None
-
-    def _save(self, epoch):
+    # -- checkpoint contents (written / read through self.ckpt_manager)
+    def _save_state(self, path, epoch):
         G, D = self.gen_model.arena, self.disc_model.arena
         state = {"epoch": epoch, "g_w": G.w.cpu(), "g_m": G.m.cpu(), "g_v": G.v.cpu(), "d_w": D.w.cpu(),
                  "d_m": D.m.cpu(), "d_v": D.v.cpu(), "g_iterations": self.g_optimizer.iterations,
                  "d_iterations": self.d_optimizer.iterations, "step_count": self.step_count}
         if self.disc_model.spectral_norm:
-            state["sn_u"] = [u.cpu() for u in self.disc_model.sn_u]
-        torch.save(state, os.path.join(self.checkpoint_path, f"ckpt-{epoch}.pt"))
-        for old in self._checkpoints()[:-2]:
-            os.remove(old)
+            D = self.disc_model
+            if D._sn_stale:                 # never trained / weights set by hand: make sigma valid before saving it
+                D.sn_power_iteration()
+            state["sn_u"] = [u.cpu() for u in D.sn_u]
+            state["sn_vraw"] = [x.cpu() for x in D.sn_vraw]
+            state["sn_scal"] = [x.cpu() for x in D.sn_scal]
+        torch.save(state, path)
 
     def _restore(self, path):
         st = torch.load(path, map_location="cpu")
@@ -153,11 +231,43 @@ class SNDCGAN(SNDCGANEngine):
             dst.copy_(st[key])
         self.g_optimizer.iterations, self.d_optimizer.iterations = st["g_iterations"], st["d_iterations"]
         self.step_count = st["step_count"]
-        if self.disc_model.spectral_norm and "sn_u" in st:
-            for u, s in zip(self.disc_model.sn_u, st["sn_u"]):
-                u.copy_(s)
+        D = self.disc_model
+        if D.spectral_norm:
+            D._sn_stale = True              # without a saved sigma the first forward runs a power iteration
+            if "sn_u" in st:
+                for u, s in zip(D.sn_u, st["sn_u"]):
+                    u.copy_(s)
+            if "sn_scal" in st and "sn_vraw" in st:   # sigma / v of the saved weights: resume is exact
+                for dst, src in zip(D.sn_vraw + D.sn_scal, st["sn_vraw"] + st["sn_scal"]):
+                    dst.copy_(src)
+                D._sn_stale = False
         self.gen_model._packed_dirty = True
         self.disc_model._packed_dirty = True
+
+    def plot_history(self):
+        """:216-225 draws the loss curves with matplotlib (absent here, and there is no display): the same four curves
+        go to <dir>/plot_line_plot_loss.png as a plain Pillow line plot."""
+        try:
+            from PIL import Image, ImageDraw
+            W, H, pad = 800, 400, 30
+            img = Image.new("RGB", (W, H), "white")
+            dr = ImageDraw.Draw(img)
+            series = [(k, v) for k, v in self.losses.items() if k != "epoch" and len(v)]
+            vals = [x for _k, v in series for x in v if math.isfinite(x)]
+            if vals:
+                lo, hi = min(vals), max(vals)
+                hi = hi if hi > lo else lo + 1.0
+                colors = ["#1f77b4", "#ff7f0e", "#2ca02c", "#d62728"]
+                for ci, (k, v) in enumerate(series):
+                    n = max(len(v) - 1, 1)
+                    pts = [(pad + (W - 2 * pad) * i / n, H - pad - (H - 2 * pad) * (x - lo) / (hi - lo))
+                           for i, x in enumerate(v) if math.isfinite(x)]
+                    if len(pts) > 1:
+                        dr.line(pts, fill=colors[ci % 4], width=2)
+                    dr.text((pad + 5, 5 + 12 * ci), f"{k} [{lo:.3g}, {hi:.3g}]", fill=colors[ci % 4])
+            img.save(os.path.join(self.dir_path, "plot_line_plot_loss.png"))
+        except Exception as e:  # a plot is a convenience, never fatal
+            print(f"(loss plot not written: {e})")
 
     def display_examples(self, samples, number_of_images, info_text):
         """:228-238 writes a matplotlib PDF; headless here: the preview strip goes to a PNG (Pillow)."""
@@ -177,8 +287,7 @@ class SNDCGAN(SNDCGANEngine):
             epoch_losses, epoch_d_vals = [], []
             batch_start_time = time()
             for i, (input_real, _) in enumerate(self.train_ds):
-                if input_real.shape[0] != self.batch_size:
-                    continue   # kernels are shaped for the configured batch; the ragged last batch is skipped
+                # a ragged last batch is trained on like any other, with batch_size latent vectors (:282-284)
                 input_real = input_real.to(dev, non_blocking=True)
                 input_z = torch.rand((self.batch_size, self.z_size), device=dev) * 2.0 - 1.0        # :283
                 out = self.train_step(input_real, input_z)                                          # :284
@@ -187,7 +296,7 @@ class SNDCGAN(SNDCGANEngine):
                 print(f"\r>Batch {i:03d}, passed time: {strftime('%M:%S', gmtime(time() - batch_start_time))}",
                       end="", flush=True)
             if not epoch_losses:
-                raise RuntimeError("dataset yielded no full batch")
+                raise RuntimeError("dataset yielded no batch")
             avg_losses = torch.stack(epoch_losses).mean(dim=0).cpu().tolist()     # one host sync per epoch
             for key, val in zip(("epoch", "avg_g_loss", "avg_d_loss", "d_real", "d_fake"), [epoch] + avg_losses):
                 local_losses[key].append(val)
@@ -199,11 +308,16 @@ class SNDCGAN(SNDCGANEngine):
             fixed_z = torch.rand((n_prev, self.z_size), device=dev) * 2.0 - 1.0
             self.display_examples(create_samples(self.gen_model, fixed_z, n_prev), n_prev, info_text)
             if epoch % checkpoint_frequency == 0:                                                   # :317
-                self._save(epoch)
+                self.ckpt_manager.save(checkpoint_number=epoch)                                     # :318
                 for key, val in local_losses.items():
                     self.losses[key] = self.losses[key] + val
                 with open(self.losses_file, mode="wb") as f:
                     pickle.dump(self.losses, f)
+                # :327-331 — per-checkpoint model exports, consumed by generator_output / generator_evaluation
+                save_model(self.gen_model, os.path.join(self.dir_path, "models", "generator", f"gen_model-{epoch}.pt"))
+                save_model(self.disc_model,
+                           os.path.join(self.dir_path, "models", "discriminator", f"disc_model-{epoch}.pt"))
+                self.plot_history()                                                                 # :333
                 local_losses = {"epoch": [], "avg_g_loss": [], "avg_d_loss": [], "d_real": [], "d_fake": []}
 
 

@@ -283,6 +283,39 @@ int b2g_spectral_norm_multi(int n_layers, const float* const* W, float* const* u
                             b2g_stream_t stream);
 int b2g_sn_grad_finalize(const float* W, float* G, const float* u, const float* v_raw, const float* scal,
                          float* dot_scratch, int K, int C, b2g_stream_t stream);
+/* Spectral norm made free (north_star item 2): the whole spectral-norm bookkeeping of one apply_gradients rides on
+ * the optimizer's own pass over the discriminator arena.
+ * sn_dot_multi: dots[l] += <G_l, W_l> for the n_layers matrices at element offsets off[l] (K[l] x C[l], row-major)
+ *       inside the arenas w / g — one launch.  dots must be zero on first use; b2g_adam_sn re-zeroes it.
+ * adam_sn: Keras Adam over the arena [0, n) where, for each listed matrix, the gradient is first mapped through
+ *       d(W/sigma)/dW (g <- g/sigma - (dots[l]/sigma^2) v u^T, with u, v_raw, scal as the forward pass used them),
+ *       and the NEXT power iteration (v_raw = W' u, t = W'^T v_raw, sigma, u) is computed from the updated rows
+ *       while they are in registers; same state layout as b2g_spectral_norm_multi.  lr_t_dev (device float) takes
+ *       precedence over lr_t when non-NULL (CUDA-graph replay).  Elements outside the matrices (biases) get plain
+ *       Adam.  Matrices must be listed in ascending offset order. */
+int b2g_sn_dot_multi(const float* w, const float* g, int n_layers, const long* off, const int* K, const int* C,
+                     float* dots, b2g_stream_t stream);
+int b2g_adam_sn(float* w, const float* g, float* m, float* v, long n, int n_layers, const long* off, const int* K,
+                const int* C, float* const* u, float* const* v_raw, float* const* t_raw, float* const* scal,
+                float* dots, float lr_t, const float* lr_t_dev, float beta1, float beta2, float eps, float gscale,
+                b2g_stream_t stream);
+
+/* ---- small kernels either side of the step (csrc/b2g_misc.cu) -------------------------------------------------
+ * dact: out = g * act'(y) elementwise from the saved forward output y (LeakyReLU/Dropout: y > 0 -> scale, y < 0 ->
+ *       alpha*scale, y == 0 -> zero; ReLU; tanh: 1 - y^2).  f32 = 0: bf16 tensors (n % 8 == 0); 1: fp32.  The stand-alone
+ *       form of the derivative epilogues, for the torch.library autograd formulas (train_step uses the fused ones).
+ * bce_logits: tf.keras.losses.BinaryCrossentropy(from_logits=True) (sndcgan/SNDCGAN.py:170): loss_out[0] =
+ *       mean_b[max(x,0) - x*y + log1p(exp(-|x|))]; dlogit (may be NULL) = (sigmoid(x) - y)/B.
+ * gather_u8_to_f32: out[b] = images[idx[b]] / 127.5 - 1 from a device-resident uint8 cache (get_dataset's Rescaling +
+ *       cache + shuffle, SNDCGAN.py:141-143); per_image = bytes of one image, a multiple of 16.
+ * colsum_f32: out[c] += sum_p x[p][c] (bias gradient on the fp32/tf32 path). */
+int b2g_dact(const void* g, const void* y, void* out, long n, int f32, int kind, float alpha, float scale, float zero,
+             b2g_stream_t stream);
+int b2g_bce_logits(const float* logits, const float* labels, int B, float* loss_out, float* dlogit,
+                   b2g_stream_t stream);
+int b2g_gather_u8_to_f32(const void* images_u8, const long* idx, float* out, int B, long per_image,
+                         b2g_stream_t stream);
+int b2g_colsum_f32(const float* x, float* out, long P, int C, b2g_stream_t stream);
 
 /* ---- host-only introspection (no CUDA calls; used by the CPU test-suite) ---------------------------------
  * conv_plan_query: tiling + tap tables of a conv role -> out[0..15] = {phases, taps, Hg, Wg, bw, bh, bn, tiles_w,

@@ -91,10 +91,16 @@ def hinge_d_loss(logits: torch.Tensor, label: float) -> torch.Tensor:
 def adam_step(w: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, t: int, lr: float,
               beta1: float = ADAM_BETA1, beta2: float = ADAM_BETA2, eps: float = ADAM_EPS) -> None:
     """Keras-2 Adam._resource_apply_dense (in place).  t is the 1-based step (iterations + 1);
-    epsilon sits OUTSIDE the bias-corrected sqrt:  w -= lr_t * m / (sqrt(v) + eps)."""
+    epsilon sits OUTSIDE the bias-corrected sqrt:  w -= lr_t * m / (sqrt(v) + eps).
+    Keras keeps the hyper-parameters in the variable's dtype (fp32) and forms `1 - beta` there
+    (Adam._prepare_local: one_minus_beta_2_t = 1 - beta_2_t): 1 - float32(0.999) = 0.00099998713, 1.3e-5 away from
+    0.001 — restated here so that v matches an fp32 implementation to rounding error whatever dtype the oracle runs in."""
+    import numpy as np
     lr_t = lr * math.sqrt(1.0 - beta2 ** t) / (1.0 - beta1 ** t)
-    m.add_((g - m) * (1.0 - beta1))
-    v.add_((g * g - v) * (1.0 - beta2))
+    c1 = float(np.float32(1.0) - np.float32(beta1))
+    c2 = float(np.float32(1.0) - np.float32(beta2))
+    m.add_((g - m) * c1)
+    v.add_((g * g - v) * c2)
     w.sub_(lr_t * m / (torch.sqrt(v) + eps))
 
 

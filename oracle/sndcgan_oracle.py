@@ -125,6 +125,30 @@ def _qw(w, emu):
 
 
 # ----------------------------------------------------------------------------------------------------------
+# spectral normalisation state (north-star option, NOT in the reference: SURVEY F1)
+# ----------------------------------------------------------------------------------------------------------
+class SNState:
+    """Persistent u (and the matching v) of the 8 discriminator matrices.  Miyato et al. (2018) Alg. 1: ONE power
+    iteration per weight update — it runs when the weights changed since the last one (`fresh` False: initial
+    weights, after every optimizer step), not once per forward pass; passes that see the same weights share sigma."""
+
+    def __init__(self, u):
+        self.u = list(u)
+        self.v = [None] * len(self.u)
+        self.fresh = False
+
+    def refresh(self, dv):
+        if self.fresh:
+            return
+        with torch.no_grad():
+            for i in range(len(self.u)):
+                wt = dv[2 * i]
+                _s, u, v = K.spectral_norm_power_iteration(wt.reshape(-1, wt.shape[-1]), self.u[i].to(wt.dtype), 1)
+                self.u[i], self.v[i] = u, v
+        self.fresh = True
+
+
+# ----------------------------------------------------------------------------------------------------------
 # forward passes
 # ----------------------------------------------------------------------------------------------------------
 def generator_forward(gv: list[torch.Tensor], z: torch.Tensor, image_size=(144, 256, 3), collect: dict | None = None,
@@ -158,15 +182,18 @@ def discriminator_forward(dv: list[torch.Tensor], x: torch.Tensor, rate: float, 
                           emu: bool = False):
     """SNDCGAN.py:70-124 with training=True dropout given as explicit keep masks (one per conv, or None).
 
-    sn_state (optional, NOT in the reference): list of 8 persistent `u` vectors; when given, every kernel is
-    divided by its spectral norm estimated with one power iteration (u, v treated as constants)."""
+    sn_state (optional, NOT in the reference): an SNState (or a list of 8 `u` vectors, wrapped into a stale one);
+    every kernel is divided by sigma = v^T W u with u, v from the state's power iteration (constants for autograd)."""
+    if isinstance(sn_state, list):
+        sn_state = SNState(sn_state)
+    if sn_state is not None:
+        sn_state.refresh(dv)
+
     def eff(i, wt):
         if sn_state is None:
             return wt
         w2d = wt.reshape(-1, wt.shape[-1])
-        with torch.no_grad():
-            _s, u, v = K.spectral_norm_power_iteration(w2d, sn_state[i], 1)
-            sn_state[i] = u
+        u, v = sn_state.u[i], sn_state.v[i]
         sigma = v @ (w2d @ u)
         if collect is not None:
             collect[f"{tag}_sigma{i}"] = sigma.detach()
@@ -250,6 +277,8 @@ class OracleSNDCGAN:
     def train_step(self, input_real, input_z, masks_a=None, masks_b=None, masks_c=None, collect: dict | None = None):
         """SNDCGAN.py:241-269.  masks_a/b/c: the 7 dropout keep-masks of the three D passes."""
         gv, dv = self.gv, self.dv
+        if isinstance(self.sn_state, list):
+            self.sn_state = SNState(self.sn_state)
         for p in gv + dv:
             p.requires_grad_(True)
         # (1) generator step, :242-249
@@ -270,6 +299,8 @@ class OracleSNDCGAN:
         if collect is not None:
             collect["d_grads1"] = [g.clone() for g in d_grads1]
         self.d_opt.apply(dv, d_grads1)
+        if self.sn_state is not None:
+            self.sn_state.fresh = False
         # (3) discriminator step on the stale fake batch, :259-267
         d_logits_fake2 = discriminator_forward(dv, g_output, self.dropout, masks_c, collect, self.sn_state, "dc",
                                                self.emu)
@@ -279,6 +310,8 @@ class OracleSNDCGAN:
         if collect is not None:
             collect["d_grads2"] = [g.clone() for g in d_grads2]
         self.d_opt.apply(dv, d_grads2)
+        if self.sn_state is not None:
+            self.sn_state.fresh = False
         for p in gv + dv:
             p.requires_grad_(False)
         return (g_loss.detach(), d_loss.detach(), d_loss_real.detach(), d_loss_fake.detach(),

@@ -1,0 +1,224 @@
+"""Whole-step parity AT THE BASELINE CONFIGS: the kernel dispatch that bench.py times (batch 64:
+CTA-pair kernels + static row schedules) and BASELINE configs[0] (batch 16, fp32 oracle, dropout 0.5), full 256x144
+resolution, against the CPU oracle (oracle/sndcgan_oracle.py = restatement of sndcgan/SNDCGAN.py:241-269).
+
+Also here, because they are compositions no single-kernel test sees:
+  * the optimizer update checked EXACTLY on the engine's own gradients (every apply_gradients call of a step);
+  * teacher-forced backward passes: the engine's Generator.backward / Discriminator.backward run on the ORACLE's saved
+    activations (so no ReLU / LeakyReLU / dropout mask can flip) and every gradient tensor — fused bias / beta column
+    sums, folded-BatchNorm gamma gradients, dropout keep-scale in the derivative epilogues — must match the fp32 oracle.
+Tolerances are stated at each assert."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import keras_ops as K
+from oracle import sndcgan_oracle as O
+from oracle.dropout_hash import keep_mask
+
+pytestmark = pytest.mark.gpu
+
+IMAGE = (144, 256, 3)
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bench_step0.json")
+
+
+def _rel_l2(a, b):
+    a = a.double().flatten().cpu()
+    b = b.double().flatten().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def _rel(a, b):
+    return abs(float(a) - float(b)) / (abs(float(b)) + 1e-12)
+
+
+def _bench_inputs(batch):
+    g = torch.Generator().manual_seed(1234)
+    real = [torch.rand((batch, *IMAGE), generator=g) * 2 - 1 for _ in range(2)]
+    z = [torch.rand((batch, 128), generator=g) * 2 - 1 for _ in range(2)]
+    return real, z
+
+
+def _masks(image_size, batch, seeds, thresh8):
+    h, w, _ = image_size
+    shapes = [(h, w, 64), (h // 2, w // 2, 128), (h // 2, w // 2, 128), (h // 4, w // 4, 256), (h // 4, w // 4, 256),
+              (h // 8, w // 8, 512), (h // 8, w // 8, 512)]
+    return [torch.from_numpy(keep_mask(batch * a * b * c, s, thresh8).astype(np.float32)).reshape(batch, a, b, c)
+            for s, (a, b, c) in zip(seeds, shapes)]
+
+
+def _check_step_outputs(out, ref_losses, ref_real, ref_fake, tag):
+    # north_star: bf16 path within 2e-2 relative on the loss; logits within 2e-2 of the logit scale
+    for name, a, b in zip(("g_loss", "d_loss", "d_loss_real", "d_loss_fake"), out[:4], ref_losses):
+        assert _rel(a, b) < 2e-2, f"{tag} {name}: {float(a)} vs oracle {float(b)}"
+    for name, a, b in (("d_logits_real", out[4], ref_real), ("d_logits_fake", out[5], ref_fake)):
+        b = torch.as_tensor(b, dtype=torch.float32).reshape(-1)
+        a = a.float().cpu().reshape(-1)
+        assert float((a - b).abs().max()) < 2e-2 * (1 + float(b.abs().max())), f"{tag} {name}"
+
+
+def test_config_c2_batch64_first_step_matches_oracle_golden():
+    """BASELINE configs[1]: batch 64, bf16, dropout 0.5 — the exact dispatch bench.py times.  The oracle's outputs for
+    this step are committed (tests/golden/bench_step0.json, generator script beside it: a batch-64 fp32 CPU step needs
+    ~12 GB and a minute, too much for every GPU test run)."""
+    from imagegeneration_b200.sndcgan import SNDCGANEngine
+    with open(GOLDEN) as f:
+        gold = json.load(f)["batch64"]
+    real, z = _bench_inputs(64)
+    eng = SNDCGANEngine(64, dropout=0.5, image_size=IMAGE, seed=62)
+    out = eng.train_step(real[0].cuda(), z[0].cuda())       # engine-chosen seeds = the golden file's masks
+    torch.cuda.synchronize()
+    _check_step_outputs(out, gold["losses"], gold["d_logits_real"], gold["d_logits_fake"], "B=64 step 0")
+    # and the replayed-graph steps that follow stay finite and keep the optimizer bookkeeping
+    for i in range(1, 4):
+        out = eng.train_step(real[i & 1].cuda(), z[i & 1].cuda())
+    torch.cuda.synchronize()
+    assert eng._graph is not None, eng._graph_failed
+    assert all(bool(torch.isfinite(o).all()) for o in out)
+    assert eng.d_optimizer.iterations == 8 and eng.g_optimizer.iterations == 4
+
+
+def test_config_c1_batch16_step_matches_fp32_oracle():
+    """BASELINE configs[0]: one G+D train_step at 256x144, batch 16, dropout 0.5, against the plain fp32 oracle run here
+    (3-4 s on the box's host cores): losses, logits, every saved activation of the generator and of the last
+    discriminator pass, and the committed golden values (so the golden file and the live oracle cannot drift apart)."""
+    from imagegeneration_b200.sndcgan import SNDCGANEngine, step_dropout_seeds
+    B = 16
+    real, z = _bench_inputs(B)
+    eng = SNDCGANEngine(B, dropout=0.5, image_size=IMAGE, seed=62)
+    orc = O.OracleSNDCGAN(IMAGE, dropout=0.5, seed=62)
+    for a, b in zip(eng.gen_model.trainable_variables + eng.disc_model.trainable_variables, orc.gv + orc.dv):
+        assert torch.equal(a.cpu(), b)                        # same initial weights without copying them over
+    t8 = eng.disc_model.thresh8
+    masks = [_masks(IMAGE, B, step_dropout_seeds(62, 0, 0, p), t8) for p in range(3)]
+    col = {}
+    ref = orc.train_step(real[0], z[0], masks[0], masks[1], masks[2], col)
+    # per-layer activations BEFORE any update (forward passes do not change state): the generator and the real-batch
+    # discriminator pass "db" (initial weights, masks of pass 1).  Activations after the first Adam step are not
+    # comparable layer by layer: Adam's first update is lr * sign(g), a bias whose gradient is ~0 steps the other way
+    # than in the oracle, and +-2e-4 on a bias is as large as conv1's activations of an untrained generator's image.
+    eng.gen_model.forward(z[0].cuda())
+    eng.disc_model.forward(real[0].cuda(), training=True, dropout_seeds=step_dropout_seeds(62, 0, 0, 1))
+    torch.cuda.synchronize()
+    for i, a in enumerate(eng.gen_model._acts):                # bf16 storage, <= 2e-2 rel-L2 (measured ~3e-3)
+        assert _rel_l2(a.float(), col[f"g_a{i}"]) < 2e-2, f"g_a{i}"
+    assert _rel_l2(eng.gen_model.g_out, col["g_out"]) < 2e-2
+    for i, a in enumerate(eng.disc_model._acts):
+        assert _rel_l2(a.float(), col[f"db_c{i + 1}"]) < 2e-2, f"db_c{i + 1}"
+    out = eng.train_step(real[0].cuda(), z[0].cuda())
+    torch.cuda.synchronize()
+    _check_step_outputs(out, ref[:4], ref[4], ref[5], "B=16 step 0")
+    with open(GOLDEN) as f:
+        gold = json.load(f)["batch16"]
+    for a, b in zip(ref[:4], gold["losses"]):
+        assert _rel(a, b) < 1e-4, "live oracle and tests/golden/bench_step0.json disagree"
+
+
+class _AdamRecorder:
+    """Wraps Adam.apply_arena: keeps (w, g, m, v) before and (w, m, v) after every update of one step."""
+
+    def __init__(self, opt):
+        self.opt, self.calls = opt, []
+        self._orig = opt.apply_arena
+        opt.apply_arena = self._apply
+
+    def _apply(self, arena, gscale=1.0, lr_t_dev=None):
+        before = [t.clone() for t in (arena.w, arena.g, arena.m, arena.v)]
+        self._orig(arena, gscale, lr_t_dev)
+        self.calls.append((before, [t.clone() for t in (arena.w, arena.m, arena.v)], self.opt.iterations, gscale))
+
+
+@pytest.mark.parametrize("image_size,batch", [((48, 64, 3), 3), ((144, 256, 3), 2)])
+def test_adam_updates_exact_on_engine_gradients(image_size, batch):
+    """Every apply_gradients of a step (1 generator + 2 discriminator, SNDCGAN.py:249,257,267) against Keras-2 Adam
+    (oracle/keras_ops.adam_step evaluated in fp64) applied to the engine's OWN gradient arena: the update
+    w_after - w_before must match to fp32 rounding (<= 1e-5 rel-L2 of the update; m, v <= 1e-6).  Replaces the vacuous
+    mean|dw| < 0.5 lr bound."""
+    from imagegeneration_b200.sndcgan import SNDCGANEngine
+    eng = SNDCGANEngine(batch, dropout=0.5, image_size=image_size, seed=62, cuda_graph=False)
+    g = torch.Generator().manual_seed(99)
+    rec_g, rec_d = _AdamRecorder(eng.g_optimizer), _AdamRecorder(eng.d_optimizer)
+    for step in range(2):
+        real = torch.rand((batch, *image_size), generator=g) * 2 - 1
+        z = torch.rand((batch, 128), generator=g) * 2 - 1
+        eng.train_step(real.cuda(), z.cuda())
+    torch.cuda.synchronize()
+    assert [c[2] for c in rec_g.calls] == [1, 2] and [c[2] for c in rec_d.calls] == [1, 2, 3, 4]
+    for tag, rec, lr in (("G", rec_g, 2e-4), ("D", rec_d, 2e-4)):
+        for (w0, g0, m0, v0), (w1, m1, v1), t, gscale in rec.calls:
+            w, gg, m, v = (x.double().cpu() for x in (w0, g0 * gscale, m0, v0))
+            K.adam_step(w, gg, m, v, t, lr)
+            assert float(gg.abs().max()) > 0, f"{tag} t={t}: gradient arena is all zero"
+            assert _rel_l2(m1, m) < 1e-6 and _rel_l2(v1, v) < 1e-6, f"{tag} t={t} slots"
+            assert _rel_l2(w1.double().cpu() - w0.double().cpu(), w - w0.double().cpu()) < 1e-5, f"{tag} t={t} update"
+
+
+def _oracle_graph(orc, real, z, masks, image_size):
+    """Generator-step graph of the oracle with every intermediate kept: returns the collect dict, the loss-side
+    gradients w.r.t. the saved activations needed to teacher-force the engine, and the parameter gradients."""
+    for p in orc.gv + orc.dv:
+        p.requires_grad_(True)
+    col = {}
+    g_out = O.generator_forward(orc.gv, z, image_size, col)
+    logits = O.discriminator_forward(orc.dv, g_out, orc.dropout, masks, col, None, "da")
+    loss = O.g_loss_fn("bce", logits)
+    g_grads = torch.autograd.grad(loss, orc.gv, retain_graph=True)
+    d_gout, d_logits = torch.autograd.grad(loss, [col["g_out"], logits], retain_graph=True)
+    d_grads = torch.autograd.grad(loss, orc.dv)
+    for p in orc.gv + orc.dv:
+        p.requires_grad_(False)
+    return col, g_grads, d_grads, d_gout.detach(), d_logits.detach(), float(loss)
+
+
+@pytest.mark.parametrize("image_size,batch", [((48, 64, 3), 3), ((144, 256, 3), 2)])
+@pytest.mark.parametrize("dropout", [0.0, 0.5])
+def test_teacher_forced_backward_matches_oracle(image_size, batch, dropout):
+    """The engine's hand-scheduled backward passes, fed the fp32 oracle's saved activations (rounded to the bf16 the
+    engine stores), its dL/dlogit and its dL/d(pre-tanh image).  With the masks pinned, bf16 storage error is the only
+    difference: every gradient tensor must be within 2e-2 rel-L2 of the fp32 oracle (measured <= 8e-3) — a 10 % scale
+    error in a fused epilogue (dropout keep-scale, column sums, gamma fold) cannot pass."""
+    from imagegeneration_b200.sndcgan import SNDCGANEngine
+    eng = SNDCGANEngine(batch, dropout=dropout, image_size=image_size, seed=62, cuda_graph=False)
+    orc = O.OracleSNDCGAN(image_size, dropout=dropout, seed=62)
+    gen = torch.Generator().manual_seed(5)
+    for lst, model in ((orc.gv, eng.gen_model), (orc.dv, eng.disc_model)):
+        for v in lst:                      # non-trivial gammas / betas / biases so that their gradients are exercised
+            if v.dim() == 1:
+                v.add_((torch.rand(v.shape, generator=gen) - 0.5) * 0.2)
+        model.set_weights(lst)
+    g = torch.Generator().manual_seed(77)
+    real = torch.rand((batch, *image_size), generator=g) * 2 - 1
+    z = torch.rand((batch, 128), generator=g) * 2 - 1
+    seeds = [4242 + i for i in range(7)]
+    t8 = eng.disc_model.thresh8
+    masks = _masks(image_size, batch, seeds, t8) if dropout else None
+    col, g_grads, d_grads, d_gout, d_logits, _ = _oracle_graph(orc, real, z, masks, image_size)
+    G, D = eng.gen_model, eng.disc_model
+    bf = lambda t: t.detach().to(torch.bfloat16).cuda().contiguous()
+
+    # ---- discriminator: forward once on the oracle's generated image (allocates buffers, packs weights), then
+    # overwrite what backward reads with the oracle's tensors
+    g_out = col["g_out"].detach().float().cuda().contiguous()
+    D.forward(g_out, training=True, dropout_seeds=seeds)
+    D.head_loss(0, 1.0, 1.0 / batch)
+    for i in range(7):
+        D._acts[i].copy_(bf(col[f"da_c{i + 1}"]))
+    D._dlogit.copy_(d_logits.flatten().cuda())
+    d_in = D.backward(need_wgrad=True, need_input_grad=True, g_out=g_out)
+    torch.cuda.synchronize()
+    for name, a, b in zip(D.arena.names, D.arena.grads, d_grads):
+        assert _rel_l2(a, b) < 2e-2, f"D grad {name}: {_rel_l2(a, b)}"
+    d_pre_tanh = d_gout * (1 - col["g_out"].detach() ** 2)
+    assert _rel_l2(d_in, d_pre_tanh) < 2e-2, "dL/d(pre-tanh generator output)"
+
+    # ---- generator: forward for buffers, then oracle activations + oracle's upstream gradient
+    G.forward(z.cuda())
+    for i in range(4):
+        G._acts[i].copy_(bf(col[f"g_a{i}"]))
+    G.backward(d_pre_tanh.float().cuda().contiguous())
+    torch.cuda.synchronize()
+    for name, a, b in zip(G.arena.names, G.arena.grads, g_grads):
+        assert _rel_l2(a, b) < 2e-2, f"G grad {name}: {_rel_l2(a, b)}"

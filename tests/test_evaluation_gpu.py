@@ -64,7 +64,7 @@ def test_calculate_fid_end_to_end():
 def test_evaluate_fid_loop_over_saved_generators():
     """generator_evaluation.py:156-175: one FID per (saved generator, real batch); identical generators give identical
     scores, a perturbed generator a different one; every score matches the oracle on the same fakes."""
-    from imagegeneration_b200.evaluation import evaluate_fid
+    from imagegeneration_b200.evaluation import evaluate_fid_models as evaluate_fid
     from imagegeneration_b200.sndcgan import create_samples, make_dcgan_discriminator, make_dcgan_generator
     from oracle import sndcgan_oracle as O
     image = (64, 128, 3)

@@ -82,9 +82,14 @@ def test_loss_bn_adam_semantics():
     g = torch.tensor([0.1], dtype=torch.float64)
     K.adam_step(w, g, m, v, 1, 2e-4)
     lr1 = 2e-4 * math.sqrt(1 - 0.999) / (1 - 0.9)
-    assert abs(float(w) - (1.0 - lr1 * 0.01 / (math.sqrt(1e-5) + 1e-7))) < 1e-12
+    # Keras forms (1 - beta) in the variable dtype, fp32: 1 - float32(0.9), 1 - float32(0.999)
+    c1, c2 = float(np.float32(1) - np.float32(0.9)), float(np.float32(1) - np.float32(0.999))
+    assert abs(c2 - 0.001) / 0.001 > 1e-5                                      # the fp32 constant is visibly not 0.001
+    assert abs(float(w) - (1.0 - lr1 * 0.1 * c1 / (math.sqrt(0.01 * c2) + 1e-7))) < 1e-12
     K.adam_step(w, g, m, v, 2, 2e-4)
-    assert abs(float(m) - 0.019) < 1e-12 and abs(float(v) - (1e-5 + 0.999e-5)) < 1e-12
+    m2 = 0.1 * c1 + (0.1 - 0.1 * c1) * c1
+    v2 = 0.01 * c2 + (0.01 - 0.01 * c2) * c2
+    assert abs(float(m) - m2) < 1e-12 and abs(float(v) - v2) < 1e-12
     assert abs(float(K.leaky_relu(torch.tensor([-2.0]))) + 0.2) < 1e-7
     assert float(K.dropout(torch.ones(4), torch.tensor([1.0, 0, 1, 0]), 0.5).sum()) == 4.0
 

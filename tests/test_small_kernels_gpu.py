@@ -382,3 +382,73 @@ def test_pack_plan_matches_single_packs():
     plan.run()
     kind, _shape, kw = jobs[0]
     assert torch.equal(outs[0], ops.pack_conv_weight(kind, ws[0], **kw))
+
+
+def test_adam_fused_with_spectral_norm():
+    """b2g_sn_dot_multi + b2g_adam_sn (spectral norm riding on the optimizer pass, north_star item 2) on the real
+    discriminator arena layout (8 matrices + biases) vs fp64: gradient through W/sigma, Keras Adam, and the NEXT power
+    iteration on the updated weights (sigma <= 1e-5 relative, Miyato et al. Alg. 1: one iteration per update)."""
+    from imagegeneration_b200 import lib as L
+    lib = L.load()
+    shapes = [(27, 64), (1024, 128), (1152, 128), (2048, 256), (2304, 256), (4096, 512), (4608, 512), (2304, 1)]
+    offs, pos = [], 0
+    for k, c in shapes:                       # kernel, then its bias (cout floats, padded to 4) like ParamArena
+        offs.append(pos)
+        pos += (k * c + 3) // 4 * 4
+        pos += (c + 3) // 4 * 4
+    n = pos
+    w = _rand((n,), 200, 0.05)
+    gen = torch.Generator().manual_seed(201)
+    for (k, c), o in zip(shapes, offs):       # spectral gap so that one iteration is well conditioned
+        a, b = torch.randn(k, generator=gen), torch.randn(c, generator=gen)
+        w[o:o + k * c] += (0.5 * torch.outer(a / a.norm(), b / b.norm())).flatten()
+    g = _rand((n,), 202, 0.01)
+    m = _rand((n,), 203, 0.003)
+    v = _rand((n,), 204, 1.0).abs() * 1e-4
+    us = []
+    for k, c in shapes:
+        u = torch.randn(c, generator=gen)
+        us.append(u / u.norm())
+    wc, gc, mc, vc = w.cuda(), g.cuda(), m.cuda(), v.cuda()
+    uc = [u.clone().cuda() for u in us]
+    vr = [torch.zeros(s[0], device="cuda") for s in shapes]
+    tr = [torch.zeros(s[1], device="cuda") for s in shapes]
+    sc = [torch.zeros(8, device="cuda") for s in shapes]
+    dots = torch.zeros(8, device="cuda")
+    arr = lambda ts: (C.c_void_p * 8)(*[t.data_ptr() for t in ts])
+    Ks = (C.c_int * 8)(*[s[0] for s in shapes])
+    Cs = (C.c_int * 8)(*[s[1] for s in shapes])
+    off_c = (C.c_long * 8)(*offs)
+    Wv = [wc[o:o + k * c] for (k, c), o in zip(shapes, offs)]
+    # the iteration the "forward pass" used
+    L.check(lib.b2g_spectral_norm_multi(8, arr(Wv), arr(uc), arr(vr), arr(tr), arr(sc), Ks, Cs, _s()), "sn", 2)
+    torch.cuda.synchronize()
+    u1 = [u.double().cpu() for u in uc]
+    v1 = [(x / x.norm()).double().cpu() for x in vr]
+    sig1 = [float(s[1]) for s in sc]
+    lr_t, b1, b2, eps, gscale = 3e-4, 0.9, 0.999, 1e-7, 0.5
+    L.check(lib.b2g_sn_dot_multi(_p(wc), _p(gc), 8, off_c, Ks, Cs, _p(dots), _s()), "dot")
+    L.check(lib.b2g_adam_sn(_p(wc), _p(gc), _p(mc), _p(vc), n, 8, off_c, Ks, Cs, arr(uc), arr(vr), arr(tr), arr(sc),
+                            _p(dots), lr_t, None, b1, b2, eps, gscale, _s()), "adam_sn")
+    torch.cuda.synchronize()
+    assert float(dots.abs().max()) == 0.0                     # consumed and re-zeroed
+    # reference in fp64
+    wd, gd, md, vd = w.double(), g.double().clone(), m.double(), v.double()
+    for i, ((k, c), o) in enumerate(zip(shapes, offs)):
+        W = wd[o:o + k * c].reshape(k, c)
+        G = gd[o:o + k * c].reshape(k, c)
+        dot = float((W * G).sum())
+        gd[o:o + k * c] = (G / sig1[i] - dot / sig1[i] ** 2 * torch.outer(v1[i], u1[i])).flatten()
+    gd *= gscale
+    md = md + (gd - md) * (1 - b1)
+    vd = vd + (gd * gd - vd) * (1 - b2)
+    w_new = wd - lr_t * md / (vd.sqrt() + eps)
+    assert _rel_l2(mc, md) < 1e-5 and _rel_l2(vc, vd) < 1e-5
+    assert _rel_l2(wc.double().cpu() - wd, w_new - wd) < 2e-4    # the update itself (fp32 rounding of w dominates)
+    assert _rel_l2(wc, w_new) < 1e-6
+    for i, ((k, c), o) in enumerate(zip(shapes, offs)):
+        Wn = w_new[o:o + k * c].reshape(k, c)
+        sigma, u2, v2 = K.spectral_norm_power_iteration(Wn, u1[i], 1)
+        assert abs(float(sc[i][1]) - float(sigma)) / float(sigma) < 1e-5, f"sigma layer {i}"
+        assert _rel_l2(uc[i], u2) < 1e-4 and _rel_l2(vr[i] / vr[i].norm(), v2) < 1e-4, f"u/v layer {i}"
+        assert float(tr[i].abs().max()) == 0.0 and float(sc[i][0]) == 0.0   # scratch re-zeroed for the next call

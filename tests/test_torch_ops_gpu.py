@@ -1,0 +1,107 @@
+"""The torch.library custom ops (imagegeneration_b200/torch_ops.py): `disc_model(x)` / `gen_model(z)` compose with torch
+autograd, so any loss can be put on top and `.backward()` fills the parameters' `.grad` (boundary item).
+
+Checked against (a) the engine's own hand-scheduled backward for the reference's BCE loss — same kernels, the only
+difference is where the activation derivative is applied (<= 1e-2 rel-L2) — and (b) the fp32 CPU oracle's autograd for a
+loss the engine does not have (least-squares GAN loss), dropout off so that no mask can differ (<= 5e-2: bf16 storage,
+measured ~1e-2)."""
+import pytest
+import torch
+
+from oracle import sndcgan_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel_l2(a, b):
+    a = a.double().flatten().cpu()
+    b = b.double().flatten().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def _models(image_size, dropout):
+    from imagegeneration_b200.sndcgan import make_dcgan_discriminator, make_dcgan_generator
+    G = make_dcgan_generator(image_size, seed=62)
+    D = make_dcgan_discriminator(dropout, image_size, seed=63)
+    gen = torch.Generator().manual_seed(5)
+    for m in (G, D):                     # non-trivial gammas / betas / biases
+        ws = [v.detach().cpu().clone() for v in m.trainable_variables]
+        for v in ws:
+            if v.dim() == 1:
+                v.add_((torch.rand(v.shape, generator=gen) - 0.5) * 0.2)
+        m.set_weights(ws)
+    return G, D
+
+
+@pytest.mark.parametrize("image_size,batch", [((16, 32, 3), 4), ((48, 64, 3), 3)])
+def test_autograd_graph_matches_engine_backward(image_size, batch):
+    from imagegeneration_b200.torch_ops import BinaryCrossentropy
+    G, D = _models(image_size, 0.5)
+    z = (torch.rand((batch, 128), generator=torch.Generator().manual_seed(1)) * 2 - 1).cuda()
+    seeds = [777 + i for i in range(7)]
+    # engine path: generator step of SNDCGAN.train_step (:243-248)
+    g_out = G.forward(z)
+    D.forward(g_out, training=True, dropout_seeds=seeds)
+    loss_e, _ = D.head_loss(0, 1.0, 1.0 / batch)
+    d_in = D.backward(need_wgrad=True, need_input_grad=True, g_out=g_out)
+    G.backward(d_in)
+    torch.cuda.synchronize()
+    eg = [g.clone() for g in G.arena.grads]
+    ed = [g.clone() for g in D.arena.grads]
+    loss_e = float(loss_e)
+    # autograd path: the same computation as a torch graph of b200gan ops
+    gp, dp = G.parameters(), D.parameters()
+    loss_fn = BinaryCrossentropy(from_logits=True)
+    with torch.enable_grad():
+        logits = D(G(z), training=True, dropout_seeds=seeds)
+        loss = loss_fn(torch.ones_like(logits), logits)
+        loss.backward()
+    torch.cuda.synchronize()
+    assert abs(float(loss) - loss_e) < 1e-4 * max(1.0, abs(loss_e))
+    for name, p, ref in zip(D.arena.names, dp, ed):
+        assert p.grad is not None and _rel_l2(p.grad, ref) < 1e-2, f"D {name}: {_rel_l2(p.grad, ref)}"
+    for name, p, ref in zip(G.arena.names, gp, eg):
+        assert p.grad is not None and _rel_l2(p.grad, ref) < 1e-2, f"G {name}: {_rel_l2(p.grad, ref)}"
+
+
+def test_custom_loss_on_top_of_disc_model_matches_oracle():
+    """A loss the engine does not implement (LSGAN: mean((D(x) - 1)^2)) on top of disc_model(x), differentiated by torch
+    autograd through the b200gan ops, against the CPU oracle's autograd (dropout 0, inference-free: training=True)."""
+    image_size, batch = (48, 64, 3), 3
+    G, D = _models(image_size, 0.0)
+    orc_dv = [v.detach().cpu().clone() for v in D.trainable_variables]
+    x = torch.rand((batch, *image_size), generator=torch.Generator().manual_seed(2)) * 2 - 1
+    dp = D.parameters()
+    with torch.enable_grad():
+        logits = D(x.cuda(), training=True)
+        loss = ((logits - 1.0) ** 2).mean()
+        loss.backward()
+    torch.cuda.synchronize()
+    for v in orc_dv:
+        v.requires_grad_(True)
+    ref_logits = O.discriminator_forward(orc_dv, x, 0.0, None)
+    ref_loss = ((ref_logits - 1.0) ** 2).mean()
+    ref_grads = torch.autograd.grad(ref_loss, orc_dv)
+    assert abs(float(loss) - float(ref_loss)) < 2e-2 * max(1.0, abs(float(ref_loss)))
+    for name, p, ref in zip(D.arena.names, dp, ref_grads):
+        assert _rel_l2(p.grad, ref) < 5e-2, f"{name}: {_rel_l2(p.grad, ref)}"
+
+
+def test_loss_fn_attribute_and_no_cpu_fallback():
+    from imagegeneration_b200.lib import B200GanError
+    from imagegeneration_b200.sndcgan import SNDCGANEngine
+    from oracle import keras_ops as K
+    eng = SNDCGANEngine(4, image_size=(16, 32, 3))
+    x = torch.randn(8, 1)
+    y = (torch.rand(8, 1) > 0.5).float()
+    xc = x.cuda().requires_grad_(True)
+    loss = eng.loss_fn(y.cuda(), xc)                       # reference attribute (SNDCGAN.py:170)
+    loss.backward()
+    xr = x.clone().requires_grad_(True)
+    per = torch.clamp(xr, min=0) - xr * y + torch.log1p(torch.exp(-xr.abs()))
+    ref = per.mean()
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 1e-6 and _rel_l2(xc.grad, xr.grad) < 1e-5
+    assert abs(float(eng.loss_fn(torch.ones(8, 1).cuda(), x.cuda())) - float(K.bce_with_logits(x, 1.0))) < 1e-6
+    with pytest.raises(B200GanError):
+        eng.loss_fn(y, x)                                  # CPU tensors: no fallback
