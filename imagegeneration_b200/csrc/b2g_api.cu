@@ -78,85 +78,140 @@ constexpr int kPackTileN = 32, kPackTileC = 64;
 struct PackJobDev {
   int kind, kh, kw, D2, D3, n_is_d3, flip, ck_pad, taps, phases, first_block;
   int Cn, Ckr, Ck, n_blocks, c_blocks;
+  int f32;  // fp32 packing (rounded to tf32) instead of bf16
   const float *w, *scale_scalar, *scale_d2, *scale_d3;
-  __nv_bfloat16* out;
+  void* out;
 };
 struct alignas(16) PackMultiParams {
   PackJobDev job[kMaxPackJobs];
   int n_jobs;
 };
 
-__global__ void __launch_bounds__(256) pack_conv_weight_multi_kernel(const __grid_constant__ PackMultiParams p) {
-  __shared__ float tile[kPackTileN][kPackTileC + 1];
+struct PackTile {
+  const PackJobDev* q;
+  const float* src;  // [D2][D3] plane of this tile's tap
+  int ph, tap, n0, c0;
+};
+__device__ __forceinline__ PackTile pack_tile_decode(const PackMultiParams& p, int t) {
   int j = 0;
-  while (j + 1 < p.n_jobs && (int)blockIdx.x >= p.job[j + 1].first_block) ++j;
+  while (j + 1 < p.n_jobs && t >= p.job[j + 1].first_block) ++j;
   const PackJobDev& q = p.job[j];
-  int t = blockIdx.x - q.first_block;
+  t -= q.first_block;
+  PackTile o;
+  o.q = &q;
   const int cb = t % q.c_blocks; t /= q.c_blocks;
   const int nb = t % q.n_blocks; t /= q.n_blocks;
-  const int tap = t % q.taps;
-  const int ph = t / q.taps;
-  const int n0 = nb * kPackTileN, c0 = cb * kPackTileC;
+  o.tap = t % q.taps;
+  o.ph = t / q.taps;
+  o.n0 = nb * kPackTileN;
+  o.c0 = cb * kPackTileC;
   int ky, kx;
   if (q.kind == B2G_CONVT_K4S2) {
     int d;
-    convt_tap(ph >> 1, tap >> 1, &ky, &d);
-    convt_tap(ph & 1, tap & 1, &kx, &d);
+    convt_tap(o.ph >> 1, o.tap >> 1, &ky, &d);
+    convt_tap(o.ph & 1, o.tap & 1, &kx, &d);
   } else {
-    ky = tap / q.kw;
-    kx = tap % q.kw;
+    ky = o.tap / q.kw;
+    kx = o.tap % q.kw;
     if (q.flip) {
       ky = q.kh - 1 - ky;
       kx = q.kw - 1 - kx;
     }
   }
-  const float* src = q.w + ((size_t)ky * q.kw + kx) * q.D2 * q.D3;  // [D2][D3] plane of this tap
+  o.src = q.w + ((size_t)ky * q.kw + kx) * q.D2 * q.D3;
+  return o;
+}
+// the 8 scaled fp32 values this thread contributes to a tile (coalesced along whichever of n / c is contiguous)
+__device__ __forceinline__ void pack_tile_load(const PackTile& t, int tid, float (&v)[8]) {
+  const PackJobDev& q = *t.q;
   const float s0 = q.scale_scalar ? *q.scale_scalar : 1.f;
-  const int tid = threadIdx.x;
   if (q.n_is_d3) {  // n = d3 is the contiguous source index: a warp reads 32 consecutive n of one c
     const int nx = tid & 31, cy = tid >> 5;
-    const int n = n0 + nx;
+    const int n = t.n0 + nx;
     const float sn = (q.scale_d3 && n < q.Cn) ? q.scale_d3[n] : 1.f;
 #pragma unroll
-    for (int r = 0; r < kPackTileC / 8; ++r) {
-      const int cl = cy + 8 * r, c = c0 + cl;
-      float v = 0.f;
+    for (int r = 0; r < 8; ++r) {
+      const int c = t.c0 + cy + 8 * r;
+      float x = 0.f;
       if (n < q.Cn && c < q.Ckr) {
-        v = src[(size_t)c * q.D3 + n] * s0;  // same multiplication order as the single-tensor kernel
-        if (q.scale_d2) v *= q.scale_d2[c];
-        v *= sn;
+        x = t.src[(size_t)c * q.D3 + n] * s0;  // same multiplication order as the single-tensor kernel
+        if (q.scale_d2) x *= q.scale_d2[c];
+        x *= sn;
       }
-      tile[nx][cl] = v;
+      v[r] = x;
     }
   } else {  // c = d3 is contiguous: 64 consecutive c of one n
     const int cx = tid & 63, ny = tid >> 6;
-    const int c = c0 + cx;
+    const int c = t.c0 + cx;
     const float sc = (q.scale_d3 && c < q.Ckr) ? q.scale_d3[c] : 1.f;
 #pragma unroll
-    for (int r = 0; r < kPackTileN / 4; ++r) {
-      const int nl = ny + 4 * r, n = n0 + nl;
-      float v = 0.f;
+    for (int r = 0; r < 8; ++r) {
+      const int n = t.n0 + ny + 4 * r;
+      float x = 0.f;
       if (n < q.Cn && c < q.Ckr) {
-        v = src[(size_t)n * q.D3 + c] * s0;
-        if (q.scale_d2) v *= q.scale_d2[n];
-        v *= sc;
+        x = t.src[(size_t)n * q.D3 + c] * s0;
+        if (q.scale_d2) x *= q.scale_d2[n];
+        x *= sc;
       }
-      tile[nl][cx] = v;
+      v[r] = x;
     }
   }
-  __syncthreads();
-  // out[ph][n][tap * Ck + c]: 8 threads write the 64 columns of one row (16 bytes each)
-  const int nl = tid >> 3, c8 = (tid & 7) * 8;
-  const int n = n0 + nl;
-  if (n < q.Cn && c0 + c8 < q.Ck) {
-    const float* tr = &tile[nl][c8];
-    uint4 o;
-    o.x = pack_bf16x2(tr[0], tr[1]);
-    o.y = pack_bf16x2(tr[2], tr[3]);
-    o.z = pack_bf16x2(tr[4], tr[5]);
-    o.w = pack_bf16x2(tr[6], tr[7]);
-    __nv_bfloat16* dst = q.out + ((size_t)ph * q.Cn + n) * ((size_t)q.taps * q.Ck) + (size_t)tap * q.Ck + c0 + c8;
-    *reinterpret_cast<uint4*>(dst) = o;
+}
+
+// Persistent blocks: tile t, t + gridDim.x, ...; the NEXT tile's loads are in flight while the current one goes through
+// shared memory (round 1 ran one tile per block: ~6 000 short-lived blocks, 34 us for 75 MB of traffic).
+__global__ void __launch_bounds__(256) pack_conv_weight_multi_kernel(const __grid_constant__ PackMultiParams p,
+                                                                     int total_tiles) {
+  __shared__ float tile[kPackTileN][kPackTileC + 1];
+  const int tid = threadIdx.x;
+  int t = blockIdx.x;
+  if (t >= total_tiles) return;
+  PackTile cur = pack_tile_decode(p, t), nxt = cur;
+  float v[8], vn[8];
+  pack_tile_load(cur, tid, v);
+  for (; t < total_tiles; t += gridDim.x) {
+    const int tn = t + gridDim.x;
+    if (tn < total_tiles) {
+      nxt = pack_tile_decode(p, tn);
+      pack_tile_load(nxt, tid, vn);
+    }
+    const PackJobDev& q = *cur.q;
+    __syncthreads();  // the previous tile's readers are done with the shared tile
+    if (q.n_is_d3) {
+      const int nx = tid & 31, cy = tid >> 5;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) tile[nx][cy + 8 * r] = v[r];
+    } else {
+      const int cx = tid & 63, ny = tid >> 6;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) tile[ny + 4 * r][cx] = v[r];
+    }
+    __syncthreads();
+    // out[ph][n][tap * Ck + c]: 8 threads write the 64 columns of one row (16 bytes each)
+    const int nl = tid >> 3, c8 = (tid & 7) * 8;
+    const int n = cur.n0 + nl;
+    if (n < q.Cn && cur.c0 + c8 < q.Ck) {
+      const float* tr = &tile[nl][c8];
+      const size_t off = ((size_t)cur.ph * q.Cn + n) * ((size_t)q.taps * q.Ck) + (size_t)cur.tap * q.Ck + cur.c0 + c8;
+      if (q.f32) {  // rounded to nearest tf32 here: tcgen05 kind::tf32 truncates the low 13 mantissa bits of what it reads
+        uint32_t t[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t[k]) : "f"(tr[k]));
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<float*>(q.out) + off);
+        dst[0] = make_uint4(t[0], t[1], t[2], t[3]);
+        dst[1] = make_uint4(t[4], t[5], t[6], t[7]);
+      } else {
+        uint4 o;
+        o.x = pack_bf16x2(tr[0], tr[1]);
+        o.y = pack_bf16x2(tr[2], tr[3]);
+        o.z = pack_bf16x2(tr[4], tr[5]);
+        o.w = pack_bf16x2(tr[6], tr[7]);
+        *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(q.out) + off) = o;
+      }
+    }
+    cur = nxt;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) v[r] = vn[r];
   }
 }
 
@@ -261,11 +316,13 @@ extern "C" int b2g_pack_conv_weight_multi(const b2g_pack_job* jobs, int n_jobs, 
     d.c_blocks = (ck + kPackTileC - 1) / kPackTileC;
     d.first_block = blocks;
     d.w = s.w; d.scale_scalar = s.scale_scalar; d.scale_d2 = s.scale_d2; d.scale_d3 = s.scale_d3;
-    d.out = static_cast<__nv_bfloat16*>(s.wpacked);
+    d.out = s.wpacked;
+    d.f32 = s.f32;
     blocks += phases * taps * d.n_blocks * d.c_blocks;
   }
   p.n_jobs = n_jobs;
-  pack_conv_weight_multi_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+  const int cap = num_sms() * 6;
+  pack_conv_weight_multi_kernel<<<blocks < cap ? blocks : cap, 256, 0, static_cast<cudaStream_t>(stream_)>>>(p, blocks);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }

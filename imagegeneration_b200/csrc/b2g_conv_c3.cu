@@ -40,7 +40,8 @@ struct C3Cfg {
   static constexpr int kABytes = 128 * 128;  // 128 pixel rows of 128 B; only the first 64 B (K = 32) are used
   static constexpr int kStages = 6;
   static constexpr int kInStages = 8;           // staged fp32 input boxes
-  static constexpr int kInStageBytes = 8192;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896)
+  static constexpr int kInStageBytes = 6144;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896); 8 KiB in
+                                                // round 1, the 16 KiB went to the epilogue's second boxes
   static constexpr int kBBytes = kBlockN * 128;
   static constexpr int kAccBufs = 4;
   static constexpr int kTmemCols = kAccBufs * kBlockN;
@@ -49,7 +50,9 @@ struct C3Cfg {
   static constexpr int kThreads = 64 + 32 * kBuilderWarps + 128 * kEpiGroups;
   static constexpr int kMainBytes = kStages * kABytes + kBBytes + kInStages * kInStageBytes;  // multiple of 1 KiB
   static constexpr int kEpiWarps = 4 * kEpiGroups;
-  static constexpr int kSmemBytes = kMainBytes + epi_tma_smem_bytes(kEpiWarps) + 512 + 1024;
+  static constexpr int kEpiBoxes = 2;           // boxes per epilogue warp (b2g_conv_epi.cuh)
+  static constexpr int kEpiBytes = epi_tma_smem_bytes(kEpiWarps, kEpiBoxes);
+  static constexpr int kSmemBytes = kMainBytes + kEpiBytes + 512 + 1024;
 };
 
 __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __grid_constant__ C3KernelParams p) {
@@ -63,7 +66,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
   uint8_t* bsm = smem + Cfg::kStages * Cfg::kABytes;
   uint8_t* insm = bsm + Cfg::kBBytes;
   uint8_t* epism = smem + Cfg::kMainBytes;  // per-warp boxes of the TMA epilogue
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epism + epi_tma_smem_bytes(Cfg::kEpiWarps));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epism + Cfg::kEpiBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint64_t* tempty_bar = tfull_bar + Cfg::kAccBufs;
@@ -91,7 +94,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       mbar_init(&in_full[s], 1);
       mbar_init(&in_empty[s], Cfg::kBuilderWarps);
     }
-    if (p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps);
+    if (p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps, Cfg::kEpiBoxes);
     fence_barrier_init();
   }
   epi_load_bias(p.e, sbias, BLOCK_N);
@@ -114,8 +117,8 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     __syncwarp();
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const TileCoord tc = decode_tile(pl, 1, tile);
+    TileWalk tc = tile_walk_begin(pl, blockIdx.x, gridDim.x);
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, tile_walk_next(pl, tc)) {
       mbar_wait(&in_empty[stage], phase ^ 1);
       if (leader) {
         mbar_expect_tx(&in_full[stage], p.in_box_bytes);
@@ -205,24 +208,38 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     const int wl = row % pl.bw, hl = (row / pl.bw) % pl.bh, nl = row / (pl.bw * pl.bh);
     // origin of this warp's 32-pixel box inside a tile (TMA epilogue)
     const int wl0 = (q * 32) % pl.bw, hl0 = ((q * 32) / pl.bw) % pl.bh, nl0 = (q * 32) / (pl.bw * pl.bh);
-    EpiWarpStage st = epi_tma_stage(epism, Cfg::kEpiWarps, warp - 2 - Cfg::kBuilderWarps);
+    constexpr int NB = Cfg::kEpiBoxes;
+    EpiWarpStageN<NB> st = epi_tma_stage<NB>(epism, Cfg::kEpiWarps, warp - 2 - Cfg::kBuilderWarps);
     const bool use_tma = p.e.tma != 0;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int c = (grp - it * kChunks) & (Cfg::kEpiGroups - 1);  // chunk c of tile `it` belongs to group (2*it + c) % 4
-      if (c >= kChunks) continue;
+    // Chunk c of tile number i (counted per CTA) belongs to epilogue group (2 * i + c) % 4, i.e. group g owns chunk g & 1 of
+    // every other tile, starting with tile number g >> 1: one division-free walk with stride 2 * gridDim.x per warp.
+    static_assert(kChunks == 2 && Cfg::kEpiGroups == 4, "chunk-to-group rotation below assumes 2 chunks, 4 groups");
+    const int c = grp & 1;
+    const int stride = 2 * gridDim.x;
+    int it = grp >> 1;
+    int tile = blockIdx.x + it * gridDim.x;
+    TileWalk tc = tile_walk_begin(pl, tile, stride);
+    for (; tile < total_tiles; tile += stride, it += 2, tile_walk_next(pl, tc)) {
       const int as = it % Cfg::kAccBufs;
-      const TileCoord tc = decode_tile(pl, 1, tile);
       const int gw = tc.tw * pl.bw + wl, gh = tc.th * pl.bh + hl, gn = tc.tn * pl.bn + nl;
       const bool valid = (gh < pl.Hg) && (gn < pl.N);
       const size_t pix = (static_cast<size_t>(gn) * pl.Hout + gh) * pl.Wout + gw;
       const int bx = tc.tw * pl.bw + wl0, by = tc.th * pl.bh + hl0, bn = tc.tn * pl.bn + nl0;
-      if (use_tma) epi_tma_begin(p.e, &p.em.ymap[0], st, c * 32, bx, by, bn);
+      // the saved-output load of this item (backward epilogue) was started right after the previous item (second box);
+      // the very first one starts here, before the accumulator wait
+      if (use_tma && st.k_begin == st.k_chunk) epi_tma_begin(e, &p.em.ymap[0], st, c * 32, bx, by, bn);
       mbar_wait_parked(&tfull_bar[as], (it / Cfg::kAccBufs) & 1);
       tc_fence_after();
       uint32_t r[32];
       __syncwarp();
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
+      if (use_tma && tile + stride < total_tiles) {
+        // the warp's next item (two tiles on) is begun into the other box now: the store that last used that box is two
+        // items old, and the load has until the next accumulator to arrive
+        TileWalk nx = tc;
+        tile_walk_next(pl, nx);
+        epi_tma_begin(e, &p.em.ymap[0], st, c * 32, nx.tw * pl.bw + wl0, nx.th * pl.bh + hl0, nx.tn * pl.bn + nl0);
+      }
       tmem_ld_wait();
       if (use_tma) epi_tma_chunk(e, &p.em.omap[0], st, sbias, r, pix, c * 32, lane, bx, by, bn, s_colsum, sd);
       else conv_epilogue_chunk(e, sbias, r, pix, c * 32, valid, s_colsum, sd);

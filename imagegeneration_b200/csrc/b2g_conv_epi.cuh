@@ -42,6 +42,8 @@ struct EpiParams {
   int cs_copies;  // the per-CTA column-sum tables hold this many copies of [Cout] (512 / Cout in the 512-float tables):
                   // warp w adds into copy w % cs_copies — fp32 shared-memory atomicAdd is a compare-and-swap loop,
                   // and with Cout = 64 eight epilogue warps would otherwise fight over the same 32 words per chunk
+  int dbg;      // measurement switch (env B2G_DBG_EPI, never set in production): bit 0 = epilogue warps drain the
+                // accumulators but skip math, saved-output loads and stores -> the launch time is the MMA/load pipeline alone
   int tma;      // 1: bf16 output (and yprev) move through per-warp shared-memory boxes and TMA (EpiTmaMaps)
   int qw, qh, qn;  // the 32 pixels one epilogue warp owns, as a box of the tile (qw * qh * qn == 32)
 };
@@ -94,6 +96,24 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
   } else if (p.act == B2G_ACT_RELU) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  if (p.drop_thresh8 == 128 && valid && p.dact == B2G_ACT_NONE && !p.f32_io && !colsum_here) {
+    // rate 0.5 (the reference's default, Trainer.py:22) on a bf16 forward epilogue: "byte >= 128" is the byte's top bit,
+    // so the keep mask of a PAIR of elements is one PRMT in sign-replication mode and the drop one AND on the packed
+    // bf16x2 word: 2 instructions per pair instead of 5-6 compare/select ones (the epilogue of the 3-channel conv is
+    // instruction-issue bound: ncu r2, 10 % of its instructions were these selects).  Same mask, bit for bit.
+    const uint32_t g0 = static_cast<uint32_t>(off >> 2);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const uint32_t b0 = b2g_dropout_bits(g0 + 2 * g, sd.lo, sd.hi), b1 = b2g_dropout_bits(g0 + 2 * g + 1, sd.lo, sd.hi);
+      uint4 o;
+      o.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]) & b2g_keep_mask_pair(b0, 0);
+      o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]) & b2g_keep_mask_pair(b0, 1);
+      o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]) & b2g_keep_mask_pair(b1, 0);
+      o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]) & b2g_keep_mask_pair(b1, 1);
+      ostore(g, o);
+    }
+    return;
   }
   if (p.drop_thresh8 > 0 && valid) {
     // element i keeps its value iff byte (i & 3) of the group's hash >= thresh8: the byte is moved to the top of
@@ -212,6 +232,7 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
 __device__ __forceinline__ void conv_epilogue_chunk(const EpiParams& p, const float* sbias, const uint32_t (&r)[32],
                                                     size_t pix, int cb, bool valid, float* s_colsum = nullptr,
                                                     EpiSeed sd = EpiSeed{0u, 0u}) {
+  if (p.dbg & 1) return;
   if (p.out_f32) {  // narrow fp32 output (3 real channels): tanh / tanh' epilogues of the generator's last layer
     if (valid && cb < p.cs) {
       float* of = reinterpret_cast<float*>(p.out) + pix * p.cs + cb;
@@ -271,52 +292,91 @@ __device__ __forceinline__ void epi_colsum_flush(const EpiParams& p, const float
 // Here each epilogue warp owns one 2 KiB shared-memory box [32 pixels][32 channels] (64-byte swizzle, conflict
 // free 16-byte accesses): the saved output arrives in it by TMA, the results leave from it by TMA.
 // ---------------------------------------------------------------------------------------------------------------
-struct EpiWarpStage {
-  uint8_t* buf;     // this warp's box (1 KiB aligned)
-  uint64_t* ybar;   // mbarrier of the saved-output loads into buf
-  uint32_t yphase;
+// Every epilogue warp owns NB boxes.  Item k (the k-th 32-pixel x 32-channel chunk the warp processes, counted over the
+// whole kernel) lives in box k % NB: a backward (dact) epilogue first loads the SAVED forward output into it by TMA
+// (epi_tma_begin), the math runs in place, the result leaves by TMA (epi_tma_chunk).  With NB = 2 (where shared memory
+// allows) begin(k + 1) is issued while item k is still being computed.
+//
+// What round 2 measured about this epilogue (tools/conv_probe.py with B2G_DBG_EPI, ncu source pages, profiles/r2_*):
+//  * a backward item is 600-1000 instructions of ONE warp's dependent work; 8 warps with 3-box rings and run-ahead loads
+//    were 45 % SLOWER than 16 warps with one box — the epilogue needs warps and fewer instructions first;
+//  * fetching the saved output with ordinary global loads (registers, one item ahead) or cp.async instead of TMA was
+//    slower still: fence.proxy.async — needed before every TMA store — waits for the thread's outstanding loads, so the
+//    "prefetch" of item k + 1 stalled item k's store (ncu: FENCE.VIEW.ASYNC / ELECT with long-scoreboard stalls);
+//    TMA loads are not on the thread's scoreboard;
+//  * tile decoding by runtime division, per item, was 12 % of the instructions (now multiply-high, FastDiv), the column
+//    sums read back from the box 17 % (now 16 LDS.32 per lane instead of 32 LDS.U16 + unconditional squares).
+template <int NB>
+struct EpiWarpStageN {
+  uint8_t* buf;      // this warp's NB boxes (1 KiB aligned), box b at buf + b * kEpiStageBytes
+  uint64_t* ybar;    // NB mbarriers of the saved-output loads
+  uint32_t k_begin;  // items begun
+  uint32_t k_chunk;  // items processed
 };
+using EpiWarpStage = EpiWarpStageN<1>;
 
 // Shared memory the TMA epilogue needs behind a kernel's own buffers (1 KiB aligned): boxes, then mbarriers.
-__host__ __device__ constexpr int epi_tma_smem_bytes(int warps) { return warps * kEpiStageBytes + 256; }
+__host__ __device__ constexpr int epi_tma_smem_bytes(int warps, int nb = 1) {
+  return warps * nb * kEpiStageBytes + ((warps * nb * 8 + 255) / 256) * 256;
+}
 
-__device__ __forceinline__ EpiWarpStage epi_tma_stage(uint8_t* base, int warps, int w) {
-  EpiWarpStage st;
-  st.buf = base + w * kEpiStageBytes;
-  st.ybar = reinterpret_cast<uint64_t*>(base + warps * kEpiStageBytes) + w;
-  st.yphase = 0;
+template <int NB = 1>
+__device__ __forceinline__ EpiWarpStageN<NB> epi_tma_stage(uint8_t* base, int warps, int w) {
+  EpiWarpStageN<NB> st;
+  st.buf = base + w * NB * kEpiStageBytes;
+  st.ybar = reinterpret_cast<uint64_t*>(base + warps * NB * kEpiStageBytes) + w * NB;
+  st.k_begin = 0;
+  st.k_chunk = 0;
   return st;
 }
 // by one thread, before fence_barrier_init() and the block-wide sync
-__device__ __forceinline__ void epi_tma_init(uint8_t* base, int warps) {
-  for (int w = 0; w < warps; ++w) mbar_init(reinterpret_cast<uint64_t*>(base + warps * kEpiStageBytes) + w, 1);
+__device__ __forceinline__ void epi_tma_init(uint8_t* base, int warps, int nb = 1) {
+  for (int w = 0; w < warps * nb; ++w) mbar_init(reinterpret_cast<uint64_t*>(base + warps * nb * kEpiStageBytes) + w, 1);
 }
 
-// Whole warp, as early as possible (before waiting for the accumulator): frees the box (the previous store has read
-// it) and starts loading the saved forward output of channels [cb, cb+32) of the warp's pixels (box origin bx, by, bn
-// in the phase grid).
-__device__ __forceinline__ void epi_tma_begin(const EpiParams& p, const CUtensorMap* ymap, const EpiWarpStage& st,
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read_n() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+
+// Whole warp: begins the warp's next item — frees its box (the store that last used it has read it) and starts loading
+// the saved forward output of channels [cb, cb+32) of the warp's pixels (box origin bx, by, bn in the phase grid).
+// Call it as early as possible (before waiting for the accumulator; with NB = 2 one item ahead).  begin(k) must come
+// after chunk(k - NB) and before chunk(k).
+template <int NB>
+__device__ __forceinline__ void epi_tma_begin(const EpiParams& p, const CUtensorMap* ymap, EpiWarpStageN<NB>& st,
                                               int cb, int bx, int by, int bn) {
+  if (p.dbg & 1) return;
+  const uint32_t b = st.k_begin % NB;
+  ++st.k_begin;
+  if (p.dact == B2G_ACT_NONE) return;  // forward epilogues have nothing to load; chunk() frees the box itself
   if (elect_one_sync()) {  // elect.sync picks the same lane for the same mask: the bulk groups stay with one thread
-    tma_store_wait_read();
-    if (p.dact != B2G_ACT_NONE) {
-      mbar_expect_tx(st.ybar, kEpiStageBytes);
-      tma_load_4d(st.buf, ymap, st.ybar, cb, bx, by, bn);
-    }
+    // NB = 1: the previous item's store; NB = 2 (one item ahead): the store of item k - 2 is the newest one issued
+    tma_store_wait_read_n<0>();
+    mbar_expect_tx(&st.ybar[b], kEpiStageBytes);
+    tma_load_4d(st.buf + b * kEpiStageBytes, ymap, &st.ybar[b], cb, bx, by, bn);
   }
   __syncwarp();
 }
 
 // Whole warp: epilogue math of one chunk (lane = pixel) through the box, then the TMA store.
-__device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensorMap* omap, EpiWarpStage& st,
+template <int NB>
+__device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensorMap* omap, EpiWarpStageN<NB>& st,
                                               const float* sbias, const uint32_t (&r)[32], size_t pix, int cb, int lane,
                                               int bx, int by, int bn, float* s_colsum = nullptr,
                                               EpiSeed sd = EpiSeed{0u, 0u}) {
-  uint8_t* row = st.buf + lane * 64;
+  if (p.dbg & 1) return;
+  const uint32_t k = st.k_chunk++;
+  const uint32_t b = k % NB;
+  uint8_t* box = st.buf + b * kEpiStageBytes;
+  uint8_t* row = box + lane * 64;
   const uint32_t sw = (lane >> 1) & 3;  // 64-byte swizzle: 16-byte group g of row i lives at g ^ ((i >> 1) & 3)
   if (p.dact != B2G_ACT_NONE) {
-    mbar_wait(st.ybar, st.yphase);
-    st.yphase ^= 1;
+    mbar_wait(&st.ybar[b], (k / NB) & 1);
+  } else {
+    // forward: the box is free once the store of item k - NB has read it (NB - 1 newer stores may still be pending)
+    if (elect_one_sync()) tma_store_wait_read_n<NB - 1>();
+    __syncwarp();
   }
   conv_epilogue_math(
       p, sbias, r, pix, cb, true,
@@ -325,28 +385,46 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
       sd);
   fence_proxy_async_smem();
   __syncwarp();
-  if (elect_one_sync()) tma_store_4d(omap, st.buf, cb, bx, by, bn);
+  if (elect_one_sync()) tma_store_4d(omap, box, cb, bx, by, bn);
   __syncwarp();
   if (p.colsum) {
-    // column sums straight from the box: lane l reads channel cb + l of the 32 pixel rows (the 32 lanes of one
-    // read cover one 64-byte row: conflict free).  Rows of pixels outside the tensor hold exact zeros (zero-filled
-    // operands, no bias in a backward epilogue).
-    float sum = 0.f, sq = 0.f;
-    const uint32_t cg = lane >> 3, ce = (lane & 7) * 2;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const uint16_t h = *reinterpret_cast<const uint16_t*>(st.buf + i * 64 + ((cg ^ ((i >> 1) & 3)) << 4) + ce);
-      const float f = __uint_as_float(static_cast<uint32_t>(h) << 16);
-      sum += f;
-      sq = fmaf(f, f, sq);
-    }
+    // Column sums straight from the box (the TMA store only READS it: no hazard).  Lane = (channel pair cp = lane & 15,
+    // pixel parity h = lane >> 4): 16 LDS.32 per lane — the 16 lanes of a half warp cover one 64-byte pixel row, the two
+    // halves rows 2j and 2j + 1 = all 32 banks, conflict free — then one shuffle joins the two parities.  Round 1 read
+    // one bf16 per lane and pixel (32 LDS.U16 + sum-of-squares FMAs even without BatchNorm statistics): 185 instructions
+    // per item, 17 % of a backward epilogue (ncu r2).  Rows of pixels outside the tensor hold exact zeros.
+    const uint32_t cp = lane & 15, h = lane >> 4;
+    const uint8_t* base = box + h * 64 + (cp & 3) * 4;
+    const uint32_t cg = cp >> 2;
+    float s0 = 0.f, s1 = 0.f;
     const int cs_off = (static_cast<int>(threadIdx.x >> 5) % p.cs_copies) * p.Cout;
-    atomicAdd(&s_colsum[cs_off + cb + lane], sum);
-    if (p.colsumsq) atomicAdd(&const_cast<float*>(sbias)[cs_off + cb + lane], sq);
+    if (p.colsumsq) {
+      float q0 = 0.f, q1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(base + j * 128 + ((cg ^ (j & 3)) << 4));
+        const float f0 = bf16_lo(w), f1 = bf16_hi(w);
+        s0 += f0; s1 += f1;
+        q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+      }
+      q0 += __shfl_xor_sync(0xffffffffu, q0, 16);
+      q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+      atomicAdd(&const_cast<float*>(sbias)[cs_off + cb + 2 * cp + h], h ? q1 : q0);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(base + j * 128 + ((cg ^ (j & 3)) << 4));
+        s0 += bf16_lo(w);
+        s1 += bf16_hi(w);
+      }
+    }
+    s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+    atomicAdd(&s_colsum[cs_off + cb + 2 * cp + h], h ? s1 : s0);
   }
 }
 
-// Whole warp, before the kernel's final block-wide sync: the last store must have read the box.
+// Whole warp, before the kernel's final block-wide sync: the last stores must have read their boxes.
 __device__ __forceinline__ void epi_tma_end() {
   if (elect_one_sync()) tma_store_wait_read();
   __syncwarp();
@@ -396,6 +474,10 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->colsumsq = a->colsumsq;
   e->cs_copies = (a->Cout > 0 && a->Cout <= 512) ? (512 / a->Cout > 0 ? 512 / a->Cout : 1) : 1;  // 512-float tables
   e->tma = 0;
+  {
+    const char* d = getenv("B2G_DBG_EPI");  // read per call: measurement runs flip it between launches
+    e->dbg = d ? atoi(d) : 0;
+  }
 }
 
 // Host: decides whether the TMA epilogue applies and builds its tensor maps (b2g_conv_epi_host.cu-free: inline).

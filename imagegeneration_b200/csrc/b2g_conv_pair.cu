@@ -37,6 +37,7 @@ struct alignas(64) PairKernelParams {
   int brows;        // rows of the packed weight matrix per phase
   int m_pairs;      // plan.m_tiles / 2
   int total_pairs;  // phases * m_pairs * n_tiles
+  FastDiv fd_nt, fd_tw, fd_th;  // tile decoding without divisions (n_tiles, tiles_w, tiles_h)
 };
 
 template <int BLOCK_N>
@@ -46,13 +47,18 @@ struct PairCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   // N <= 128 tiles: the TMA epilogue's per-warp boxes (b2g_conv_epi.cuh) take the room of one pipeline stage
   static constexpr bool kEpiTma = BLOCK_N <= 128;
-  static constexpr int kStages = BLOCK_N == 256 ? 6 : (BLOCK_N == 128 ? 7 : 8);
+  static constexpr int kStages = BLOCK_N == 256 ? 6 : (BLOCK_N == 128 ? 6 : 7);  // N <= 128: one stage less than in
+                                                                                 // round 1, its room went to the second epilogue box
   static constexpr int kAccBufs = BLOCK_N <= 64 ? 4 : 2;
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
+  // 16 epilogue warps; N <= 128 (TMA epilogue): two 2 KiB boxes per warp (b2g_conv_epi.cuh), so an item's saved-output
+  // load does not wait for the previous item's store to drain — 8 warps with deeper box rings were measured 15-45 %
+  // slower in round 2, the backward epilogue is bound by per-warp instruction latency
   static constexpr int kEpiGroups = 4;
+  static constexpr int kEpiBoxes = kEpiTma ? 2 : 0;
   static constexpr int kThreads = 64 + 128 * kEpiGroups;
   static constexpr int kEpiWarps = 4 * kEpiGroups;
-  static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps) : 0;
+  static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps, kEpiBoxes) : 0;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 256 + 1024;
   static_assert(kSmemBytes + 4096 <= 227 * 1024, "shared memory budget (incl. the static bias / column-sum tables)");
 };
@@ -62,14 +68,14 @@ struct PairCoord {
 };
 __device__ __forceinline__ PairCoord decode_pair(const PairKernelParams& p, int pair, int rank) {
   PairCoord c;
-  c.n_tile = pair % p.n_tiles;
-  int rest = pair / p.n_tiles;
-  const int m = 2 * (rest % p.m_pairs) + rank;
-  c.phase = rest / p.m_pairs;
-  c.tw = m % p.plan.tiles_w;
-  const int r2 = m / p.plan.tiles_w;
-  c.th = r2 % p.plan.tiles_h;
-  c.tn = r2 / p.plan.tiles_h;
+  int rest;
+  fast_divmod(pair, p.fd_nt, rest, c.n_tile);
+  c.phase = 0;  // rest / m_pairs is the phase (0..3): comparisons, m_pairs is too large for the multiply-high bound
+  while (rest >= p.m_pairs) { rest -= p.m_pairs; ++c.phase; }
+  const int m = 2 * rest + rank;
+  int r2;
+  fast_divmod(m, p.fd_tw, r2, c.tw);
+  fast_divmod(r2, p.fd_th, c.tn, c.th);
   return c;
 }
 
@@ -106,7 +112,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
       mbar_init(&tfull_bar[a], 1);                         // multicast tcgen05.commit
       mbar_init(&tempty_bar[a], 2 * 4 * kGroupsPerTile);   // epilogue warps of BOTH CTAs (leader's copy is used)
     }
-    if (Cfg::kEpiTma && p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps);
+    if (Cfg::kEpiTma && p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps, Cfg::kEpiBoxes);
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
@@ -196,16 +202,35 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
     const uint32_t tempty_leader = mapa_shared(smem_u32(&tempty_bar[0]), 0);
     // origin of this warp's 32-pixel box inside a tile (TMA epilogue)
     const int wl0 = (q * 32) % pl.bw, hl0 = ((q * 32) / pl.bw) % pl.bh, nl0 = (q * 32) / (pl.bw * pl.bh);
-    EpiWarpStage st = epi_tma_stage(epism, Cfg::kEpiWarps, warp - 2);
+    constexpr int NB = Cfg::kEpiBoxes > 0 ? Cfg::kEpiBoxes : 1;
+    EpiWarpStageN<NB> st = epi_tma_stage<NB>(epism, Cfg::kEpiWarps, warp - 2);
     const bool use_tma = Cfg::kEpiTma && p.e.tma != 0;
+    // first chunk of tile number `i` (counted per cluster) that belongs to this warp's group; >= kChunks: none
+    auto first_chunk = [&](int i) {
+      return kChunks < Cfg::kEpiGroups ? ((grp - i * kChunks) & (Cfg::kEpiGroups - 1)) : grp;
+    };
+    // begin pointer of the TMA epilogue (see b2g_conv_rows.cu): the next item (pair, chunk) that has not been begun
+    int b_pair = cluster_id, b_it = 0, b_c = first_chunk(0);
+    auto ensure_begun = [&](uint32_t n) {
+      if (!use_tma) return;
+      while (st.k_begin - st.k_chunk < n) {
+        while (b_pair < p.total_pairs && b_c >= kChunks) {
+          b_pair += n_clusters;
+          ++b_it;
+          b_c = first_chunk(b_it);
+        }
+        if (b_pair >= p.total_pairs) return;
+        const PairCoord bt = decode_pair(p, b_pair, rank);
+        epi_tma_begin(e, &p.em.ymap[bt.phase], st, bt.n_tile * BLOCK_N + b_c * 32, bt.tw * pl.bw + wl0,
+                      bt.th * pl.bh + hl0, bt.tn * pl.bn + nl0);
+        b_c += Cfg::kEpiGroups;
+      }
+    };
     int it = 0;
     for (int pair = cluster_id; pair < p.total_pairs; pair += n_clusters, ++it) {
       const int as = it % Cfg::kAccBufs;
-      int c_first = grp;
-      if (kChunks < Cfg::kEpiGroups) {
-        c_first = (grp - it * kChunks) & (Cfg::kEpiGroups - 1);
-        if (c_first >= kChunks) continue;
-      }
+      const int c_first = first_chunk(it);
+      if (c_first >= kChunks) continue;
       const PairCoord tc = decode_pair(p, pair, rank);
       const int gw = tc.tw * pl.bw + wl, gh = tc.th * pl.bh + hl, gn = tc.tn * pl.bn + nl;
       const bool valid = (gh < pl.Hg) && (gn < pl.N);
@@ -213,15 +238,15 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
       const size_t pix = (static_cast<size_t>(gn) * pl.Hout + oy) * pl.Wout + ox;
       const int col0 = tc.n_tile * BLOCK_N;
       const int bx = tc.tw * pl.bw + wl0, by = tc.th * pl.bh + hl0, bn = tc.tn * pl.bn + nl0;
-      if (use_tma) epi_tma_begin(p.e, &p.em.ymap[tc.phase], st, col0 + c_first * 32, bx, by, bn);
+      ensure_begun(1);
       mbar_wait_parked(&tfull_bar[as], (it / Cfg::kAccBufs) & 1);
       tc_fence_after();
 #pragma unroll 1
       for (int c = c_first; c < kChunks; c += Cfg::kEpiGroups) {
-        if (use_tma && c != c_first) epi_tma_begin(p.e, &p.em.ymap[tc.phase], st, col0 + c * 32, bx, by, bn);
         uint32_t r[32];
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
+        ensure_begun(NB);
         tmem_ld_wait();
         if (use_tma) epi_tma_chunk(e, &p.em.omap[tc.phase], st, sbias, r, pix, col0 + c * 32, lane, bx, by, bn, s_colsum, sd);
         else conv_epilogue_chunk(e, sbias, r, pix, col0 + c * 32, valid, s_colsum, sd);
@@ -296,6 +321,9 @@ int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   kp.n_tiles = a->Cout / block_n;
   kp.m_pairs = pl.m_tiles / 2;
   kp.total_pairs = pl.phases * kp.m_pairs * kp.n_tiles;
+  kp.fd_nt = make_fastdiv(kp.n_tiles, kp.total_pairs);
+  kp.fd_tw = make_fastdiv(pl.tiles_w, pl.m_tiles);
+  kp.fd_th = make_fastdiv(pl.tiles_h, pl.m_tiles);
 
   const size_t es = 2;
   const char* base = static_cast<const char*>(a->in);

@@ -33,6 +33,7 @@ struct alignas(64) RowsKernelParams {
   int brows;         // rows of the packed weight matrix per phase
   int total_tiles;   // PG * n_tiles * N * row_blocks * tiles_w
   int tiles_per_pg;  // n_tiles * N * row_blocks * tiles_w
+  FastDiv fd_tw, fd_rb, fd_n, fd_nt;  // tile decoding without divisions (tiles_w, row_blocks, N, n_tiles)
 };
 
 template <int BLOCK_N, class SS = RowsDyn>
@@ -44,15 +45,21 @@ struct RowsCfg {
   static constexpr int kBStages = SS::kStatic ? SS::kSB : (BLOCK_N == 128 ? 6 : 8);
   static constexpr int kBarBytes = 512;
   static constexpr int kMainBytes = kSlabs * kSlabBytes + kBStages * kBBytes;  // multiple of 1 KiB
-  static constexpr int kEpiWarps = 16;
-  // the TMA epilogue's per-warp boxes go behind the rings when they fit (b2g_conv_epi.cuh)
-  static constexpr bool kEpiTma =
-      BLOCK_N >= 64 && kMainBytes + epi_tma_smem_bytes(kEpiWarps) + kBarBytes + 1024 + 4096 <= 227 * 1024;
-  static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps) : 0;
+  // Epilogue: 4 groups x 4 TMEM lane quarters = 16 warps, each with kEpiBoxes 2 KiB output boxes for the TMA epilogue
+  // (b2g_conv_epi.cuh).  Measured in round 2 (ncu source page + tools/conv_probe.py): a backward epilogue item is ~600-1000
+  // instructions of ONE warp's dependent work — 8 warps with run-ahead loads were 45 % slower than 16 warps; the
+  // epilogue needs warps and fewer instructions, not deeper load pipelines.
+  static constexpr int kEpiGroups = 4;
+  static constexpr int kEpiWarps = 4 * kEpiGroups;
+  static constexpr bool fits(int nb) {
+    return kMainBytes + epi_tma_smem_bytes(kEpiWarps, nb) + kBarBytes + 1024 + 4096 <= 227 * 1024;
+  }
+  static constexpr int kEpiBoxes = BLOCK_N < 64 ? 0 : (fits(2) ? 2 : (fits(1) ? 1 : 0));
+  static constexpr bool kEpiTma = kEpiBoxes > 0;
+  static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps, kEpiBoxes) : 0;
   static constexpr int kSmemBytes = kMainBytes + kEpiBytes + kBarBytes + 1024;
   static_assert(2 * (kSlabs + kBStages) * 8 + 4 * 8 + 8 <= kBarBytes, "barrier area");
   static_assert(kSmemBytes + 4096 <= 227 * 1024, "shared memory budget (incl. the static bias / column-sum tables)");
-  static constexpr int kEpiGroups = 4;
   static constexpr int kThreads = 96 + 128 * kEpiGroups;
 };
 
@@ -61,15 +68,13 @@ struct RowsTile {
 };
 __device__ __forceinline__ RowsTile decode_rows_tile(const RowsKernelParams& p, int tile) {
   RowsTile t;
-  const int tw = tile % p.plan.tiles_w;
-  tile /= p.plan.tiles_w;
+  int tw, yb;
+  fast_divmod(tile, p.fd_tw, tile, tw);
   t.w0 = tw * 128;
-  t.y0 = (tile % p.geom.row_blocks) * p.geom.R;
-  tile /= p.geom.row_blocks;
-  t.n = tile % p.plan.N;
-  tile /= p.plan.N;
-  t.n_tile = tile % p.n_tiles;
-  t.pg = tile / p.n_tiles;
+  fast_divmod(tile, p.fd_rb, tile, yb);
+  t.y0 = yb * p.geom.R;
+  fast_divmod(tile, p.fd_n, tile, t.n);
+  fast_divmod(tile, p.fd_nt, t.pg, t.n_tile);
   return t;
 }
 
@@ -176,7 +181,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], 4 * Cfg::kEpiGroups);
     }
-    if (Cfg::kEpiTma && p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps);
+    if (Cfg::kEpiTma && p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps, Cfg::kEpiBoxes);
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
@@ -331,24 +336,35 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     const int grp = (warp - 3) >> 2;
     const int row = q * 32 + lane;
     constexpr int kChunks = BLOCK_N / 32;
-    EpiWarpStage st = epi_tma_stage(epism, Cfg::kEpiWarps, warp - 3);
+    constexpr int NB = Cfg::kEpiBoxes > 0 ? Cfg::kEpiBoxes : 1;
+    EpiWarpStageN<NB> st = epi_tma_stage<NB>(epism, Cfg::kEpiWarps, warp - 3);
     const bool use_tma = Cfg::kEpiTma && p.e.tma != 0;
+    const int n_items = n_acc * kChunks;  // items (accumulator, 32-channel chunk) of a tile; this warp: grp, grp + G, ...
+    // Begin pointer of the TMA epilogue: the next item (tile, idx) of this warp that has not been begun (box freed,
+    // saved-output load started).  ensure_begun(n) keeps n items begun beyond the ones already processed: 1 before the
+    // accumulator wait (the first item's load overlaps the wait), NB inside the item loop (NB = 2: one item ahead).
+    int b_tile = blockIdx.x, b_idx = grp;
+    auto ensure_begun = [&](uint32_t n) {
+      if (!use_tma || grp >= n_items) return;
+      while (st.k_begin - st.k_chunk < n) {
+        if (b_idx >= n_items) { b_tile += gridDim.x; b_idx = grp; }
+        if (b_tile >= p.total_tiles) return;
+        const RowsTile bt = decode_rows_tile(p, b_tile);
+        const int acc = b_idx / kChunks, c = b_idx % kChunks;
+        epi_tma_begin(e, &p.em.ymap[bt.pg * P + acc % P], st, bt.n_tile * BLOCK_N + c * 32, bt.w0 + q * 32,
+                      bt.y0 + acc / P, bt.n);
+        b_idx += Cfg::kEpiGroups;
+      }
+    };
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int as = it & 1;
       const RowsTile t = decode_rows_tile(p, tile);
-      // TMA epilogue: the warp's box of item (acc, c) = 32 pixels from t.w0 + 32 q of grid row t.y0 + acc / P, in
-      // the output phase's sub-grid; the first item's saved-output load starts before the accumulator wait
-      if (use_tma && grp < n_acc * kChunks) {
-        const int acc = grp / kChunks;
-        epi_tma_begin(p.e, &p.em.ymap[t.pg * P + acc % P], st, t.n_tile * BLOCK_N + (grp % kChunks) * 32,
-                      t.w0 + q * 32, t.y0 + acc / P, t.n);
-      }
+      ensure_begun(1);
       // backward epilogues: the saved-output boxes of the warp's remaining items of this tile go to L2 now, while the
-      // MMAs of the tile still run — a warp has ONE box, so each item's load is issued only after the previous store
-      // has drained and its DRAM latency was the critical path of the epilogue (ncu source page)
-      if (use_tma && p.e.dact != B2G_ACT_NONE) {
-        for (int idx = grp + Cfg::kEpiGroups; idx < n_acc * kChunks; idx += Cfg::kEpiGroups) {
+      // MMAs of the tile still run
+      if (use_tma && e.dact != B2G_ACT_NONE) {
+        for (int idx = grp + Cfg::kEpiGroups; idx < n_items; idx += Cfg::kEpiGroups) {
           const int acc = idx / kChunks, c = idx % kChunks;
           if (elect_one_sync())
             tma_prefetch_4d(&p.em.ymap[t.pg * P + acc % P], t.n_tile * BLOCK_N + c * 32, t.w0 + q * 32, t.y0 + acc / P, t.n);
@@ -358,7 +374,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
       mbar_wait_parked(&tfull[as], (it >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int idx = grp; idx < n_acc * kChunks; idx += Cfg::kEpiGroups) {
+      for (int idx = grp; idx < n_items; idx += Cfg::kEpiGroups) {
         const int acc = idx / kChunks, c = idx % kChunks;
         const int r = acc / P, phase = t.pg * P + acc % P;
         const int gy = t.y0 + r;
@@ -366,11 +382,11 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
         const int oy = gy * pl.os + pl.ph_y[phase], ox = (t.w0 + row) * pl.os + pl.ph_x[phase];
         const size_t pix = (static_cast<size_t>(t.n) * pl.Hout + oy) * pl.Wout + ox;
         const int cb = t.n_tile * BLOCK_N + c * 32;
-        if (use_tma && idx != grp) epi_tma_begin(p.e, &p.em.ymap[phase], st, cb, t.w0 + q * 32, gy, t.n);
         uint32_t v[32];
         __syncwarp();
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * (n_acc * BLOCK_N) + acc * BLOCK_N + c * 32,
                       v);
+        ensure_begun(NB);
         tmem_ld_wait();
         if (use_tma) epi_tma_chunk(e, &p.em.omap[phase], st, sbias, v, pix, cb, lane, t.w0 + q * 32, gy, t.n, s_colsum, sd);
         else conv_epilogue_chunk(e, sbias, v, pix, cb, valid, s_colsum, sd);
@@ -406,12 +422,19 @@ static int launch_rows(const RowsKernelParams& kp, cudaStream_t stream) {
   return B2G_OK;
 }
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
 static int rows_ring(int block_n) { return block_n == 128 ? RowsCfg<128>::kSlabs : RowsCfg<64>::kSlabs; }
 
 // compile-time schedules of the model's four wide roles: <kind, Cin/64, R, P, N tile, slab ring, weight-tile ring>
 using RowsConv3 = RowsStatic<B2G_CONV_K3S1, 2, 2, 1, 128, 4, 6>;    // D.conv3 fwd / dgrad (128 -> 128 @72x128)
 using RowsConv2 = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 8>;    // D.conv2 fwd (64 -> 128, 144x256 -> 72x128)
-using RowsConvT3 = RowsStatic<B2G_CONVT_K4S2, 2, 2, 2, 64, 6, 8>;   // G.convT3 fwd / D.conv2 dgrad (128 -> 64)
+using RowsConv2b = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 4>;   // same role, 4 weight stages: room for 3 epilogue boxes
+using RowsConvT3 = RowsStatic<B2G_CONVT_K4S2, 2, 2, 2, 64, 6, 4>;   // G.convT3 fwd / D.conv2 dgrad (128 -> 64); 4 weight
+                                                                    // stages (8 in round 1): room for a second epilogue box
 using RowsConvT4 = RowsStatic<B2G_CONV_K3S1, 1, 4, 1, 32, 6, 9>;    // G.convT4 fwd / D.conv1 dgrad (64 -> 3)
 
 // Tries the compile-time kernel SS for this role: the host schedule is rebuilt with SS's slab ring and must equal
@@ -429,11 +452,6 @@ static bool try_static(const ConvPlan& pl, int block_n, RowsKernelParams* kp) {
   return true;
 }
 
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return v ? atoi(v) : dflt;
-}
-
 int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, void* stream_, bool* handled,
                      bool static_only) {
   *handled = false;
@@ -445,7 +463,7 @@ int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   int which = 0;  // 0 = generic table-driven kernel, 1..4 = compile-time schedule
   if (env_int("B2G_ROWS_STATIC", 1)) {
     if (try_static<128, RowsConv3>(pl, block_n, &kp)) which = 1;
-    else if (try_static<128, RowsConv2>(pl, block_n, &kp)) which = 2;
+    else if (try_static<128, RowsConv2>(pl, block_n, &kp)) which = env_int("B2G_ROWS_CONV2_SB4", 1) ? 5 : 2;
     else if (try_static<64, RowsConvT3>(pl, block_n, &kp)) which = 3;
     else if (try_static<32, RowsConvT4>(pl, block_n, &kp)) which = 4;
   }
@@ -457,6 +475,7 @@ int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
     const bool room = which == 1   ? RowsCfg<128, RowsConv3>::kEpiTma
                       : which == 2 ? RowsCfg<128, RowsConv2>::kEpiTma
                       : which == 3 ? RowsCfg<64, RowsConvT3>::kEpiTma
+                      : which == 5 ? RowsCfg<128, RowsConv2b>::kEpiTma
                                    : false;
     int rc = fill_epi_tma(a, pl, room, &kp.e, &kp.em, /*row32=*/true);
     if (rc) return rc;
@@ -465,6 +484,10 @@ int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   kp.n_tiles = a->Cout / block_n;
   kp.tiles_per_pg = kp.n_tiles * pl.N * kp.geom.row_blocks * pl.tiles_w;
   kp.total_tiles = kp.geom.PG * kp.tiles_per_pg;
+  kp.fd_tw = make_fastdiv(pl.tiles_w, kp.total_tiles);
+  kp.fd_rb = make_fastdiv(kp.geom.row_blocks, kp.total_tiles);
+  kp.fd_n = make_fastdiv(pl.N, kp.total_tiles);
+  kp.fd_nt = make_fastdiv(kp.n_tiles, kp.total_tiles);
 
   const size_t es = 2;
   const char* base = static_cast<const char*>(a->in);
@@ -501,6 +524,7 @@ int launch_conv_rows(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
     case 2: rc = launch_rows<128, RowsConv2>(kp, stream); break;
     case 3: rc = launch_rows<64, RowsConvT3>(kp, stream); break;
     case 4: rc = launch_rows<32, RowsConvT4>(kp, stream); break;
+    case 5: rc = launch_rows<128, RowsConv2b>(kp, stream); break;
     default:
       switch (block_n) {
         case 128: rc = launch_rows<128>(kp, stream); break;

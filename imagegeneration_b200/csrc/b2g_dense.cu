@@ -11,20 +11,21 @@ namespace b2g {
 // ---------------------------------------------------------------------------------------------------------
 // D head: partial dot products  part[b][s] = sum_{j in slice s} x[b][j] * w[j]
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) dhead_partial_kernel(const __nv_bfloat16* __restrict__ x,
+template <typename T>
+__global__ void __launch_bounds__(256) dhead_partial_kernel(const T* __restrict__ x,
                                                             const float* __restrict__ w, float* __restrict__ part,
                                                             int F, int S) {
   const int b = blockIdx.y, s = blockIdx.x;
   const int per = ((F / 8 + S - 1) / S);  // 8-element groups per slice
   const int g0 = s * per, g1 = min(g0 + per, F / 8);
-  const uint4* xp = reinterpret_cast<const uint4*>(x + (size_t)b * F);
+  const T* xp = x + (size_t)b * F;
   const float4* wp = reinterpret_cast<const float4*>(w);
   float acc = 0.f;
   for (int g = g0 + threadIdx.x; g < g1; g += 256) {
-    const uint4 v = __ldg(xp + g);
+    float v[8];
+    edge_load8(xp + (size_t)g * 8, v);
     const float4 wa = __ldg(wp + 2 * g), wb = __ldg(wp + 2 * g + 1);
-    acc += bf16_lo(v.x) * wa.x + bf16_hi(v.x) * wa.y + bf16_lo(v.y) * wa.z + bf16_hi(v.y) * wa.w +
-           bf16_lo(v.z) * wb.x + bf16_hi(v.z) * wb.y + bf16_lo(v.w) * wb.z + bf16_hi(v.w) * wb.w;
+    acc += v[0] * wa.x + v[1] * wa.y + v[2] * wa.z + v[3] * wa.w + v[4] * wb.x + v[5] * wb.y + v[6] * wb.z + v[7] * wb.w;
   }
   __shared__ float red[8];
 #pragma unroll
@@ -90,10 +91,11 @@ __global__ void dhead_loss_kernel(const float* __restrict__ part, int S, const f
 
 // Head backward: dx[b][j] = dlogit[b] * wscale * w[j] * act'(x[b][j]);  dw[j] (+)= sum_b dlogit[b] * x[b][j];
 // db (+)= sum_b dlogit[b].   act' = LeakyReLU/Dropout derivative recovered from the saved conv7 output x.
-__global__ void __launch_bounds__(256) dhead_bwd_kernel(const __nv_bfloat16* __restrict__ x,
+template <typename T>
+__global__ void __launch_bounds__(256) dhead_bwd_kernel(const T* __restrict__ x,
                                                         const float* __restrict__ w, const float* __restrict__ wscale,
                                                         const float* __restrict__ dlogit, int B, int F, float alpha,
-                                                        float dscale, float dzero, __nv_bfloat16* __restrict__ dx,
+                                                        float dscale, float dzero, T* __restrict__ dx,
                                                         float* __restrict__ dw, float* __restrict__ db) {
   const int g = blockIdx.x * 256 + threadIdx.x;
   if (g == 0 && db) {
@@ -108,12 +110,12 @@ __global__ void __launch_bounds__(256) dhead_bwd_kernel(const __nv_bfloat16* __r
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   for (int b = 0; b < B; ++b) {
     const float dl = __ldg(dlogit + b);
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + (size_t)b * F) + g);
-    const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+    float yv[8];
+    edge_load8(x + (size_t)b * F + (size_t)g * 8, yv);
     float o[8];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const float y0 = bf16_lo(w4[i]), y1 = bf16_hi(w4[i]);
+      const float y0 = yv[2 * i], y1 = yv[2 * i + 1];
       acc[2 * i] += dl * y0;
       acc[2 * i + 1] += dl * y1;
       const float f0 = y0 > 0.f ? dscale : (y0 < 0.f ? alpha * dscale : dzero);
@@ -121,10 +123,7 @@ __global__ void __launch_bounds__(256) dhead_bwd_kernel(const __nv_bfloat16* __r
       o[2 * i] = dl * wv[2 * i] * f0;
       o[2 * i + 1] = dl * wv[2 * i + 1] * f1;
     }
-    uint4 ov;
-    ov.x = pack_bf16x2(o[0], o[1]); ov.y = pack_bf16x2(o[2], o[3]);
-    ov.z = pack_bf16x2(o[4], o[5]); ov.w = pack_bf16x2(o[6], o[7]);
-    reinterpret_cast<uint4*>(dx + (size_t)b * F)[g] = ov;
+    edge_store8(dx + (size_t)b * F + (size_t)g * 8, o);
   }
   if (dw) {
     float4* dp = reinterpret_cast<float4*>(dw) + 2 * g;
@@ -140,10 +139,10 @@ __global__ void __launch_bounds__(256) dhead_bwd_kernel(const __nv_bfloat16* __r
 
 using namespace b2g;
 
-extern "C" int b2g_dhead_fwd_loss(const void* x, const float* w, const float* wscale, const float* bias, int B,
-                                  int F, int loss_kind, float label, float inv_batch, float* workspace,
-                                  int workspace_floats, float* logits, float* dlogit, float* loss_out,
-                                  b2g_stream_t stream_) {
+static int dhead_fwd_loss_any(const void* x, const float* w, const float* wscale, const float* bias, int B,
+                              int F, int loss_kind, float label, float inv_batch, float* workspace,
+                              int workspace_floats, float* logits, float* dlogit, float* loss_out, bool f32,
+                              b2g_stream_t stream_) {
   if (!x || !w || !bias || !workspace || !logits || !dlogit || !loss_out)
     return fail(B2G_E_INVALID_ARG, "b2g_dhead_fwd_loss: null pointer");
   if (F % 8) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dhead_fwd_loss: F must be a multiple of 8");
@@ -152,7 +151,8 @@ extern "C" int b2g_dhead_fwd_loss(const void* x, const float* w, const float* ws
   if (S > 64) S = 64;
   if (workspace_floats < B * S) return fail(B2G_E_INVALID_ARG, "b2g_dhead_fwd_loss: workspace needs %d floats", B * S);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  dhead_partial_kernel<<<dim3(S, B), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), w, workspace, F, S);
+  if (f32) dhead_partial_kernel<float><<<dim3(S, B), 256, 0, stream>>>(static_cast<const float*>(x), w, workspace, F, S);
+  else dhead_partial_kernel<__nv_bfloat16><<<dim3(S, B), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), w, workspace, F, S);
   B2G_LAUNCH_CHECK();
   dhead_loss_kernel<<<1, 256, 0, stream>>>(workspace, S, wscale, bias, B, loss_kind, label, inv_batch, logits, dlogit,
                                            loss_out);
@@ -160,15 +160,44 @@ extern "C" int b2g_dhead_fwd_loss(const void* x, const float* w, const float* ws
   return B2G_OK;
 }
 
-extern "C" int b2g_dhead_bwd(const void* x, const float* w, const float* wscale, const float* dlogit, int B, int F,
-                             float alpha, float dscale, float dzero, void* dx, float* dw, float* db,
-                             b2g_stream_t stream_) {
+extern "C" int b2g_dhead_fwd_loss(const void* x, const float* w, const float* wscale, const float* bias, int B,
+                                  int F, int loss_kind, float label, float inv_batch, float* workspace,
+                                  int workspace_floats, float* logits, float* dlogit, float* loss_out,
+                                  b2g_stream_t stream) {
+  return dhead_fwd_loss_any(x, w, wscale, bias, B, F, loss_kind, label, inv_batch, workspace, workspace_floats, logits,
+                            dlogit, loss_out, false, stream);
+}
+extern "C" int b2g_dhead_fwd_loss_f32(const float* x, const float* w, const float* wscale, const float* bias, int B,
+                                      int F, int loss_kind, float label, float inv_batch, float* workspace,
+                                      int workspace_floats, float* logits, float* dlogit, float* loss_out,
+                                      b2g_stream_t stream) {
+  return dhead_fwd_loss_any(x, w, wscale, bias, B, F, loss_kind, label, inv_batch, workspace, workspace_floats, logits,
+                            dlogit, loss_out, true, stream);
+}
+
+static int dhead_bwd_any(const void* x, const float* w, const float* wscale, const float* dlogit, int B, int F,
+                         float alpha, float dscale, float dzero, void* dx, float* dw, float* db, bool f32,
+                         b2g_stream_t stream_) {
   if (!x || !w || !dlogit || !dx) return fail(B2G_E_INVALID_ARG, "b2g_dhead_bwd: null pointer");
   if (F % 8) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dhead_bwd: F must be a multiple of 8");
   const int grid = (F / 8 + 255) / 256;
-  dhead_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const __nv_bfloat16*>(x), w, wscale, dlogit, B, F, alpha, dscale, dzero,
-      static_cast<__nv_bfloat16*>(dx), dw, db);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (f32)
+    dhead_bwd_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(x), w, wscale, dlogit, B, F, alpha, dscale,
+                                                      dzero, static_cast<float*>(dx), dw, db);
+  else
+    dhead_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), w, wscale, dlogit, B, F,
+                                                              alpha, dscale, dzero, static_cast<__nv_bfloat16*>(dx), dw, db);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
+}
+extern "C" int b2g_dhead_bwd(const void* x, const float* w, const float* wscale, const float* dlogit, int B, int F,
+                             float alpha, float dscale, float dzero, void* dx, float* dw, float* db,
+                             b2g_stream_t stream) {
+  return dhead_bwd_any(x, w, wscale, dlogit, B, F, alpha, dscale, dzero, dx, dw, db, false, stream);
+}
+extern "C" int b2g_dhead_bwd_f32(const float* x, const float* w, const float* wscale, const float* dlogit, int B, int F,
+                                 float alpha, float dscale, float dzero, float* dx, float* dw, float* db,
+                                 b2g_stream_t stream) {
+  return dhead_bwd_any(x, w, wscale, dlogit, B, F, alpha, dscale, dzero, dx, dw, db, true, stream);
 }

@@ -33,6 +33,7 @@ struct alignas(64) StemFwdParams {
   float inv_std;
   float alpha;  // LeakyReLU slope of the output activation (0 = ReLU)
   __nv_bfloat16* out;
+  float* out_f32;  // non-null: full-precision output (the fp32/tf32 parity path) instead of `out`
   int B, F, b0, tiles;
 };
 
@@ -143,7 +144,9 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_fwd_kernel(const __grid_
           if (b < p.B)  // 32 consecutive features per warp: one 64-byte line per sample
           {
             const float y = fmaf(__uint_as_float(r[c]), g, be);
-            p.out[(size_t)b * p.F + j] = __float2bfloat16_rn(fmaxf(y, y * p.alpha));  // alpha in [0, 1)
+            const float a = fmaxf(y, y * p.alpha);  // alpha in [0, 1)
+            if (p.out_f32) p.out_f32[(size_t)b * p.F + j] = a;
+            else p.out[(size_t)b * p.F + j] = __float2bfloat16_rn(a);
           }
         }
       }
@@ -346,7 +349,7 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_bwd_kernel(const __grid_
 using namespace b2g;
 
 static int dense_g_fwd_any(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
-                           float alpha, void* out, int B, int F, b2g_stream_t stream_) {
+                           float alpha, void* out, int B, int F, b2g_stream_t stream_, bool out_f32 = false) {
   if (alpha < 0.f || alpha >= 1.f) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_fwd: alpha must be in [0, 1)");
   if (!z || !W || !gamma || !beta || !out) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_fwd: null pointer");
   if (F % 128 || F <= 0 || B <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_fwd: F=%d must be a multiple of 128", F);
@@ -372,7 +375,8 @@ static int dense_g_fwd_any(const float* z, const float* W, const float* gamma, c
     if (rc) return rc;
   }
   p.gamma = gamma; p.beta = beta; p.inv_std = inv_std; p.alpha = alpha;
-  p.out = static_cast<__nv_bfloat16*>(out);
+  p.out = out_f32 ? nullptr : static_cast<__nv_bfloat16*>(out);
+  p.out_f32 = out_f32 ? static_cast<float*>(out) : nullptr;
   p.B = B; p.F = F; p.tiles = F / 128;
   const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   for (int b0 = 0; b0 < B; b0 += kStemBC) {
@@ -392,8 +396,14 @@ extern "C" int b2g_dense_g_fwd_leaky(const float* z, const float* W, const float
   return dense_g_fwd_any(z, W, gamma, beta, inv_std, alpha, out, B, F, stream);
 }
 
-extern "C" int b2g_dense_g_bwd(const float* z, const float* W, const float* gamma, float inv_std, const void* dq,
-                               float* dW, float* dgamma, float* dbeta, int B, int F, b2g_stream_t stream_) {
+extern "C" int b2g_dense_g_fwd_f32(const float* z, const float* W, const float* gamma, const float* beta, float inv_std,
+                                   float* out, int B, int F, b2g_stream_t stream) {
+  return dense_g_fwd_any(z, W, gamma, beta, inv_std, 0.f, out, B, F, stream, true);
+}
+
+// `first` = false: accumulate onto dW / dgamma / dbeta from the first sample chunk on (second pass of the fp32 variant)
+static int dense_g_bwd_any(const float* z, const float* W, const float* gamma, float inv_std, const void* dq,
+                           float* dW, float* dgamma, float* dbeta, int B, int F, bool first, b2g_stream_t stream_) {
   if (!z || !W || !gamma || !dq || !dW || !dgamma || !dbeta) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_bwd: null pointer");
   if (F % 128 || F <= 0 || B <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_bwd: F=%d must be a multiple of 128", F);
   static bool attr_set = false;
@@ -416,9 +426,50 @@ extern "C" int b2g_dense_g_bwd(const float* z, const float* W, const float* gamm
   const int grid = p.tiles < num_sms() ? p.tiles : num_sms();
   for (int b0 = 0; b0 < B; b0 += kStemBC) {
     p.b0 = b0;
-    p.accumulate = b0 > 0;
+    p.accumulate = b0 > 0 || !first;
     stem_bwd_kernel<<<grid, kStemThreads, StemBwdCfg::kSmemBytes, static_cast<cudaStream_t>(stream_)>>>(p);
     B2G_LAUNCH_CHECK();
   }
   return B2G_OK;
+}
+
+extern "C" int b2g_dense_g_bwd(const float* z, const float* W, const float* gamma, float inv_std, const void* dq,
+                               float* dW, float* dgamma, float* dbeta, int B, int F, b2g_stream_t stream) {
+  return dense_g_bwd_any(z, W, gamma, inv_std, dq, dW, dgamma, dbeta, B, F, true, stream);
+}
+
+namespace b2g {
+// fp32 -> bf16 hi + bf16 lo (x = hi + lo up to 2^-17 relative): lets the bf16 tensor-core backward consume fp32 gradients
+__global__ void __launch_bounds__(256) split_hi_lo_kernel(const float4* __restrict__ x, uint2* __restrict__ hi,
+                                                          uint2* __restrict__ lo, long n4) {
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < n4; i += gridDim.x * 256L) {
+    const float4 v = __ldg(x + i);
+    const float f[4] = {v.x, v.y, v.z, v.w};
+    float h[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = __bfloat162float(__float2bfloat16_rn(f[k]));
+    hi[i] = make_uint2(pack_bf16x2(h[0], h[1]), pack_bf16x2(h[2], h[3]));
+    lo[i] = make_uint2(pack_bf16x2(f[0] - h[0], f[1] - h[1]), pack_bf16x2(f[2] - h[2], f[3] - h[3]));
+  }
+}
+}  // namespace b2g
+
+// fp32 gradient dq (the fp32/tf32 parity path): split into bf16 hi + lo in `scratch` (2 * B * F bf16 elements), then two
+// passes of the tensor-core backward, the second accumulating — products exact to 2^-17.
+extern "C" int b2g_dense_g_bwd_f32(const float* z, const float* W, const float* gamma, float inv_std, const float* dq,
+                                   void* scratch, float* dW, float* dgamma, float* dbeta, int B, int F,
+                                   b2g_stream_t stream_) {
+  if (!dq || !scratch) return fail(B2G_E_INVALID_ARG, "b2g_dense_g_bwd_f32: null pointer");
+  if (F % 128 || F <= 0 || B <= 0) return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_dense_g_bwd_f32: F=%d must be a multiple of 128", F);
+  const long n4 = (long)B * F / 4;
+  __nv_bfloat16* hi = static_cast<__nv_bfloat16*>(scratch);
+  __nv_bfloat16* lo = hi + (size_t)B * F;
+  long blocks = (n4 + 255) / 256;
+  if (blocks > num_sms() * 16L) blocks = num_sms() * 16L;
+  split_hi_lo_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      reinterpret_cast<const float4*>(dq), reinterpret_cast<uint2*>(hi), reinterpret_cast<uint2*>(lo), n4);
+  B2G_LAUNCH_CHECK();
+  int rc = dense_g_bwd_any(z, W, gamma, inv_std, hi, dW, dgamma, dbeta, B, F, true, stream_);
+  if (rc) return rc;
+  return dense_g_bwd_any(z, W, gamma, inv_std, lo, dW, dgamma, dbeta, B, F, false, stream_);
 }

@@ -15,12 +15,13 @@ namespace b2g {
 // ---------------------------------------------------------------------------------------------------------
 // 3 -> 64 : thread per output pixel, 64 fp32 accumulators, weights broadcast from shared memory
 // ---------------------------------------------------------------------------------------------------------
+template <typename T64>
 __global__ void __launch_bounds__(128) conv3x3_c3_to_c64_kernel(
     const float* __restrict__ in,  // [N,H,W,3] fp32
     const float* __restrict__ w,   // [3][3][3][64] fp32
-    const float* __restrict__ wscale, const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int N, int H,
+    const float* __restrict__ wscale, const float* __restrict__ bias, T64* __restrict__ out, int N, int H,
     int W, int act, float alpha, int drop_thresh8, float drop_scale, uint32_t seed_lo, uint32_t seed_hi,
-    const __nv_bfloat16* __restrict__ yprev, int dact) {
+    const T64* __restrict__ yprev, int dact) {
   __shared__ float4 ws[27 * 16];  // [tap*3+c3][16 float4 = 64 c64]
   __shared__ float bs[64];
   const float sc = wscale ? *wscale : 1.f;
@@ -74,36 +75,26 @@ __global__ void __launch_bounds__(128) conv3x3_c3_to_c64_kernel(
       }
     }
     if (dact == B2G_ACT_RELU) {
-      const uint4* yp = reinterpret_cast<const uint4*>(yprev + off);
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
-        const uint4 yv = __ldg(yp + g);
-        const uint32_t w4[4] = {yv.x, yv.y, yv.z, yv.w};
+        float y[8];
+        edge_load8(yprev + off + g * 8, y);
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          if (!(bf16_lo(w4[b]) > 0.f)) acc[g * 8 + b * 2] = 0.f;
-          if (!(bf16_hi(w4[b]) > 0.f)) acc[g * 8 + b * 2 + 1] = 0.f;
-        }
+        for (int b = 0; b < 8; ++b)
+          if (!(y[b] > 0.f)) acc[g * 8 + b] = 0.f;
       }
     }
-    uint4* op = reinterpret_cast<uint4*>(out + off);
 #pragma unroll
-    for (int g = 0; g < 8; ++g) {
-      uint4 o;
-      o.x = pack_bf16x2(acc[g * 8 + 0], acc[g * 8 + 1]);
-      o.y = pack_bf16x2(acc[g * 8 + 2], acc[g * 8 + 3]);
-      o.z = pack_bf16x2(acc[g * 8 + 4], acc[g * 8 + 5]);
-      o.w = pack_bf16x2(acc[g * 8 + 6], acc[g * 8 + 7]);
-      op[g] = o;
-    }
+    for (int g = 0; g < 8; ++g) edge_store8(out + off + g * 8, &acc[g * 8]);
   }
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // 64 -> 3 (flipped taps): thread per output pixel, bf16 input read as 16-byte vectors
 // ---------------------------------------------------------------------------------------------------------
+template <typename T64>
 __global__ void __launch_bounds__(128) conv3x3_c64_to_c3_kernel(
-    const __nv_bfloat16* __restrict__ in,  // [N,H,W,64] bf16
+    const T64* __restrict__ in,            // [N,H,W,64] bf16 or fp32
     const float* __restrict__ w,           // [3][3][3][64] fp32
     const float* __restrict__ wscale, float* __restrict__ out, int N, int H, int W, int act,
     const float* __restrict__ yprev, int dact) {
@@ -129,15 +120,15 @@ __global__ void __launch_bounds__(128) conv3x3_c64_to_c3_kernel(
       for (int kx = 0; kx < 3; ++kx) {
         const int xx = x + kx - 1;
         if (xx < 0 || xx >= W) continue;
-        const uint4* ip = reinterpret_cast<const uint4*>(in + (nbase + (long)yy * W + xx) * 64);
+        const T64* ip = in + (nbase + (long)yy * W + xx) * 64;
         const float4* wt = ws + (ky * 3 + kx) * 64;
 #pragma unroll
         for (int g = 0; g < 8; ++g) {
-          const uint4 v = __ldg(ip + g);
-          const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+          float v[8];
+          edge_load8(ip + g * 8, v);
 #pragma unroll
           for (int b = 0; b < 4; ++b) {
-            const float lo = bf16_lo(w4[b]), hi = bf16_hi(w4[b]);
+            const float lo = v[b * 2], hi = v[b * 2 + 1];
             const float4 wl = wt[g * 8 + b * 2], wh = wt[g * 8 + b * 2 + 1];
             a0 += lo * wl.x + hi * wh.x;
             a1 += lo * wl.y + hi * wh.y;
@@ -170,8 +161,9 @@ __global__ void __launch_bounds__(128) conv3x3_c64_to_c3_kernel(
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kWgPix = 128;  // pixels staged per block iteration
 
+template <typename T64>
 __global__ void __launch_bounds__(256) wgrad3x3_c3_c64_kernel(const float* __restrict__ t3,  // [N,H,W,3] fp32
-                                                              const __nv_bfloat16* __restrict__ t64,  // [N,H,W,64]
+                                                              const T64* __restrict__ t64,   // [N,H,W,64] bf16 / fp32
                                                               float* __restrict__ dw,     // [27][64] accumulate
                                                               float* __restrict__ dbias,  // [64] accumulate or NULL
                                                               int N, int H, int W) {
@@ -212,11 +204,7 @@ __global__ void __launch_bounds__(256) wgrad3x3_c3_c64_kernel(const float* __res
       const int pl = i >> 3, g = i & 7;
       const long pix = p0 + pl;
       float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (pix < total) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(t64 + pix * 64) + g);
-        f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
-        f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
-      }
+      if (pix < total) edge_load8(t64 + pix * 64 + g * 8, f);
       *reinterpret_cast<float4*>(&b_s[pl][g * 8]) = make_float4(f[0], f[1], f[2], f[3]);
       *reinterpret_cast<float4*>(&b_s[pl][g * 8 + 4]) = make_float4(f[4], f[5], f[6], f[7]);
     }
@@ -267,45 +255,88 @@ static int edge_grid(long pixels, int threads) {
   return (int)(blocks < cap ? blocks : cap);
 }
 
-extern "C" int b2g_conv3x3_c3_to_c64(const float* in, const float* w, const float* wscale, const float* bias,
-                                     void* out, int N, int H, int W, int act, float alpha, int dropout_thresh8,
-                                     unsigned long long dropout_seed, const void* yprev, int dact,
-                                     b2g_stream_t stream_) {
+static int conv3x3_c3_to_c64_any(const float* in, const float* w, const float* wscale, const float* bias,
+                                 void* out, int N, int H, int W, int act, float alpha, int dropout_thresh8,
+                                 unsigned long long dropout_seed, const void* yprev, int dact, bool f32,
+                                 b2g_stream_t stream_) {
   if (!in || !w || !out) return fail(B2G_E_INVALID_ARG, "b2g_conv3x3_c3_to_c64: null pointer");
   if (dact != B2G_ACT_NONE && (dact != B2G_ACT_RELU || !yprev))
     return fail(B2G_E_INVALID_ARG, "b2g_conv3x3_c3_to_c64: dact must be NONE or RELU with yprev");
   if (dropout_thresh8 < 0 || dropout_thresh8 > 255) return fail(B2G_E_INVALID_ARG, "bad dropout_thresh8");
   const long pixels = (long)N * H * W;
-  conv3x3_c3_to_c64_kernel<<<edge_grid(pixels, 128), 128, 0, static_cast<cudaStream_t>(stream_)>>>(
-      in, w, wscale, bias, static_cast<__nv_bfloat16*>(out), N, H, W, act, alpha, dropout_thresh8,
-      256.f / (256.f - (float)dropout_thresh8), (uint32_t)(dropout_seed & 0xFFFFFFFFull),
-      (uint32_t)(dropout_seed >> 32), static_cast<const __nv_bfloat16*>(yprev), dact);
+  const float ds = 256.f / (256.f - (float)dropout_thresh8);
+  const uint32_t slo = (uint32_t)(dropout_seed & 0xFFFFFFFFull), shi = (uint32_t)(dropout_seed >> 32);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (f32)
+    conv3x3_c3_to_c64_kernel<float><<<edge_grid(pixels, 128), 128, 0, stream>>>(
+        in, w, wscale, bias, static_cast<float*>(out), N, H, W, act, alpha, dropout_thresh8, ds, slo, shi,
+        static_cast<const float*>(yprev), dact);
+  else
+    conv3x3_c3_to_c64_kernel<__nv_bfloat16><<<edge_grid(pixels, 128), 128, 0, stream>>>(
+        in, w, wscale, bias, static_cast<__nv_bfloat16*>(out), N, H, W, act, alpha, dropout_thresh8, ds, slo, shi,
+        static_cast<const __nv_bfloat16*>(yprev), dact);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
+extern "C" int b2g_conv3x3_c3_to_c64(const float* in, const float* w, const float* wscale, const float* bias,
+                                     void* out, int N, int H, int W, int act, float alpha, int dropout_thresh8,
+                                     unsigned long long dropout_seed, const void* yprev, int dact,
+                                     b2g_stream_t stream) {
+  return conv3x3_c3_to_c64_any(in, w, wscale, bias, out, N, H, W, act, alpha, dropout_thresh8, dropout_seed, yprev, dact,
+                               false, stream);
+}
+extern "C" int b2g_conv3x3_c3_to_c64_f32(const float* in, const float* w, const float* wscale, const float* bias,
+                                         float* out, int N, int H, int W, int act, float alpha, int dropout_thresh8,
+                                         unsigned long long dropout_seed, const float* yprev, int dact,
+                                         b2g_stream_t stream) {
+  return conv3x3_c3_to_c64_any(in, w, wscale, bias, out, N, H, W, act, alpha, dropout_thresh8, dropout_seed, yprev, dact,
+                               true, stream);
+}
 
-extern "C" int b2g_conv3x3_c64_to_c3(const void* in, const float* w, const float* wscale, float* out, int N, int H,
-                                     int W, int act, const float* yprev, int dact, b2g_stream_t stream_) {
+static int conv3x3_c64_to_c3_any(const void* in, const float* w, const float* wscale, float* out, int N, int H,
+                                 int W, int act, const float* yprev, int dact, bool f32, b2g_stream_t stream_) {
   if (!in || !w || !out) return fail(B2G_E_INVALID_ARG, "b2g_conv3x3_c64_to_c3: null pointer");
   if (dact != B2G_ACT_NONE && (dact != B2G_ACT_TANH || !yprev))
     return fail(B2G_E_INVALID_ARG, "b2g_conv3x3_c64_to_c3: dact must be NONE or TANH with yprev");
   const long pixels = (long)N * H * W;
-  conv3x3_c64_to_c3_kernel<<<edge_grid(pixels, 128), 128, 0, static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const __nv_bfloat16*>(in), w, wscale, out, N, H, W, act, yprev, dact);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (f32)
+    conv3x3_c64_to_c3_kernel<float><<<edge_grid(pixels, 128), 128, 0, stream>>>(static_cast<const float*>(in), w, wscale,
+                                                                               out, N, H, W, act, yprev, dact);
+  else
+    conv3x3_c64_to_c3_kernel<__nv_bfloat16><<<edge_grid(pixels, 128), 128, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(in), w, wscale, out, N, H, W, act, yprev, dact);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
 }
+extern "C" int b2g_conv3x3_c64_to_c3(const void* in, const float* w, const float* wscale, float* out, int N, int H,
+                                     int W, int act, const float* yprev, int dact, b2g_stream_t stream) {
+  return conv3x3_c64_to_c3_any(in, w, wscale, out, N, H, W, act, yprev, dact, false, stream);
+}
+extern "C" int b2g_conv3x3_c64_to_c3_f32(const float* in, const float* w, const float* wscale, float* out, int N, int H,
+                                         int W, int act, const float* yprev, int dact, b2g_stream_t stream) {
+  return conv3x3_c64_to_c3_any(in, w, wscale, out, N, H, W, act, yprev, dact, true, stream);
+}
 
-extern "C" int b2g_wgrad3x3_c3_c64(const float* t3, const void* t64, float* dw, float* dbias, int N, int H, int W,
-                                   b2g_stream_t stream_) {
+static int wgrad3x3_c3_c64_any(const float* t3, const void* t64, float* dw, float* dbias, int N, int H, int W, bool f32,
+                               b2g_stream_t stream_) {
   if (!t3 || !t64 || !dw) return fail(B2G_E_INVALID_ARG, "b2g_wgrad3x3_c3_c64: null pointer");
   const long chunks = ((long)N * H * W + kWgPix - 1) / kWgPix;
   const long cap = (long)num_sms() * 2;
   const int grid = (int)(chunks < cap ? chunks : cap);
-  wgrad3x3_c3_c64_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      t3, static_cast<const __nv_bfloat16*>(t64), dw, dbias, N, H, W);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (f32) wgrad3x3_c3_c64_kernel<float><<<grid, 256, 0, stream>>>(t3, static_cast<const float*>(t64), dw, dbias, N, H, W);
+  else wgrad3x3_c3_c64_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(t3, static_cast<const __nv_bfloat16*>(t64), dw, dbias, N, H, W);
   B2G_LAUNCH_CHECK();
   return B2G_OK;
+}
+extern "C" int b2g_wgrad3x3_c3_c64(const float* t3, const void* t64, float* dw, float* dbias, int N, int H, int W,
+                                   b2g_stream_t stream) {
+  return wgrad3x3_c3_c64_any(t3, t64, dw, dbias, N, H, W, false, stream);
+}
+extern "C" int b2g_wgrad3x3_c3_c64_f32(const float* t3, const float* t64, float* dw, float* dbias, int N, int H, int W,
+                                       b2g_stream_t stream) {
+  return wgrad3x3_c3_c64_any(t3, t64, dw, dbias, N, H, W, true, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -83,6 +83,9 @@ __device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity)
         : "r"(smem_u32(bar)), "r"(parity), "r"(20000u)
         : "memory");
     if (ok) break;
+    // the suspend hint alone still came back every ~100 ns (ncu r2: 12 % of conv_c3's executed instructions were this
+    // loop, 20 waiting warps per CTA): back off explicitly, the waits of these warps are microseconds long
+    __nanosleep(spins < 4 ? 96u : 256u);
     if (++spins > (1u << 22)) __trap();
   }
 }
@@ -347,6 +350,14 @@ __host__ __device__ __forceinline__ uint32_t b2g_dropout_bits(uint32_t group, ui
   x ^= x >> 16;
   return x;
 }
+// byte-sign masks of a hash word for packed bf16 pairs: result half h is 0xFFFF iff byte (2*pair + h) of `bits` has its
+// top bit set (byte >= 128), else 0 — PRMT's sign-replication mode, one instruction per pair of elements
+__device__ __forceinline__ uint32_t b2g_keep_mask_pair(uint32_t bits, int pair) {
+  uint32_t m;
+  if (pair == 0) asm("prmt.b32 %0, %1, %1, 0x9988;" : "=r"(m) : "r"(bits));
+  else asm("prmt.b32 %0, %1, %1, 0xBBAA;" : "=r"(m) : "r"(bits));
+  return m;
+}
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -354,5 +365,27 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
+
+// 8 consecutive elements of an activation tensor stored as bf16 (training path) or fp32 (the fp32/tf32 parity path,
+// SNDCGANEngine(dtype="tf32")): shared by the CUDA-core edge kernels and the discriminator head
+__device__ __forceinline__ void edge_load8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ void edge_load8(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ void edge_store8(__nv_bfloat16* p, const float* f) {
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(p) = o;
+}
+__device__ __forceinline__ void edge_store8(float* p, const float* f) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(f[0], f[1], f[2], f[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(f[4], f[5], f[6], f[7]);
+}
 
 }  // namespace b2g

@@ -64,6 +64,7 @@ class PackJob(C.Structure):
         ("n_is_d3", C.c_int), ("flip", C.c_int), ("ck_pad", C.c_int),
         ("w", C.c_void_p), ("scale_scalar", C.c_void_p), ("scale_d2", C.c_void_p), ("scale_d3", C.c_void_p),
         ("wpacked", C.c_void_p),
+        ("f32", C.c_int),
     ]
 
 
@@ -146,6 +147,15 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_sn_dot_multi": [_P, _P, _I, _P, _P, _P, _P, _P],
     # w, g, m, v, n, n_layers, off*, K*, C*, u**, v_raw**, t_raw**, scal**, dots, lr_t, lr_t_dev, b1, b2, eps, gscale, stream
     "b2g_adam_sn": [_P, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _F, _P, _F, _F, _F, _F, _P],
+    # fp32 variants of the edge / head / stem kernels (the fp32/tf32 parity path)
+    "b2g_conv3x3_c3_to_c64_f32": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _I, _U64, _P, _I, _P],
+    "b2g_conv3x3_c64_to_c3_f32": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
+    "b2g_wgrad3x3_c3_c64_f32": [_P, _P, _P, _P, _I, _I, _I, _P],
+    "b2g_dhead_fwd_loss_f32": [_P, _P, _P, _P, _I, _I, _I, _F, _F, _P, _I, _P, _P, _P, _P],
+    "b2g_dhead_bwd_f32": [_P, _P, _P, _P, _I, _I, _F, _F, _F, _P, _P, _P, _P],
+    "b2g_dense_g_fwd_f32": [_P, _P, _P, _P, _F, _P, _I, _I, _P],
+    # z, W, gamma, inv_std, dq, scratch, dW, dgamma, dbeta, B, F, stream
+    "b2g_dense_g_bwd_f32": [_P, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _P],
     # g, y, out, n, f32, kind, alpha, scale, zero, stream
     "b2g_dact": [_P, _P, _P, _L, _I, _I, _F, _F, _F, _P],
     # logits, labels, B, loss_out, dlogit, stream

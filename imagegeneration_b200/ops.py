@@ -91,7 +91,8 @@ class PackPlan:
 
     def add(self, kind: int, w: torch.Tensor, n_is_d3: bool, flip: bool = False,
             scale_scalar: torch.Tensor | None = None, scale_d2: torch.Tensor | None = None,
-            scale_d3: torch.Tensor | None = None, ck_pad: int = 0) -> torch.Tensor:
+            scale_d3: torch.Tensor | None = None, ck_pad: int = 0, tf32: bool = False) -> torch.Tensor:
+        """tf32=True: fp32 packing rounded to tf32 (the kind::tf32 conv path) instead of bf16."""
         _need_cuda(w, scale_scalar, scale_d2, scale_d3)
         k, phases, taps = _KIND_GEOM[kind]
         kh, kw, d2, d3 = w.shape
@@ -100,10 +101,12 @@ class PackPlan:
         if len(self._jobs) >= self.MAX_JOBS:
             raise B200GanError(f"PackPlan: more than {self.MAX_JOBS} jobs")
         cn, ck = (d3, d2) if n_is_d3 else (d2, d3)
-        out = torch.empty((phases, cn, taps * max(ck, ck_pad)), dtype=torch.bfloat16, device=w.device)
+        out = torch.empty((phases, cn, taps * max(ck, ck_pad)), dtype=torch.float32 if tf32 else torch.bfloat16,
+                          device=w.device)
         self._jobs.append(_lib.PackJob(kind=kind, kh=kh, kw=kw, D2=d2, D3=d3, n_is_d3=int(n_is_d3), flip=int(flip),
                                        ck_pad=ck_pad, w=_ptr(w), scale_scalar=_ptr(scale_scalar),
-                                       scale_d2=_ptr(scale_d2), scale_d3=_ptr(scale_d3), wpacked=_ptr(out)))
+                                       scale_d2=_ptr(scale_d2), scale_d3=_ptr(scale_d3), wpacked=_ptr(out),
+                                       f32=int(tf32)))
         self._keep.append((w, scale_scalar, scale_d2, scale_d3, out))
         self._arr = None
         return out

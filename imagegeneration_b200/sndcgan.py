@@ -223,10 +223,13 @@ class Generator:
 
     # -- engine
     def _buf(self, key, shape, dtype):
-        t = self._bufs.get(key)
-        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+        # one buffer per (name, shape, dtype), never freed: a captured CUDA graph keeps the addresses of the
+        # full-batch buffers, so a ragged batch in between must not make the allocator recycle them
+        k = (key, tuple(shape), dtype)
+        t = self._bufs.get(k)
+        if t is None:
             t = torch.empty(shape, dtype=dtype, device=self.device)
-            self._bufs[key] = t
+            self._bufs[k] = t
         return t
 
     def repack(self):
@@ -435,10 +438,13 @@ class Discriminator:
         return logits.clone()
 
     def _buf(self, key, shape, dtype):
-        t = self._bufs.get(key)
-        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+        # one buffer per (name, shape, dtype), never freed: a captured CUDA graph keeps the addresses of the
+        # full-batch buffers, so a ragged batch in between must not make the allocator recycle them
+        k = (key, tuple(shape), dtype)
+        t = self._bufs.get(k)
+        if t is None:
             t = torch.empty(shape, dtype=dtype, device=self.device)
-            self._bufs[key] = t
+            self._bufs[k] = t
         return t
 
     def repack(self):
@@ -572,13 +578,27 @@ class Discriminator:
         return d_in
 
 
-def make_dcgan_generator(output_size, device="cuda", seed=62) -> Generator:
-    """sndcgan/SNDCGAN.py:25."""
+def _check_dtype(dtype):
+    if dtype not in ("bf16", "tf32"):
+        raise B200GanError("dtype must be 'bf16' (training path) or 'tf32' (fp32 storage / kind::tf32 parity path)")
+
+
+def make_dcgan_generator(output_size, device="cuda", seed=62, dtype="bf16") -> Generator:
+    """sndcgan/SNDCGAN.py:25.  dtype="tf32": the fp32-storage / kind::tf32 parity path (sndcgan_tf32.py)."""
+    _check_dtype(dtype)
+    if dtype == "tf32":
+        from .sndcgan_tf32 import GeneratorTF32
+        return GeneratorTF32(output_size, device=device, seed=seed)
     return Generator(output_size, device=device, seed=seed)
 
 
-def make_dcgan_discriminator(dropout_rate, input_size, device="cuda", seed=63, spectral_norm=False) -> Discriminator:
+def make_dcgan_discriminator(dropout_rate, input_size, device="cuda", seed=63, spectral_norm=False,
+                             dtype="bf16") -> Discriminator:
     """sndcgan/SNDCGAN.py:69."""
+    _check_dtype(dtype)
+    if dtype == "tf32":
+        from .sndcgan_tf32 import DiscriminatorTF32
+        return DiscriminatorTF32(dropout_rate, input_size, device=device, seed=seed, spectral_norm=spectral_norm)
     return Discriminator(dropout_rate, input_size, device=device, seed=seed, spectral_norm=spectral_norm)
 
 
@@ -594,7 +614,7 @@ class SNDCGANEngine:
 
     def __init__(self, batch_size, dropout=0.5, learning_rate_disc=2e-4, learning_rate_gen=2e-4,
                  image_size=(144, 256, 3), z_size=Z_SIZE, device="cuda", seed=62, spectral_norm=False, loss="bce",
-                 process_group=None, cuda_graph=None):
+                 process_group=None, cuda_graph=None, dtype="bf16"):
         if z_size != Z_SIZE:
             raise B200GanError("z_size must be 128 (sndcgan/Trainer.py:8)")
         if loss not in ("bce", "hinge"):
@@ -605,10 +625,14 @@ class SNDCGANEngine:
         self.image_size = tuple(image_size)
         self.device = torch.device(device)
         self.loss = loss
-        self.gen_model = make_dcgan_generator(output_size=image_size, device=device, seed=seed)          # :164
+        _check_dtype(dtype)
+        self.dtype = dtype
+        if dtype == "tf32":
+            cuda_graph = False            # parity configuration: eager steps, host dropout seeds
+        self.gen_model = make_dcgan_generator(output_size=image_size, device=device, seed=seed, dtype=dtype)   # :164
         self.g_optimizer = Adam(learning_rate=learning_rate_gen)                                         # :165
         self.disc_model = make_dcgan_discriminator(dropout, input_size=image_size, device=device, seed=seed + 1,
-                                                   spectral_norm=spectral_norm)                          # :167
+                                                   spectral_norm=spectral_norm, dtype=dtype)             # :167
         self.d_optimizer = Adam(learning_rate=learning_rate_disc)                                        # :168
         from .torch_ops import BinaryCrossentropy
         self.loss_fn = BinaryCrossentropy(from_logits=True)                                              # :170

@@ -338,6 +338,8 @@ def build_parser():
     p.add_argument("--spectral-norm", action="store_true", help="spectral normalisation of D (not in the reference)")
     p.add_argument("--loss", choices=["bce", "hinge"], default="bce")
     p.add_argument("--seed", type=int, default=62)
+    p.add_argument("--dtype", choices=["bf16", "tf32"], default="bf16",
+                   help="bf16 activations (default) or the fp32-storage / kind::tf32 parity path")
     return p
 
 
@@ -345,7 +347,7 @@ def main(argv=None):
     args = build_parser().parse_args(argv)
     sndcgan = SNDCGAN(args.dirPath, args.data, args.bSize, args.dropout, args.learnRateDisc, args.learnRateGen,
                       args.liveOutput, args.continue_, image_size, z_size, spectral_norm=args.spectral_norm,
-                      loss=args.loss, seed=args.seed)
+                      loss=args.loss, seed=args.seed, dtype=args.dtype)
     sndcgan.train(args.epochs + 1, args.ckptFreq)
 
 

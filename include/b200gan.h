@@ -137,6 +137,7 @@ typedef struct b2g_pack_job {
   const float* scale_d2;
   const float* scale_d3;
   void* wpacked;
+  int f32; /* 0: bf16 packing; 1: fp32 packing rounded to tf32 (what b2g_pack_conv_weight_f32 writes) */
 } b2g_pack_job;
 int b2g_pack_conv_weight_multi(const b2g_pack_job* jobs, int n_jobs, b2g_stream_t stream);
 
@@ -299,6 +300,27 @@ int b2g_adam_sn(float* w, const float* g, float* m, float* v, long n, int n_laye
                 const int* C, float* const* u, float* const* v_raw, float* const* t_raw, float* const* scal,
                 float* dots, float lr_t, const float* lr_t_dev, float beta1, float beta2, float eps, float gscale,
                 b2g_stream_t stream);
+
+/* ---- fp32 variants for the fp32/tf32 parity path (SNDCGANEngine(dtype="tf32"), north_star: per-layer <= 1e-3) ----
+ * The 64-channel side of the 3-channel edge layers, the discriminator head's input and the generator stem's output /
+ * incoming gradient are fp32 tensors here; arithmetic is exact fp32 on CUDA cores for the edge layers and the head,
+ * kind::tf32 (forward) / bf16 hi+lo split products (backward, `scratch` = 2*B*F bf16 elements) for the stem. */
+int b2g_conv3x3_c3_to_c64_f32(const float* in, const float* w, const float* wscale, const float* bias, float* out, int N,
+                              int H, int W, int act, float alpha, int dropout_thresh8, unsigned long long dropout_seed,
+                              const float* yprev, int dact, b2g_stream_t stream);
+int b2g_conv3x3_c64_to_c3_f32(const float* in, const float* w, const float* wscale, float* out, int N, int H, int W,
+                              int act, const float* yprev, int dact, b2g_stream_t stream);
+int b2g_wgrad3x3_c3_c64_f32(const float* t3, const float* t64, float* dw, float* dbias, int N, int H, int W,
+                            b2g_stream_t stream);
+int b2g_dhead_fwd_loss_f32(const float* x, const float* w, const float* wscale, const float* bias, int B, int F,
+                           int loss_kind, float label, float inv_batch, float* workspace, int workspace_floats,
+                           float* logits, float* dlogit, float* loss_out, b2g_stream_t stream);
+int b2g_dhead_bwd_f32(const float* x, const float* w, const float* wscale, const float* dlogit, int B, int F, float alpha,
+                      float dscale, float dzero, float* dx, float* dw, float* db, b2g_stream_t stream);
+int b2g_dense_g_fwd_f32(const float* z, const float* W, const float* gamma, const float* beta, float inv_std, float* out,
+                        int B, int F, b2g_stream_t stream);
+int b2g_dense_g_bwd_f32(const float* z, const float* W, const float* gamma, float inv_std, const float* dq, void* scratch,
+                        float* dW, float* dgamma, float* dbeta, int B, int F, b2g_stream_t stream);
 
 /* ---- small kernels either side of the step (csrc/b2g_misc.cu) -------------------------------------------------
  * dact: out = g * act'(y) elementwise from the saved forward output y (LeakyReLU/Dropout: y > 0 -> scale, y < 0 ->
