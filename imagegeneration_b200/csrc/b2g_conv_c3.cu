@@ -40,8 +40,7 @@ struct C3Cfg {
   static constexpr int kABytes = 128 * 128;  // 128 pixel rows of 128 B; only the first 64 B (K = 32) are used
   static constexpr int kStages = 6;
   static constexpr int kInStages = 8;           // staged fp32 input boxes
-  static constexpr int kInStageBytes = 6144;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896); 8 KiB in
-                                                // round 1, the 16 KiB went to the epilogue's second boxes
+  static constexpr int kInStageBytes = 8192;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896)
   static constexpr int kBBytes = kBlockN * 128;
   static constexpr int kAccBufs = 4;
   static constexpr int kTmemCols = kAccBufs * kBlockN;
@@ -50,7 +49,7 @@ struct C3Cfg {
   static constexpr int kThreads = 64 + 32 * kBuilderWarps + 128 * kEpiGroups;
   static constexpr int kMainBytes = kStages * kABytes + kBBytes + kInStages * kInStageBytes;  // multiple of 1 KiB
   static constexpr int kEpiWarps = 4 * kEpiGroups;
-  static constexpr int kEpiBoxes = 2;           // boxes per epilogue warp (b2g_conv_epi.cuh)
+  static constexpr int kEpiBoxes = 1;           // boxes per epilogue warp (b2g_conv_epi.cuh); a second one measured neutral
   static constexpr int kEpiBytes = epi_tma_smem_bytes(kEpiWarps, kEpiBoxes);
   static constexpr int kSmemBytes = kMainBytes + kEpiBytes + 512 + 1024;
 };
@@ -233,8 +232,8 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       uint32_t r[32];
       __syncwarp();
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
-      if (use_tma && tile + stride < total_tiles) {
-        // the warp's next item (two tiles on) is begun into the other box now: the store that last used that box is two
+      if (NB >= 2 && use_tma && tile + stride < total_tiles) {
+        // (two boxes only) the warp's next item (two tiles on) is begun into the other box now: the store that last used that box is two
         // items old, and the load has until the next accumulator to arrive
         TileWalk nx = tc;
         tile_walk_next(pl, nx);

@@ -47,15 +47,14 @@ struct PairCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   // N <= 128 tiles: the TMA epilogue's per-warp boxes (b2g_conv_epi.cuh) take the room of one pipeline stage
   static constexpr bool kEpiTma = BLOCK_N <= 128;
-  static constexpr int kStages = BLOCK_N == 256 ? 6 : (BLOCK_N == 128 ? 6 : 7);  // N <= 128: one stage less than in
-                                                                                 // round 1, its room went to the second epilogue box
+  static constexpr int kStages = BLOCK_N == 256 ? 6 : (BLOCK_N == 128 ? 7 : 8);
   static constexpr int kAccBufs = BLOCK_N <= 64 ? 4 : 2;
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
-  // 16 epilogue warps; N <= 128 (TMA epilogue): two 2 KiB boxes per warp (b2g_conv_epi.cuh), so an item's saved-output
-  // load does not wait for the previous item's store to drain — 8 warps with deeper box rings were measured 15-45 %
-  // slower in round 2, the backward epilogue is bound by per-warp instruction latency
+  // 16 epilogue warps; N <= 128 (TMA epilogue): one 2 KiB box per warp (b2g_conv_epi.cuh).  Measured in round 2: a second
+  // box (paid for with one pipeline stage) changed nothing here (D.conv4 dgrad 181 -> 187 us), 8 warps with 3-box rings
+  // were 15-45 % slower — the backward epilogue is bound by per-warp instruction latency, not by the box hand-over
   static constexpr int kEpiGroups = 4;
-  static constexpr int kEpiBoxes = kEpiTma ? 2 : 0;
+  static constexpr int kEpiBoxes = kEpiTma ? 1 : 0;
   static constexpr int kThreads = 64 + 128 * kEpiGroups;
   static constexpr int kEpiWarps = 4 * kEpiGroups;
   static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps, kEpiBoxes) : 0;

@@ -61,14 +61,23 @@ def main():
     t0, t1 = steps[-1].time_range.start, steps[-1].time_range.end
     ks = sorted([e for e in evs if e.time_range.start >= t0 and e.time_range.end <= t1 + 2000],
                 key=lambda e: e.time_range.start)
-    ks = [e for e in ks if "Memcpy" not in e.name and "Memset" not in e.name or True]
+    seen, uniq = set(), []
+    for e in ks:                       # record_function ranges ("nccl:all_reduce") duplicate the kernels they wrap
+        key = (e.time_range.start, e.time_range.end)
+        if e.name.startswith("nccl:") or key in seen:
+            continue
+        seen.add(key)
+        uniq.append(e)
+    ks = uniq
     first = ks[0].time_range.start
     last = max(e.time_range.end for e in ks)
     nccl = [e for e in ks if "nccl" in e.name.lower()]
     ours = [e for e in ks if "nccl" not in e.name.lower()]
     out = {"world": world, "rank": rank, "batch": args.batch, "graph": args.graph,
            "step_span_us": last - first, "our_kernels": len(ours), "our_busy_us": sum(e.time_range.end - e.time_range.start for e in ours),
-           "nccl": [], "gaps_over_5us": []}
+           "nccl": [], "gaps_over_5us": [],
+           "kernels": [[e.name[:48], round(e.time_range.start - first, 1), round(e.time_range.end - e.time_range.start, 1)]
+                       for e in ks]}
     for e in nccl:
         s, d = e.time_range.start - first, e.time_range.end - e.time_range.start
         overl = [o for o in ours if o.time_range.start < e.time_range.end and o.time_range.end > e.time_range.start]
@@ -86,7 +95,7 @@ def main():
     with open(f"gpurun_out/dp_timeline_n{world}_g{args.graph}_rank{rank}.json", "w") as f:
         json.dump(out, f, indent=1)
     if rank == 0:
-        print(json.dumps({k: v for k, v in out.items() if k not in ("nccl", "gaps_over_5us")}))
+        print(json.dumps({k: v for k, v in out.items() if k not in ("nccl", "gaps_over_5us", "kernels")}))
         print("nccl:", json.dumps(out["nccl"]))
         print("gaps:", json.dumps(sorted(out["gaps_over_5us"], key=lambda g: -g["gap_us"])[:12]))
     eng.close()
