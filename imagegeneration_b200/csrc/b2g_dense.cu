@@ -201,3 +201,52 @@ extern "C" int b2g_dhead_bwd_f32(const float* x, const float* w, const float* ws
                                  b2g_stream_t stream) {
   return dhead_bwd_any(x, w, wscale, dlogit, B, F, alpha, dscale, dzero, dx, dw, db, true, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of b2g_dhead_fwd_loss (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  The partial-sum scratch (part[b][s], at most 64 slices per sample) lives in a file-scope device array, so
+// the caller passes no workspace.  Every GPU that loads the library holds the kB2gHeadScratchFloats * 4 = 256 KiB until
+// the process exits.  Nothing in the array has to start at zero: dhead_partial_kernel writes every part[b][s] that
+// dhead_loss_kernel reads.  ALL calls share the one array: two calls that overlap on the GPU (different streams) race.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kB2gHeadScratchFloats = 64 * 1024;  // 64 slices x up to 1024 samples
+static __device__ __align__(256) float g_b2g_head_scratch[kB2gHeadScratchFloats];
+
+// In host code `g_b2g_head_scratch` is only a stand-in symbol, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+static int head_scratch_ptr(float** out) {
+  constexpr int kMaxDev = 64;
+  static float* ptrs[kMaxDev] = {nullptr};
+  int dev = 0;
+  B2G_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) return fail(B2G_E_CUDA, "b2g_dhead_fwd_loss_static: device index %d out of range", dev);
+  float* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* sym = nullptr;
+    B2G_CUDA_CHECK(cudaGetSymbolAddress(&sym, g_b2g_head_scratch));
+    if (!sym) return fail(B2G_E_CUDA, "b2g_dhead_fwd_loss_static: cudaGetSymbolAddress returned a null address");
+    p = static_cast<float*>(sym);
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);  // racing threads store the same value
+  }
+  *out = p;
+  return B2G_OK;
+}
+
+extern "C" int b2g_dhead_fwd_loss_static(const void* x, const float* w, const float* wscale, const float* bias, int B,
+                                         int F, int loss_kind, float label, float inv_batch, float* logits,
+                                         float* dlogit, float* loss_out, b2g_stream_t stream) {
+  if (B < 1) return fail(B2G_E_INVALID_ARG, "b2g_dhead_fwd_loss_static: B must be positive");
+  int S = (4 * num_sms() + B - 1) / B;  // same slicing as b2g_dhead_fwd_loss
+  if (S < 1) S = 1;
+  if (S > 64) S = 64;
+  if ((long)B * S > kB2gHeadScratchFloats)
+    return fail(B2G_E_UNSUPPORTED_SHAPE,
+                "b2g_dhead_fwd_loss_static: batch %d needs %ld scratch floats, the static scratch holds %d (use "
+                "b2g_dhead_fwd_loss with a caller workspace)", B, (long)B * S, kB2gHeadScratchFloats);
+  float* scratch = nullptr;
+  const int rc = head_scratch_ptr(&scratch);
+  if (rc) return rc;
+  return dhead_fwd_loss_any(x, w, wscale, bias, B, F, loss_kind, label, inv_batch, scratch, kB2gHeadScratchFloats, logits,
+                            dlogit, loss_out, false, stream);
+}

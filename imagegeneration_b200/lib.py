@@ -127,6 +127,8 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_dense_g_bwd": [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _P],
     # x, w, wscale, bias, B, F, loss_kind, label, inv_batch, ws, ws_floats, logits, dlogit, loss_out, stream
     "b2g_dhead_fwd_loss": [_P, _P, _P, _P, _I, _I, _I, _F, _F, _P, _I, _P, _P, _P, _P],
+    # x, w, wscale, bias, B, F, loss_kind, label, inv_batch, logits, dlogit, loss_out, stream  (static scratch, no alloc)
+    "b2g_dhead_fwd_loss_static": [_P, _P, _P, _P, _I, _I, _I, _F, _F, _P, _P, _P, _P],
     # x, w, wscale, dlogit, B, F, alpha, dscale, dzero, dx, dw, db, stream
     "b2g_dhead_bwd": [_P, _P, _P, _P, _I, _I, _F, _F, _F, _P, _P, _P, _P],
     # w, g, m, v, n, lr_t, b1, b2, eps, gscale, stream

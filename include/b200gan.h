@@ -251,6 +251,16 @@ int b2g_dhead_fwd_loss(const void* x, const float* w, const float* wscale, const
                        float* logits, float* dlogit, float* loss_out, b2g_stream_t stream);
 int b2g_dhead_bwd(const void* x, const float* w, const float* wscale, const float* dlogit, int B, int F, float alpha,
                   float dscale, float dzero, void* dx, float* dw, float* db, b2g_stream_t stream);
+/* b2g_dhead_fwd_loss without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments and results as b2g_dhead_fwd_loss (bf16 x) minus `workspace`:
+ * the partial sums live in a 256 KiB static device array inside the library (held by every GPU that loads it until the
+ * process exits).  Limit: B * min(64, ceil(4 * SMs / B)) <= 65536 floats, i.e. any batch up to 1024; larger batches
+ * return B2G_E_UNSUPPORTED_SHAPE.  Calls no cudaMalloc / cudaFree / allocating routine.  All calls share the array:
+ * calls that overlap on the GPU (different streams) race — serialise them. */
+int b2g_dhead_fwd_loss_static(const void* x, const float* w, const float* wscale, const float* bias, int B, int F,
+                              int loss_kind, float label, float inv_batch, float* logits, float* dlogit,
+                              float* loss_out, b2g_stream_t stream);
 
 /* ---- parameter-side kernels -------------------------------------------------------------------------------
  * adam: Keras-2 Adam on a flat fp32 arena (all variables of one network): one launch per apply_gradients
