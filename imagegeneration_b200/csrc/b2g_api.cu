@@ -1,5 +1,6 @@
 // b2g_api.cu — library-wide state of the C ABI: version, thread-local error text, driver entry points,
 // and the weight re-packing kernel that feeds the implicit-GEMM convolutions.
+#include <stdlib.h>
 #include <string.h>
 
 #include "b2g_conv.cuh"
@@ -321,7 +322,11 @@ extern "C" int b2g_pack_conv_weight_multi(const b2g_pack_job* jobs, int n_jobs, 
     blocks += phases * taps * d.n_blocks * d.c_blocks;
   }
   p.n_jobs = n_jobs;
-  const int cap = num_sms() * 6;
+  // one tile per block: measured (tools/sn_probe.py) 34-40 us for the discriminator's 14 packings, against 42-57 us for
+  // persistent blocks with a register-prefetched next tile (grid = 6 blocks per SM) — the tiles are short and the
+  // block scheduler overlaps them better than one block's own prefetch does.  B2G_PACK_PERSISTENT=1 keeps the other form.
+  static int persistent = []() { const char* e = getenv("B2G_PACK_PERSISTENT"); return e ? atoi(e) : 0; }();
+  const int cap = persistent ? num_sms() * 6 : blocks;
   pack_conv_weight_multi_kernel<<<blocks < cap ? blocks : cap, 256, 0, static_cast<cudaStream_t>(stream_)>>>(p, blocks);
   B2G_LAUNCH_CHECK();
   return B2G_OK;

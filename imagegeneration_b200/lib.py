@@ -158,6 +158,19 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_dense_g_fwd_f32": [_P, _P, _P, _P, _F, _P, _I, _I, _P],
     # z, W, gamma, inv_std, dq, scratch, dW, dgamma, dbeta, B, F, stream
     "b2g_dense_g_bwd_f32": [_P, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _P],
+    # CycleGAN path (csrc/b2g_cyclegan.cu)
+    # in, in_f32, N, Hin, Win, C, ldc, kh, kw, mode, stride, pad_t, pad_l, reflect, Hout, Wout, out, Mpad, Kpad, stream
+    "b2g_im2col": [_P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _L, _I, _P],
+    # w, taps, D2, D3, n_is_d3, out, Npad, Kpad, stream
+    "b2g_pack_gemm_weight": [_P, _I, _I, _I, _I, _P, _I, _I, _P],
+    # dpad, dx, N, H, W, C, ldc, pad, stream
+    "b2g_reflect_fold": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
+    # a, res, gamma, beta, y, stat, N, H, W, C, ldc, act, alpha, eps, y_f32, stream
+    "b2g_rownorm_fwd": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _F, _I, _P],
+    # dy, y, a, res, gamma, stat, da, dgamma, dbeta, N, H, W, C, ldc, act, alpha, y_f32, stream
+    "b2g_rownorm_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _I, _P],
+    # a, b, n, scale, loss_out, da, stream
+    "b2g_l1_loss": [_P, _P, _L, _F, _P, _P, _P],
     # g, y, out, n, f32, kind, alpha, scale, zero, stream
     "b2g_dact": [_P, _P, _P, _L, _I, _I, _F, _F, _F, _P],
     # logits, labels, B, loss_out, dlogit, stream

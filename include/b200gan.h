@@ -349,6 +349,33 @@ int b2g_gather_u8_to_f32(const void* images_u8, const long* idx, float* out, int
                          b2g_stream_t stream);
 int b2g_colsum_f32(const float* x, float* out, long P, int C, b2g_stream_t stream);
 
+/* ---- CycleGAN path (cyclegan/CycleGAN.py) — csrc/b2g_cyclegan.cu ----------------------------
+ * Convolutions of arbitrary geometry run as gather + GEMM: b2g_im2col writes the bf16 matrix [Mpad][Kpad] (row = output
+ * pixel (n, oy, ox), column = (ky, kx, c); padding rows / columns zero) that b2g_conv_igemm (kind K1S1) multiplies with
+ * a b2g_pack_gemm_weight matrix and b2g_conv_wgrad (kind K1S1) reduces into the Keras-layout weight gradient.
+ *   im2col mode 0: in[n, oy*stride + ky - pad_t, ox*stride + kx - pad_l, c]  (Conv2D forward :98,:131,:142 — `reflect`
+ *                  folds ReflectionPadding2D :37-57 into the gather —, Conv2DTranspose input gradient);
+ *          mode 1: in[n, (oy + pad_t - ky)/stride, (ox + pad_l - kx)/stride, c] where the divisions are exact
+ *                  (Conv2DTranspose forward :152, Conv2D input gradient).   `in`: bf16 or fp32 NHWC, channel stride ldc.
+ *   pack_gemm_weight: out[n][tap*Ck + c] bf16 [Npad][Kpad] from fp32 w[tap][D2][D3]; (n, c) = (d3, d2) if n_is_d3 else (d2, d3).
+ *   reflect_fold: gradient of ReflectionPadding2D: dx[N,H,W,C] from dpad[N,H+2p,W+2p,(ldc)].
+ *   rownorm_fwd/bwd: tensorflow_addons InstanceNormalization(axis=1) on NHWC as the reference uses it (:65,69,99,132,143,
+ *                  153) = statistics per image ROW (n, h) over W x C, gamma/beta [H], with the following activation
+ *                  (none / ReLU / LeakyReLU / tanh) and, when `res` is given, the ResBlock's add + ReLU in front (:89-91);
+ *                  a/da: bf16 with channel stride ldc, y/dy: bf16 or fp32 [.., C]; stat: 2 floats per row; dgamma/dbeta +=.
+ *   l1_loss: loss_out[0] += scale * mean|a - b|, da = scale * sign(a - b) / n   (calc_cycle_loss / identity_loss :199-207). */
+int b2g_im2col(const void* in, int in_f32, int N, int Hin, int Win, int C, int ldc, int kh, int kw, int mode, int stride,
+               int pad_t, int pad_l, int reflect, int Hout, int Wout, void* out, long Mpad, int Kpad, b2g_stream_t stream);
+int b2g_pack_gemm_weight(const float* w, int taps, int D2, int D3, int n_is_d3, void* out, int Npad, int Kpad,
+                         b2g_stream_t stream);
+int b2g_reflect_fold(const void* dpad, void* dx, int N, int H, int W, int C, int ldc, int pad, b2g_stream_t stream);
+int b2g_rownorm_fwd(const void* a, const void* res, const float* gamma, const float* beta, void* y, float* stat, int N,
+                    int H, int W, int C, int ldc, int act, float alpha, float eps, int y_f32, b2g_stream_t stream);
+int b2g_rownorm_bwd(const void* dy, const void* y, const void* a, const void* res, const float* gamma, const float* stat,
+                    void* da, float* dgamma, float* dbeta, int N, int H, int W, int C, int ldc, int act, float alpha,
+                    int y_f32, b2g_stream_t stream);
+int b2g_l1_loss(const float* a, const float* b, long n, float scale, float* loss_out, float* da, b2g_stream_t stream);
+
 /* ---- host-only introspection (no CUDA calls; used by the CPU test-suite) ---------------------------------
  * conv_plan_query: tiling + tap tables of a conv role -> out[0..15] = {phases, taps, Hg, Wg, bw, bh, bn, tiles_w,
  *   tiles_h, tiles_n, m_tiles, Hout, Wout, out_stride, n_input_maps, 0}; out[16+i] = input map of tap entry i,
