@@ -462,15 +462,15 @@ def run_b200(args):
         roof[name] = {"bound": "tensor", "achieved": fl / sec / 1e12, "peak": peak_tf, "unit": "TFLOP/s",
                       "frac": fl / sec / 1e12 / peak_tf, "traffic": None, "launches_per_step": cnt,
                       "ms_per_step": sec * 1e3, "peak_kind": f"{peak_kind} {peak_name}"}
-    # DRAM bytes per launch of the same kernel families from one ncu capture of one step (profiles/, committed with
-    # the command that produced it); None when the file is absent
+    # DRAM bytes per launch of the same kernel families from one ncu capture of one step at the round's HEAD
+    # (profiles/r2_conv_traffic.json names the build and the command); None when the file is absent or the dtype differs
     try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_conv_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_conv_traffic.json")) as f:
             traffic = json.load(f)
         for name, v in roof.items():
-            if name in traffic:
+            if name in traffic and args.dtype == "bf16":
                 v["traffic"] = traffic[name]["dram_bytes_per_launch"]
-                v["traffic_source"] = "profiles/r1_conv_traffic.json (ncu dram__bytes_read+write per launch, one step)"
+                v["traffic_source"] = "profiles/r2_conv_traffic.json: " + traffic.get("source", "")
     except (OSError, ValueError, KeyError):
         pass
     tc_ms = sum(v["ms_per_step"] for v in roof.values())

@@ -516,7 +516,8 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   const int tf32 = a->tf32 ? 1 : 0;  // fp32 operands, kind::tf32 (the per-layer parity path)
   if (tf32 && a->kind == B2G_CONV_K1S1)
     return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_conv_wgrad: the tf32 path covers K3S1 / K4S2");
-  const bool taps_ok = !tf32 && a->Cb % 128 == 0 && (a->ca_valid == 0 || a->ca_valid == a->Ca) && !a->dbias;
+  const bool taps_ok = !tf32 && a->Cb % 128 == 0 && (a->ca_valid == 0 || a->ca_valid == a->Ca) && !a->dbias &&
+                       (a->Ca <= 256 || a->Ca % 256 == 0);  // the tap-grouped kernels split Ca into chunks of min(Ca, 256)
   // Measured on B200 (profiles/r1_wgrad_variants.md): grouping taps wins when the other kernel's N tile would be
   // narrow (Cb == 128: 64->128 and 128->128 layers); for Cb >= 256 the per-tap kernel with vector reds is faster.
   const bool use_taps = taps_ok && (force_taps < 0 ? a->Cb == 128 : force_taps != 0);
