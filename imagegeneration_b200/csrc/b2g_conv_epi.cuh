@@ -46,6 +46,10 @@ struct EpiParams {
                 // accumulators but skip math, saved-output loads and stores -> the launch time is the MMA/load pipeline alone
   int tma;      // 1: bf16 output (and yprev) move through per-warp shared-memory boxes and TMA (EpiTmaMaps)
   int qw, qh, qn;  // the 32 pixels one epilogue warp owns, as a box of the tile (qw * qh * qn == 32)
+  int lean;     // TMA epilogue only (fill_epi_tma): 0 = general math (conv_epilogue_math); 1 = lean forward (bias, none /
+                // ReLU / max-form LeakyReLU, dropout off or rate 0.5); 2 = lean ReLU'; 3 = lean LeakyReLU' with a zero
+                // saved output -> 0 (dropout layers); 4 = lean LeakyReLU' with zero counted as negative.  Same results
+                // bit for bit, a third of the instructions (epi_lean_fwd / epi_lean_bwd)
 };
 
 // The dropout seed of a call, resolved once per epilogue warp (it may live in device memory for graph replay).  Kept
@@ -98,27 +102,30 @@ __device__ __forceinline__ void conv_epilogue_math(const EpiParams& p, const flo
     for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
   }
   if (p.drop_thresh8 == 128 && valid && p.dact == B2G_ACT_NONE && !p.f32_io && !colsum_here) {
-    // rate 0.5 (the reference's default, Trainer.py:22) on a bf16 forward epilogue: "byte >= 128" is the byte's top bit,
-    // so the keep mask of a PAIR of elements is one PRMT in sign-replication mode and the drop one AND on the packed
-    // bf16x2 word: 2 instructions per pair instead of 5-6 compare/select ones (the epilogue of the 3-channel conv is
-    // instruction-issue bound: ncu r2, 10 % of its instructions were these selects).  Same mask, bit for bit.
-    const uint32_t g0 = static_cast<uint32_t>(off >> 2);
+    // rate 0.5 (the reference's default, Trainer.py:22) on a bf16 forward epilogue: ONE hash word for the thread's 32
+    // elements (b2g_keep128); word << s carries the keep bits of elements 4s .. 4s+3 at the byte tops, PRMT in
+    // sign-replication mode makes the bf16x2 AND masks: 1.25 instructions per element plus one hash per 32.
+    const uint32_t w = b2g_dropout_bits(static_cast<uint32_t>(off >> 5), sd.lo, sd.hi);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
-      const uint32_t b0 = b2g_dropout_bits(g0 + 2 * g, sd.lo, sd.hi), b1 = b2g_dropout_bits(g0 + 2 * g + 1, sd.lo, sd.hi);
+      const uint32_t y0 = w << (2 * g), y1 = w << (2 * g + 1);
       uint4 o;
-      o.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]) & b2g_keep_mask_pair(b0, 0);
-      o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]) & b2g_keep_mask_pair(b0, 1);
-      o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]) & b2g_keep_mask_pair(b1, 0);
-      o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]) & b2g_keep_mask_pair(b1, 1);
+      o.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]) & b2g_keep_mask_pair(y0, 0);
+      o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]) & b2g_keep_mask_pair(y0, 1);
+      o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]) & b2g_keep_mask_pair(y1, 0);
+      o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]) & b2g_keep_mask_pair(y1, 1);
       ostore(g, o);
     }
     return;
   }
-  if (p.drop_thresh8 > 0 && valid) {
-    // element i keeps its value iff byte (i & 3) of the group's hash >= thresh8: the byte is moved to the top of
-    // the word and compared with thresh8 << 24 (the junk below it cannot change the outcome); the 1/(1-rate)
-    // scale was applied before the activation (pre_scale)
+  if (p.drop_thresh8 == 128 && valid) {  // same one-bit masks, fp32 selects (fp32/tf32 path, fused column sums)
+    const uint32_t w = b2g_dropout_bits(static_cast<uint32_t>(off >> 5), sd.lo, sd.hi);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = b2g_keep128(w, j) ? v[j] : 0.f;
+  } else if (p.drop_thresh8 > 0 && valid) {
+    // general rates: element i keeps its value iff byte (i & 3) of the hash of group i >> 2 is >= thresh8: the byte is
+    // moved to the top of the word and compared with thresh8 << 24 (the junk below it cannot change the outcome); the
+    // 1/(1-rate) scale was applied before the activation (pre_scale)
     const uint32_t g0 = static_cast<uint32_t>(off >> 2);
     const uint32_t t24 = static_cast<uint32_t>(p.drop_thresh8) << 24;
 #pragma unroll
@@ -292,6 +299,120 @@ __device__ __forceinline__ void epi_colsum_flush(const EpiParams& p, const float
 // Here each epilogue warp owns one 2 KiB shared-memory box [32 pixels][32 channels] (64-byte swizzle, conflict
 // free 16-byte accesses): the saved output arrives in it by TMA, the results leave from it by TMA.
 // ---------------------------------------------------------------------------------------------------------------
+// ---------------------------------------------------------------------------------------------------------------
+// Lean epilogue math of the TMA epilogue (EpiParams::lean).  ncu of round 2 showed the epilogue warps of every layer with
+// <= 128 output channels issue-bound: 600-1000 instructions per 32x32 item, most of them one-fp32-lane-at-a-time math,
+// a dropout hash per 4 elements and compare/select chains.  Here: packed fp32 pairs (FFMA2 / FMUL2), one dropout hash
+// per 32 elements (b2g_keep128), derivative selects as bf16x2 compare masks (HSET2) + one LOP3 on packed words, ReLU
+// folded into the bf16 conversion.  Bit-identical to conv_epilogue_math for the cases fill_epi_tma routes here.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_bf16x2_relu(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+// s += bf16 half of w, exact widening inside the add (FHADD.BF16 takes the register half directly: no unpack)
+__device__ __forceinline__ void bf2_acc(uint32_t w, float& s_lo, float& s_hi) {
+  asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %2;\n\tadd.rn.f32.bf16 %0, l, %0;\n\tadd.rn.f32.bf16 %1, h, %1;\n\t}"
+      : "+f"(s_lo), "+f"(s_hi)
+      : "r"(w));
+}
+__device__ __forceinline__ void bf2_acc_sq(uint32_t w, float& q_lo, float& q_hi) {
+  asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %2;\n\tfma.rn.f32.bf16 %0, l, l, %0;\n\tfma.rn.f32.bf16 %1, h, h, %1;\n\t}"
+      : "+f"(q_lo), "+f"(q_hi)
+      : "r"(w));
+}
+
+// forward: r = the thread's 32 accumulator columns [cb, cb+32) of its pixel; `grp32` = (flat element index of the first
+// one) >> 5; results go to the thread's 64-byte row of the warp's box (64-byte swizzle `sw`).
+__device__ __forceinline__ void epi_lean_fwd(const EpiParams& p, const float* sbias, const uint32_t (&r)[32], uint32_t grp32,
+                                             int cb, uint8_t* row, uint32_t sw, EpiSeed sd) {
+  uint64_t v[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) v[k] = f2_pack(__uint_as_float(r[2 * k]), __uint_as_float(r[2 * k + 1]));
+  const uint64_t ps2 = f2_pack(p.pre_scale, p.pre_scale);
+  if (p.bias) {  // (acc * pre_scale + bias * pre_scale): the shared table holds the scaled bias
+#pragma unroll
+    for (int k4 = 0; k4 < 8; ++k4) {
+      const float4 b4 = *reinterpret_cast<const float4*>(&sbias[cb + k4 * 4]);
+      v[2 * k4] = f2_fma(v[2 * k4], ps2, f2_pack(b4.x, b4.y));
+      v[2 * k4 + 1] = f2_fma(v[2 * k4 + 1], ps2, f2_pack(b4.z, b4.w));
+    }
+  } else if (p.pre_scale != 1.f) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = f2_mul(v[k], ps2);
+  }
+  uint32_t o[16];
+  if (p.act == B2G_ACT_LEAKY) {  // max(v, alpha * v), 0 <= alpha <= 1
+    const uint64_t al2 = f2_pack(p.alpha, p.alpha);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      float v0, v1, a0, a1;
+      f2_unpack(v[k], v0, v1);
+      f2_unpack(f2_mul(v[k], al2), a0, a1);
+      o[k] = pack_bf16x2(fmaxf(v0, a0), fmaxf(v1, a1));
+    }
+  } else if (p.act == B2G_ACT_RELU) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      float v0, v1;
+      f2_unpack(v[k], v0, v1);
+      o[k] = pack_bf16x2_relu(v0, v1);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      float v0, v1;
+      f2_unpack(v[k], v0, v1);
+      o[k] = pack_bf16x2(v0, v1);
+    }
+  }
+  if (p.drop_thresh8 == 128) {
+    const uint32_t w = b2g_dropout_bits(grp32, sd.lo, sd.hi);
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      const uint32_t y = w << s;
+      o[2 * s] &= b2g_keep_mask_pair(y, 0);
+      o[2 * s + 1] &= b2g_keep_mask_pair(y, 1);
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < 4; ++g)
+    *reinterpret_cast<uint4*>(row + ((g ^ sw) << 4)) = make_uint4(o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+}
+
+// backward: the thread's row of the box holds the saved forward output y; it is replaced by acc * act'(y).
+// MODE 2: ReLU' (y > 0);  3: LeakyReLU' scale / alpha*scale / 0 for y > 0 / < 0 / == 0;  4: y <= 0 -> alpha*scale.
+template <int MODE>
+__device__ __forceinline__ void epi_lean_bwd(const EpiParams& p, const uint32_t (&r)[32], uint8_t* row, uint32_t sw) {
+  const float as = p.dact_alpha * p.dact_scale;
+  const uint64_t s2 = f2_pack(p.dact_scale, p.dact_scale), as2 = f2_pack(as, as);
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint4* slot = reinterpret_cast<uint4*>(row + ((g ^ sw) << 4));
+    const uint4 yv = *slot;
+    const uint32_t y4[4] = {yv.x, yv.y, yv.z, yv.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const float v0 = __uint_as_float(r[g * 8 + b * 2]), v1 = __uint_as_float(r[g * 8 + b * 2 + 1]);
+      const uint32_t pos = bf2_gt0_mask(y4[b]);
+      if (MODE == 2) {
+        o[b] = pack_bf16x2(v0, v1) & pos;
+      } else {
+        const uint64_t v = f2_pack(v0, v1);
+        float a0, a1, b0, b1;
+        f2_unpack(f2_mul(v, s2), a0, a1);
+        f2_unpack(f2_mul(v, as2), b0, b1);
+        const uint32_t pa = pack_bf16x2(a0, a1), pb = pack_bf16x2(b0, b1);
+        if (MODE == 4) o[b] = (pa & pos) | (pb & ~pos);
+        else o[b] = (pa & pos) | (pb & bf2_lt0_mask(y4[b]));
+      }
+    }
+    *slot = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 // Every epilogue warp owns NB boxes.  Item k (the k-th 32-pixel x 32-channel chunk the warp processes, counted over the
 // whole kernel) lives in box k % NB: a backward (dact) epilogue first loads the SAVED forward output into it by TMA
 // (epi_tma_begin), the math runs in place, the result leaves by TMA (epi_tma_chunk).  With NB = 2 (where shared memory
@@ -378,11 +499,20 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
     if (elect_one_sync()) tma_store_wait_read_n<NB - 1>();
     __syncwarp();
   }
-  conv_epilogue_math(
-      p, sbias, r, pix, cb, true,
-      [&](int g) { return *reinterpret_cast<const uint4*>(row + ((g ^ sw) << 4)); },
-      [&](int g, const uint4& o) { *reinterpret_cast<uint4*>(row + ((g ^ sw) << 4)) = o; }, nullptr, false, nullptr,
-      sd);
+  if (p.lean == 1)
+    epi_lean_fwd(p, sbias, r, static_cast<uint32_t>((pix * p.Cout + cb) >> 5), cb, row, sw, sd);
+  else if (p.lean == 2)
+    epi_lean_bwd<2>(p, r, row, sw);
+  else if (p.lean == 3)
+    epi_lean_bwd<3>(p, r, row, sw);
+  else if (p.lean == 4)
+    epi_lean_bwd<4>(p, r, row, sw);
+  else
+    conv_epilogue_math(
+        p, sbias, r, pix, cb, true,
+        [&](int g) { return *reinterpret_cast<const uint4*>(row + ((g ^ sw) << 4)); },
+        [&](int g, const uint4& o) { *reinterpret_cast<uint4*>(row + ((g ^ sw) << 4)) = o; }, nullptr, false, nullptr,
+        sd);
   fence_proxy_async_smem();
   __syncwarp();
   if (elect_one_sync()) tma_store_4d(omap, box, cb, bx, by, bn);
@@ -403,20 +533,16 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         const uint32_t w = *reinterpret_cast<const uint32_t*>(base + j * 128 + ((cg ^ (j & 3)) << 4));
-        const float f0 = bf16_lo(w), f1 = bf16_hi(w);
-        s0 += f0; s1 += f1;
-        q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+        bf2_acc(w, s0, s1);
+        bf2_acc_sq(w, q0, q1);
       }
       q0 += __shfl_xor_sync(0xffffffffu, q0, 16);
       q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
       atomicAdd(&const_cast<float*>(sbias)[cs_off + cb + 2 * cp + h], h ? q1 : q0);
     } else {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const uint32_t w = *reinterpret_cast<const uint32_t*>(base + j * 128 + ((cg ^ (j & 3)) << 4));
-        s0 += bf16_lo(w);
-        s1 += bf16_hi(w);
-      }
+      for (int j = 0; j < 16; ++j)  // one mixed-precision add per element (FHADD.BF16), no unpacking
+        bf2_acc(*reinterpret_cast<const uint32_t*>(base + j * 128 + ((cg ^ (j & 3)) << 4)), s0, s1);
     }
     s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
     s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
@@ -474,6 +600,7 @@ inline void fill_epi_params(const b2g_conv_args* a, EpiParams* e) {
   e->colsumsq = a->colsumsq;
   e->cs_copies = (a->Cout > 0 && a->Cout <= 512) ? (512 / a->Cout > 0 ? 512 / a->Cout : 1) : 1;  // 512-float tables
   e->tma = 0;
+  e->lean = 0;
   {
     const char* d = getenv("B2G_DBG_EPI");  // read per call: measurement runs flip it between launches
     e->dbg = d ? atoi(d) : 0;
@@ -511,6 +638,20 @@ inline int fill_epi_tma(const b2g_conv_args* a, const ConvPlan& pl, bool enabled
   }
   e->tma = 1;
   e->qw = qw; e->qh = qh; e->qn = qn;
+  {
+    static int lean_env = []() { const char* s = getenv("B2G_EPI_LEAN"); return s ? atoi(s) : 1; }();
+    const bool act_ok = a->act == B2G_ACT_NONE || a->act == B2G_ACT_RELU || (a->act == B2G_ACT_LEAKY && e->leaky_max);
+    const bool drop_ok = a->dropout_thresh8 == 0 || a->dropout_thresh8 == 128;
+    e->lean = 0;
+    if (!lean_env) {
+    } else if (a->dact == B2G_ACT_NONE && !a->colsum && !a->colsumsq && act_ok && drop_ok) {
+      e->lean = 1;
+    } else if (a->dact != B2G_ACT_NONE && !a->bias && a->act == B2G_ACT_NONE && !a->dropout_thresh8 && !a->colsumsq) {
+      if (a->dact == B2G_ACT_RELU) e->lean = 2;
+      else if (a->dact == B2G_ACT_LEAKY && a->dact_zero == 0.f) e->lean = 3;
+      else if (a->dact == B2G_ACT_LEAKY && a->dact_zero == a->dact_alpha * a->dact_scale) e->lean = 4;
+    }
+  }
   return B2G_OK;
 }
 

@@ -62,7 +62,14 @@ __global__ void __launch_bounds__(128) conv3x3_c3_to_c64_kernel(
       for (int c = 0; c < 64; ++c) acc[c] = acc[c] > 0.f ? acc[c] : acc[c] * alpha;
     }
     const size_t off = (size_t)pix * 64;
-    if (drop_thresh8 > 0) {
+    if (drop_thresh8 == 128) {  // rate 0.5: one bit per element, one hash word per 32 elements (b2g_keep128)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t w = b2g_dropout_bits((uint32_t)(off >> 5) + h, seed_lo, seed_hi);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) acc[h * 32 + e] = b2g_keep128(w, e) ? acc[h * 32 + e] * drop_scale : 0.f;
+      }
+    } else if (drop_thresh8 > 0) {
       const uint32_t g0 = (uint32_t)(off >> 2);
 #pragma unroll
       for (int g = 0; g < 16; ++g) {

@@ -327,7 +327,8 @@ __host__ __device__ constexpr uint32_t umma_idesc(uint32_t fmt, uint32_t a_mn_ma
 }
 
 // ---------------------------------------------------------------------------------------------
-// counter-based dropout RNG: one 32-bit hash per 4 consecutive elements, one byte per element.
+// counter-based dropout RNG: one 32-bit hash per 4 consecutive elements, one byte per element (general rates), or per
+// 32 consecutive elements, one bit per element (rate 0.5, see b2g_keep128).
 // Restated bit-exactly in oracle/dropout_hash.py so the CPU oracle can be fed the same masks.
 // ---------------------------------------------------------------------------------------------
 __host__ __device__ __forceinline__ uint32_t b2g_mix32(uint32_t x) {
@@ -350,12 +351,60 @@ __host__ __device__ __forceinline__ uint32_t b2g_dropout_bits(uint32_t group, ui
   x ^= x >> 16;
   return x;
 }
-// byte-sign masks of a hash word for packed bf16 pairs: result half h is 0xFFFF iff byte (2*pair + h) of `bits` has its
-// top bit set (byte >= 128), else 0 — PRMT's sign-replication mode, one instruction per pair of elements
+// Rate 0.5 (thresh8 == 128, the reference's default, Trainer.py:22) spends ONE BIT per element instead of a byte: the
+// hash word of group (flat element index >> 5) covers 32 consecutive elements, element e = index & 31 is KEPT iff bit
+// 8 * (e & 3) + 7 - (e >> 2) of the word is set.  The odd bit order is what makes the packed epilogue cheap: word << s
+// moves the bits of elements 4s .. 4s+3 to the tops of the four bytes, where PRMT's sign-replication mode turns each
+// pair of them into a bf16x2 AND mask (b2g_keep_mask_pair) — one hash (9 instructions) per 32 elements instead of per 4,
+// measured as the largest single item of the forward epilogues' instruction count in round 2.  Restated in
+// oracle/dropout_hash.py (keep_mask with thresh8 == 128).
+__host__ __device__ __forceinline__ uint32_t b2g_keep128(uint32_t word, uint32_t e) {
+  return (word >> (8u * (e & 3u) + 7u - (e >> 2))) & 1u;
+}
+// byte-sign masks of a word for packed bf16 pairs: result half h is 0xFFFF iff byte (2*pair + h) of `bits` has its
+// top bit set, else 0 — PRMT's sign-replication mode, one instruction per pair of elements
 __device__ __forceinline__ uint32_t b2g_keep_mask_pair(uint32_t bits, int pair) {
   uint32_t m;
   if (pair == 0) asm("prmt.b32 %0, %1, %1, 0x9988;" : "=r"(m) : "r"(bits));
   else asm("prmt.b32 %0, %1, %1, 0xBBAA;" : "=r"(m) : "r"(bits));
+  return m;
+}
+
+// ---------------------------------------------------------------------------------------------
+// packed fp32 pairs (sm_100: FMUL2 / FFMA2 / FADD2 process two fp32 lanes per issue slot) and bf16x2 compare masks
+// (HSET2.BF16_V2: 0xFFFF per true half) — the epilogues are instruction-issue bound, not FLOP bound
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t bf2_gt0_mask(uint32_t y) {
+  uint32_t m;
+  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(y), "r"(0u));
+  return m;
+}
+__device__ __forceinline__ uint32_t bf2_lt0_mask(uint32_t y) {
+  uint32_t m;
+  asm("set.lt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(y), "r"(0u));
   return m;
 }
 

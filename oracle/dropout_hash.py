@@ -4,7 +4,8 @@ Bit-exact numpy restatement of the counter-based dropout RNG in imagegeneration_
 (b2g_mix32 / b2g_dropout_bits).  TensorFlow's stateful RNG stream (tf.nn.dropout behind
 tf.keras.layers.Dropout, sndcgan/SNDCGAN.py:78) cannot be reproduced outside TF, so parity tests feed the
 oracle the very keep-masks the CUDA kernels apply: element i of a flat NHWC activation is DROPPED when
-byte (i & 3) of hash(i >> 2, seed) is < thresh8, i.e. with probability thresh8 / 256.
+byte (i & 3) of hash(i >> 2, seed) is < thresh8, i.e. with probability thresh8 / 256; rate 0.5 (thresh8 = 128) spends
+one bit per element instead (hash(i >> 5, seed), see keep_mask).
 """
 from __future__ import annotations
 
@@ -40,10 +41,22 @@ def dropout_bits(group: np.ndarray, seed: int) -> np.ndarray:
 
 
 def keep_mask(numel: int, seed: int, thresh8: int) -> np.ndarray:
-    """uint8 keep mask (1 = kept) for a flat activation of `numel` elements (numel % 4 == 0)."""
+    """uint8 keep mask (1 = kept) for a flat activation of `numel` elements (numel % 4 == 0).
+
+    thresh8 == 128 (rate 0.5, the reference's default): one BIT per element — element e = i & 31 of the hash word of
+    group i >> 5 is kept iff bit 8 * (e & 3) + 7 - (e >> 2) is set (b2g_keep128 in b2g_ptx.cuh).
+    Other rates: one BYTE per element — byte i & 3 of the hash word of group i >> 2 is >= thresh8."""
     assert numel % 4 == 0
     if thresh8 <= 0:
         return np.ones(numel, dtype=np.uint8)
+    if thresh8 == 128:
+        words = (numel + 31) // 32
+        with np.errstate(over="ignore"):
+            bits = dropout_bits(np.arange(words, dtype=np.uint32), seed)
+        e = np.arange(32, dtype=np.uint32)
+        pos = np.uint32(8) * (e & np.uint32(3)) + np.uint32(7) - (e >> np.uint32(2))
+        keep = (bits[:, None] >> pos[None, :]) & np.uint32(1)
+        return keep.reshape(-1)[:numel].astype(np.uint8)
     groups = np.arange(numel // 4, dtype=np.uint32)
     with np.errstate(over="ignore"):
         bits = dropout_bits(groups, seed)
