@@ -7,12 +7,18 @@
 //                 the box starts 4 pixels left of the tile because TMA wants a 16-byte aligned start offset)
 //                 through an 8-stage ring — the HBM/L2 latency is hidden by the ring, not by the builder threads
 //   warp 1      : TMEM allocator + MMA issuer — one K=32 step (two K=16 MMAs, M=128, N=64) per 128-pixel tile
-//   warps 2..5  : patch builders, one pixel per thread: 27 conflict-free LDS.32 from the staged box + a ones
+//   warps 2..3  : patch builders, two pixels per thread: 27 conflict-free LDS.32 from the staged box + a ones
 //                 column -> 32 bf16 = 4 x 16 B written at the SW128-swizzled position of the pixel's row,
 //                 fence.proxy.async, mbarrier arrive.  This is the im2col27 tensor of b2g_edge.cu, never leaving
 //                 the SM.
-//   warps 6..21 : epilogue (4 groups x 4 TMEM lane quarters, 4 accumulator buffers): bias / LeakyReLU / dropout or
-//                 ReLU' from the saved output, bf16 NHWC stores (b2g_conv_epi.cuh)
+//   warps 4..15 : epilogue (3 groups x 4 TMEM lane quarters, 4 accumulator buffers).  A warp takes BOTH 32-channel
+//                 halves of its 32 pixels in one visit (two tcgen05.ld in flight, the accumulator is released as soon as
+//                 they land): bias / LeakyReLU / dropout or ReLU' from the saved output (lean math of b2g_conv_epi.cuh)
+//                 into a [32 pixels][64 channels] 128-byte-swizzled box, ONE TMA store of whole 128-byte lines per
+//                 visit, two boxes per warp.  Round 2 measured the 16-warp / 32-channel-item form latency-bound: per
+//                 item ~4000 cycles of one warp for ~250 instructions, a third of the stall samples in per-item
+//                 bookkeeping (tile walk, coordinates, fence / elect / store) — twice the work per visit halves that
+//                 and doubles the independent work a warp has in flight.
 //
 // HBM traffic per pixel: 12 B read + 128 B written (+128 B for the dact variant), against 12+128 (im2col27) +
 // 128+128 (K1S1 GEMM) for the two-kernel route.  Replaces D.conv1 forward (Conv2D 3->64 k3 s1 + bias + LeakyReLU +
@@ -31,33 +37,35 @@ struct alignas(64) C3KernelParams {
   CUtensorMap imap;  // fp32 input seen as 8-byte elements: dims {W*3/2, H, N}, box {(bw+8)*3/2, bh+2, bn}
   ConvPlan plan;     // K1S1 geometry: 128-pixel boxes (bw, bh, bn) over the N x H x W grid
   EpiParams e;
-  EpiTmaMaps em;     // TMA epilogue (used when e.tma)
+  EpiTmaMaps em;     // 32-channel maps of b2g_conv_epi.cuh (unused here: kept so fill_epi_tma decides e.tma / e.lean)
+  CUtensorMap omap64, ymap64;  // TMA epilogue (used when e.tma): bf16 NHWC output / saved output, box {64 channels, qw,
+                               // qh, qn} = 32 pixels x 128 bytes, 128-byte swizzle
   int in_box_bytes;  // bytes one input box delivers
 };
 
 struct C3Cfg {
   static constexpr int kBlockN = 64;
   static constexpr int kABytes = 128 * 128;  // 128 pixel rows of 128 B; only the first 64 B (K = 32) are used
-  static constexpr int kStages = 6;
-  static constexpr int kInStages = 8;           // staged fp32 input boxes
+  static constexpr int kStages = 4;
+  static constexpr int kInStages = 6;           // staged fp32 input boxes
   static constexpr int kInStageBytes = 8192;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896)
   static constexpr int kBBytes = kBlockN * 128;
   static constexpr int kAccBufs = 4;
   static constexpr int kTmemCols = kAccBufs * kBlockN;
-  static constexpr int kBuilderWarps = 4;
-  static constexpr int kEpiGroups = 4;
+  static constexpr int kBuilderWarps = 2;       // 64 threads, two pixel rows each (16 warps per CTA = 4 per scheduler: 128 registers)
+  static constexpr int kEpiGroups = 3;
   static constexpr int kThreads = 64 + 32 * kBuilderWarps + 128 * kEpiGroups;
   static constexpr int kMainBytes = kStages * kABytes + kBBytes + kInStages * kInStageBytes;  // multiple of 1 KiB
   static constexpr int kEpiWarps = 4 * kEpiGroups;
-  static constexpr int kEpiBoxes = 1;           // boxes per epilogue warp (b2g_conv_epi.cuh); a second one measured neutral
-  static constexpr int kEpiBytes = epi_tma_smem_bytes(kEpiWarps, kEpiBoxes);
+  static constexpr int kEpiBoxes = 2;           // boxes per epilogue warp
+  static constexpr int kEpiBoxBytes = 4096;     // [32 pixels][64 channels] bf16
+  static constexpr int kEpiBytes = kEpiWarps * kEpiBoxes * kEpiBoxBytes + 256;  // boxes, then their mbarriers
   static constexpr int kSmemBytes = kMainBytes + kEpiBytes + 512 + 1024;
 };
 
 __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __grid_constant__ C3KernelParams p) {
   using Cfg = C3Cfg;
   constexpr int BLOCK_N = Cfg::kBlockN;
-  constexpr int kChunks = BLOCK_N / 32;
   __shared__ float sbias[512];     // bias table, or 8 copies of the [64] sums of squares (EpiParams::cs_copies)
   __shared__ float s_colsum[512];  // 8 copies of the [64] column sums: one per pair of epilogue warps
   extern __shared__ uint8_t smem_raw[];
@@ -86,14 +94,16 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     }
     for (int a = 0; a < Cfg::kAccBufs; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], 4 * kChunks);
+      mbar_init(&tempty_bar[a], 4);  // the four lane-quarter warps of the group that owns the tile
     }
     mbar_init(bfull_bar, 1);
     for (int s = 0; s < Cfg::kInStages; ++s) {
       mbar_init(&in_full[s], 1);
       mbar_init(&in_empty[s], Cfg::kBuilderWarps);
     }
-    if (p.e.tma) epi_tma_init(epism, Cfg::kEpiWarps, Cfg::kEpiBoxes);
+    if (p.e.tma)
+      for (int w = 0; w < Cfg::kEpiWarps * Cfg::kEpiBoxes; ++w)
+        mbar_init(reinterpret_cast<uint64_t*>(epism + Cfg::kEpiWarps * Cfg::kEpiBoxes * Cfg::kEpiBoxBytes) + w, 1);
     fence_barrier_init();
   }
   epi_load_bias(p.e, sbias, BLOCK_N);
@@ -156,37 +166,53 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
     }
   } else if (warp < 2 + Cfg::kBuilderWarps) {
-    // ------------------------------------------------ patch builders: thread m owns pixel row m of the A tile
-    const int m = threadIdx.x - 64;
-    const int wl = m % pl.bw, hl = (m / pl.bw) % pl.bh, nl = m / (pl.bw * pl.bh);
-    const uint32_t row_off = m * 128, sw = m & 7;
-    // this thread's window inside a staged box [bn][bh + 2][(bw + 8) * 3 floats]: rows hl..hl+2, nine consecutive
-    // floats from pixel wl + 3 (= image pixel x - 1).  Consecutive lanes are 3 words apart: conflict-free LDS.32.
+    // ------------------------------------------------ patch builders: thread t owns pixel rows t and t + 64 of the A tile
+    const int t = threadIdx.x - 64;
     const int pitch = (pl.bw + 8) * 3;
-    const int win_off = ((nl * (pl.bh + 2) + hl) * (pl.bw + 8) + wl + 3) * 3;
+    uint32_t row_off[2], swz[2];
+    int win_off[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int m = t + 64 * r;
+      const int wl = m % pl.bw, hl = (m / pl.bw) % pl.bh, nl = m / (pl.bw * pl.bh);
+      row_off[r] = m * 128;
+      swz[r] = m & 7;
+      // the row's window inside a staged box [bn][bh + 2][(bw + 8) * 3 floats]: rows hl..hl+2, nine consecutive floats
+      // from pixel wl + 3 (= image pixel x - 1).  Consecutive lanes are 3 words apart: conflict-free LDS.32.
+      win_off[r] = ((nl * (pl.bh + 2) + hl) * (pl.bw + 8) + wl + 3) * 3;
+    }
     int stage = 0, istage = 0;
     uint32_t phase = 0, iphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      float v[32];
+      float v[2][28];
       mbar_wait_parked(&in_full[istage], iphase);
-      const float* src = reinterpret_cast<const float*>(insm + istage * Cfg::kInStageBytes) + win_off;
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky)
+      for (int r = 0; r < 2; ++r) {
+        const float* src = reinterpret_cast<const float*>(insm + istage * Cfg::kInStageBytes) + win_off[r];
 #pragma unroll
-        for (int j = 0; j < 9; ++j) v[ky * 9 + j] = src[ky * pitch + j];  // j = kx * 3 + c
-      v[27] = 1.f;
+        for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-      for (int k = 28; k < 32; ++k) v[k] = 0.f;
+          for (int j = 0; j < 9; ++j) v[r][ky * 9 + j] = src[ky * pitch + j];  // j = kx * 3 + c
+        v[r][27] = 1.f;
+      }
       mbar_wait_parked(&empty_bar[stage], phase ^ 1);
-      uint8_t* dst = smem + stage * Cfg::kABytes + row_off;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint4 o;
-        o.x = pack_bf16x2(v[j * 8 + 0], v[j * 8 + 1]);
-        o.y = pack_bf16x2(v[j * 8 + 2], v[j * 8 + 3]);
-        o.z = pack_bf16x2(v[j * 8 + 4], v[j * 8 + 5]);
-        o.w = pack_bf16x2(v[j * 8 + 6], v[j * 8 + 7]);
-        *reinterpret_cast<uint4*>(dst + ((j ^ sw) << 4)) = o;  // 128-byte swizzle: 16-byte chunk j of row m -> j ^ (m & 7)
+      for (int r = 0; r < 2; ++r) {
+        uint8_t* dst = smem + stage * Cfg::kABytes + row_off[r];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 o;
+          o.x = pack_bf16x2(v[r][j * 8 + 0], v[r][j * 8 + 1]);
+          o.y = pack_bf16x2(v[r][j * 8 + 2], v[r][j * 8 + 3]);
+          if (j < 3) {
+            o.z = pack_bf16x2(v[r][j * 8 + 4], v[r][j * 8 + 5]);
+            o.w = pack_bf16x2(v[r][j * 8 + 6], v[r][j * 8 + 7]);
+          } else {
+            o.z = 0u;  // k = 28 .. 31: zero padding of the K = 32 step
+            o.w = 0u;
+          }
+          *reinterpret_cast<uint4*>(dst + ((j ^ swz[r]) << 4)) = o;  // 128-byte swizzle: 16-byte chunk j of row m -> j ^ (m & 7)
+        }
       }
       fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's async-proxy reads
       __syncwarp();
@@ -202,49 +228,135 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     const EpiParams& e = p.e;                 // stays in the constant bank
     const EpiSeed sd = epi_resolve_seed(p.e);  // dropout seed possibly read from device memory
     const int q = warp & 3;
-    const int grp = (warp - 2 - Cfg::kBuilderWarps) >> 2;
+    const int ew = warp - 2 - Cfg::kBuilderWarps;
+    const int grp = ew >> 2;
     const int row = q * 32 + lane;
     const int wl = row % pl.bw, hl = (row / pl.bw) % pl.bh, nl = row / (pl.bw * pl.bh);
     // origin of this warp's 32-pixel box inside a tile (TMA epilogue)
     const int wl0 = (q * 32) % pl.bw, hl0 = ((q * 32) / pl.bw) % pl.bh, nl0 = (q * 32) / (pl.bw * pl.bh);
     constexpr int NB = Cfg::kEpiBoxes;
-    EpiWarpStageN<NB> st = epi_tma_stage<NB>(epism, Cfg::kEpiWarps, warp - 2 - Cfg::kBuilderWarps);
-    const bool use_tma = p.e.tma != 0;
-    // Chunk c of tile number i (counted per CTA) belongs to epilogue group (2 * i + c) % 4, i.e. group g owns chunk g & 1 of
-    // every other tile, starting with tile number g >> 1: one division-free walk with stride 2 * gridDim.x per warp.
-    static_assert(kChunks == 2 && Cfg::kEpiGroups == 4, "chunk-to-group rotation below assumes 2 chunks, 4 groups");
-    const int c = grp & 1;
-    const int stride = 2 * gridDim.x;
-    int it = grp >> 1;
+    uint8_t* const boxes = epism + ew * NB * Cfg::kEpiBoxBytes;
+    uint64_t* const ybar = reinterpret_cast<uint64_t*>(epism + Cfg::kEpiWarps * NB * Cfg::kEpiBoxBytes) + ew * NB;
+    const bool use_tma = e.tma != 0;
+    const bool bwd = e.dact != B2G_ACT_NONE;
+    const int lean = e.lean;
+    const int cs_off = (warp % e.cs_copies) * BLOCK_N;
+    // this thread's 128-byte row of a box: 16-byte group j lives at j ^ (lane & 7) (128-byte swizzle); the two 32-channel
+    // halves are groups 0..3 and 4..7 = two 64-byte half rows with the 64-byte-style swizzle (lane & 3) inside
+    const uint32_t s7 = lane & 7, sw = s7 & 3;
+    const uint32_t half0 = (s7 & 4) << 4, half1 = half0 ^ 64;
+    // saved-output load of the warp's visit number k into box k % NB (the store that last used that box must have read it)
+    uint32_t k_begin = 0, k_done = 0;
+    auto begin = [&](int bx, int by, int bn) {
+      const uint32_t b = k_begin % NB;
+      ++k_begin;
+      if (elect_one_sync()) {
+        tma_store_wait_read_n<0>();
+        mbar_expect_tx(&ybar[b], Cfg::kEpiBoxBytes);
+        tma_load_4d(boxes + b * Cfg::kEpiBoxBytes, &p.ymap64, &ybar[b], 0, bx, by, bn);
+      }
+      __syncwarp();
+    };
+    // group g owns every third tile of the CTA, starting with tile number g: a division-free walk per warp
+    const int stride = Cfg::kEpiGroups * gridDim.x;
+    int it = grp;
     int tile = blockIdx.x + it * gridDim.x;
     TileWalk tc = tile_walk_begin(pl, tile, stride);
-    for (; tile < total_tiles; tile += stride, it += 2, tile_walk_next(pl, tc)) {
+    for (; tile < total_tiles; tile += stride, it += Cfg::kEpiGroups, tile_walk_next(pl, tc)) {
       const int as = it % Cfg::kAccBufs;
-      const int gw = tc.tw * pl.bw + wl, gh = tc.th * pl.bh + hl, gn = tc.tn * pl.bn + nl;
-      const bool valid = (gh < pl.Hg) && (gn < pl.N);
-      const size_t pix = (static_cast<size_t>(gn) * pl.Hout + gh) * pl.Wout + gw;
       const int bx = tc.tw * pl.bw + wl0, by = tc.th * pl.bh + hl0, bn = tc.tn * pl.bn + nl0;
-      // the saved-output load of this item (backward epilogue) was started right after the previous item (second box);
-      // the very first one starts here, before the accumulator wait
-      if (use_tma && st.k_begin == st.k_chunk) epi_tma_begin(e, &p.em.ymap[0], st, c * 32, bx, by, bn);
+      const int gw = tc.tw * pl.bw + wl, gh = tc.th * pl.bh + hl, gn = tc.tn * pl.bn + nl;
+      const size_t pix = (static_cast<size_t>(gn) * pl.Hout + gh) * pl.Wout + gw;
+      const bool dbg = (e.dbg & 1) != 0;
+      if (use_tma && bwd && !dbg && k_begin == k_done) begin(bx, by, bn);  // the very first visit; later ones are begun one ahead
       mbar_wait_parked(&tfull_bar[as], (it / Cfg::kAccBufs) & 1);
       tc_fence_after();
-      uint32_t r[32];
+      uint32_t r0[32], r1[32];
       __syncwarp();
-      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
-      if (NB >= 2 && use_tma && tile + stride < total_tiles) {
-        // (two boxes only) the warp's next item (two tiles on) is begun into the other box now: the store that last used that box is two
-        // items old, and the load has until the next accumulator to arrive
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N;
+      tmem_ld_32x32(taddr, r0);
+      tmem_ld_32x32(taddr + 32, r1);
+      if (use_tma && bwd && !dbg && tile + stride < total_tiles) {
+        // the warp's next visit is begun into the other box now: its load has until the next accumulator to arrive
         TileWalk nx = tc;
         tile_walk_next(pl, nx);
-        epi_tma_begin(e, &p.em.ymap[0], st, c * 32, nx.tw * pl.bw + wl0, nx.th * pl.bh + hl0, nx.tn * pl.bn + nl0);
+        begin(nx.tw * pl.bw + wl0, nx.th * pl.bh + hl0, nx.tn * pl.bn + nl0);
       }
       tmem_ld_wait();
-      if (use_tma) epi_tma_chunk(e, &p.em.omap[0], st, sbias, r, pix, c * 32, lane, bx, by, bn, s_colsum, sd);
-      else conv_epilogue_chunk(e, sbias, r, pix, c * 32, valid, s_colsum, sd);
-      tc_fence_before();
+      tc_fence_before();  // both halves are in registers: the accumulator goes back to the MMA warp before the math
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      if (dbg) continue;
+      if (!use_tma) {
+        const bool valid = (gh < pl.Hg) && (gn < pl.N);
+        conv_epilogue_chunk(e, sbias, r0, pix, 0, valid, s_colsum, sd);
+        conv_epilogue_chunk(e, sbias, r1, pix, 32, valid, s_colsum, sd);
+        continue;
+      }
+      const uint32_t k = k_done++;
+      const uint32_t b = k % NB;
+      uint8_t* box = boxes + b * Cfg::kEpiBoxBytes;
+      uint8_t* rowp = box + lane * 128;
+      if (bwd) {
+        mbar_wait(&ybar[b], (k / NB) & 1);
+      } else {
+        if (elect_one_sync()) tma_store_wait_read_n<NB - 1>();  // the store of visit k - NB has read this box
+        __syncwarp();
+      }
+      const uint32_t grp32 = static_cast<uint32_t>((pix * BLOCK_N) >> 5);
+      if (lean == 1) {
+        epi_lean_fwd(e, sbias, r0, grp32, 0, rowp + half0, sw, sd);
+        epi_lean_fwd(e, sbias, r1, grp32 + 1, 32, rowp + half1, sw, sd);
+      } else if (lean == 2) {
+        epi_lean_bwd<2>(e, r0, rowp + half0, sw);
+        epi_lean_bwd<2>(e, r1, rowp + half1, sw);
+      } else if (lean == 3) {
+        epi_lean_bwd<3>(e, r0, rowp + half0, sw);
+        epi_lean_bwd<3>(e, r1, rowp + half1, sw);
+      } else if (lean == 4) {
+        epi_lean_bwd<4>(e, r0, rowp + half0, sw);
+        epi_lean_bwd<4>(e, r1, rowp + half1, sw);
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          uint8_t* hp = rowp + (c ? half1 : half0);
+          uint32_t rr[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) rr[j] = c ? r1[j] : r0[j];
+          conv_epilogue_math(
+              e, sbias, rr, pix, c * 32, true,
+              [&](int g) { return *reinterpret_cast<const uint4*>(hp + ((g ^ sw) << 4)); },
+              [&](int g, const uint4& o) { *reinterpret_cast<uint4*>(hp + ((g ^ sw) << 4)) = o; }, nullptr, false, nullptr,
+              sd);
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (elect_one_sync()) tma_store_4d(&p.omap64, box, 0, bx, by, bn);
+      __syncwarp();
+      if (e.colsum) {
+        // Column sums straight from the box (the TMA store only READS it).  Lane = channel pair: word `lane` of every
+        // pixel row, conflict free (a row's 32 words are a permutation of the banks); rows of pixels outside the tensor
+        // hold exact zeros.  One mixed-precision add per element, no shuffles: each lane owns its two channels.
+        const uint32_t gq = lane >> 2, wo = (lane & 3) * 4;
+        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+        if (e.colsumsq) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const uint32_t w = *reinterpret_cast<const uint32_t*>(box + j * 128 + ((gq ^ (j & 7)) << 4) + wo);
+            bf2_acc(w, s0, s1);
+            bf2_acc_sq(w, q0, q1);
+          }
+          atomicAdd(&sbias[cs_off + 2 * lane], q0);
+          atomicAdd(&sbias[cs_off + 2 * lane + 1], q1);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            bf2_acc(*reinterpret_cast<const uint32_t*>(box + j * 128 + ((gq ^ (j & 7)) << 4) + wo), s0, s1);
+        }
+        atomicAdd(&s_colsum[cs_off + 2 * lane], s0);
+        atomicAdd(&s_colsum[cs_off + 2 * lane + 1], s1);
+      }
     }
     if (use_tma) epi_tma_end();
   }
@@ -279,6 +391,18 @@ int launch_conv_c3(const b2g_conv_args* a, void* stream_) {
   {
     int rc = fill_epi_tma(a, kp.plan, true, &kp.e, &kp.em);
     if (rc) return rc;
+    if (kp.e.tma) {  // the same 32-pixel boxes, all 64 channels of a pixel per row
+      const ConvPlan& pl = kp.plan;
+      const uint64_t dims[4] = {64u, (uint64_t)pl.Wout, (uint64_t)pl.Hout, (uint64_t)pl.N};
+      const uint64_t str[3] = {64u * 2u, (uint64_t)pl.Wout * 64u * 2u, (uint64_t)pl.Hout * pl.Wout * 64u * 2u};
+      const uint32_t box[4] = {64u, (uint32_t)kp.e.qw, (uint32_t)kp.e.qh, (uint32_t)kp.e.qn};
+      rc = make_tmap(&kp.omap64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a->out, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc) return rc;
+      if (a->dact != B2G_ACT_NONE) {
+        rc = make_tmap(&kp.ymap64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a->yprev, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+      }
+    }
   }
   {
     const ConvPlan& pl = kp.plan;
