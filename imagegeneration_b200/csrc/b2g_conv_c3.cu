@@ -185,7 +185,9 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
     uint32_t phase = 0, iphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       float v[2][28];
-      mbar_wait_parked(&in_full[istage], iphase);
+      // the builders are on the critical path of every tile: plain try_wait polling, no back-off sleep (a parked wait
+      // woke them up to 256 ns late, half of the per-tile budget)
+      mbar_wait(&in_full[istage], iphase);
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
         const float* src = reinterpret_cast<const float*>(insm + istage * Cfg::kInStageBytes) + win_off[r];
@@ -195,7 +197,7 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
           for (int j = 0; j < 9; ++j) v[r][ky * 9 + j] = src[ky * pitch + j];  // j = kx * 3 + c
         v[r][27] = 1.f;
       }
-      mbar_wait_parked(&empty_bar[stage], phase ^ 1);
+      mbar_wait(&empty_bar[stage], phase ^ 1);
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
         uint8_t* dst = smem + stage * Cfg::kABytes + row_off[r];
