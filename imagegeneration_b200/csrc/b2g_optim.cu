@@ -748,6 +748,70 @@ static int adam_any(float* w, const float* g, float* m, float* v, long n, float 
   return B2G_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Data-parallel Adam over NVSwitch multicast memory (NVLS): gradient all-reduce + update + weight broadcast in ONE pass.
+// Rank r owns elements [begin, end) of the arena.  For those it reads the SUM of every replica's gradient with
+// multimem.ld_reduce (the switch adds the N copies on the way), applies Adam with its LOCAL m / v (optimizer state is
+// sharded: each rank keeps only its slice current) and writes the new weights to EVERY replica with multimem.st.
+// Per GPU that is |arena| bytes out + |arena| bytes in over NVLink instead of a ring / tree all-reduce followed by N
+// identical full-arena Adam passes; replicas stay bit-identical because each element is computed once.
+// The caller brackets the launch with cross-rank barriers (all gradients written before / all weights written after).
+// No counterpart in the reference (single-GPU TensorFlow); replaces NCCL all-reduce + b2g_adam on the data-parallel path.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 mc_ld_reduce_add(const float4* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void mc_st(float4* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+__global__ void __launch_bounds__(256) adam_nvls_kernel(float4* __restrict__ w_mc, const float4* __restrict__ g_mc,
+                                                        const float4* __restrict__ w_loc, float4* __restrict__ m,
+                                                        float4* __restrict__ v, long i0, long i1, float lr_t_val,
+                                                        const float* __restrict__ lr_t_dev, float b1, float b2, float eps,
+                                                        float gscale) {
+  const float lr_t = lr_t_dev ? *lr_t_dev : lr_t_val;
+  const float c1 = 1.f - b1, c2 = 1.f - b2;
+  for (long i = i0 + blockIdx.x * (long)blockDim.x + threadIdx.x; i < i1; i += (long)gridDim.x * blockDim.x) {
+    float4 gw = mc_ld_reduce_add(g_mc + i), mw = m[i], vw = v[i], ww = w_loc[i];
+    float* gp = &gw.x; float* mp = &mw.x; float* vp = &vw.x; float* wp = &ww.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gg = gp[k] * gscale;
+      mp[k] += (gg - mp[k]) * c1;
+      vp[k] += (gg * gg - vp[k]) * c2;
+      wp[k] -= lr_t * mp[k] / (sqrtf(vp[k]) + eps);
+    }
+    m[i] = mw; v[i] = vw;
+    mc_st(w_mc + i, ww);
+  }
+}
+
+extern "C" int b2g_adam_nvls(void* w_mc, const void* g_mc, const float* w_local, float* m, float* v, long begin, long end,
+                             float lr_t, const float* lr_t_dev, float beta1, float beta2, float eps, float gscale,
+                             b2g_stream_t stream_) {
+  if (!w_mc || !g_mc || !w_local || !m || !v) return fail(B2G_E_INVALID_ARG, "b2g_adam_nvls: null pointer");
+  if (begin < 0 || end < begin || begin % 4 || end % 4)
+    return fail(B2G_E_UNSUPPORTED_SHAPE, "b2g_adam_nvls: slice [%ld, %ld) must be non-negative multiples of 4", begin, end);
+  if (end == begin) return B2G_OK;
+  const long n4 = (end - begin) / 4;
+  long blocks = (n4 + 255) / 256;
+  const long cap = (long)num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  adam_nvls_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      reinterpret_cast<float4*>(w_mc), reinterpret_cast<const float4*>(g_mc), reinterpret_cast<const float4*>(w_local),
+      reinterpret_cast<float4*>(m), reinterpret_cast<float4*>(v), begin / 4, end / 4, lr_t, lr_t_dev, beta1, beta2, eps,
+      gscale);
+  B2G_LAUNCH_CHECK();
+  return B2G_OK;
+}
+
 extern "C" int b2g_adam(float* w, const float* g, float* m, float* v, long n, float lr_t, float beta1, float beta2,
                         float eps, float gscale, b2g_stream_t stream) {
   return adam_any(w, g, m, v, n, lr_t, nullptr, beta1, beta2, eps, gscale, stream);

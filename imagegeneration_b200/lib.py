@@ -135,6 +135,7 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_adam": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _P],
     # w, g, m, v, n, lr_t_dev, b1, b2, eps, gscale, stream
     "b2g_adam_dev": [_P, _P, _P, _P, _L, _P, _F, _F, _F, _F, _P],
+    "b2g_adam_nvls": [_P, _P, _P, _P, _P, _L, _L, _F, _P, _F, _F, _F, _F, _P],
     # step_ctr, seed_base, seeds21, lr3, lr_g, lr_d, b1, b2, stream
     "b2g_step_prologue": [_P, C.c_ulonglong, _P, _P, _F, _F, _F, _F, _P],
     # x, out, P, C, stream

@@ -130,6 +130,19 @@ class Adam:
         check(_lib.load().b2g_adam(_p(arena.w), _p(arena.g), _p(arena.m), _p(arena.v), arena.numel, self._lr_t(),
                                    self.beta_1, self.beta_2, self.epsilon, gscale, _stream()), "b2g_adam")
 
+    def apply_arena_nvls(self, arena: ParamArena, nv: dict, gscale: float, lr_t_dev: torch.Tensor | None = None) -> None:
+        """Data-parallel apply_gradients over NVSwitch multicast memory (b2g_adam_nvls): this rank reduces, updates and
+        broadcasts its slice of the arena; the barriers make all gradients final before and all weights visible after."""
+        lr_t = 0.0
+        if lr_t_dev is None:
+            self.iterations += 1
+            lr_t = self._lr_t()
+        nv["hg"].barrier(channel=0)
+        check(_lib.load().b2g_adam_nvls(C.c_void_p(nv["w_mc"]), C.c_void_p(nv["g_mc"]), _p(nv["w_full"]), _p(nv["m_full"]),
+                                        _p(nv["v_full"]), nv["begin"], nv["end"], lr_t, _p(lr_t_dev), self.beta_1,
+                                        self.beta_2, self.epsilon, gscale, _stream()), "b2g_adam_nvls")
+        nv["hw"].barrier(channel=1)
+
     def _lr_t(self) -> float:
         t = self.iterations
         return self.learning_rate * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
@@ -650,6 +663,27 @@ class SNDCGANEngine:
             dist.broadcast(self.disc_model.arena.w, src=0, group=process_group)
             self.gen_model._packed_dirty = True
             self.disc_model._packed_dirty = True
+        # The generator's 164 MB gradient all-reduce hides behind both discriminator steps, but its NCCL kernel holds SMs
+        # meanwhile, and a persistent grid of one CTA per SM then runs in TWO waves: the CTAs that found their SM taken
+        # start when the others finish, with a full static share of the tiles (per-rank timeline, profiles/r2_dp_timeline.md:
+        # every kernel that overlaps an NCCL kernel takes 1.4-1.9x its time, +0.32 ms per step at 2 GPUs).  So the hidden
+        # all-reduce gets its OWN communicator capped at B2G_DP_G_CTAS CTAs (slow, but it has ~5 ms to finish), and the
+        # kernels launched while it may be in flight leave exactly that many SMs free (b2g_set_sm_limit).
+        self.pg_g = self.pg
+        self._g_ctas = 0
+        if self.world > 1:
+            import torch.distributed as dist
+            n = int(os.environ.get("B2G_DP_G_CTAS", "4"))
+            if n > 0 and dist.get_backend(process_group) == "nccl":
+                opts = dist.ProcessGroupNCCL.Options()
+                opts.config.max_ctas = n
+                opts.config.min_ctas = n
+                self.pg_g = dist.new_group(ranks=list(range(self.world)), backend="nccl", pg_options=opts)
+                self._g_ctas = n
+                dist.all_reduce(torch.zeros(1, device=self.device), group=self.pg_g)   # communicator set up before any capture
+        self._nvls = None
+        if self.world > 1:
+            self._setup_nvls()
         self.gpu_launches = 0
         # Single-GPU steps with engine-chosen dropout seeds are replayed as ONE CUDA graph after two eager steps
         # (the per-step scalars — dropout seeds, Adam's bias-corrected rates — then come from device memory, written
@@ -660,6 +694,58 @@ class SNDCGANEngine:
         self._graph = None
         self._graph_failed = None
         self._eager_steps = 0
+
+    def _setup_nvls(self) -> None:
+        """Data parallel on an NVSwitch box: the discriminator's two EXPOSED gradient all-reduces + Adam passes of a step
+        become b2g_adam_nvls launches (reduce in the switch, sharded update, multicast weight store).  Its weight and
+        gradient arenas move into symmetric memory bound to a multicast object (torch.distributed._symmetric_memory does
+        the cuMem / cuMulticast plumbing); m and v stay local, each rank keeping its own slice current
+        (gather_optimizer_state() before a checkpoint).  Falls back to NCCL all-reduce + b2g_adam when multicast memory is
+        unavailable, for a spectrally-normalised discriminator (its fused b2g_adam_sn pass needs whole matrices), on the
+        fp32/tf32 parity path, or with B2G_DP_NVLS=0."""
+        import torch.distributed as dist
+        D = self.disc_model
+        if (os.environ.get("B2G_DP_NVLS", "1") == "0" or D.spectral_norm or self.dtype != "bf16"
+                or dist.get_backend(self.pg) != "nccl"):
+            return
+        try:
+            import torch.distributed._symmetric_memory as symm
+            a = D.arena
+            per = (a.numel + 4 * self.world - 1) // (4 * self.world) * 4
+            padded = per * self.world
+            w_s = symm.empty(padded, dtype=torch.float32, device=self.device)
+            g_s = symm.empty(padded, dtype=torch.float32, device=self.device)
+            hw = symm.rendezvous(w_s, self.pg)
+            hg = symm.rendezvous(g_s, self.pg)
+            if not hw.multicast_ptr or not hg.multicast_ptr:
+                return
+        except Exception as e:      # no multicast support in this driver / container: NCCL path
+            if os.environ.get("B2G_DP_NVLS") == "1":
+                raise
+            self._nvls_error = repr(e)
+            return
+        w_s.zero_()
+        g_s.zero_()
+        w_s[:a.numel].copy_(a.w)
+        m_full = torch.zeros(padded, dtype=torch.float32, device=self.device)
+        v_full = torch.zeros(padded, dtype=torch.float32, device=self.device)
+        a.w, a.g, a.m, a.v = w_s[:a.numel], g_s[:a.numel], m_full[:a.numel], v_full[:a.numel]
+        D._pack_plan = None
+        D._packed_dirty = True
+        self._nvls = {"hw": hw, "hg": hg, "w_mc": hw.multicast_ptr, "g_mc": hg.multicast_ptr, "w_full": w_s, "g_full": g_s,
+                      "m_full": m_full, "v_full": v_full, "begin": self.rank * per, "end": (self.rank + 1) * per, "per": per}
+        torch.cuda.synchronize()
+        dist.barrier(group=self.pg)
+
+    def gather_optimizer_state(self) -> None:
+        """NVLS data parallel keeps Adam's m / v of the discriminator sharded by rank; this all-gathers the slices so that
+        every rank holds the full state (call before saving a checkpoint).  No-op otherwise."""
+        if self._nvls is None:
+            return
+        import torch.distributed as dist
+        nv = self._nvls
+        for full in (nv["m_full"], nv["v_full"]):
+            dist.all_gather_into_tensor(full, full[nv["begin"]:nv["end"]].clone(), group=self.pg)
 
     def close(self) -> None:
         """Drops the captured CUDA graph (it references the NCCL kernels of a data-parallel step) and waits for the
@@ -676,11 +762,11 @@ class SNDCGANEngine:
     def _dropout_seeds(self, pass_idx: int):
         return step_dropout_seeds(self.seed, self.rank, self.step_count, pass_idx)
 
-    def _allreduce(self, flat, async_op=False):
+    def _allreduce(self, flat, async_op=False, group=None):
         if self.world == 1:
             return None
         from .dp import allreduce_sum_
-        return allreduce_sum_(flat, self.pg, async_op)
+        return allreduce_sum_(flat, group if group is not None else self.pg, async_op)
 
     def _d_backward_allreduce(self, D):
         """Discriminator backward with its gradient all-reduce (data parallel): the tail of the arena (conv6, conv7,
@@ -691,8 +777,10 @@ class SNDCGANEngine:
             return
         split = D.arena.offsets[D.EARLY_GRAD_FIRST_VAR]
         pending = []
+        # off by default since round 2: the timeline showed the overlapped weight-gradient kernels losing more (two waves:
+        # +71 / +44 us) than the 19 MB reduction saves when it is hidden
         early = ((not D.spectral_norm) and not torch.cuda.is_current_stream_capturing()
-                 and os.environ.get("B2G_DP_EARLY_ALLREDUCE", "1") != "0")
+                 and os.environ.get("B2G_DP_EARLY_ALLREDUCE", "0") != "0")
         D.backward(need_wgrad=True, need_input_grad=False,
                    on_tail_grads_ready=(lambda: pending.append(self._allreduce(D.arena.g[split:], async_op=True)))
                    if early else None)
@@ -703,6 +791,16 @@ class SNDCGANEngine:
                     w.wait()
         else:
             self._allreduce(D.arena.g)
+
+    def _d_update(self, D, gs, lr_dev):
+        """tape.gradient + apply_gradients of the discriminator (SNDCGAN.py:256-257 / :266-267), data parallel included."""
+        if self._nvls is not None:
+            D.backward(need_wgrad=True, need_input_grad=False)
+            self.d_optimizer.apply_arena_nvls(D.arena, self._nvls, gs, lr_dev)
+            D._packed_dirty = True
+            return
+        self._d_backward_allreduce(D)
+        self.d_optimizer.apply_model(D, gs, lr_dev)
 
     def train_step(self, input_real, input_z, dropout_seeds=None):
         """One G update + two D updates, in the reference's order (SNDCGAN.py:241-269).
@@ -798,7 +896,7 @@ class SNDCGANEngine:
         g_loss, _ = D.head_loss(g_kind, 1.0, inv_b)                                 # :245-246
         d_gout = D.backward(need_wgrad=False, need_input_grad=True, g_out=g_output)
         G.backward(d_gout)                                                          # :248
-        g_work = self._allreduce(G.arena.g, async_op=True)
+        g_work = self._allreduce(G.arena.g, async_op=True, group=self.pg_g)
         # G's Adam (:249) is issued at the end of the step: nothing below reads the generator's weights, so the
         # result is identical and its gradient all-reduce overlaps both discriminator steps.
 
@@ -806,8 +904,9 @@ class SNDCGANEngine:
         # While the generator's 164 MB all-reduce is in flight its NCCL kernel holds some SMs; a persistent grid of
         # one CTA per SM would wait for them (two waves).  B2G_DP_SM_RESERVE=n leaves n SMs free for the first
         # discriminator forward (and backward with B2G_DP_SM_RESERVE_BWD=1) after the all-reduce is launched.
-        reserve = int(os.environ.get("B2G_DP_SM_RESERVE", "0")) if g_work is not None else 0
-        reserve_bwd = reserve and os.environ.get("B2G_DP_SM_RESERVE_BWD", "0") == "1"
+        # (B2G_DP_SM_RESERVE overrides the count; B2G_DP_G_WINDOW = 1: reserve during step (2) only, 2: steps (2) and (3).)
+        reserve = int(os.environ.get("B2G_DP_SM_RESERVE", str(self._g_ctas))) if g_work is not None else 0
+        window = int(os.environ.get("B2G_DP_G_WINDOW", "2"))
         lib = _lib.load()
         if reserve:
             check(lib.b2g_set_sm_limit(max(8, lib.b2g_num_sms() - reserve)), "b2g_set_sm_limit", 0)
@@ -815,20 +914,18 @@ class SNDCGANEngine:
             D.forward(input_real, training=True, dropout_seeds=sb)                  # :252
             d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b_real)       # :253-254
             d_logits_real = d_logits_real.clone()
-            if reserve and not reserve_bwd:
+            self._d_update(D, gs, lr_d1)                                            # :256-257
+            if reserve and window < 2:
                 check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
-            self._d_backward_allreduce(D)                                           # :256
+
+            # (3) discriminator step on the stale fake batch (:259-267)
+            D.forward(g_output, training=True, dropout_seeds=sc)                    # :260
+            d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)            # :261-262
+            d_logits_fake = d_logits_fake.clone()   # D.logits is a reused buffer: the caller gets its own tensor
+            self._d_update(D, gs, lr_d2)                                            # :266-267
         finally:
             if reserve:
                 check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
-        self.d_optimizer.apply_model(D, gs, lr_d1)                                  # :257
-
-        # (3) discriminator step on the stale fake batch (:259-267)
-        D.forward(g_output, training=True, dropout_seeds=sc)                        # :260
-        d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)                # :261-262
-        self._d_backward_allreduce(D)                                               # :266
-        d_logits_fake = d_logits_fake.clone()       # D.logits is a reused buffer: the caller gets its own tensor
-        self.d_optimizer.apply_model(D, gs, lr_d2)                                  # :267
 
         if g_work is not None:
             g_work.wait()

@@ -211,6 +211,7 @@ class SNDCGAN(SNDCGANEngine):
 
     # -- checkpoint contents (written / read through self.ckpt_manager)
     def _save_state(self, path, epoch):
+        self.gather_optimizer_state()       # NVLS data parallel shards the discriminator's Adam state (no-op otherwise)
         G, D = self.gen_model.arena, self.disc_model.arena
         state = {"epoch": epoch, "g_w": G.w.cpu(), "g_m": G.m.cpu(), "g_v": G.v.cpu(), "d_w": D.w.cpu(),
                  "d_m": D.m.cpu(), "d_v": D.v.cpu(), "g_iterations": self.g_optimizer.iterations,

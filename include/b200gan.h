@@ -279,6 +279,18 @@ int b2g_adam(float* w, const float* g, float* m, float* v, long n, float lr_t, f
 /* Adam with lr_t read from device memory (one float) — the graph-replay form of b2g_adam. */
 int b2g_adam_dev(float* w, const float* g, float* m, float* v, long n, const float* lr_t_dev, float beta1,
                  float beta2, float eps, float gscale, b2g_stream_t stream);
+/* Data-parallel Adam over NVSwitch multicast (NVLS) memory: the gradient all-reduce, the update and the weight broadcast
+ * of optimizer.apply_gradients (sndcgan/SNDCGAN.py:257,:267) under data parallelism (north_star item 4) in ONE pass.
+ * w_mc / g_mc: MULTICAST addresses of the weight / gradient arenas (every rank's replica bound to one multicast object,
+ * e.g. torch.distributed._symmetric_memory); w_local, m, v: this rank's own buffers.  The calling rank owns elements
+ * [begin, end) (multiples of 4): it reads the sum of all replicas' gradients (multimem.ld_reduce), applies Keras Adam
+ * with gscale (1/world) and its local m / v — optimizer state is sharded by slice — and stores the new weights into
+ * every replica (multimem.st).  lr_t_dev non-NULL: the rate is read from device memory (graph replay).  The caller
+ * must put a cross-rank barrier before the call (all gradients final) and after it (all weights written).
+ * No counterpart in the reference (single-GPU TensorFlow). */
+int b2g_adam_nvls(void* w_mc, const void* g_mc, const float* w_local, float* m, float* v, long begin, long end,
+                  float lr_t, const float* lr_t_dev, float beta1, float beta2, float eps, float gscale,
+                  b2g_stream_t stream);
 /* First node of a captured training step (sndcgan/SNDCGAN.py:241-269 replayed as one CUDA graph): reads the step
  * index s = *step_ctr, writes the 21 dropout seeds of the step (3 discriminator passes x 7 layers:
  * splitmix64(seed_base ^ ((3 s + pass) * 8 + layer))) and the three bias-corrected Adam rates
