@@ -264,6 +264,216 @@ static int launch_wgrad(const WgradKernelParams& kp, int total_items, cudaStream
 
 
 // ------------------------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2) for the layers with >= 256 channels on both sides.  Round 2's ncu of wgrad_kernel<256>:
+// tensor pipe 67 %, 1.8 GB per launch from L2 = 15 TB/s — the one-CTA tile (M = 128, N = 256) needs 48 KB of operands
+// per 128 x 256 x 64 MMA group, 96 B/clk/SM, more than the L2 -> SM path sustains.  A pair of CTAs shares one
+// M = 256 x N = 256 tile: each loads its own 128 M-side channels and HALF of the N-side channels (32 KB per k-step
+// instead of 48), the leader issues one tcgen05.mma.cta_group::2 that reads both halves, each CTA's TMEM holds its own
+// 128 accumulator rows and its four epilogue warps add them into dW (same vector reds as the one-CTA kernel).
+// Same protocol as conv_pair_kernel (b2g_conv_pair.cu): the leader's full barrier counts the TMA bytes of both CTAs,
+// tcgen05.commit is multicast to both, accumulator release = remote arrive on the leader's barrier.
+// ------------------------------------------------------------------------------------------------------------
+struct WgradPairCfg {
+  static constexpr int kBlockN = 256;
+  static constexpr int kBoxBytes = 64 * 128;            // one [64 pixels][64 channels] box
+  static constexpr int kMBytes = 2 * kBoxBytes;         // this CTA's 128 M-side channels
+  static constexpr int kNBytes = 2 * kBoxBytes;         // this CTA's half (128) of the 256 N-side channels
+  static constexpr int kStageBytes = kMBytes + kNBytes;  // 32 KB
+  static constexpr int kStages = 6;
+  static constexpr int kTmemCols = 2 * kBlockN;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(kWgradThreads, 1) wgrad_pair_kernel(const __grid_constant__ WgradKernelParams p) {
+  using Cfg = WgradPairCfg;
+  constexpr int BLOCK_N = Cfg::kBlockN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();  // 0 = MMA leader
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const ConvPlan& pl = p.plan;
+  const int total_items = pl.taps * p.m_tiles * p.n_tiles * p.splits;  // m_tiles counts 256-channel PAIRS of M tiles here
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);   // leader's producer: one arrive.expect_tx covering the bytes of both CTAs
+      mbar_init(&empty_bar[s], 1);  // multicast tcgen05.commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);   // multicast tcgen05.commit
+      mbar_init(&tempty_bar[a], 8);  // four epilogue warps of BOTH CTAs (the leader's copy is used)
+    }
+    fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < pl.n_amaps; ++i) tma_prefetch_desc(&p.smap[i]);
+    tma_prefetch_desc(&p.umap);
+  }
+  if (warp == 1) tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised and its TMEM is allocated before any remote signal
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------ TMA producer (both CTAs)
+    const uint32_t leader = elect_one_sync();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int item = cluster_id; item < total_items; item += n_clusters) {
+      const WgradItem wi = decode_item(p, item);
+      const CUtensorMap* sm = &p.smap[pl.tap_map[wi.tap]];
+      const int dy = pl.tap_dy[wi.tap], dx = pl.tap_dx[wi.tap];
+      const int m_c0 = (wi.m_tile * 2 + rank) * 128, n_c0 = wi.n_tile * BLOCK_N + rank * (BLOCK_N / 2);
+      for (int pt = wi.p_begin; pt < wi.p_end; ++pt) {
+        const int tw = pt % pl.tiles_w;
+        const int r2 = pt / pl.tiles_w;
+        const int th = r2 % pl.tiles_h;
+        const int tn = r2 / pl.tiles_h;
+        const int w0 = tw * pl.bw, h0 = th * pl.bh, n0 = tn * pl.bn;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (leader) {
+          uint8_t* m_dst = smem + stage * Cfg::kStageBytes;
+          uint8_t* n_dst = m_dst + Cfg::kMBytes;
+          const uint32_t bar = mapa_shared(smem_u32(&full_bar[stage]), 0);  // the MMA leader's full barrier
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+          const CUtensorMap* mm = p.m_is_shifted ? sm : &p.umap;
+          const CUtensorMap* nm = p.m_is_shifted ? &p.umap : sm;
+          const int mdx = p.m_is_shifted ? dx : 0, mdy = p.m_is_shifted ? dy : 0;
+          const int ndx = p.m_is_shifted ? 0 : dx, ndy = p.m_is_shifted ? 0 : dy;
+#pragma unroll
+          for (int g = 0; g < 2; ++g)
+            tma_load_4d_pair(m_dst + g * Cfg::kBoxBytes, mm, bar, m_c0 + g * 64, w0 + mdx, h0 + mdy, n0);
+#pragma unroll
+          for (int g = 0; g < 2; ++g)
+            tma_load_4d_pair(n_dst + g * Cfg::kBoxBytes, nm, bar, n_c0 + g * 64, w0 + ndx, h0 + ndy, n0);
+        }
+        __syncwarp();
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------ MMA issuer (leader CTA only)
+    if (rank == 0) {
+      const uint32_t leader = elect_one_sync();
+      constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, /*A MN-major*/ 1, /*B MN-major*/ 1, 256, BLOCK_N);
+      const uint32_t smem_base = smem_u32(smem);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int item = cluster_id; item < total_items; item += n_clusters, ++it) {
+        const WgradItem wi = decode_item(p, item);
+        const int as = it & 1;
+        mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+        const int k_steps = wi.p_end - wi.p_begin;
+        for (int ks = 0; ks < k_steps; ++ks) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t m_addr = smem_base + stage * Cfg::kStageBytes;
+          const uint64_t mdesc = umma_smem_desc(m_addr, Cfg::kBoxBytes, 1024);
+          const uint64_t ndesc = umma_smem_desc(m_addr + Cfg::kMBytes, Cfg::kBoxBytes, 1024);
+          if (leader) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)  // 16 pixels per MMA = two 8-line swizzle groups = 2048 bytes (>> 4 = 128)
+              umma_f16_pair(d_tmem, mdesc + 128 * k, ndesc + 128 * k, idesc, (ks | k) != 0);
+            umma_commit_pair(&empty_bar[stage], 3);
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        if (leader) umma_commit_pair(&tfull_bar[as], 3);
+        __syncwarp();
+      }
+    }
+  } else {
+    // ------------------------------------------------ epilogue: this CTA's 128 accumulator rows (both CTAs)
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const uint32_t tempty_leader = mapa_shared(smem_u32(&tempty_bar[0]), 0);
+    int it = 0;
+    for (int item = cluster_id; item < total_items; item += n_clusters, ++it) {
+      const WgradItem wi = decode_item(p, item);
+      const int as = it & 1;
+      const bool nonempty = wi.p_end > wi.p_begin;
+      mbar_wait(&tfull_bar[as], (it >> 1) & 1);
+      tc_fence_after();
+      const int m = (wi.m_tile * 2 + rank) * 128 + row;
+      float* obase = p.out + (size_t)wi.tap * p.Ca * p.Cb;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t r[32];
+        __syncwarp();
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
+        tmem_ld_wait();
+        if (nonempty) {
+          const int n = wi.n_tile * BLOCK_N + c * 32;
+          if (p.m_is_shifted) {  // out[a = m][b = n..n+31]: contiguous per thread
+            float* dst = obase + (size_t)m * p.Cb + n;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(__uint_as_float(r[j])),
+                           "f"(__uint_as_float(r[j + 1])), "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
+                           : "memory");
+          } else {  // out[a = n + j][b = m]: coalesced across the warp's lanes
+#pragma unroll
+            for (int j = 0; j < 32; ++j) atomicAdd(obase + (size_t)(n + j) * p.Cb + m, __uint_as_float(r[j]));
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(tempty_leader + as * 8);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // no CTA frees TMEM / exits while its peer may still signal or read it
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+static int launch_wgrad_pair(const WgradKernelParams& kp, int total_items, cudaStream_t stream) {
+  using Cfg = WgradPairCfg;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(wgrad_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int clusters = num_sms() / 2;
+  if (total_items < clusters) clusters = total_items;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * clusters, 1, 1);
+  cfg.blockDim = dim3(kWgradThreads, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B2G_CUDA_CHECK(cudaLaunchKernelEx(&cfg, wgrad_pair_kernel, kp));
+  return B2G_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------------------------
 // Tap-grouped variant (the default for the 128+-channel layers): M side = 128 channels of the UNSHIFTED operand,
 // N side = up to 256 columns made of `T` taps x `cc` channels of the shifted operand (cc = min(Ca, 256),
 // T = 256 / cc).  One unshifted tile feeds T taps, every MMA is N=256 wide (MMA-bound instead of smem-bound for
@@ -577,10 +787,14 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
   kp.Ca = a->Ca;
   kp.Cb = a->Cb;
   kp.out = a->dw;
+  // CTA-pair kernel: both sides in whole 256-channel tiles, plain bf16 gradient (B2G_WGRAD_PAIR=0 turns it off)
+  static int pair_env = []() { const char* e = getenv("B2G_WGRAD_PAIR"); return e ? atoi(e) : 1; }();
+  const bool use_pair = pair_env && !tf32 && block_n == 256 && kp.Cm % 256 == 0 && kp.ca_valid == a->Ca && !a->dbias;
+  if (use_pair) kp.m_tiles = kp.Cm / 256;  // the pair kernel counts PAIRS of 128-channel M tiles
   // split-K: equal-length work items, just under 4 whole rounds over the SMs (no ragged last round)
   const int base_items = pl.taps * kp.m_tiles * kp.n_tiles;
   static int rounds1 = []() { const char* e = getenv("B2G_WGRAD_ROUNDS1"); int r = e ? atoi(e) : 4; return r > 0 ? r : 4; }();
-  int splits = rounds1 * num_sms() / base_items;
+  int splits = rounds1 * (use_pair ? num_sms() / 2 : num_sms()) / base_items;
   if (splits > kp.ptiles / 8) splits = kp.ptiles / 8;
   if (splits < 1) splits = 1;
   kp.splits = splits;
@@ -614,6 +828,7 @@ extern "C" int b2g_conv_wgrad(const b2g_wgrad_args* a, b2g_stream_t stream_) {
     if (rc) return rc;
   }
   const int total_items = base_items * kp.splits;
+  if (use_pair) return launch_wgrad_pair(kp, total_items, stream);
   if (tf32) return block_n == 128 ? launch_wgrad<128, true>(kp, total_items, stream)
                                   : launch_wgrad<64, true>(kp, total_items, stream);
   switch (block_n) {
