@@ -403,9 +403,20 @@ def identity_loss(real_image, same_image):
 # CycleGAN (cyclegan/CycleGAN.py:211-382, without the reference's data loader / plots / checkpoint files)
 # ----------------------------------------------------------------------------------------------------------
 class CycleGAN:
-    def __init__(self, batch_size, image_size=(128, 128, 3), device="cuda", seed=62):
+    def __init__(self, batch_size, image_size=(128, 128, 3), device="cuda", seed=62, cuda_graph=None):
         _lib.load()
         self.batch_size, self.image_size = batch_size, tuple(image_size)
+        # The step is ~1 900 small launches (gather + GEMM per conv, row norms, autograd glue): launched eagerly the HOST
+        # is the bottleneck (55 ms per step at batch 8 for ~20 ms of kernels).  After two eager steps the whole step —
+        # forward passes, torch.autograd's backward, the four Adam updates (bias-corrected rates read from device memory)
+        # — is captured into ONE CUDA graph and replayed.  cuda_graph=False / B2G_CUDA_GRAPH=0 keeps every step eager.
+        import os
+        if cuda_graph is None:
+            cuda_graph = os.environ.get("B2G_CUDA_GRAPH", "1") != "0"
+        self.cuda_graph = bool(cuda_graph)
+        self._graph = None
+        self._graph_failed = None
+        self._eager_steps = 0
         self.generator_g = define_generator(image_size, device, seed)            # X -> Y   (:235)
         self.generator_f = define_generator(image_size, device, seed + 1)        # Y -> X
         self.discriminator_x = define_discriminator(image_size, device, seed + 2)
@@ -464,15 +475,61 @@ class CycleGAN:
                 "total_cycle_loss": total_cycle_loss.detach(),
                 "disc_x_loss": disc_x_loss.detach(), "disc_y_loss": disc_y_loss.detach()}
 
+    def _step_body(self, real_x, real_y, lr_dev=None):
+        out = self.compute_gradients(real_x, real_y)
+        with torch.no_grad():
+            for i, (m, opt) in enumerate(self._models()):                          # :372-377
+                opt.apply_arena(m.arena, 1.0, None if lr_dev is None else lr_dev[i:i + 1])
+        return {k: v for k, v in out.items() if not k.startswith("disc_")}
+
+    def _capture_graph(self, real_x, real_y):
+        """Captures one whole step (autograd backward included) into a CUDA graph over static input buffers.  The Adam
+        rates are read from a 4-float device tensor refreshed before every replay."""
+        try:
+            self._g_x, self._g_y = real_x.clone(), real_y.clone()
+            self._g_lr = torch.zeros(4, dtype=F32, device=real_x.device)
+            snap = [(m.arena.w.clone(), m.arena.m.clone(), m.arena.v.clone()) for m, _ in self._models()]
+            # capture must not change the training state: the weights / Adam slots it touches are restored afterwards
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):                  # warm-up on a side stream (allocator + autograd state)
+                self._step_body(self._g_x, self._g_y, self._g_lr)
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._g_out = self._step_body(self._g_x, self._g_y, self._g_lr)
+            for (m, _), (w, mm, vv) in zip(self._models(), snap):
+                m.arena.w.copy_(w)
+                m.arena.m.copy_(mm)
+                m.arena.v.copy_(vv)
+            self._graph = graph
+        except Exception as e:          # capture is an optimisation: fall back to eager launches, keep the reason
+            self._graph = None
+            self._graph_failed = repr(e)
+            self.cuda_graph = False
+            torch.cuda.synchronize()
+
     def train_step(self, real_x, real_y):
         """cyclegan/CycleGAN.py:325-382: returns the reference's seven losses (CUDA scalars)."""
         if not real_x.is_cuda or not real_y.is_cuda:
             raise B200GanError("b200gan ops need CUDA tensors: there is no CPU fallback")
-        out = self.compute_gradients(real_x.to(F32), real_y.to(F32))
-        with torch.no_grad():
-            for m, opt in self._models():                                          # :372-377
-                opt.apply_arena(m.arena)
-        return {k: v for k, v in out.items() if not k.startswith("disc_")}
+        real_x, real_y = real_x.to(F32), real_y.to(F32)
+        usable = (self.cuda_graph and self._eager_steps >= 2 and tuple(real_x.shape) == (self.batch_size, *self.image_size)
+                  and real_y.shape == real_x.shape)
+        if usable and self._graph is None:
+            self._capture_graph(real_x, real_y)
+        if usable and self._graph is not None:
+            lrs = []
+            for _, opt in self._models():
+                opt.iterations += 1
+                lrs.append(opt._lr_t())
+            self._g_lr.copy_(torch.tensor(lrs, dtype=F32), non_blocking=False)
+            self._g_x.copy_(real_x)
+            self._g_y.copy_(real_y)
+            self._graph.replay()
+            return {k: v.clone() for k, v in self._g_out.items()}
+        self._eager_steps += 1
+        return self._step_body(real_x, real_y)
 
     def train(self, loader, epochs):
         """The inner loop of :384-402 over any iterable of (batch_x, batch_y) fp32 NHWC CUDA tensors in [-1, 1]."""

@@ -193,3 +193,24 @@ def test_train_step_matches_oracle():
     upd, want = eng.generator_g.arena.w.double().cpu() - w0.double().cpu(), w - w0.double().cpu()
     assert float((upd - want).norm() / want.norm()) < 1e-4
     assert _rel_l2(eng.generator_g.arena.g, g0) < 0.05          # same inputs, same weights: same gradients (fp32 atomics)
+
+
+def test_train_step_graph_replay_tracks_eager_steps():
+    """The whole step (forward passes, torch.autograd backward, four Adam updates) replayed as one CUDA graph after two
+    eager steps: same losses and weights as an all-eager engine on the same batches (fp32 atomics in the weight gradients:
+    statistical bound), Adam's iteration counters advance, capturing does not move the training state."""
+    from imagegeneration_b200.cyclegan import CycleGAN
+    size, B = (96, 96, 3), 2
+    eager, graph = CycleGAN(B, size, seed=5, cuda_graph=False), CycleGAN(B, size, seed=5, cuda_graph=True)
+    for step in range(5):
+        x, y = _rand((B, *size), 100 + step).cuda(), _rand((B, *size), 200 + step).cuda()
+        le, lg = eager.train_step(x, y), graph.train_step(x, y)
+        torch.cuda.synchronize()
+        for k in le:
+            assert abs(float(le[k]) - float(lg[k])) < 2e-2 * max(1.0, abs(float(le[k]))), (step, k, float(le[k]), float(lg[k]))
+    assert graph._graph is not None, graph._graph_failed
+    assert all(opt.iterations == 5 for _, opt in graph._models())
+    for (me, _), (mg, _) in zip(eager._models(), graph._models()):
+        dw = float((me.arena.w - mg.arena.w).abs().max())
+        assert dw <= 5 * 2e-4 * 1.01, dw          # five Adam steps of lr 2e-4 bound any divergence
+        assert _rel_l2(mg.arena.w, me.arena.w) < 5e-3
