@@ -41,7 +41,8 @@ struct RowsCfg {
   static constexpr int kSlabBytes = 17 * 1024;                       // 130 px * 128 B = 16640, padded to 1 KiB
   static constexpr int kSlabTx = kRowsSlabPixels * 128;              // bytes one slab TMA delivers
   static constexpr int kSlabs = SS::kStatic ? SS::kS : (BLOCK_N == 128 ? 7 : 8);
-  static constexpr int kBBytes = BLOCK_N * 128;
+  static constexpr int kBTile = BLOCK_N * 128;                       // one [BLOCK_N][64] weight tile
+  static constexpr int kBBytes = (SS::kMerge ? 2 : 1) * kBTile;      // merged schedules stack two tiles per stage
   static constexpr int kBStages = SS::kStatic ? SS::kSB : (BLOCK_N == 128 ? 6 : 8);
   static constexpr int kBarBytes = 512;
   static constexpr int kMainBytes = kSlabs * kSlabBytes + kBStages * kBBytes;  // multiple of 1 KiB
@@ -117,7 +118,8 @@ __device__ __forceinline__ void rows_static_step(uint32_t leader, uint32_t slab_
   constexpr int S = SS::kS, SB = SS::kSB, R = SS::kR, P = SS::kP;
   constexpr int bst = J % SB;
   constexpr int need = st.slab0 + R - 1, prev = SS::need_before(J), rel0 = SS::released_before(J);
-  constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, BLOCK_N);
+  constexpr uint32_t idesc = umma_idesc(/*bf16*/ 1, 0, 0, 128, st.wide ? 2 * BLOCK_N : BLOCK_N);
+  static_assert(!st.wide || SS::kMerge, "wide step in a schedule without stacked weight stages");
   mbar_wait(&bfull[bst], par_b0 ^ ((J / SB) & 1));
 #pragma unroll
   for (int i = prev + 1; i <= need; ++i) mbar_wait(&sfull[i % S], par_s0 ^ ((i / S) & 1));
@@ -126,6 +128,8 @@ __device__ __forceinline__ void rows_static_step(uint32_t leader, uint32_t slab_
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const int acc = st.acc0 + r * P;
+      static_assert(!st.wide || SS::written_before(J, st.acc0) == SS::written_before(J, st.acc0 + 1),
+                    "a wide step has ONE accumulate flag for both accumulators");
       umma_f16_k64(d_base + acc * BLOCK_N,
                    slab_lo0 + ((st.slab0 + r) % S) * (Cfg::kSlabBytes >> 4) + st.dxi * 8,
                    b_lo0 + bst * (Cfg::kBBytes >> 4), idesc, SS::written_before(J, acc) ? 1u : 0u);
@@ -234,11 +238,14 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
       const int n_steps = sc.n_steps;
       const int brow0 = c.pg * P * p.brows + c.nt * BLOCK_N;
       for (int j = 0; j < n_steps; ++j) {
-        const int bcol = sc.steps[j].bcol, phl = sc.steps[j].phase_l;
+        const int bcol = sc.steps[j].bcol, phl = sc.steps[j].phase_l, wide = SS::kMerge ? sc.steps[j].wide : 0;
         mbar_wait(&bempty[stage], par ^ 1);
         if (leader) {
-          mbar_expect_tx(&bfull[stage], Cfg::kBBytes);
+          mbar_expect_tx(&bfull[stage], wide ? 2 * Cfg::kBTile : Cfg::kBTile);
           tma_load_2d(bsm + stage * Cfg::kBBytes, &p.bmap, &bfull[stage], bcol * 64, brow0 + phl * p.brows);
+          if (wide)  // the next local phase's tile for the same shift, stacked behind the first: rows BLOCK_N .. 2 BLOCK_N - 1
+            tma_load_2d(bsm + stage * Cfg::kBBytes + Cfg::kBTile, &p.bmap, &bfull[stage], sc.steps[j].bcol2 * 64,
+                        brow0 + (phl + 1) * p.brows);
         }
         __syncwarp();
         if (++stage == Cfg::kBStages) { stage = 0; par ^= 1; }
@@ -433,8 +440,9 @@ static int rows_ring(int block_n) { return block_n == 128 ? RowsCfg<128>::kSlabs
 using RowsConv3 = RowsStatic<B2G_CONV_K3S1, 2, 2, 1, 128, 4, 6>;    // D.conv3 fwd / dgrad (128 -> 128 @72x128)
 using RowsConv2 = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 8>;    // D.conv2 fwd (64 -> 128, 144x256 -> 72x128)
 using RowsConv2b = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 4>;   // same role, 4 weight stages: room for 3 epilogue boxes
-using RowsConvT3 = RowsStatic<B2G_CONVT_K4S2, 2, 2, 2, 64, 6, 4>;   // G.convT3 fwd / D.conv2 dgrad (128 -> 64); 4 weight
-                                                                    // stages (8 in round 1): room for a second epilogue box
+using RowsConvT3 = RowsStatic<B2G_CONVT_K4S2, 2, 2, 2, 64, 6, 3, true>;  // G.convT3 fwd / D.conv2 dgrad (128 -> 64): merged
+                                                                         // dx = 0 steps (12 instead of 16 per super-tile),
+                                                                         // 3 stacked weight stages of 16 KB
 using RowsConvT4 = RowsStatic<B2G_CONV_K3S1, 1, 4, 1, 32, 6, 9>;    // G.convT4 fwd / D.conv1 dgrad (64 -> 3)
 
 // Tries the compile-time kernel SS for this role: the host schedule is rebuilt with SS's slab ring and must equal
@@ -444,7 +452,7 @@ static bool try_static(const ConvPlan& pl, int block_n, RowsKernelParams* kp) {
   if (block_n != BLOCK_N || pl.kind != SS::kKind || pl.Cin != SS::kCh * 64) return false;
   RowsGeom g;
   RowsSched sc[2];
-  if (!build_rows_sched(pl, block_n, SS::kS, &g, sc)) return false;
+  if (!build_rows_sched(pl, block_n, SS::kS, &g, sc, SS::kMerge)) return false;
   if (!rows_static_matches<SS>(g, sc)) return false;
   kp->geom = g;
   kp->sched[0] = sc[0];
@@ -562,6 +570,34 @@ extern "C" int b2g_conv_rows_plan_query(int kind, int N, int Hin, int Win, int C
     const RowsStep& st = sc[pg].steps[j];
     int* o = out + 8 + 3 * kRowsMaxSlabs + 6 * j;
     o[0] = st.bcol; o[1] = st.phase_l; o[2] = st.slab0; o[3] = st.dxi; o[4] = st.acc0; o[5] = st.rel;
+  }
+  return B2G_OK;
+}
+
+// The schedule with merged dx = 0 steps (transposed conv, two phases per group; RowsStep::wide): as above, 8 ints per
+// step from out[8 + 72]: {bcol, phase_l, slab0, dxi, acc0, rel, wide, bcol2}; out needs 8 + 72 + 8 * 64 ints.
+extern "C" int b2g_conv_rows_plan_query_merged(int kind, int N, int Hin, int Win, int Cin, int block_n, int pg, int ring,
+                                               int* out, int out_len) {
+  using namespace b2g;
+  if (!out || out_len < 8 + 3 * kRowsMaxSlabs + 8 * kRowsMaxSteps) return fail(B2G_E_INVALID_ARG, "rows_plan_query_merged: out too small");
+  memset(out, 0, sizeof(int) * out_len);
+  ConvPlan pl;
+  if (!build_conv_plan(kind, N, Hin, Win, Cin, block_n, 128, &pl)) return B2G_OK;
+  RowsGeom g;
+  RowsSched sc[2];
+  if (block_n != 32 && block_n != 64 && block_n != 128) return B2G_OK;
+  if (!build_rows_sched(pl, block_n, ring > 0 ? ring : rows_ring(block_n), &g, sc, true)) return B2G_OK;
+  if (pg < 0 || pg >= g.PG) return fail(B2G_E_INVALID_ARG, "rows_plan_query_merged: phase group %d out of range", pg);
+  out[0] = 1; out[1] = g.R; out[2] = g.P; out[3] = g.PG; out[4] = g.n_acc; out[5] = g.row_blocks;
+  out[6] = sc[pg].n_slabs; out[7] = sc[pg].n_steps;
+  for (int i = 0; i < sc[pg].n_slabs; ++i) {
+    out[8 + 3 * i] = sc[pg].slab_map[i]; out[9 + 3 * i] = sc[pg].slab_dy[i]; out[10 + 3 * i] = sc[pg].slab_chunk[i];
+  }
+  for (int j = 0; j < sc[pg].n_steps; ++j) {
+    const RowsStep& st = sc[pg].steps[j];
+    int* o = out + 8 + 3 * kRowsMaxSlabs + 8 * j;
+    o[0] = st.bcol; o[1] = st.phase_l; o[2] = st.slab0; o[3] = st.dxi; o[4] = st.acc0; o[5] = st.rel; o[6] = st.wide;
+    o[7] = st.bcol2;
   }
   return B2G_OK;
 }

@@ -28,7 +28,9 @@ struct RowsStep {
   int8_t dxi;      // pixel shift inside the slab: dx + 1
   int8_t acc0;     // accumulator of row r = 0
   int8_t rel;      // slabs released after this step
-  int8_t pad;
+  int8_t wide;     // 1: merged step — the SAME shifted slab feeds local phases phase_l and phase_l + 1 with ONE MMA of
+                   // N = 2 * BLOCK_N (weight tiles bcol | bcol2 stacked in one stage, accumulators acc0 and acc0 + 1)
+  int16_t bcol2;   // wide steps: k-block of the second phase's weight tile
 };
 
 struct RowsSched {
@@ -43,7 +45,13 @@ struct RowsGeom {
 };
 
 // One attempt with a fixed number of rows per super-tile.
-constexpr bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGeom* g, RowsSched* sched /*[2]*/) {
+// merge (transposed conv, P = 2): the two sub-pixel phases of a phase group (px = 0, 1) both use the dx = 0 shift of every
+// input row — with N = 64 tiles each MMA group reads 16 KB of A and 8 KB of B from shared memory for 128 tensor cycles
+// of math (192 B/clk against the 128 B/clk the operand path delivers, measured in round 1 and 2).  One N = 128 MMA for
+// both phases reads the A operand once: 80 instead of 96 KB per (row, dy, channel chunk).  The wide step is issued FIRST
+// of its dy so that at the first step of a super-tile both accumulators are still unwritten (one accumulate flag).
+constexpr bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGeom* g, RowsSched* sched /*[2]*/,
+                              bool merge = false) {
   const int chunks = pl.Cin / 64;
   g->R = R;
   g->P = P;
@@ -78,23 +86,53 @@ constexpr bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGe
           last_use[base + i] = -1;
         }
         s.n_slabs += cnt;
-        for (int dy = dmin; dy <= dmax; ++dy)
+        for (int dy = dmin; dy <= dmax; ++dy) {
+          // merged step: taps t0 of local phase 0 and t1 of local phase 1 with this dy and the same dx
+          int mt0 = -1, mt1 = -1;
+          if (merge && P == 2)
+            for (int t0 = 0; t0 < pl.taps && mt0 < 0; ++t0)
+              for (int t1 = 0; t1 < pl.taps; ++t1) {
+                const int e0 = (pg * P) * pl.taps + t0, e1 = (pg * P + 1) * pl.taps + t1;
+                if (pl.tap_map[e0] == m && pl.tap_map[e1] == m && pl.tap_dy[e0] == dy && pl.tap_dy[e1] == dy &&
+                    pl.tap_dx[e0] == pl.tap_dx[e1]) {
+                  mt0 = t0;
+                  mt1 = t1;
+                  break;
+                }
+              }
+          if (mt0 >= 0) {
+            if (s.n_steps >= kRowsMaxSteps) return false;
+            RowsStep& st = s.steps[s.n_steps];
+            st.bcol = (int16_t)(mt0 * chunks + c);
+            st.bcol2 = (int16_t)(mt1 * chunks + c);
+            st.phase_l = 0;
+            st.slab0 = (int8_t)(base + dy - dmin);
+            st.dxi = (int8_t)(pl.tap_dx[(pg * P) * pl.taps + mt0] + 1);
+            st.acc0 = 0;
+            st.rel = 0;
+            st.wide = 1;
+            for (int r = 0; r < R; ++r) last_use[st.slab0 + r] = s.n_steps;
+            ++s.n_steps;
+          }
           for (int pl_ = 0; pl_ < P; ++pl_)
             for (int t = 0; t < pl.taps; ++t) {
               const int e = (pg * P + pl_) * pl.taps + t;
               if (pl.tap_map[e] != m || pl.tap_dy[e] != dy) continue;
+              if (mt0 >= 0 && ((pl_ == 0 && t == mt0) || (pl_ == 1 && t == mt1))) continue;  // covered by the wide step
               if (s.n_steps >= kRowsMaxSteps) return false;
               RowsStep& st = s.steps[s.n_steps];
               st.bcol = (int16_t)(t * chunks + c);
+              st.bcol2 = 0;
               st.phase_l = (int8_t)pl_;
               st.slab0 = (int8_t)(base + dy - dmin);
               st.dxi = (int8_t)(pl.tap_dx[e] + 1);
               st.acc0 = (int8_t)pl_;
               st.rel = 0;
-              st.pad = 0;
+              st.wide = 0;
               for (int r = 0; r < R; ++r) last_use[st.slab0 + r] = s.n_steps;
               ++s.n_steps;
             }
+        }
       }
     }
     // FIFO release counts; the live span (needed slab - released slabs) must fit the ring
@@ -117,7 +155,8 @@ constexpr bool try_rows_sched(const ConvPlan& pl, int ring, int R, int P, RowsGe
 // Builds the geometry and one schedule per phase group: the largest R in {4, 2, 1} whose accumulators fit 256 TMEM
 // columns (x2 buffers) and whose schedule fits the tables and the slab ring.  `ring` = slab stages the kernel owns.
 // Returns false when the role does not fit (the caller falls back to the per-tap kernel).
-constexpr bool build_rows_sched(const ConvPlan& pl, int block_n, int ring, RowsGeom* g, RowsSched* sched /*[2]*/) {
+constexpr bool build_rows_sched(const ConvPlan& pl, int block_n, int ring, RowsGeom* g, RowsSched* sched /*[2]*/,
+                                bool merge = false) {
   if (pl.kind == B2G_CONV_K1S1) return false;
   if (pl.bw != 128 || pl.bh != 1 || pl.bn != 1) return false;
   if (pl.Cin % 64 || block_n > 256) return false;
@@ -127,7 +166,7 @@ constexpr bool build_rows_sched(const ConvPlan& pl, int block_n, int ring, RowsG
   if (R > 4) R = 4;
   while (R > 1 && R > pl.Hg) R /= 2;
   for (; R >= 1; R /= 2)
-    if (try_rows_sched(pl, ring, R, P, g, sched)) return true;
+    if (try_rows_sched(pl, ring, R, P, g, sched, merge && 2 * block_n <= 256)) return true;
   return false;
 }
 
@@ -146,12 +185,14 @@ struct RowsSchedPair {
 
 struct RowsDyn {  // generic kernel: table-driven issue loop, default ring sizes
   static constexpr bool kStatic = false;
+  static constexpr bool kMerge = false;
   static constexpr int kS = 0, kSB = 0;
 };
 
-template <int KIND, int CH, int R_, int P_, int BN, int S_, int SB_>
+template <int KIND, int CH, int R_, int P_, int BN, int S_, int SB_, bool MERGE_ = false>
 struct RowsStatic {
   static constexpr bool kStatic = true;
+  static constexpr bool kMerge = MERGE_;
   static constexpr int kKind = KIND, kCh = CH, kR = R_, kP = P_, kS = S_, kSB = SB_;
   static constexpr RowsSchedPair make() {
     ConvPlan pl{};
@@ -159,7 +200,7 @@ struct RowsStatic {
     const bool ok_plan = build_conv_plan(KIND, 1, KIND == B2G_CONV_K4S2 ? 16 : 8, KIND == B2G_CONV_K4S2 ? 256 : 128,
                                          CH * 64, BN, 128, &pl);
     RowsSchedPair sp{};
-    sp.ok = ok_plan && try_rows_sched(pl, S_, R_, P_, &sp.g, sp.s);
+    sp.ok = ok_plan && try_rows_sched(pl, S_, R_, P_, &sp.g, sp.s, MERGE_);
     return sp;
   }
   static constexpr bool ok() { return make().ok; }
@@ -182,8 +223,10 @@ struct RowsStatic {
   static constexpr bool written_before(int J, int acc) {
     const RowsSchedPair sp = make();
     for (int j = 0; j < J; ++j)
-      for (int r = 0; r < R_; ++r)
+      for (int r = 0; r < R_; ++r) {
         if (sp.s[0].steps[j].acc0 + r * P_ == acc) return true;
+        if (sp.s[0].steps[j].wide && sp.s[0].steps[j].acc0 + 1 + r * P_ == acc) return true;
+      }
     return false;
   }
   static_assert(S_ >= 1 && SB_ >= 1, "ring sizes");
@@ -198,7 +241,7 @@ inline bool rows_static_matches(const RowsGeom& g, const RowsSched* sched) {
     if (sched[pg].n_slabs != sp.s[0].n_slabs || sched[pg].n_steps != sp.s[0].n_steps) return false;
     for (int j = 0; j < sp.s[0].n_steps; ++j) {
       const RowsStep &a = sched[pg].steps[j], &b = sp.s[0].steps[j];
-      if (a.slab0 != b.slab0 || a.dxi != b.dxi || a.acc0 != b.acc0 || a.rel != b.rel) return false;
+      if (a.slab0 != b.slab0 || a.dxi != b.dxi || a.acc0 != b.acc0 || a.rel != b.rel || a.wide != b.wide) return false;
     }
   }
   return true;

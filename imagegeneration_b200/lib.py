@@ -201,6 +201,7 @@ _EXTRA_SIGNATURES: dict[str, list] = {
     "b2g_avgpool8_bf16": [_P, _P, _I, _I, _I, _I, _P],
     # kind, N, Hin, Win, Cin, block_n, phase_group, out, out_len   (host-only)
     "b2g_conv_rows_plan_query": [_I, _I, _I, _I, _I, _I, _I, C.POINTER(C.c_int), _I],
+    "b2g_conv_rows_plan_query_merged": [_I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(C.c_int), _I],
 }
 
 

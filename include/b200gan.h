@@ -399,6 +399,11 @@ int b2g_l1_loss(const float* a, const float* b, long n, float scale, float* loss
  *   dx+1, accumulator of row 0, slabs released after the step}.  out_len >= 464.
  */
 int b2g_conv_rows_plan_query(int kind, int N, int Hin, int Win, int Cin, int block_n, int pg, int* out, int out_len);
+/* Same, for the schedule with MERGED steps (transposed conv with two sub-pixel phases per group: the dx = 0 shift of an
+ * input row feeds both phases with one MMA of twice the tile width); ring = slab ring size (0: default).  8 ints per step
+ * from out[8 + 72]: {bcol, phase_l, slab0, dxi, acc0, rel, wide, bcol2}; out needs 8 + 72 + 8 * 64 ints. */
+int b2g_conv_rows_plan_query_merged(int kind, int N, int Hin, int Win, int Cin, int block_n, int pg, int ring, int* out,
+                                    int out_len);
 int b2g_conv_plan_query(int kind, int N, int Hin, int Win, int tile_pixels, int* out, int out_len);
 long b2g_pack_source_index(int kind, int kh, int kw, int D2, int D3, int n_is_d3, int flip, int ck_pad, long i);
 
