@@ -55,6 +55,10 @@ struct RowsCfg {
   static constexpr bool fits(int nb) {
     return kMainBytes + epi_tma_smem_bytes(kEpiWarps, nb) + kBarBytes + 1024 + 4096 <= 227 * 1024;
   }
+  // Tried after the merged schedule (round 2) and NOT kept: the conv_c3-style "fat" epilogue for the N = 64 role — a warp
+  // takes all 64 channels of one accumulator per visit (two tcgen05.ld in flight, early accumulator release, one 4 KiB
+  // 128-byte-swizzled box).  With 19 warps the CTA is capped at 96 registers (64 of them accumulators) and one box per
+  // warp: G.convT3 forward 167 -> 189 us, D.conv2 input gradient unchanged at 196 us, MMA pipeline alone 150 -> 157 us.
   static constexpr int kEpiBoxes = BLOCK_N < 64 ? 0 : (fits(2) ? 2 : (fits(1) ? 1 : 0));
   static constexpr bool kEpiTma = kEpiBoxes > 0;
   static constexpr int kEpiBytes = kEpiTma ? epi_tma_smem_bytes(kEpiWarps, kEpiBoxes) : 0;
