@@ -225,3 +225,32 @@ def test_row_slab_schedule_geometry_of_the_model_layers():
     # narrow layers stay on the per-tap kernel
     assert _rows_plan(K3S1, 64, 36, 64, 256, 128, 0)["handled"] == 0
     assert _rows_plan(K1S1, 64, 144, 256, 64, 64, 0)["handled"] == 0
+
+
+def test_merged_rows_schedule_covers_the_same_taps():
+    """RowsStep::wide (transposed conv, two sub-pixel phases per group): the merged schedule of the G.convT3 / D.conv2-dgrad
+    role issues the dx = 0 shift of every dy ONCE for both phases (N = 2 x 64), first of its dy, and still covers every
+    (phase, weight k-block) of the unmerged schedule exactly once; the slab ring of 6 divides the slabs, 3 weight stages
+    divide the 12 steps (the compile-time kernel's static_asserts rely on both)."""
+    from imagegeneration_b200 import lib
+    kind, n, h, w, cin, bn = 2, 4, 72, 128, 128, 64      # B2G_CONVT_K4S2
+    for pg in (0, 1):
+        base = _rows_plan(kind, n, h, w, cin, bn, pg)
+        out = (C.c_int * (8 + 72 + 8 * 64))()
+        assert lib.load().b2g_conv_rows_plan_query_merged(kind, n, h, w, cin, bn, pg, 6, out, len(out)) == 0
+        v = list(out)
+        assert v[0] == 1 and v[1:6] == [base["R"], base["P"], base["PG"], base["n_acc"], base["row_blocks"]]
+        assert v[6] == base["n_slabs"] == 6 and v[7] == 12 and base["n_steps"] == 16
+        steps = [tuple(v[80 + 8 * j:88 + 8 * j]) for j in range(v[7])]
+        want = sorted((phl, bcol, slab0, dxi) for (bcol, phl, slab0, dxi, acc0, rel) in base["steps"])
+        got = []
+        for (bcol, phl, slab0, dxi, acc0, rel, wide, bcol2) in steps:
+            assert acc0 == phl
+            got.append((phl, bcol, slab0, dxi))
+            if wide:
+                assert phl == 0 and dxi == 1                      # the shared shift is dx = 0
+                got.append((1, bcol2, slab0, dxi))
+        assert sorted(got) == want
+        assert sum(s[6] for s in steps) == 4                      # 2 dy x 2 channel chunks
+        assert steps[0][6] == 1                                   # a fresh super-tile starts with a wide step
+        assert sum(s[5] for s in steps) == v[6]                   # every slab released exactly once
