@@ -186,11 +186,13 @@ __global__ void __launch_bounds__(256) bn_apply_act_kernel(const uint4* __restri
   }
 }
 
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const uint4* __restrict__ g, const uint4* __restrict__ x,
+// g and dx MAY ALIAS (wgan.py applies the backward in place over the gradient buffer): neither is __restrict__ and g is
+// read with a plain load, not through the read-only (.nc) path; a thread reads element i before it writes element i.
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const uint4* g, const uint4* __restrict__ x,
                                                            const float* __restrict__ stat,
                                                            const float* __restrict__ gamma,
                                                            const float* __restrict__ red, float inv_p,
-                                                           uint4* __restrict__ dx, float* __restrict__ dgamma,
+                                                           uint4* dx, float* __restrict__ dgamma,
                                                            float* __restrict__ dbeta, long n8, int C) {
   // per-channel constants once per block (threads 0..C-1 add the partial copies), then 24 shared loads per thread
   extern __shared__ float sk[];  // [3][C]: a, c1, c0
@@ -225,7 +227,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const uint4* __restri
   // plain grid-stride loop: measured 0.96 of the copy peak as is (a 2x unrolled variant with clamped loads was slower)
   for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < n8; i += (long)gridDim.x * 256) {
     float fg[8], fx[8];
-    unpack8(__ldg(g + i), fg);
+    unpack8(g[i], fg);
     unpack8(__ldg(x + i), fx);
 #pragma unroll
     for (int k = 0; k < 8; ++k) fg[k] = fmaf(a[k], fg[k], fmaf(c1[k], fx[k], c0[k]));
