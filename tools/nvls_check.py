@@ -31,8 +31,20 @@ def run(nvls, graph):
         z = (torch.rand((batch, 128), generator=g) * 2 - 1).cuda()
         outs.append([float(x) for x in eng.train_step(real, z)[:4]])
     torch.cuda.synchronize()
-    eng.gather_optimizer_state()
+    if eng._nvls is not None:       # before the gather only this rank's slice of Adam's m / v is current ...
+        nv = eng._nvls
+        own = nv["m_full"][nv["begin"]:nv["end"]].abs().sum()
+        assert float(own) > 0
+    eng.gather_optimizer_state()    # ... afterwards every rank holds every slice
     D = eng.disc_model.arena
+    if eng._nvls is not None:
+        nv, per = eng._nvls, eng._nvls["per"]
+        for r in range(world):
+            hi = min((r + 1) * per, D.numel)
+            assert float(nv["m_full"][r * per:hi].abs().sum()) > 0 and float(nv["v_full"][r * per:hi].abs().sum()) > 0, r
+        mine = nv["m_full"].clone()
+        dist.broadcast(mine, src=0)
+        assert torch.equal(mine, nv["m_full"])          # identical on every rank
     res = (outs, D.w.clone(), D.m.clone(), D.v.clone(), eng.gen_model.arena.w.clone())
     eng.close()
     return res
@@ -95,6 +107,8 @@ for graph in (False, True):
         print(f"graph={graph}: max loss diff vs NCCL path after 5 steps {lo:.3e}; max |dw| {dw:.3e} (10 updates of lr 2e-4); "
               f"replicas bit-identical across ranks: {bool(flags.item())}", flush=True)
     assert lo < 5e-3 and dw <= 10 * 2e-4 * 1.01, (lo, dw)
+    rel_v = float((ref[3] - got[3]).norm() / ref[3].norm())
+    assert rel_v < 5e-2, rel_v                           # gathered second-moment state tracks the NCCL path's
     assert flags.item() == 1
 if rank == 0:
     print("nvls_check ok", flush=True)
