@@ -433,6 +433,11 @@ struct EpiWarpStageN {
   uint64_t* ybar;    // NB mbarriers of the saved-output loads
   uint32_t k_begin;  // items begun
   uint32_t k_chunk;  // items processed
+  // running column sums of this lane's two channels (plain sums only; with colsumsq the per-item path is used): kept in
+  // registers ACROSS items while the warp stays on the same channels (it does: a warp's chunk is fixed by its group),
+  // combined across the lane halves and added to the CTA's table once, in epi_tma_colsum_flush
+  float cs0, cs1;
+  int cs_cb;         // first channel of the 32-channel chunk the running sums belong to; -1: none
 };
 using EpiWarpStage = EpiWarpStageN<1>;
 
@@ -448,6 +453,9 @@ __device__ __forceinline__ EpiWarpStageN<NB> epi_tma_stage(uint8_t* base, int wa
   st.ybar = reinterpret_cast<uint64_t*>(base + warps * NB * kEpiStageBytes) + w * NB;
   st.k_begin = 0;
   st.k_chunk = 0;
+  st.cs0 = 0.f;
+  st.cs1 = 0.f;
+  st.cs_cb = -1;
   return st;
 }
 // by one thread, before fence_barrier_init() and the block-wide sync
@@ -478,6 +486,22 @@ __device__ __forceinline__ void epi_tma_begin(const EpiParams& p, const CUtensor
     tma_load_4d(st.buf + b * kEpiStageBytes, ymap, &st.ybar[b], cb, bx, by, bn);
   }
   __syncwarp();
+}
+
+// Whole warp: adds the running column sums of the warp (EpiWarpStageN::cs0 / cs1) into the CTA's shared table.  Call
+// when the warp moves to other channels and before the kernel's final block-wide sync.
+template <int NB>
+__device__ __forceinline__ void epi_tma_colsum_flush(const EpiParams& p, EpiWarpStageN<NB>& st, float* s_colsum, int lane) {
+  if (st.cs_cb < 0) return;
+  const uint32_t cp = lane & 15, h = lane >> 4;
+  const int cs_off = (static_cast<int>(threadIdx.x >> 5) % p.cs_copies) * p.Cout;
+  float s0 = st.cs0, s1 = st.cs1;
+  s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+  s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+  atomicAdd(&s_colsum[cs_off + st.cs_cb + 2 * cp + h], h ? s1 : s0);
+  st.cs0 = 0.f;
+  st.cs1 = 0.f;
+  st.cs_cb = -1;
 }
 
 // Whole warp: epilogue math of one chunk (lane = pixel) through the box, then the TMA store.
@@ -540,9 +564,19 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
       q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
       atomicAdd(&const_cast<float*>(sbias)[cs_off + cb + 2 * cp + h], h ? q1 : q0);
     } else {
+      // plain sums: accumulate into the warp's running registers (no shuffle, no shared atomic per item)
+      if (st.cs_cb != cb) {
+        epi_tma_colsum_flush(p, st, s_colsum, lane);
+        st.cs_cb = cb;
+      }
+      s0 = st.cs0;
+      s1 = st.cs1;
 #pragma unroll
       for (int j = 0; j < 16; ++j)  // one mixed-precision add per element (FHADD.BF16), no unpacking
         bf2_acc(*reinterpret_cast<const uint32_t*>(base + j * 128 + ((cg ^ (j & 3)) << 4)), s0, s1);
+      st.cs0 = s0;
+      st.cs1 = s1;
+      return;
     }
     s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
     s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
@@ -554,6 +588,11 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
 __device__ __forceinline__ void epi_tma_end() {
   if (elect_one_sync()) tma_store_wait_read();
   __syncwarp();
+}
+template <int NB>
+__device__ __forceinline__ void epi_tma_end(const EpiParams& p, EpiWarpStageN<NB>& st, float* s_colsum, int lane) {
+  if (p.colsum) epi_tma_colsum_flush(p, st, s_colsum, lane);
+  epi_tma_end();
 }
 
 // The dropout seed of this call: from the arguments, or read from device memory when the call asked for it

@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_leader + as * 8);
     }
-    if (use_tma) epi_tma_end();
+    if (use_tma) epi_tma_end(e, st, s_colsum, lane);
   }
 
   tc_fence_before();

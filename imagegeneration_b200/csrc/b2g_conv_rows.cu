@@ -173,7 +173,14 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const ConvPlan& pl = p.plan;
-  const int R = p.geom.R, P = p.geom.P, n_acc = p.geom.n_acc;
+  // compile-time schedules know R and P: the per-item "acc / P", "acc % P" of the epilogue become shifts instead of
+  // runtime integer divisions
+  int R = p.geom.R, P = p.geom.P, n_acc = p.geom.n_acc;
+  if constexpr (SS::kStatic) {
+    R = SS::kR;
+    P = SS::kP;
+    n_acc = SS::kR * SS::kP;
+  }
   const uint32_t tmem_cols = 2u * n_acc * BLOCK_N;
 
   if (threadIdx.x == 0) {
@@ -355,12 +362,18 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     // saved-output load started).  ensure_begun(n) keeps n items begun beyond the ones already processed: 1 before the
     // accumulator wait (the first item's load overlaps the wait), NB inside the item loop (NB = 2: one item ahead).
     int b_tile = blockIdx.x, b_idx = grp;
+    RowsTile bt = decode_rows_tile(p, b_tile);  // decoded once per tile, not per item (the divisions are a dependent
+                                                // chain of ~40 instructions: a quarter of the epilogue warps' stall
+                                                // samples sat in this bookkeeping, ncu round 2)
     auto ensure_begun = [&](uint32_t n) {
       if (!use_tma || grp >= n_items) return;
       while (st.k_begin - st.k_chunk < n) {
-        if (b_idx >= n_items) { b_tile += gridDim.x; b_idx = grp; }
+        if (b_idx >= n_items) {
+          b_tile += gridDim.x;
+          b_idx = grp;
+          if (b_tile < p.total_tiles) bt = decode_rows_tile(p, b_tile);
+        }
         if (b_tile >= p.total_tiles) return;
-        const RowsTile bt = decode_rows_tile(p, b_tile);
         const int acc = b_idx / kChunks, c = b_idx % kChunks;
         epi_tma_begin(e, &p.em.ymap[bt.pg * P + acc % P], st, bt.n_tile * BLOCK_N + c * 32, bt.w0 + q * 32,
                       bt.y0 + acc / P, bt.n);
@@ -406,7 +419,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[as]);
     }
-    if (use_tma) epi_tma_end();
+    if (use_tma) epi_tma_end(e, st, s_colsum, lane);
   }
 
   tc_fence_before();

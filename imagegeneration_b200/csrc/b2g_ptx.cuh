@@ -85,7 +85,7 @@ __device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity)
     if (ok) break;
     // the suspend hint alone still came back every ~100 ns (ncu r2: 12 % of conv_c3's executed instructions were this
     // loop, 20 waiting warps per CTA): back off explicitly, the waits of these warps are microseconds long
-    __nanosleep(spins < 4 ? 96u : 256u);
+    __nanosleep(spins < 8 ? 20u : 64u);
     if (++spins > (1u << 22)) __trap();
   }
 }
