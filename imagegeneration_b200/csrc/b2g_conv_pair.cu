@@ -210,6 +210,8 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
     };
     // begin pointer of the TMA epilogue (see b2g_conv_rows.cu): the next item (pair, chunk) that has not been begun
     int b_pair = cluster_id, b_it = 0, b_c = first_chunk(0);
+    int c_pair = -1;   // the pair the main loop decoded last: begin() of the same pair reuses its coordinates (the
+    PairCoord c_tc{};  // multiply-high divisions are a dependent chain the epilogue warps stall on, ncu round 2)
     auto ensure_begun = [&](uint32_t n) {
       if (!use_tma) return;
       while (st.k_begin - st.k_chunk < n) {
@@ -219,7 +221,7 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
           b_c = first_chunk(b_it);
         }
         if (b_pair >= p.total_pairs) return;
-        const PairCoord bt = decode_pair(p, b_pair, rank);
+        const PairCoord bt = b_pair == c_pair ? c_tc : decode_pair(p, b_pair, rank);
         epi_tma_begin(e, &p.em.ymap[bt.phase], st, bt.n_tile * BLOCK_N + b_c * 32, bt.tw * pl.bw + wl0,
                       bt.th * pl.bh + hl0, bt.tn * pl.bn + nl0);
         b_c += Cfg::kEpiGroups;
@@ -231,6 +233,8 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
       const int c_first = first_chunk(it);
       if (c_first >= kChunks) continue;
       const PairCoord tc = decode_pair(p, pair, rank);
+      c_pair = pair;
+      c_tc = tc;
       const int gw = tc.tw * pl.bw + wl, gh = tc.th * pl.bh + hl, gn = tc.tn * pl.bn + nl;
       const bool valid = (gh < pl.Hg) && (gn < pl.N);
       const int oy = gh * pl.os + pl.ph_y[tc.phase], ox = gw * pl.os + pl.ph_x[tc.phase];
