@@ -107,8 +107,13 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t saddr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
   return r;
 }
+// Arrive on an mbarrier of another CTA of the cluster (accumulator release of the CTA-pair kernels).  Default semantics
+// (release at CTA scope), as CUTLASS's ClusterBarrier::arrive does: what the arrival orders is the warp's tcgen05.ld
+// reads of TMEM (tcgen05.wait::ld + tcgen05.fence::before_thread_sync precede it) — no global memory.  The
+// .release.cluster form used until round 2 compiled to MEMBAR.ALL.GPU + ERRBAR, i.e. every arrival waited for ALL of the
+// thread's outstanding global stores: a quarter of conv_pair<128>'s stall samples sat on these two instructions (ncu).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------
