@@ -50,7 +50,7 @@ struct C3Cfg {
   static constexpr int kInStages = 6;           // staged fp32 input boxes
   static constexpr int kInStageBytes = 8192;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896)
   static constexpr int kBBytes = kBlockN * 128;
-  static constexpr int kAccBufs = 4;
+  static constexpr int kAccBufs = 8;            // all 512 TMEM columns (4 until round 2)
   static constexpr int kTmemCols = kAccBufs * kBlockN;
   static constexpr int kBuilderWarps = 2;       // 64 threads, two pixel rows each (16 warps per CTA = 4 per scheduler: 128 registers)
   static constexpr int kEpiGroups = 3;

@@ -48,7 +48,7 @@ struct PairCfg {
   // N <= 128 tiles: the TMA epilogue's per-warp boxes (b2g_conv_epi.cuh) take the room of one pipeline stage
   static constexpr bool kEpiTma = BLOCK_N <= 128;
   static constexpr int kStages = BLOCK_N == 256 ? 6 : (BLOCK_N == 128 ? 7 : 8);
-  static constexpr int kAccBufs = BLOCK_N <= 64 ? 4 : 2;
+  static constexpr int kAccBufs = BLOCK_N <= 128 ? 4 : 2;  // N = 128: four accumulators since round 2 (two before; TMEM has the columns)
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
   // 16 epilogue warps; N <= 128 (TMA epilogue): one 2 KiB box per warp (b2g_conv_epi.cuh).  Measured in round 2: a second
   // box (paid for with one pipeline stage) changed nothing here (D.conv4 dgrad 181 -> 187 us), 8 warps with 3-box rings

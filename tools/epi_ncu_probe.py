@@ -26,3 +26,12 @@ wt2 = ops.pack_conv_weight(ops.CONVT_K4S2, W(4, 4, 128, 256), n_is_d3=False)
 ops.conv_igemm(ops.CONVT_K4S2, x256, wt2, o128, yprev=y128, dact=ops.ACT_LEAKY, dact_alpha=0.1, dact_scale=2.0, colsum=cs128)
 torch.cuda.synchronize()
 print("done")
+# conv_pair<256> roles: D.conv6 input gradient (transposed, 512 -> 256, 4 phases) and D.conv5 forward (256 -> 256)
+x512 = rnd(B, 18, 32, 512); o256 = torch.empty((B, 36, 64, 256), device="cuda", dtype=torch.bfloat16); y256 = rnd(B, 36, 64, 256)
+cs256 = torch.zeros(256, device="cuda"); b256 = torch.zeros(256, device="cuda")
+wt6 = ops.pack_conv_weight(ops.CONVT_K4S2, W(4, 4, 256, 512), n_is_d3=False)
+ops.conv_igemm(ops.CONVT_K4S2, x512, wt6, o256, yprev=y256, dact=ops.ACT_LEAKY, dact_alpha=0.1, dact_scale=2.0, colsum=cs256)
+w5 = ops.pack_conv_weight(ops.CONV_K3S1, W(3, 3, 256, 256), n_is_d3=True)
+ops.conv_igemm(ops.CONV_K3S1, y256, w5, o256, bias=b256, act=ops.ACT_LEAKY, alpha=0.1, dropout_thresh8=128, dropout_seed=7)
+torch.cuda.synchronize()
+print("done 256")
