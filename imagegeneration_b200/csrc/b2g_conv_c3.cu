@@ -50,7 +50,7 @@ struct C3Cfg {
   static constexpr int kInStages = 6;           // staged fp32 input boxes
   static constexpr int kInStageBytes = 8192;    // upper bound of one box (128-px row tile: 136 * 12 * 3 = 4896)
   static constexpr int kBBytes = kBlockN * 128;
-  static constexpr int kAccBufs = 8;            // all 512 TMEM columns (4 until round 2)
+  static constexpr int kAccBufs = 4;            // 8 (all of TMEM) measured the same (round 2)
   static constexpr int kTmemCols = kAccBufs * kBlockN;
   static constexpr int kBuilderWarps = 2;       // 64 threads, two pixel rows each (16 warps per CTA = 4 per scheduler: 128 registers)
   static constexpr int kEpiGroups = 3;
@@ -289,11 +289,15 @@ __global__ void __launch_bounds__(C3Cfg::kThreads, 1) conv_c3_kernel(const __gri
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[as]);
       if (dbg) continue;
+      const bool valid = (gh < pl.Hg) && (gn < pl.N);
       if (!use_tma) {
-        const bool valid = (gh < pl.Hg) && (gn < pl.N);
         conv_epilogue_chunk(e, sbias, r0, pix, 0, valid, s_colsum, sd);
         conv_epilogue_chunk(e, sbias, r1, pix, 32, valid, s_colsum, sd);
         continue;
+      }
+      if (e.colsum && (!bwd || e.dact_zero != 0.f) && !valid) {  // see conv_pair_kernel: pixels outside the tensor
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { r0[j] = 0u; r1[j] = 0u; }
       }
       const uint32_t k = k_done++;
       const uint32_t b = k % NB;

@@ -546,7 +546,8 @@ __device__ __forceinline__ void epi_tma_chunk(const EpiParams& p, const CUtensor
     // pixel parity h = lane >> 4): 16 LDS.32 per lane — the 16 lanes of a half warp cover one 64-byte pixel row, the two
     // halves rows 2j and 2j + 1 = all 32 banks, conflict free — then one shuffle joins the two parities.  Round 1 read
     // one bf16 per lane and pixel (32 LDS.U16 + sum-of-squares FMAs even without BatchNorm statistics): 185 instructions
-    // per item, 17 % of a backward epilogue (ncu r2).  Rows of pixels outside the tensor hold exact zeros.
+    // per item, 17 % of a backward epilogue (ncu r2).  Rows of pixels outside the tensor hold exact zeros: masked by the
+    // zero-filled saved output when act'(0) = 0, else the callers clear those pixels' accumulators (zero_oob).
     const uint32_t cp = lane & 15, h = lane >> 4;
     const uint8_t* base = box + h * 64 + (cp & 3) * 4;
     const uint32_t cg = cp >> 2;

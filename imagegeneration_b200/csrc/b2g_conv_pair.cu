@@ -40,14 +40,19 @@ struct alignas(64) PairKernelParams {
   FastDiv fd_nt, fd_tw, fd_th;  // tile decoding without divisions (n_tiles, tiles_w, tiles_h)
 };
 
-template <int BLOCK_N>
+// BOXES: N = 256 only — give up one pipeline stage for the TMA epilogue's boxes.  Used for the BACKWARD roles of the
+// >= 256-channel layers: their direct epilogue loads the saved output with one 64-byte global load per lane and pixel row
+// (uncoalesced, a fifth of the stall samples on the first use of what it loaded) and sums columns with a 31-shuffle
+// butterfly per chunk (ncu round 2: D.conv6 input gradient 134 us at 66 % tensor-pipe activity against 117 us / 88 % for a
+// forward role of the same size).
+template <int BLOCK_N, bool BOXES = false>
 struct PairCfg {
   static constexpr int kABytes = 128 * 128;
   static constexpr int kBBytes = (BLOCK_N / 2) * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
   // N <= 128 tiles: the TMA epilogue's per-warp boxes (b2g_conv_epi.cuh) take the room of one pipeline stage
-  static constexpr bool kEpiTma = BLOCK_N <= 128;
-  static constexpr int kStages = BLOCK_N == 256 ? 6 : (BLOCK_N == 128 ? 7 : 8);
+  static constexpr bool kEpiTma = BLOCK_N <= 128 || BOXES;
+  static constexpr int kStages = BLOCK_N == 256 ? (BOXES ? 5 : 6) : (BLOCK_N == 128 ? 7 : 8);
   static constexpr int kAccBufs = BLOCK_N <= 128 ? 4 : 2;  // N = 128: four accumulators since round 2 (two before; TMEM has the columns)
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
   // 16 epilogue warps; N <= 128 (TMA epilogue): one 2 KiB box per warp (b2g_conv_epi.cuh).  Measured in round 2: a second
@@ -78,10 +83,10 @@ __device__ __forceinline__ PairCoord decode_pair(const PairKernelParams& p, int 
   return c;
 }
 
-template <int BLOCK_N>
-__global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
+template <int BLOCK_N, bool BOXES = false>
+__global__ void __launch_bounds__(PairCfg<BLOCK_N, BOXES>::kThreads, 1)
     conv_pair_kernel(const __grid_constant__ PairKernelParams p) {
-  using Cfg = PairCfg<BLOCK_N>;
+  using Cfg = PairCfg<BLOCK_N, BOXES>;
   constexpr int kChunks = BLOCK_N / 32;
   constexpr int kGroupsPerTile = kChunks < Cfg::kEpiGroups ? kChunks : Cfg::kEpiGroups;
   __shared__ float sbias[512];
@@ -204,6 +209,11 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
     constexpr int NB = Cfg::kEpiBoxes > 0 ? Cfg::kEpiBoxes : 1;
     EpiWarpStageN<NB> st = epi_tma_stage<NB>(epism, Cfg::kEpiWarps, warp - 2);
     const bool use_tma = Cfg::kEpiTma && p.e.tma != 0;
+    // Column sums are read back from the warp's box, which also holds the pixels of a ragged tile that lie OUTSIDE the
+    // tensor (the TMA store clips them).  Their accumulators are not zero (the taps of a pixel just outside reach into the
+    // image); with act'(0) = 0 the zero-filled saved output masks them, with act'(0) != 0 (no-dropout layers, WGAN) the
+    // accumulators are cleared instead.
+    const bool zero_oob = e.colsum != nullptr && (e.dact == B2G_ACT_NONE || e.dact_zero != 0.f);  // forward statistics too
     // first chunk of tile number `i` (counted per cluster) that belongs to this warp's group; >= kChunks: none
     auto first_chunk = [&](int i) {
       return kChunks < Cfg::kEpiGroups ? ((grp - i * kChunks) & (Cfg::kEpiGroups - 1)) : grp;
@@ -251,6 +261,10 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, r);
         ensure_begun(NB);
         tmem_ld_wait();
+        if (use_tma && zero_oob && !valid) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = 0u;
+        }
         if (use_tma) epi_tma_chunk(e, &p.em.omap[tc.phase], st, sbias, r, pix, col0 + c * 32, lane, bx, by, bn, s_colsum, sd);
         else conv_epilogue_chunk(e, sbias, r, pix, col0 + c * 32, valid, s_colsum, sd);
       }
@@ -271,12 +285,12 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N>::kThreads, 1)
   }
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool BOXES = false>
 static int launch_pair(const PairKernelParams& kp, cudaStream_t stream) {
-  using Cfg = PairCfg<BLOCK_N>;
+  using Cfg = PairCfg<BLOCK_N, BOXES>;
   static bool attr_set = false;
   if (!attr_set) {
-    B2G_CUDA_CHECK(cudaFuncSetAttribute(conv_pair_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B2G_CUDA_CHECK(cudaFuncSetAttribute(conv_pair_kernel<BLOCK_N, BOXES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         Cfg::kSmemBytes));
     attr_set = true;
   }
@@ -295,7 +309,7 @@ static int launch_pair(const PairKernelParams& kp, cudaStream_t stream) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B2G_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_pair_kernel<BLOCK_N>, kp));
+  B2G_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_pair_kernel<BLOCK_N, BOXES>, kp));
   return B2G_OK;
 }
 
@@ -314,9 +328,11 @@ int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   PairKernelParams kp;
   memset(&kp, 0, sizeof(kp));
   kp.plan = pl;
+  // backward roles at N = 256 take the TMA epilogue (one stage fewer); B2G_PAIR_BOXES256=0 keeps the direct one
+  const bool boxes256 = block_n == 256 && a->dact != B2G_ACT_NONE && !a->tf32 && env_int("B2G_PAIR_BOXES256", 1);
   fill_epi_params(a, &kp.e);
   {
-    int rc = fill_epi_tma(a, pl, block_n <= 128, &kp.e, &kp.em);
+    int rc = fill_epi_tma(a, pl, block_n <= 128 || boxes256, &kp.e, &kp.em);
     if (rc) return rc;
   }
   kp.brows = a->Cout;
@@ -359,7 +375,7 @@ int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   int rc;
   switch (block_n) {
-    case 256: rc = launch_pair<256>(kp, stream); break;
+    case 256: rc = (boxes256 && kp.e.tma) ? launch_pair<256, true>(kp, stream) : launch_pair<256>(kp, stream); break;
     case 128: rc = launch_pair<128>(kp, stream); break;
     default: rc = launch_pair<64>(kp, stream); break;
   }

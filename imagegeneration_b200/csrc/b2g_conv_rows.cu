@@ -357,6 +357,7 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
     constexpr int NB = Cfg::kEpiBoxes > 0 ? Cfg::kEpiBoxes : 1;
     EpiWarpStageN<NB> st = epi_tma_stage<NB>(epism, Cfg::kEpiWarps, warp - 3);
     const bool use_tma = Cfg::kEpiTma && p.e.tma != 0;
+    const bool zero_oob = e.colsum != nullptr && (e.dact == B2G_ACT_NONE || e.dact_zero != 0.f);
     const int n_items = n_acc * kChunks;  // items (accumulator, 32-channel chunk) of a tile; this warp: grp, grp + G, ...
     // Begin pointer of the TMA epilogue: the next item (tile, idx) of this warp that has not been begun (box freed,
     // saved-output load started).  ensure_begun(n) keeps n items begun beyond the ones already processed: 1 before the
@@ -412,6 +413,10 @@ __global__ void __launch_bounds__(RowsCfg<BLOCK_N, SS>::kThreads, 1)
                       v);
         ensure_begun(NB);
         tmem_ld_wait();
+        if (use_tma && zero_oob && !valid) {  // see conv_pair_kernel: pixels of a ragged tile outside the tensor
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
         if (use_tma) epi_tma_chunk(e, &p.em.omap[phase], st, sbias, v, pix, cb, lane, t.w0 + q * 32, gy, t.n, s_colsum, sd);
         else conv_epilogue_chunk(e, sbias, v, pix, cb, valid, s_colsum, sd);
       }

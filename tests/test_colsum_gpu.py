@@ -89,3 +89,31 @@ def test_colsum_rejected_on_forward_epilogues():
     with pytest.raises(B200GanError):
         ops.conv_igemm(ops.CONV_K3S1, x, wp, bias=torch.zeros(64, device="cuda"), act=ops.ACT_LEAKY, alpha=0.1,
                        colsum=torch.zeros(64, device="cuda"))
+
+
+@pytest.mark.parametrize("kind,n,h,w,cin,cout", [
+    ("CONVT", 3, 6, 8, 512, 256),     # CTA pair N = 256, boxes for the backward role, ragged tiles (3 images, 6 rows)
+    ("K3S1", 3, 12, 16, 256, 256),    # same, 3x3
+    ("CONVT", 3, 10, 16, 256, 128),   # CTA pair N = 128, ragged
+    ("K3S1", 3, 5, 128, 128, 128),    # row-slab kernel, odd height
+])
+def test_fused_colsum_ragged_tiles_with_nonzero_derivative_at_zero(kind, n, h, w, cin, cout):
+    """act'(0) != 0 (layers without dropout, WGAN: dact_zero = alpha * scale): the pixels of a ragged tile that lie outside
+    the tensor have non-zero accumulators (their taps reach into the image) and a zero-filled saved output does NOT mask
+    them — the kernels must clear them before the box column sums (regression: 2.5-4 % error in round 2)."""
+    from imagegeneration_b200 import ops
+    k = {"K3S1": ops.CONV_K3S1, "CONVT": ops.CONVT_K4S2}[kind]
+    x = _rand((n, h, w, cin), 1).to(torch.bfloat16).cuda()
+    if kind == "CONVT":
+        wp = ops.pack_conv_weight(k, _rand((4, 4, cout, cin), 2, 0.05).cuda(), n_is_d3=False)
+        oshape = (n, 2 * h, 2 * w, cout)
+    else:
+        wp = ops.pack_conv_weight(k, _rand((3, 3, cin, cout), 2, 0.05).cuda(), n_is_d3=True)
+        oshape = (n, h, w, cout)
+    yp = _yprev(oshape, 3)
+    cs = torch.zeros(cout, device="cuda")
+    out = ops.conv_igemm(k, x, wp, yprev=yp, dact=ops.ACT_LEAKY, dact_alpha=0.1, dact_scale=1.0, dact_zero=0.1, colsum=cs)
+    torch.cuda.synchronize()
+    want = out.double().sum(dim=(0, 1, 2))
+    err = (cs.double() - want).abs().max() / (want.abs().max() + 1e-30)
+    assert float(err) < 2e-5, float(err)
