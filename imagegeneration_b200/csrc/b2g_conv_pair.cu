@@ -56,7 +56,8 @@ struct PairCfg {
   static constexpr int kAccBufs = BLOCK_N <= 128 ? 4 : 2;  // N = 128: four accumulators since round 2 (two before; TMEM has the columns)
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
   // 16 epilogue warps; N <= 128 (TMA epilogue): one 2 KiB box per warp (b2g_conv_epi.cuh).  Measured in round 2: a second
-  // box (paid for with one pipeline stage) changed nothing here (D.conv4 dgrad 181 -> 187 us), 8 warps with 3-box rings
+  // box (paid for with one pipeline stage) changed nothing here (D.conv4 dgrad 181 -> 187 us; again neutral after the
+  // four accumulator buffers and the cheap remote arrive: 162 -> 161 us), 8 warps with 3-box rings
   // were 15-45 % slower — the backward epilogue is bound by per-warp instruction latency, not by the box hand-over
   static constexpr int kEpiGroups = 4;
   static constexpr int kEpiBoxes = kEpiTma ? 1 : 0;
