@@ -877,6 +877,17 @@ class SNDCGANEngine:
         self.disc_model._packed_dirty = True
         return tuple(o.clone() for o in self._graph_outs)   # the graph's own buffers are rewritten by the next replay
 
+    @staticmethod
+    def _nvtx(name=None):
+        """NVTX ranges around the three phases of the step when B2G_NVTX=1 (nsys / ncu --nvtx timelines): _nvtx(name) opens
+        a range, _nvtx() closes it.  No-op otherwise."""
+        if os.environ.get("B2G_NVTX", "0") != "1":
+            return
+        if name is None:
+            torch.cuda.nvtx.range_pop()
+        else:
+            torch.cuda.nvtx.range_push(name)
+
     def _step_body(self, input_real, input_z, sa, sb, sc, lr_dev):
         """The launches of one step.  sa/sb/sc: 7 dropout seeds per discriminator pass (ints, or 1-element device
         tensors under graph capture); lr_dev: None, or the three device-resident Adam rates (G, D first, D second)."""
@@ -891,38 +902,43 @@ class SNDCGANEngine:
         d_kind = LOSS_BCE if self.loss == "bce" else LOSS_HINGE_D
 
         # (1) generator step (:242-249)
+        self._nvtx("b2g:generator_step")
         g_output = G.forward(input_z)                                               # :243
         D.forward(g_output, training=True, dropout_seeds=sa)                        # :244
         g_loss, _ = D.head_loss(g_kind, 1.0, inv_b)                                 # :245-246
         d_gout = D.backward(need_wgrad=False, need_input_grad=True, g_out=g_output)
         G.backward(d_gout)                                                          # :248
+        self._nvtx()
         g_work = self._allreduce(G.arena.g, async_op=True, group=self.pg_g)
         # G's Adam (:249) is issued at the end of the step: nothing below reads the generator's weights, so the
         # result is identical and its gradient all-reduce overlaps both discriminator steps.
 
         # (2) discriminator step on the real batch (:251-257)
-        # While the generator's 164 MB all-reduce is in flight its NCCL kernel holds some SMs; a persistent grid of
-        # one CTA per SM would wait for them (two waves).  B2G_DP_SM_RESERVE=n leaves n SMs free for the first
-        # discriminator forward (and backward with B2G_DP_SM_RESERVE_BWD=1) after the all-reduce is launched.
-        # (B2G_DP_SM_RESERVE overrides the count; B2G_DP_G_WINDOW = 1: reserve during step (2) only, 2: steps (2) and (3).)
+        # While the generator's 164 MB all-reduce is in flight its NCCL kernel holds B2G_DP_G_CTAS SMs; a persistent grid of
+        # one CTA per SM would wait for them (two waves), so every kernel launched in that window runs on that many fewer
+        # SMs.  (B2G_DP_SM_RESERVE overrides the count; B2G_DP_G_WINDOW = 1: step (2) only, 2 (default): steps (2) and (3).)
         reserve = int(os.environ.get("B2G_DP_SM_RESERVE", str(self._g_ctas))) if g_work is not None else 0
         window = int(os.environ.get("B2G_DP_G_WINDOW", "2"))
         lib = _lib.load()
         if reserve:
             check(lib.b2g_set_sm_limit(max(8, lib.b2g_num_sms() - reserve)), "b2g_set_sm_limit", 0)
         try:
+            self._nvtx("b2g:discriminator_step_real")
             D.forward(input_real, training=True, dropout_seeds=sb)                  # :252
             d_loss_real, d_logits_real = D.head_loss(d_kind, 1.0, inv_b_real)       # :253-254
             d_logits_real = d_logits_real.clone()
             self._d_update(D, gs, lr_d1)                                            # :256-257
+            self._nvtx()
             if reserve and window < 2:
                 check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
 
             # (3) discriminator step on the stale fake batch (:259-267)
+            self._nvtx("b2g:discriminator_step_fake")
             D.forward(g_output, training=True, dropout_seeds=sc)                    # :260
             d_loss_fake, d_logits_fake = D.head_loss(d_kind, 0.0, inv_b)            # :261-262
             d_logits_fake = d_logits_fake.clone()   # D.logits is a reused buffer: the caller gets its own tensor
             self._d_update(D, gs, lr_d2)                                            # :266-267
+            self._nvtx()
         finally:
             if reserve:
                 check(lib.b2g_set_sm_limit(0), "b2g_set_sm_limit", 0)
