@@ -470,6 +470,20 @@ class WGANEngine:
             from .dp import allreduce_sum_
             allreduce_sum_(flat, self.pg, False)
 
+    def average_bn_statistics(self):
+        """Data parallel keeps BatchNorm's batch statistics per GPU (north_star item 4), so the MOVING mean / variance of
+        the replicas drift apart while the weights stay identical.  Before anything that reads the moving statistics is
+        shared between ranks — generator.predict for saved samples, a checkpoint, a model export — this averages them
+        across the ranks (moving statistics are running averages of per-batch values: the mean over ranks is the
+        running average over the global batches' per-shard statistics).  No-op on one GPU."""
+        if self.world == 1:
+            return
+        import torch.distributed as dist
+        for model in (self.generator_model, self.critic_model):
+            for t in model.bn.moving_mean + model.bn.moving_var:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.pg)
+                t.mul_(1.0 / self.world)
+
     def train_critic_on_batch(self, x, label: float):
         """critic_model.train_on_batch(x, label*ones) (WGAN.py:298,303): returns the loss (CUDA scalar)."""
         Cm = self.critic_model
