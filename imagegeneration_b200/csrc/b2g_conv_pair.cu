@@ -330,7 +330,10 @@ int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
   memset(&kp, 0, sizeof(kp));
   kp.plan = pl;
   // backward roles at N = 256 take the TMA epilogue (one stage fewer); B2G_PAIR_BOXES256=0 keeps the direct one
-  const bool boxes256 = block_n == 256 && a->dact != B2G_ACT_NONE && !a->tf32 && env_int("B2G_PAIR_BOXES256", 1);
+  const int boxes_env = env_int("B2G_PAIR_BOXES256", 1);  // 2: forward roles too — measured neutral (conv / wgrad launches
+                                                          // of a step 7.76 vs 7.78 ms): their direct stores hide behind the MMAs
+  const bool boxes256 = block_n == 256 && !a->tf32 && !a->out_f32 && !a->colsumsq &&
+                        (boxes_env == 2 || (boxes_env == 1 && a->dact != B2G_ACT_NONE));
   fill_epi_params(a, &kp.e);
   {
     int rc = fill_epi_tma(a, pl, block_n <= 128 || boxes256, &kp.e, &kp.em);
