@@ -459,7 +459,9 @@ static int env_int(const char* name, int dflt) {
 static int rows_ring(int block_n) { return block_n == 128 ? RowsCfg<128>::kSlabs : RowsCfg<64>::kSlabs; }
 
 // compile-time schedules of the model's four wide roles: <kind, Cin/64, R, P, N tile, slab ring, weight-tile ring>
-using RowsConv3 = RowsStatic<B2G_CONV_K3S1, 2, 2, 1, 128, 4, 6>;    // D.conv3 fwd / dgrad (128 -> 128 @72x128)
+using RowsConv3 = RowsStatic<B2G_CONV_K3S1, 2, 2, 1, 128, 4, 6>;    // D.conv3 fwd / dgrad (128 -> 128 @72x128); 3 weight
+                                                                    // stages + a second epilogue box measured WORSE on the
+                                                                    // same box (fwd 138 -> 144 us, dgrad 142 -> 151 us)
 using RowsConv2 = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 8>;    // D.conv2 fwd (64 -> 128, 144x256 -> 72x128)
 using RowsConv2b = RowsStatic<B2G_CONV_K4S2, 1, 2, 1, 128, 4, 4>;   // same role, 4 weight stages: room for 3 epilogue boxes
 using RowsConvT3 = RowsStatic<B2G_CONVT_K4S2, 2, 2, 2, 64, 6, 3, true>;  // G.convT3 fwd / D.conv2 dgrad (128 -> 64): merged
