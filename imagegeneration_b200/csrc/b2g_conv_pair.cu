@@ -35,6 +35,7 @@ struct alignas(64) PairKernelParams {
   int n_tiles;      // Cout / BLOCK_N
   EpiTmaMaps em;    // TMA epilogue (used when e.tma)
   int brows;        // rows of the packed weight matrix per phase
+  int arrive_release_cluster;  // measurement switch: 1 = the old .release.cluster remote arrive
   int m_pairs;      // plan.m_tiles / 2
   int total_pairs;  // phases * m_pairs * n_tiles
   FastDiv fd_nt, fd_tw, fd_th;  // tile decoding without divisions (n_tiles, tiles_w, tiles_h)
@@ -53,6 +54,9 @@ struct PairCfg {
   // N <= 128 tiles: the TMA epilogue's per-warp boxes (b2g_conv_epi.cuh) take the room of one pipeline stage
   static constexpr bool kEpiTma = BLOCK_N <= 128 || BOXES;
   static constexpr int kStages = BLOCK_N == 256 ? (BOXES ? 5 : 6) : (BLOCK_N == 128 ? 7 : 8);
+  // N = 128: four accumulators since round 2 (TMEM has the columns).  A same-box A/B against two buffers measured NO
+  // difference (G.convT2 forward 152.6 us, D.conv4 input gradient 164.9 us both ways) — an apparent 10 % gain in an earlier
+  // run was the difference between two boxes of the pool; kept because it costs nothing.
   static constexpr int kAccBufs = BLOCK_N <= 128 ? 4 : 2;  // N = 128: four accumulators since round 2 (two before; TMEM has the columns)
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
   // 16 epilogue warps; N <= 128 (TMA epilogue): one 2 KiB box per warp (b2g_conv_epi.cuh).  Measured in round 2: a second
@@ -271,7 +275,10 @@ __global__ void __launch_bounds__(PairCfg<BLOCK_N, BOXES>::kThreads, 1)
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(tempty_leader + as * 8);
+      if (lane == 0) {
+        if (p.arrive_release_cluster) mbar_arrive_cluster_release(tempty_leader + as * 8);
+        else mbar_arrive_cluster(tempty_leader + as * 8);
+      }
     }
     if (use_tma) epi_tma_end(e, st, s_colsum, lane);
   }
@@ -339,6 +346,7 @@ int launch_conv_pair(const b2g_conv_args* a, const ConvPlan& pl, int block_n, vo
     int rc = fill_epi_tma(a, pl, block_n <= 128 || boxes256, &kp.e, &kp.em);
     if (rc) return rc;
   }
+  kp.arrive_release_cluster = env_int("B2G_PAIR_ARRIVE_RELEASE_CLUSTER", 0);
   kp.brows = a->Cout;
   kp.cin_chunks = a->Cin / 64;
   kp.n_tiles = a->Cout / block_n;

@@ -115,6 +115,10 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t saddr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// the form used until round 2, kept for same-box A/B measurements (B2G_PAIR_ARRIVE_RELEASE_CLUSTER=1)
+__device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 
 // ---------------------------------------------------------------------------------------------
 // TMA tiled loads (global -> shared, completion on an mbarrier)
